@@ -1,0 +1,263 @@
+"""bench.py -- images/s of the hot path (Segment forward + fused mask decode) on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  torchrun ... bench.py --gpus N ...          (one rank per GPU, batch-sharded, no collective)
+
+A step = forward of one synthetic batch (BASELINE.json configs[1]: 64 x 3x512x512 per GPU)
+followed by the mask decode of its logits.  Prints ONE JSON line (contract in the task brief).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PER_IMAGE_512 = 1.1876e9      # 2 x 593.8 M MACs of the reference graph
+DECODE_BYTES_PER_PIXEL = 5         # fp32 logit in + 1 mask byte out (identity size) + 20 B stats/instance
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--precision", choices=("bf16", "fp32"), default="bf16")
+    ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
+    ap.add_argument("--size", type=int, default=512)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sust=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU with NVML during the timed region."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.mhz, self.reasons, self.max_mhz = index, False, [], set(), None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                     nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+            while not self.stop_flag:
+                self.mhz.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.reasons |= {n for bit, n in names.items() if r & bit}
+                time.sleep(0.02)
+        except Exception as e:  # NVML missing: record that instead of guessing
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def summary(self):
+        m = sorted(self.mhz)
+        return {"sm_mhz": m[len(m) // 2] if m else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def cpu_reference_arm(B, size, steps, warmup, threads=None):
+    """The reference's CPU implementation of the path: its torch-CPU forward (restated in
+    oracle/segment_oracle.py, bit-equal to the reference module) + the C decode restatement."""
+    import numpy as np
+    import torch
+
+    from instancesegmentation_b200 import synth
+    from oracle import decode_oracle
+    from oracle.segment_oracle import segment_forward
+    if threads:
+        torch.set_num_threads(threads)
+    z = np.load(os.path.join(ROOT, "tests", "golden", "segment3_state.npz"))
+    sd = {k: torch.from_numpy(z[k]) for k in z.files}
+    x = torch.from_numpy(synth.batch(B, size, size, seed=1234))
+    boxes = np.tile(np.array([0, 0, size, size], np.int32), (B, 1))
+    decode_oracle.build()
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        y = segment_forward(sd, x)
+        decode_oracle.decode(y[:, 0].numpy(), boxes)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    t = sum(times) / len(times)
+    return B / t, t, torch.get_num_threads()
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU path, all host threads, bounded sample."""
+    if rank != 0:
+        return
+    B = 8  # bounded sample of the 64-image workload (the CPU path is ~4 orders slower)
+    ips, t, threads = cpu_reference_arm(B, args.size, max(args.steps, 1), min(args.warmup, 2))
+    sample = f"{B} of {args.batch} images per step, fp32, torch CPU conv + scalar C decode"
+    print(json.dumps({
+        "impl": "reference", "metric": "images/sec", "value": ips, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"Segment(3) forward + mask decode, {args.size}x{args.size}, identity-size decode",
+                   "sample": sample},
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_ours(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from instancesegmentation_b200 import Segment, synth
+    from instancesegmentation_b200.decode import decode_masks
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, S, K, W = args.batch, args.size, args.steps, max(args.warmup, 3)
+    z = np.load(os.path.join(ROOT, "tests", "golden", "segment3_state.npz"))
+    model = Segment(3)
+    model.load_state_dict({k: torch.from_numpy(z[k]) for k in z.files}, strict=True)
+    model.precision, model.max_batch = args.precision, B
+    model = model.to(dev).eval()
+
+    # inputs: rank r owns images [r*B, (r+1)*B) of the global batch (contiguous shard);
+    # NBUF distinct batches rotate so that consecutive steps never re-read L2-resident inputs
+    NBUF = 3
+    base = synth.batch(8, S, S, seed=1234 + 8 * rank)
+    host = [torch.from_numpy(np.concatenate([np.roll(base, i + 1 + j, axis=0) for i in range(B // 8 or 1)])[:B]
+                             .copy()).pin_memory() for j in range(NBUF)]
+    xs = [h.to(dev) for h in host]
+    boxes = np.tile(np.array([0, 0, S, S], np.int32), (B, 1))
+    masks_buf = torch.empty(B * S * S, dtype=torch.uint8, device=dev)
+
+    def step(x):
+        with torch.no_grad():
+            return decode_masks(model(x), boxes, out=masks_buf)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(W):
+        step(xs[i % NBUF])
+    eng = next(iter(model._engines.values()))
+    # ---- timed region: device-resident inputs ----
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3 * K + 1)]
+    barrier()
+    ev[0].record()
+    for i in range(K):
+        x = xs[i % NBUF]
+        with torch.no_grad():
+            y = model(x)
+        ev[3 * i + 1].record()          # forward | decode boundary
+        decode_masks(y, boxes, out=masks_buf)
+        ev[3 * i + 2].record()
+        ev[3 * i + 3].record()
+    barrier()
+    sampler.stop_flag = True
+    sampler.join()
+    total_ms = ev[0].elapsed_time(ev[3 * K])
+    fwd_ms = sum((ev[3 * i].elapsed_time(ev[3 * i + 1]) for i in range(K)))
+    dec_ms = sum((ev[3 * i + 1].elapsed_time(ev[3 * i + 2]) for i in range(K)))
+    # ---- end-to-end through the public API with host buffers ----
+    out_host = torch.empty(B * S * S, dtype=torch.uint8).pin_memory()
+    stats_host = torch.empty((B, 5), dtype=torch.int32).pin_memory()
+
+    def e2e_step(i):
+        x = host[i % NBUF].to(dev, non_blocking=True)
+        r = step(x)
+        out_host.copy_(r.masks[:B * S * S], non_blocking=True)
+        stats_host[:, 0].copy_(r.area, non_blocking=True)
+        stats_host[:, 1:].copy_(r.bbox, non_blocking=True)
+
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        e2e_step(i)
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+
+    t = torch.tensor([total_ms, fwd_ms, dec_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, fwd_ms, dec_ms, e2e_ms = t.tolist()
+    if rank == 0:
+        pk = peaks()
+        imgs = world * B * K
+        flop_img = FLOP_PER_IMAGE_512 * (S / 512) ** 2
+        conv_tf = (B * K * flop_img) / (fwd_ms * 1e-3) / 1e12           # per GPU
+        dec_bytes = B * (S * S * DECODE_BYTES_PER_PIXEL + 20)
+        dec_gbs = dec_bytes * K / (dec_ms * 1e-3) / 1e9
+        line = {
+            "metric": "images/sec", "value": imgs / (total_ms * 1e-3), "unit": "images/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+            "config": {"workload": f"configs[1]: Segment(3) inference batch {B}/GPU at 3x{S}x{S} "
+                                   f"{args.precision} + fused mask decode (identity size, 0/1 masks+area+bbox)",
+                       "global_batch": world * B, "parallelism": f"batch-shard x{world}, no collective",
+                       "l2": f"inputs rotate over {NBUF} batches ({NBUF * B * 3 * S * S * 4 / 1e6:.0f} MB) and the "
+                             f"activation workspace is {eng.workspace_bytes / 1e6:.0f} MB, both > 126 MB L2"},
+            "roofline": {"bound": "tensor", "achieved": conv_tf, "peak": pk["tf_sust"] / 1e0, "unit": "TFLOP/s",
+                         "frac": conv_tf / pk["tf_sust"], "traffic": None,
+                         "what": f"conv stack ({eng.launches_per_forward} launches/forward), algorithmic "
+                                 f"{flop_img / 1e9:.4f} GFLOP/image, peak = sustained bf16 of {pk['src']}",
+                         "ms_per_forward": fwd_ms / K},
+            "roofline_decode": {"bound": "hbm", "achieved": dec_gbs, "peak": pk["hbm"], "unit": "GB/s",
+                                "frac": dec_gbs / pk["hbm"], "traffic": None, "bytes_per_launch": dec_bytes,
+                                "ms_per_decode": dec_ms / K},
+            "e2e": {"value": imgs / (e2e_ms * 1e-3), "unit": "images/s",
+                    "h2d_bytes_per_step": B * 3 * S * S * 4, "d2h_bytes_per_step": B * S * S + B * 20},
+            "gpu_launches": K * (eng.launches_per_forward + 3),
+            "clocks": sampler.summary(),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            ips, tt, threads = cpu_reference_arm(8, S, 3, 1)
+            line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": threads, "kind": "port",
+                                    "sample": f"8 of {B} images per step x 3 steps, fp32 torch-CPU forward "
+                                              f"(oracle restatement, bit-equal to the reference) + scalar C decode"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+    if world == 1 and args.gpus > 1:
+        # not launched by torchrun: re-launch ourselves one rank per GPU
+        import subprocess
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29511", os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,125 @@
+/* libisg -- C ABI of the B200-native (sm_100a) hot path of YanMiaoW/instanceSegmentation:
+ * the forward of the network in model/segment.py and the mask decode meant for infer.py.
+ *
+ * The reference has no FFI seam (pure Python over torch library ops); the entry points
+ * below are what a binding for this path would call, each citing the reference code it
+ * replaces.  INTEGRATION.md shows the ctypes stub.
+ *
+ * Conventions
+ *  - every pointer named *_dev is a caller-owned device pointer on the plan's device;
+ *    pointers named *_host are host pointers; nothing crosses the ABI by ownership except
+ *    the opaque plan handle;
+ *  - `stream` is a cudaStream_t passed as void*; all work is asynchronous on it;
+ *  - return value: 0 = ok, negative = isg_status; isg_last_error() gives the message of
+ *    the calling thread's last failure; no C++ exception crosses the boundary;
+ *  - a plan is used by one host thread at a time; plans on different devices are
+ *    independent (one process or thread per GPU, no collective on the inference path).
+ */
+#ifndef ISG_H_
+#define ISG_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define ISG_API __attribute__((visibility("default")))
+#else
+#define ISG_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct isg_plan isg_plan;
+
+enum isg_status {
+    ISG_OK = 0,
+    ISG_ERR_ARG = -1,      /* bad argument (size rule, null pointer, count mismatch) */
+    ISG_ERR_CUDA = -2,     /* a CUDA runtime / driver call failed */
+    ISG_ERR_STATE = -3,    /* call order (forward before weights were loaded, ...) */
+    ISG_ERR_ARCH = -4      /* device is not sm_100 */
+};
+
+enum isg_mode {
+    ISG_MODE_FP32 = 0,     /* fp32 storage + fp32 FMA, BatchNorm as fp32 epilogue affine (<=1e-4 vs reference) */
+    ISG_MODE_BF16 = 1      /* NHWC bf16 activations; GEMM-shaped convs on tcgen05 with fp32 TMEM accumulators */
+};
+
+ISG_API const char* isg_last_error(void);
+ISG_API int isg_version(void);
+
+/* ---- network description: the 588 state_dict entries of Segment(in_channel) ----------
+ * (model/segment.py:347-440; key grammar in SURVEY.md section 2.3).  Index order equals
+ * the reference's state_dict() order. */
+ISG_API int isg_state_count(int in_channel);
+ISG_API const char* isg_state_name(int in_channel, int index);
+ISG_API int64_t isg_state_numel(int in_channel, int index);
+ISG_API int isg_state_is_int64(int in_channel, int index); /* 1 for *.num_batches_tracked */
+
+/* ---- plan: replaces Segment.__init__ + .to(device) + .eval() (train_instance.py:294,350,396) */
+ISG_API int isg_plan_create(int device, int in_channel, int height, int width, int max_batch,
+                    int mode, isg_plan** out);
+ISG_API int isg_plan_destroy(isg_plan* plan);
+ISG_API size_t isg_plan_workspace_bytes(const isg_plan* plan);
+
+/* replaces model.load_state_dict(checkpoint["state_dict"]) (train_instance.py:325):
+ * tensors_host[i] points at the contiguous host data of state entry i (fp32, or int64 for
+ * num_batches_tracked, which is ignored); numels[i] is checked against isg_state_numel.
+ * BatchNorm folding / weight packing for the kernels happens here. */
+ISG_API int isg_plan_load_weights(isg_plan* plan, const void* const* tensors_host,
+                          const int64_t* numels, int count);
+
+/* replaces Segment.forward (model/segment.py:466-508): x_dev is fp32 NCHW
+ * [batch,in_channel,H,W]; logits_dev receives fp32 [batch,1,H,W] raw logits.  Any batch
+ * size is accepted; it is processed in groups of max_batch. */
+ISG_API int isg_forward(isg_plan* plan, const float* x_dev, int batch, float* logits_dev, void* stream);
+
+/* number of kernels isg_forward launches per group of <= max_batch images */
+ISG_API int isg_plan_launches_per_forward(const isg_plan* plan);
+/* conv/convT multiply-accumulates per image of the reference graph (SURVEY 8d constant) */
+ISG_API int64_t isg_plan_macs_per_image(const isg_plan* plan);
+
+/* test hooks: named intermediate activations of the last forward group, copied out as
+ * fp32 NCHW [n,C,h,w] (blocking).  Names follow oracle/segment_oracle.py taps. */
+ISG_API int isg_plan_tap_count(const isg_plan* plan);
+ISG_API const char* isg_plan_tap_name(const isg_plan* plan, int index);
+ISG_API int isg_plan_tap_shape(const isg_plan* plan, int index, int* channels, int* height, int* width);
+ISG_API int isg_plan_tap_read(isg_plan* plan, int index, int n, float* out_host);
+
+/* ---- mask decode (the body infer.py never got; sigmoid = model/segment.py:534, soft mask
+ * = train_instance.py:398-399; semantics in DESIGN.md section 3) -------------------------
+ * logits_dev: [n_inst,h,w] fp32 (logits_bf16 = 0) or bf16 (= 1).
+ * boxes_dev:  [n_inst,4] int32 {x0,y0,wk,hk}: placement in the source canvas / output size.
+ * mask_off_dev: [n_inst] int64 byte offsets of each instance's tightly packed hk*wk mask.
+ * masks_dev:  0/1 bytes.  soft_dev (nullable): trunc(p*255) bytes, same layout.
+ * area_dev [n_inst] int32, bbox_dev [n_inst,4] int32 {xmin,ymin,xmax+1,ymax+1} canvas
+ * coordinates, zeros when empty.  max_wk/max_hk: upper bounds of wk/hk (grid sizing). */
+ISG_API int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int h, int w,
+               const int32_t* boxes_dev, const int64_t* mask_off_dev, int max_wk, int max_hk,
+               float threshold, uint8_t* masks_dev, uint8_t* soft_dev, int32_t* area_dev,
+               int32_t* bbox_dev, void* stream);
+
+/* id map [n_img,canvas_h,canvas_w] int32: per pixel the 1-based index of the covering
+ * instance with set mask and largest probability (ties -> lowest index), 0 = background.
+ * img_first_dev [n_img+1] int32: instances of image i are img_first[i]..img_first[i+1]-1. */
+ISG_API int isg_idmap(const void* logits_dev, int logits_bf16, int h, int w, const int32_t* boxes_dev,
+              const int32_t* img_first_dev, int n_img, int canvas_h, int canvas_w,
+              float threshold, int32_t* idmap_dev, void* stream);
+
+/* intersection/union counts of two 0/1 byte masks (train_instance.py:402-403 mask_iou):
+ * inter_union_dev[0] += |a&b|, [1] += |a|b| (caller zeroes them). */
+ISG_API int isg_mask_iou_counts(const uint8_t* a_dev, const uint8_t* b_dev, int64_t n,
+                        unsigned long long* inter_union_dev, void* stream);
+
+/* ---- training step exchange (train_instance.py:379-380) ---------------------
+ * fused "unscale + Adam" over the flat fp32 gradient bucket after the NCCL all-reduce:
+ * g = grad * grad_scale; standard Adam (lr, beta1, beta2, eps), bias-corrected by `step`. */
+ISG_API int isg_adam_step(float* param_dev, const float* grad_dev, float* exp_avg_dev,
+                  float* exp_avg_sq_dev, int64_t n, float grad_scale, float lr, float beta1,
+                  float beta2, float eps, int step, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ISG_H_ */

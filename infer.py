@@ -1,0 +1,81 @@
+"""Inference CLI with the reference's call surface (reference infer.py:12-36): flags
+``-i/--test-image-dir``, ``-o/--output-dir``, ``--continue-test`` and ``path_decompose``.
+The reference's loop body stops after ``path_decompose``; here it is completed: load ->
+resize to the network size -> Normalize(0.5, 0.5) (train_instance.py:80-85) -> Segment
+forward (libisg) -> mask decode back to the source resolution (libisg) -> ``<name>.png``.
+"""
+import argparse
+import glob
+import os
+
+
+def parse_args(argv=None):
+    ap = argparse.ArgumentParser(description="inference image")
+    ap.add_argument("-i", "--test-image-dir", required=True, help="image test dir")
+    ap.add_argument("-o", "--output-dir", required=True, help="image save dir")
+    ap.add_argument("--continue-test", action="store_true", help="skip existing file.")
+    # additions (the reference never loads a model, so it has no such flags)
+    ap.add_argument("--checkpoint", default=None, help="*.pth written by train_instance.py:497-507")
+    ap.add_argument("--size", type=int, default=480, help="network input size (multiple of 16)")
+    ap.add_argument("--precision", choices=("fp32", "bf16"), default="fp32")
+    ap.add_argument("--batch", type=int, default=16)
+    ap.add_argument("--soft", action="store_true", help="also write the 0-255 soft mask")
+    return ap.parse_args(argv)
+
+
+def path_decompose(path):
+    """-> (dirname, basename without extension, extension without dot)"""
+    head, tail = os.path.split(path)
+    stem, ext = os.path.splitext(tail)
+    return head, stem, os.path.splitext(path)[-1][1:]
+
+
+def list_images(directory):
+    # same pattern as the reference (infer.py:35); note it is a character class, not a list
+    return sorted(glob.glob(os.path.join(directory, "*[jpg,png,jpgerr]")))
+
+
+def run(args):
+    import cv2
+    import numpy as np
+    import torch
+
+    from instancesegmentation_b200.decode import decode_masks
+    from model.segment import Segment
+
+    dev = torch.device("cuda", torch.cuda.current_device())
+    model = Segment(3)
+    if args.checkpoint:
+        ck = torch.load(args.checkpoint, map_location="cpu")
+        model.load_state_dict(ck["state_dict"] if "state_dict" in ck else ck)
+    model.precision, model.max_batch = args.precision, args.batch
+    model.to(dev).eval()
+    os.makedirs(args.output_dir, exist_ok=True)
+    todo = []
+    for path in list_images(args.test_image_dir):
+        _, stem, _ = path_decompose(path)
+        dst = os.path.join(args.output_dir, stem + ".png")
+        if not (args.continue_test and os.path.exists(dst)):
+            todo.append((path, dst))
+    S = args.size
+    for i in range(0, len(todo), args.batch):
+        chunk, imgs, boxes = todo[i:i + args.batch], [], []
+        for path, _ in chunk:
+            bgr = cv2.imread(path, cv2.IMREAD_COLOR)
+            if bgr is None:
+                raise IOError(f"cannot read {path}")
+            boxes.append((0, 0, bgr.shape[1], bgr.shape[0]))
+            rgb = cv2.cvtColor(cv2.resize(bgr, (S, S)), cv2.COLOR_BGR2RGB)
+            imgs.append((rgb.transpose(2, 0, 1).astype(np.float32) / 255.0 - 0.5) / 0.5)
+        x = torch.from_numpy(np.stack(imgs)).pin_memory().to(dev, non_blocking=True)
+        with torch.no_grad():
+            res = decode_masks(model(x), np.array(boxes, np.int32), want_soft=args.soft)
+        for n, (_, dst) in enumerate(chunk):
+            cv2.imwrite(dst, res.mask(n).cpu().numpy() * 255)
+            if args.soft:
+                cv2.imwrite(dst[:-4] + "_soft.png", res.soft_mask(n).cpu().numpy())
+    return len(todo)
+
+
+if __name__ == "__main__":
+    print(f"{run(parse_args())} images written")

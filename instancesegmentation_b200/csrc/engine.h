@@ -1,0 +1,61 @@
+// Plan = topology of Segment(in_channel) at a fixed HxW, lowered to a list of kernel
+// launches over a private activation workspace (NHWC).
+#pragma once
+#include <functional>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "netspec.h"
+
+namespace isg {
+
+struct TensorD {
+    std::string name;
+    int C, Cs, H, W;      // logical channels, storage stride, spatial size (per image)
+    size_t off;           // byte offset in the workspace
+    bool tap;             // exposed through isg_plan_tap_*
+};
+
+// host view of the caller's state_dict during isg_plan_load_weights
+struct HostWeights {
+    const StateSpec* spec;
+    const void* const* ptrs;
+    const float* get(const std::string& name) const {
+        auto it = spec->index.find(name);
+        return it == spec->index.end() ? nullptr : static_cast<const float*>(ptrs[it->second]);
+    }
+};
+
+struct Op {
+    std::string name;
+    // fills this op's slice of the host staging copy of the weight arena
+    std::function<void(const HostWeights&, float* arena_host)> pack;
+    // enqueues the kernel for `n` images
+    std::function<cudaError_t(int n, const float* x, float* logits, cudaStream_t)> launch;
+};
+
+}  // namespace isg
+
+struct isg_plan {
+    int device = 0, cin = 3, H = 0, W = 0, max_batch = 0, mode = 0;
+    bool weights_loaded = false;
+    isg::StateSpec spec;
+    std::vector<isg::TensorD> tensors;
+    std::vector<isg::Op> ops;
+    size_t ws_bytes = 0, arena_floats = 0;
+    char* ws = nullptr;        // activation workspace (device)
+    float* arena = nullptr;    // packed weights (device)
+    std::vector<float> arena_host;
+    int64_t macs_per_image = 0;
+    int last_n = 0;
+    std::vector<int> taps;     // tensor ids
+
+    size_t esize() const { return mode == ISG_MODE_BF16 ? 2 : 4; }
+    void* tptr(int id) const { return ws + tensors[id].off; }
+};
+
+namespace isg {
+int build_plan(isg_plan* p);  // engine_build.cu
+}

@@ -1,0 +1,164 @@
+// C ABI of libisg (include/isg.h): network description, plan lifetime, forward, test taps.
+#include <map>
+#include <mutex>
+
+#include "engine.h"
+
+using namespace isg;
+
+namespace {
+std::mutex g_spec_mu;
+std::map<int, StateSpec> g_specs;
+const StateSpec& spec_for(int cin) {
+    std::lock_guard<std::mutex> lk(g_spec_mu);
+    auto it = g_specs.find(cin);
+    if (it == g_specs.end()) it = g_specs.emplace(cin, build_state_spec(cin)).first;
+    return it->second;
+}
+
+// NHWC (storage T, stride Cs) -> NCHW fp32, used only by the tap reader
+template <typename T>
+__global__ void tap_to_nchw(const T* in, float* out, int C, int Cs, int H, int W, int total) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    int x = i % W, y = (i / W) % H, c = (i / (W * H)) % C, b = i / (W * H * C);
+    out[i] = ld1(in + (((size_t)b * H + y) * W + x) * Cs + c);
+}
+}  // namespace
+
+extern "C" {
+
+const char* isg_last_error(void) { return err_slot().c_str(); }
+int isg_version(void) { return 100; }
+
+int isg_state_count(int in_channel) { return (int)spec_for(in_channel).entries.size(); }
+const char* isg_state_name(int in_channel, int index) {
+    const StateSpec& s = spec_for(in_channel);
+    return index >= 0 && index < (int)s.entries.size() ? s.entries[index].name.c_str() : nullptr;
+}
+int64_t isg_state_numel(int in_channel, int index) {
+    const StateSpec& s = spec_for(in_channel);
+    return index >= 0 && index < (int)s.entries.size() ? s.entries[index].numel : -1;
+}
+int isg_state_is_int64(int in_channel, int index) {
+    const StateSpec& s = spec_for(in_channel);
+    return index >= 0 && index < (int)s.entries.size() ? (int)s.entries[index].is_i64 : -1;
+}
+
+int isg_plan_create(int device, int in_channel, int height, int width, int max_batch, int mode,
+                    isg_plan** out) {
+    if (!out) return fail(ISG_ERR_ARG, "isg_plan_create: out is null");
+    *out = nullptr;
+    if (in_channel < 1 || in_channel > 64) return fail(ISG_ERR_ARG, "in_channel %d out of range [1,64]", in_channel);
+    if (height < 16 || width < 16 || height % 16 || width % 16)
+        return fail(ISG_ERR_ARG, "H and W must be multiples of 16 (>=16), got %dx%d", height, width);
+    if (max_batch < 1) return fail(ISG_ERR_ARG, "max_batch must be >= 1");
+    if (mode != ISG_MODE_FP32 && mode != ISG_MODE_BF16) return fail(ISG_ERR_ARG, "unknown mode %d", mode);
+    ISG_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    ISG_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(ISG_ERR_ARCH, "libisg is built for sm_100a only; device %d is sm_%d%d", device, prop.major,
+                    prop.minor);
+    std::unique_ptr<isg_plan> p(new isg_plan);
+    p->device = device; p->cin = in_channel; p->H = height; p->W = width;
+    p->max_batch = max_batch; p->mode = mode;
+    p->spec = build_state_spec(in_channel);
+    build_plan(p.get());
+    ISG_CUDA(cudaMalloc(&p->ws, p->ws_bytes));
+    ISG_CUDA(cudaMemset(p->ws, 0, p->ws_bytes));  // pad channels stay zero for the plan's lifetime
+    ISG_CUDA(cudaMalloc(&p->arena, p->arena_floats * sizeof(float)));
+    p->arena_host.assign(p->arena_floats, 0.f);
+    ISG_CUDA(cudaDeviceSynchronize());
+    *out = p.release();
+    return ISG_OK;
+}
+
+int isg_plan_destroy(isg_plan* plan) {
+    if (!plan) return ISG_OK;
+    cudaSetDevice(plan->device);
+    cudaFree(plan->ws);
+    cudaFree(plan->arena);
+    delete plan;
+    return ISG_OK;
+}
+
+size_t isg_plan_workspace_bytes(const isg_plan* plan) { return plan ? plan->ws_bytes : 0; }
+int isg_plan_launches_per_forward(const isg_plan* plan) { return plan ? (int)plan->ops.size() : 0; }
+int64_t isg_plan_macs_per_image(const isg_plan* plan) { return plan ? plan->macs_per_image : 0; }
+
+int isg_plan_load_weights(isg_plan* plan, const void* const* tensors_host, const int64_t* numels, int count) {
+    if (!plan || !tensors_host || !numels) return fail(ISG_ERR_ARG, "isg_plan_load_weights: null argument");
+    const auto& e = plan->spec.entries;
+    if (count != (int)e.size())
+        return fail(ISG_ERR_ARG, "expected %d state tensors, got %d", (int)e.size(), count);
+    for (int i = 0; i < count; ++i) {
+        if (numels[i] != e[i].numel)
+            return fail(ISG_ERR_ARG, "state tensor %d (%s): expected %lld elements, got %lld", i,
+                        e[i].name.c_str(), (long long)e[i].numel, (long long)numels[i]);
+        if (!tensors_host[i]) return fail(ISG_ERR_ARG, "state tensor %d (%s) is null", i, e[i].name.c_str());
+    }
+    HostWeights hw{&plan->spec, tensors_host};
+    for (auto& op : plan->ops) op.pack(hw, plan->arena_host.data());
+    ISG_CUDA(cudaSetDevice(plan->device));
+    ISG_CUDA(cudaDeviceSynchronize());  // no forward may still be reading the old weights
+    ISG_CUDA(cudaMemcpy(plan->arena, plan->arena_host.data(), plan->arena_floats * sizeof(float),
+                        cudaMemcpyHostToDevice));
+    plan->weights_loaded = true;
+    return ISG_OK;
+}
+
+int isg_forward(isg_plan* plan, const float* x_dev, int batch, float* logits_dev, void* stream) {
+    if (!plan || !x_dev || !logits_dev) return fail(ISG_ERR_ARG, "isg_forward: null argument");
+    if (!plan->weights_loaded) return fail(ISG_ERR_STATE, "isg_forward before isg_plan_load_weights");
+    if (batch < 0) return fail(ISG_ERR_ARG, "negative batch");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t in_img = (size_t)plan->cin * plan->H * plan->W, out_img = (size_t)plan->H * plan->W;
+    for (int b0 = 0; b0 < batch; b0 += plan->max_batch) {
+        const int n = batch - b0 < plan->max_batch ? batch - b0 : plan->max_batch;
+        for (auto& op : plan->ops) {
+            cudaError_t e = op.launch(n, x_dev + b0 * in_img, logits_dev + b0 * out_img, st);
+            if (e != cudaSuccess)
+                return fail(ISG_ERR_CUDA, "launch of %s failed: %s", op.name.c_str(), cudaGetErrorString(e));
+        }
+        plan->last_n = n;
+    }
+    return ISG_OK;
+}
+
+int isg_plan_tap_count(const isg_plan* plan) { return plan ? (int)plan->taps.size() : 0; }
+const char* isg_plan_tap_name(const isg_plan* plan, int index) {
+    if (!plan || index < 0 || index >= (int)plan->taps.size()) return nullptr;
+    return plan->tensors[plan->taps[index]].name.c_str();
+}
+int isg_plan_tap_shape(const isg_plan* plan, int index, int* channels, int* height, int* width) {
+    if (!plan || index < 0 || index >= (int)plan->taps.size()) return fail(ISG_ERR_ARG, "bad tap index");
+    const TensorD& t = plan->tensors[plan->taps[index]];
+    if (channels) *channels = t.C;
+    if (height) *height = t.H;
+    if (width) *width = t.W;
+    return ISG_OK;
+}
+int isg_plan_tap_read(isg_plan* plan, int index, int n, float* out_host) {
+    if (!plan || !out_host || index < 0 || index >= (int)plan->taps.size())
+        return fail(ISG_ERR_ARG, "isg_plan_tap_read: bad argument");
+    if (n < 1 || n > plan->max_batch) return fail(ISG_ERR_ARG, "tap read of %d images (max_batch %d)", n, plan->max_batch);
+    const TensorD& t = plan->tensors[plan->taps[index]];
+    const int total = n * t.C * t.H * t.W;
+    float* tmp = nullptr;
+    ISG_CUDA(cudaSetDevice(plan->device));
+    ISG_CUDA(cudaDeviceSynchronize());
+    ISG_CUDA(cudaMalloc(&tmp, (size_t)total * sizeof(float)));
+    if (plan->mode == ISG_MODE_BF16)
+        tap_to_nchw<bf16><<<cdiv(total, 256), 256>>>(reinterpret_cast<const bf16*>(plan->ws + t.off), tmp, t.C, t.Cs,
+                                                     t.H, t.W, total);
+    else
+        tap_to_nchw<float><<<cdiv(total, 256), 256>>>(reinterpret_cast<const float*>(plan->ws + t.off), tmp, t.C,
+                                                      t.Cs, t.H, t.W, total);
+    cudaError_t e = cudaMemcpy(out_host, tmp, (size_t)total * sizeof(float), cudaMemcpyDeviceToHost);
+    cudaFree(tmp);
+    if (e != cudaSuccess) return fail(ISG_ERR_CUDA, "tap copy failed: %s", cudaGetErrorString(e));
+    return ISG_OK;
+}
+
+}  // extern "C"

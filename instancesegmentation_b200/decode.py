@@ -1,0 +1,116 @@
+"""Mask decode -- the body the reference's infer.py never got (infer.py:32-36): logits ->
+sigmoid (model/segment.py:534) -> bilinear resize to each instance's source box ->
+threshold -> per-instance binary masks, areas, boxes, optional soft masks
+(train_instance.py:398-399) and the per-image id map.  Runs in libisg.so only."""
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+@dataclass
+class DecodeResult:
+    masks: torch.Tensor            # flat uint8 (0/1) on the device
+    soft: Optional[torch.Tensor]   # flat uint8 trunc(p*255), same layout, or None
+    offsets: np.ndarray            # int64 [N+1] host byte offsets (instance n starts at offsets[n])
+    boxes: np.ndarray              # int32 [N,4] host (x0,y0,wk,hk)
+    area: torch.Tensor             # int32 [N] device
+    bbox: torch.Tensor             # int32 [N,4] device (xmin,ymin,xmax+1,ymax+1), zeros if empty
+    idmap: Optional[torch.Tensor] = None  # int32 [n_img,Hs,Ws] device
+
+    def mask(self, n):
+        wk, hk = int(self.boxes[n, 2]), int(self.boxes[n, 3])
+        o = int(self.offsets[n])
+        return self.masks[o:o + hk * wk].view(hk, wk)
+
+    def soft_mask(self, n):
+        wk, hk = int(self.boxes[n, 2]), int(self.boxes[n, 3])
+        o = int(self.offsets[n])
+        return self.soft[o:o + hk * wk].view(hk, wk)
+
+
+def mask_offsets(boxes, align=16):
+    """Byte offset of every instance's hk*wk mask; starts are `align`-byte aligned so the
+    kernel's 4-byte stores are always used (align=1 gives the oracle's tight packing)."""
+    boxes = np.asarray(boxes, np.int32).reshape(-1, 4)
+    sizes = boxes[:, 2].astype(np.int64) * boxes[:, 3].astype(np.int64)
+    off = np.zeros(len(boxes) + 1, np.int64)
+    for i, s in enumerate(sizes):
+        off[i + 1] = (off[i] + s + align - 1) // align * align
+    return off
+
+
+def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=None, canvas=None,
+                 align=16, out=None):
+    """``logits``: CUDA fp32/bf16 [N,h,w] or [N,1,h,w].  ``boxes``: int32 [N,4] (x0,y0,wk,hk) on
+    the host (None = identity: every map decoded at its own size at the canvas origin).
+    ``img_first`` (int32 [n_img+1]) + ``canvas`` (Hs, Ws) additionally produce the id map."""
+    if not logits.is_cuda:
+        raise _lib.IsgError("decode_masks runs on CUDA only; there is no CPU path")
+    if logits.dim() == 4:
+        if logits.shape[1] != 1:
+            raise ValueError("logits must have one channel")
+        logits = logits[:, 0]
+    if logits.dtype not in (torch.float32, torch.bfloat16):
+        raise TypeError(f"logits must be float32 or bfloat16, got {logits.dtype}")
+    logits = logits.contiguous()
+    N, h, w = logits.shape
+    if boxes is None:
+        boxes = np.tile(np.array([0, 0, w, h], np.int32), (N, 1))
+    boxes = np.ascontiguousarray(np.asarray(boxes, np.int32).reshape(-1, 4))
+    if len(boxes) != N:
+        raise ValueError(f"{N} logit maps but {len(boxes)} boxes")
+    if N and (boxes[:, 2:] < 1).any():
+        raise ValueError("box width/height must be >= 1")
+    off = mask_offsets(boxes, align)
+    dev = logits.device
+    total = max(int(off[-1]), 1)
+    l = _lib.lib()
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream().cuda_stream
+        if out is not None:
+            masks = out
+            if masks.numel() < total or masks.dtype != torch.uint8:
+                raise ValueError("out buffer too small or not uint8")
+        else:
+            masks = torch.empty(total, dtype=torch.uint8, device=dev)
+        soft = torch.empty(total, dtype=torch.uint8, device=dev) if want_soft else None
+        area = torch.empty(max(N, 1), dtype=torch.int32, device=dev)[:N]
+        bbox = torch.empty((max(N, 1), 4), dtype=torch.int32, device=dev)[:N]
+        boxes_d = torch.from_numpy(boxes).to(dev, non_blocking=False)
+        off_d = torch.from_numpy(off[:-1].copy()).to(dev)
+        if N:
+            _lib.check(l.isg_decode(logits.data_ptr(), int(logits.dtype == torch.bfloat16), N, h, w,
+                                    boxes_d.data_ptr(), off_d.data_ptr(), int(boxes[:, 2].max()),
+                                    int(boxes[:, 3].max()), float(threshold), masks.data_ptr(),
+                                    soft.data_ptr() if want_soft else None, area.data_ptr(),
+                                    bbox.data_ptr(), st))
+        idmap = None
+        if img_first is not None:
+            if canvas is None:
+                raise ValueError("canvas=(Hs, Ws) is required with img_first")
+            first = np.ascontiguousarray(np.asarray(img_first, np.int32))
+            n_img = len(first) - 1
+            idmap = torch.empty((n_img, canvas[0], canvas[1]), dtype=torch.int32, device=dev)
+            first_d = torch.from_numpy(first).to(dev)
+            _lib.check(l.isg_idmap(logits.data_ptr(), int(logits.dtype == torch.bfloat16), h, w,
+                                   boxes_d.data_ptr(), first_d.data_ptr(), n_img, canvas[0], canvas[1],
+                                   float(threshold), idmap.data_ptr(), st))
+    return DecodeResult(masks, soft, off, boxes, area, bbox, idmap)
+
+
+def mask_iou(a, b):
+    """intersection / union of two 0/1 uint8 CUDA tensors (train_instance.py:402-403)."""
+    a, b = a.contiguous().view(-1), b.contiguous().view(-1)
+    if a.numel() != b.numel():
+        raise ValueError("mask sizes differ")
+    cnt = torch.zeros(2, dtype=torch.int64, device=a.device)
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.lib().isg_mask_iou_counts(a.data_ptr(), b.data_ptr(), a.numel(), cnt.data_ptr(),
+                                                  torch.cuda.current_stream().cuda_stream))
+    inter, union = cnt.tolist()
+    return inter / union if union else 0.0

@@ -95,14 +95,17 @@ def _wide(sd, p, x):
 
 
 @torch.no_grad()
-def segment_forward(sd, x, taps=None):
-    """Raw logits [B,1,H,W] for fp32 CPU ``x`` [B,C,H,W]; segment.py:466-508.
+def segment_forward(sd, x, taps=None, dtype=torch.float32):
+    """Raw logits [B,1,H,W] for CPU ``x`` [B,C,H,W]; segment.py:466-508.
 
     ``taps`` (optional dict) receives the named intermediate activations used by
-    the layer-wise parity tests.
+    the layer-wise parity tests.  ``dtype=torch.float64`` evaluates the same graph in
+    double precision: the yardstick for how far the reference's own fp32 arithmetic is
+    from the exact value of its graph.
     """
-    sd = {k: v.detach().to("cpu") for k, v in sd.items()}
-    x = x.detach().to("cpu", torch.float32)
+    sd = {k: (v.detach().to("cpu", dtype) if v.dtype.is_floating_point else v.detach().to("cpu"))
+          for k, v in sd.items()}
+    x = x.detach().to("cpu", dtype)
     t = {} if taps is None else taps
     y = _unit(sd, "init_conv.layer1", x, "prelu", stride=2, padding=2)
     t["stem1"] = y

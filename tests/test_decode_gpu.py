@@ -1,0 +1,107 @@
+"""GPU parity tests of the mask decode: bit-exact masks / soft bytes / area / bbox / ids against
+oracle/decode_oracle.c on the same inputs, plus size-independent properties at full size."""
+import numpy as np
+import pytest
+import torch
+
+from instancesegmentation_b200 import synth
+from instancesegmentation_b200.decode import decode_masks, mask_iou
+from oracle import decode_oracle as D
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare(L, boxes, thr=0.5, soft=False, align=16):
+    r = decode_masks(torch.from_numpy(L).cuda(), boxes, threshold=thr, want_soft=soft, align=align)
+    o = D.decode(L, boxes, thr=thr, want_soft=soft)
+    masks = r.masks.cpu().numpy()
+    for n in range(len(boxes)):
+        want = o["masks"][o["off"][n]:o["off"][n + 1]]
+        got = masks[r.offsets[n]:r.offsets[n] + len(want)]
+        assert np.array_equal(got, want), (n, int((got != want).sum()))
+        if soft:
+            ws = o["soft"][o["off"][n]:o["off"][n + 1]]
+            gs = r.soft.cpu().numpy()[r.offsets[n]:r.offsets[n] + len(ws)]
+            assert np.array_equal(gs, ws), (n, int((gs != ws).sum()))
+    assert np.array_equal(r.area.cpu().numpy(), o["area"])
+    assert np.array_equal(r.bbox.cpu().numpy(), o["bbox"])
+    return r, o
+
+
+def test_identity_size_bit_exact():
+    L = synth.logits(3, 64, 96, seed=1)
+    L[0, :2, :8] = [[0.0, 1e-9, 1e-7, 6e-8, -1e-9, 5.9e-8, 6.1e-8, 3e-8]] * 2  # around sigmoid == 0.5
+    L[1, 0, :4] = [np.nan, np.inf, -np.inf, 1e-38]
+    _compare(L, np.array([[0, 0, 96, 64]] * 3, np.int32), soft=True)
+    _compare(L, np.array([[0, 0, 96, 64]] * 3, np.int32))
+
+
+def test_ragged_boxes_up_and_down_sampling():
+    L = synth.logits(6, 64, 80, seed=2)
+    boxes = np.array([[0, 0, 160, 128], [5, 7, 37, 23], [1, 2, 80, 64], [9, 9, 81, 63],
+                      [0, 3, 7, 200], [4, 4, 333, 5]], np.int32)
+    for align in (16, 1):     # aligned (4-byte stores) and tight packing (byte stores)
+        _compare(L, boxes, align=align)
+    _compare(L, boxes, soft=True)
+    _compare(L, boxes, thr=0.3)
+    _compare(L, boxes, thr=0.9)
+
+
+def test_degenerate_masks():
+    L = np.stack([np.full((32, 32), -9, np.float32), np.full((32, 32), 9, np.float32),
+                  np.where(np.arange(1024).reshape(32, 32) == 517, 6, -6).astype(np.float32)])
+    boxes = np.array([[3, 4, 32, 32], [0, 0, 50, 20], [10, 10, 32, 32]], np.int32)
+    r, _ = _compare(L, boxes)
+    assert r.area.tolist() == [0, 1000, 1]
+    assert r.bbox.tolist() == [[0, 0, 0, 0], [0, 0, 50, 20], [10 + 5, 10 + 16, 10 + 6, 10 + 17]]
+    r1, _ = _compare(L[:1], np.array([[0, 0, 1, 1]], np.int32))
+    assert r1.masks.numel() >= 1
+    empty = decode_masks(torch.zeros((0, 16, 16), device="cuda"))
+    assert empty.area.numel() == 0
+
+
+def test_many_overlapping_instances_and_idmap():
+    n_img, per = 2, 24
+    boxes, first = synth.boxes(n_img, per, 96, 128, seed=7, lo=12, hi=90)
+    L = synth.logits(n_img * per, 32, 48, seed=3)
+    r = decode_masks(torch.from_numpy(L).cuda(), boxes, img_first=first, canvas=(96, 128))
+    o = D.decode(L, boxes)
+    assert np.array_equal(r.area.cpu().numpy(), o["area"])
+    want = D.idmap(L, boxes, first, 96, 128)
+    got = r.idmap.cpu().numpy()
+    assert np.array_equal(got, want), int((got != want).sum())
+    assert got.max() > per  # ids are 1-based global instance indices
+
+
+def test_bf16_logits():
+    L = torch.from_numpy(synth.logits(2, 48, 64, seed=9)).to(torch.bfloat16)
+    boxes = np.array([[0, 0, 64, 48], [2, 2, 100, 70]], np.int32)
+    r = decode_masks(L.cuda(), boxes, want_soft=True)
+    o = D.decode(L.float().numpy(), boxes, want_soft=True)
+    for n in range(2):
+        want = o["masks"][o["off"][n]:o["off"][n + 1]]
+        assert np.array_equal(r.masks.cpu().numpy()[r.offsets[n]:r.offsets[n] + len(want)], want)
+    assert np.array_equal(r.area.cpu().numpy(), o["area"])
+
+
+def test_full_size_properties():
+    """BASELINE config sizes, checked through properties (the scalar oracle is too slow here)."""
+    N, h, w = 16, 512, 512
+    L = torch.from_numpy(synth.logits(N, h, w, seed=4)).cuda()
+    r = decode_masks(L)
+    m = r.masks.view(N, h, w)
+    assert torch.equal(m.bool(), torch.sigmoid(L) > 0.5) or (m.bool() != (torch.sigmoid(L) > 0.5)).sum() <= 2
+    assert torch.equal(r.area, m.sum(dim=(1, 2), dtype=torch.int32))
+    again = decode_masks(L)                                   # idempotent / deterministic
+    assert torch.equal(again.masks, r.masks) and torch.equal(again.bbox, r.bbox)
+    neg = decode_masks(-L)                                    # complement away from ties
+    assert int((neg.masks.view(N, h, w) + m != 1).sum()) <= int((L == 0).sum()) + 2
+    for n in range(N):                                        # bbox is tight
+        ys, xs = torch.nonzero(m[n], as_tuple=True)
+        assert r.bbox[n].tolist() == [int(xs.min()), int(ys.min()), int(xs.max()) + 1, int(ys.max()) + 1]
+    up = decode_masks(L[:2], np.array([[0, 0, 1024, 1024]] * 2, np.int32))   # 2x upsampling
+    o = D.decode(L[:1, :64, :64].cpu().contiguous().numpy(), np.array([[0, 0, 128, 128]], np.int32))
+    sub = decode_masks(L[:1, :64, :64].contiguous(), np.array([[0, 0, 128, 128]], np.int32))
+    assert np.array_equal(sub.masks.cpu().numpy()[:128 * 128], o["masks"])
+    assert abs(int(up.area[0]) - 4 * int(r.area[0])) <= 0.02 * 4 * int(r.area[0]) + 64
+    assert mask_iou(r.masks, again.masks) == 1.0

@@ -1,0 +1,132 @@
+"""GPU parity tests of the forward: CUDA engine (through the C ABI) vs the oracle restatement
+and the committed reference logits.  Tolerances: fp32 mode 1e-4 max-abs on logits
+(BASELINE.json north_star); bf16 mode is reported against torch's own bf16 error, see
+DESIGN.md section 5."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, randomized_state
+from instancesegmentation_b200 import Segment, synth
+from oracle.segment_oracle import segment_forward
+
+pytestmark = pytest.mark.gpu
+FP32_TOL = 1e-4
+
+
+def _model(sd, cin=3, precision="fp32", max_batch=8):
+    m = Segment(cin)
+    m.load_state_dict(sd, strict=True)
+    m.precision, m.max_batch = precision, max_batch
+    return m.cuda().eval()
+
+
+def _engine(m):
+    return next(iter(m._engines.values()))
+
+
+def test_fp32_matches_committed_reference_logits(golden_state, golden_logits):
+    meta = json.load(open(os.path.join(GOLDEN, "segment3_golden.json")))
+    m = _model(golden_state)
+    for name, c in meta["cases"].items():
+        x = torch.from_numpy(synth.batch(c["B"], c["H"], c["W"], seed=c["seed"], kind=c["kind"])).cuda()
+        with torch.no_grad():
+            y = m(x)
+        assert y.shape == (c["B"], 1, c["H"], c["W"]) and y.dtype == torch.float32 and y.is_cuda
+        err = np.abs(y.cpu().numpy() - golden_logits[name]).max()
+        scale = max(1.0, c["logit_absmax"] / 3.0)   # the noise case has logits ~4x larger
+        print(f"{name}: max-abs err {err:.3e}")
+        assert err <= FP32_TOL * scale, (name, err)
+
+
+def test_fp32_layerwise_against_oracle(golden_state):
+    m = _model(golden_state)
+    x = torch.from_numpy(synth.batch(2, 96, 160, seed=4321))
+    taps = {}
+    want = segment_forward(golden_state, x, taps)
+    with torch.no_grad():
+        got = m(x.cuda()).cpu()
+    mine = _engine(m).taps(2)
+    report = {}
+    for k, t in mine.items():
+        assert k in taps, k
+        assert t.shape == taps[k].shape, (k, t.shape, taps[k].shape)
+        report[k] = float((t - taps[k]).abs().max())
+    print({k: f"{v:.2e}" for k, v in report.items()})
+    first_bad = next((k for k, v in report.items() if v > 1e-4 * max(1.0, float(taps[k].abs().max()))), None)
+    assert first_bad is None, (first_bad, report)
+    assert float((got - want).abs().max()) <= FP32_TOL
+
+
+@pytest.mark.parametrize("B,H,W", [(1, 16, 16), (3, 64, 64), (1, 480, 480), (2, 512, 512), (5, 32, 208)])
+def test_fp32_sizes_and_batches(golden_state, B, H, W):
+    m = _model(golden_state, max_batch=2)   # B=3,5 exercise the max_batch grouping
+    x = torch.from_numpy(synth.batch(B, H, W, seed=9000 + H))
+    want = segment_forward(golden_state, x)
+    with torch.no_grad():
+        got = m(x.cuda()).cpu()
+    err = float((got - want).abs().max())
+    print(f"B{B} {H}x{W}: {err:.3e}")
+    assert err <= FP32_TOL
+
+
+def test_fp32_1024(golden_state):
+    m = _model(golden_state, max_batch=1)
+    x = torch.from_numpy(synth.batch(1, 1024, 1024, seed=31))
+    want = segment_forward(golden_state, x)
+    with torch.no_grad():
+        got = m(x.cuda()).cpu()
+    assert float((got - want).abs().max()) <= FP32_TOL
+
+
+def test_fp32_in_channel_20():
+    ref = randomized_state(20, seed=5)
+    sd = ref.state_dict()
+    m = _model(sd, cin=20)
+    x = torch.from_numpy(synth.batch(2, 64, 96, seed=1, channels=20))
+    want = segment_forward(sd, x)
+    with torch.no_grad():
+        got = m.train_batch(x[:, :3].cuda(), x[:, 3:].cuda()).cpu()   # segment.py:531-534
+    assert float((got - torch.sigmoid(want)).abs().max()) <= 2e-5
+    with torch.no_grad():
+        assert float((m(x.cuda()).cpu() - want).abs().max()) <= FP32_TOL
+
+
+def test_weight_reload_and_batch_independence(golden_state):
+    m = _model(golden_state)
+    x = torch.from_numpy(synth.batch(4, 64, 64, seed=50)).cuda()
+    with torch.no_grad():
+        y4 = m(x)
+        y1 = torch.cat([m(x[i:i + 1]) for i in range(4)])
+        assert torch.equal(y4, y1)          # batch sharding is exact
+        sd2 = {k: (v * 1.01 if v.dtype.is_floating_point and k.endswith("conv.weight") else v)
+               for k, v in golden_state.items()}
+        m.load_state_dict(sd2)
+        y2 = m(x)
+    assert float((y2 - y4).abs().max()) > 1e-4
+    assert float((y2.cpu() - segment_forward(sd2, x.cpu())).abs().max()) <= FP32_TOL
+
+
+def test_bf16_mode_error_is_reported_and_bounded(golden_state):
+    """bf16 storage: error must stay below torch's own bf16 execution of the same network
+    (SURVEY 7.3-A measured 1.0 max / 0.08 mean for it)."""
+    x = torch.from_numpy(synth.batch(2, 256, 256, seed=77))
+    want = segment_forward(golden_state, x)
+    m = _model(golden_state, precision="bf16")
+    with torch.no_grad():
+        got = m(x.cuda()).cpu()
+    ours = (got - want).abs()
+    ref = Segment(3)
+    ref.load_state_dict(golden_state)
+    ref = ref.cuda().train(False)
+    # torch's bf16 path of the same graph (autograd route of the drop-in, eval BN)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        tb = ref._forward_autograd(x.cuda()).float().cpu()
+    theirs = (tb - want).abs()
+    print(f"bf16 ours max {ours.max():.3e} mean {ours.mean():.3e} | torch autocast max "
+          f"{theirs.max():.3e} mean {theirs.mean():.3e}")
+    assert float(ours.mean()) <= max(float(theirs.mean()), 0.1)
+    assert float(ours.max()) <= max(float(theirs.max()), 1.5)

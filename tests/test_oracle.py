@@ -1,0 +1,113 @@
+"""CPU tests: the oracle against the reference's own outputs (golden fixtures written by
+tests/golden/make_golden.py from the unmodified reference, and the reference itself when
+/root/reference is present)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from conftest import GOLDEN
+from instancesegmentation_b200 import synth
+from oracle import decode_oracle as D
+from oracle.segment_oracle import segment_forward
+
+KEYS_SHA = "36e3e48511037b2aa7dfd8a2157f14fb05dcd0c6baa67b4c979f76567e94261b"
+
+
+def test_golden_state_keys(golden_state):
+    assert len(golden_state) == 588
+    assert hashlib.sha256("\n".join(golden_state.keys()).encode()).hexdigest() == KEYS_SHA
+
+
+def test_oracle_forward_matches_golden_logits(golden_state, golden_logits):
+    meta = json.load(open(os.path.join(GOLDEN, "segment3_golden.json")))
+    for name, c in meta["cases"].items():
+        x = torch.from_numpy(synth.batch(c["B"], c["H"], c["W"], seed=c["seed"], kind=c["kind"]))
+        y = segment_forward(golden_state, x).numpy()
+        err = np.abs(y - golden_logits[name]).max()
+        # same torch ops as the reference: bit-equal in the generating container; other CPUs
+        # may pick different conv algorithms, hence the re-association allowance
+        assert err <= 5e-5, (name, err)
+
+
+def test_oracle_forward_matches_reference_module(reference_module, golden_state):
+    m = reference_module.Segment(3)
+    m.load_state_dict(golden_state, strict=True)
+    m.eval()
+    x = torch.from_numpy(synth.batch(2, 64, 112, seed=77))
+    taps = {}
+    with torch.no_grad():
+        want = m(x)
+    got = segment_forward(golden_state, x, taps)
+    assert torch.equal(want, got)
+    assert taps["init_down"].shape == (2, 19, 16, 28) and taps["bottle3_8"].shape == (2, 128, 4, 7)
+
+
+def test_oracle_forward_in_channel_20(reference_module):
+    torch.manual_seed(3)
+    m = reference_module.Segment(20).eval()
+    x = torch.randn(1, 20, 32, 48)
+    with torch.no_grad():
+        want = m(x)
+    assert torch.equal(want, segment_forward(m.state_dict(), x))
+
+
+def test_sigmoid_oracle_close_to_torch():
+    rng = np.random.default_rng(0)
+    x = np.concatenate([np.linspace(-30, 30, 6001), rng.normal(0, 2, 6000),
+                        [0.0, 1e-30, -1e-30, 88.0, -88.0, 200.0, -200.0]]).astype(np.float32)
+    s = D.sigmoid(x)
+    t = torch.sigmoid(torch.from_numpy(x)).numpy()
+    assert np.abs(s.astype(np.float64) - t).max() < 2.5e-7
+    assert np.all(np.diff(s[:6001]) >= 0)
+    assert s[-2] == 1.0 and s[-1] == 0.0
+    assert np.isnan(D.sigmoid(np.array([np.nan], np.float32))[0])
+
+
+def test_decode_oracle_against_torch_interpolate():
+    L = synth.logits(4, 48, 64, seed=5)
+    boxes = np.array([[0, 0, 64, 48], [3, 5, 128, 96], [1, 1, 23, 17], [7, 2, 100, 31]], np.int32)
+    r = D.decode(L, boxes, want_soft=True)
+    mism = 0
+    for n, (x0, y0, wk, hk) in enumerate(boxes):
+        p = F.interpolate(torch.sigmoid(torch.from_numpy(L[n:n + 1, None])), size=(int(hk), int(wk)),
+                          mode="bilinear", align_corners=False)[0, 0].numpy()
+        mine = r["masks"][r["off"][n]:r["off"][n + 1]].reshape(hk, wk)
+        safe = np.abs(p - 0.5) > 1e-5           # torch differs from the restatement by <= ~2 ulp
+        assert np.array_equal(mine[safe], (p > 0.5)[safe].astype(np.uint8))
+        mism += int((mine != (p > 0.5)).sum())
+        soft = r["soft"][r["off"][n]:r["off"][n + 1]].reshape(hk, wk).astype(np.int32)
+        assert np.abs(soft - (p * 255).astype(np.int32)).max() <= 1
+        assert r["area"][n] == int(mine.sum())
+        ys, xs = np.nonzero(mine)
+        if len(ys):
+            assert list(r["bbox"][n]) == [x0 + xs.min(), y0 + ys.min(), x0 + xs.max() + 1, y0 + ys.max() + 1]
+    assert mism <= 2
+
+
+def test_decode_oracle_edge_cases():
+    L = np.stack([np.full((16, 16), -5, np.float32), np.full((16, 16), 5, np.float32),
+                  np.where(np.arange(256).reshape(16, 16) == 37, 4, -4).astype(np.float32)])
+    boxes = np.array([[2, 3, 16, 16], [0, 0, 16, 16], [5, 5, 16, 16]], np.int32)
+    r = D.decode(L, boxes)
+    assert list(r["area"]) == [0, 256, 1]
+    assert list(r["bbox"][0]) == [0, 0, 0, 0]
+    assert list(r["bbox"][1]) == [0, 0, 16, 16]
+    assert list(r["bbox"][2]) == [5 + 5, 5 + 2, 5 + 6, 5 + 3]
+    # identity size: sigmoid(x) > 0.5 (not x > 0: tiny positive logits round to exactly 0.5)
+    tiny = np.array([[[1e-9, 1e-6, -1e-6, 0.0]]], np.float32)
+    assert list(D.decode(tiny, np.array([[0, 0, 4, 1]], np.int32))["masks"]) == [0, 1, 0, 0]
+
+
+def test_idmap_oracle_rules():
+    L = np.stack([np.full((8, 8), 1.0, np.float32), np.full((8, 8), 2.0, np.float32),
+                  np.full((8, 8), 2.0, np.float32), np.full((8, 8), -1.0, np.float32)])
+    boxes = np.array([[0, 0, 8, 8], [4, 0, 8, 8], [4, 4, 8, 8], [0, 0, 16, 16]], np.int32)
+    ids = D.idmap(L, boxes, [0, 4], 12, 10)[0]
+    assert ids[0, 0] == 1 and ids[0, 5] == 2      # higher probability wins
+    assert ids[5, 5] == 2                          # tie between 2 and 3 -> lowest index
+    assert ids[9, 9] == 3 and ids[11, 0] == 0      # box clipped by the canvas; unset mask -> 0
+    assert D.mask_iou([1, 1, 0, 0], [1, 0, 1, 0]) == 1 / 3
