@@ -51,6 +51,8 @@ struct isg_plan {
     int64_t macs_per_image = 0;
     int last_n = 0;
     std::vector<int> taps;     // tensor ids
+    bool use_tc = false;       // bf16 mode: GEMM-shaped convs on tcgen05 (ISG_NO_TC=1 disables)
+    std::vector<std::function<int()>> finalizers;  // run once after the workspace is allocated (tensor maps)
 
     size_t esize() const { return mode == ISG_MODE_BF16 ? 2 : 4; }
     void* tptr(int id) const { return ws + tensors[id].off; }

@@ -2,12 +2,16 @@
 // function registers (a) a packer that rewrites the reference-layout weights into the
 // kernel's layout inside the weight arena and (b) a launch closure.
 #include <cmath>
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "engine.h"
 #include "kernels_cc.cuh"
 #include "kernels_misc.cuh"
 #include "kernels_pw.cuh"
+#include "tc_conv.cuh"
+#include "tc_host.h"
 
 namespace isg {
 namespace {
@@ -25,7 +29,7 @@ struct Builder {
 
     // ---- tensors / arena ----
     int tensor(const std::string& name, int C, int H, int W, bool tap = false) {
-        TensorD t{name, C, round_up(C, 8), H, W, P->ws_bytes, tap};
+        TensorD t{name, C, round_up(C, sizeof(T) == 2 ? 16 : 8), H, W, P->ws_bytes, tap};
         size_t bytes = (size_t)P->max_batch * H * W * t.Cs * sizeof(T);
         P->ws_bytes += (bytes + 255) / 256 * 256;
         P->tensors.push_back(t);
@@ -108,6 +112,15 @@ struct Builder {
         int out = -1; int pool_out = -1;
     };
     void emit_pw(const PwSpec& s);
+    enum TcKind { TC_PW = 0, TC_S2D = 1, TC_C3X3 = 2 };
+    struct TcPart { int tensor; std::string conv, bn; bool bias_only; int cin_off, cin_total; };
+    struct TcSpec {
+        std::string name; int kind = TC_PW; std::vector<TcPart> parts;
+        int act = ACT_NONE; std::string slope; int res = -1; int res_mode = 0; int out = -1;
+    };
+    bool emit_tc(const TcSpec& s);
+    bool try_tc_from_pw(const PwSpec& s);
+    void emit_pool2(const std::string& name, int tin, int tout);
     void emit_convt4(const std::string& name, const std::string& prefix, int tin, int tout);
     void emit_tail(int tin);
 
@@ -121,11 +134,13 @@ struct Builder {
 };
 
 #include "engine_emit.inl"
+#include "engine_tc.inl"
 #include "engine_blocks.inl"
 
 }  // namespace
 
 int build_plan(isg_plan* p) {
+    p->use_tc = p->mode == ISG_MODE_BF16 && !getenv("ISG_NO_TC");
     if (p->mode == ISG_MODE_BF16) Builder<bf16>(p).build();
     else Builder<float>(p).build();
     return 0;

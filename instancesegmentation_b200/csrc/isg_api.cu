@@ -69,6 +69,10 @@ int isg_plan_create(int device, int in_channel, int height, int width, int max_b
     ISG_CUDA(cudaMemset(p->ws, 0, p->ws_bytes));  // pad channels stay zero for the plan's lifetime
     ISG_CUDA(cudaMalloc(&p->arena, p->arena_floats * sizeof(float)));
     p->arena_host.assign(p->arena_floats, 0.f);
+    for (auto& fin : p->finalizers) {
+        int rc = fin();
+        if (rc) { cudaFree(p->ws); cudaFree(p->arena); return rc; }
+    }
     ISG_CUDA(cudaDeviceSynchronize());
     *out = p.release();
     return ISG_OK;

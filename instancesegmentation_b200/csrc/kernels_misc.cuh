@@ -48,6 +48,22 @@ __global__ void __launch_bounds__(256) dw_kernel(DwParams p) {
 }
 
 // ---------------------------------------------------------------------------------
+// 2x2 max-pool, NHWC (F.max_pool2d, segment.py:145): materialises `residual_1`, which both
+// the block's own 1x1 skip conv and the decoder's concat (segment.py:331) consume.
+// ---------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) pool2_kernel(const T* __restrict__ in, T* __restrict__ out, int Ho, int Wo,
+                                                    int Cs, int total /* B*Ho*Wo*(Cs/4) */) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int cg = Cs >> 2, c = (i % cg) * 4, pix = i / cg;
+    const int x = pix % Wo, y = (pix / Wo) % Ho, b = pix / (Wo * Ho);
+    const T* s = in + (((size_t)b * 2 * Ho + 2 * y) * 2 * Wo + 2 * x) * Cs + c;
+    const size_t row = (size_t)2 * Wo * Cs;
+    st4(out + (size_t)pix * Cs + c, max4(max4(ld4(s), ld4(s + Cs)), max4(ld4(s + row), ld4(s + row + Cs))));
+}
+
+// ---------------------------------------------------------------------------------
 // ConvTranspose2d k4 s2 p1, C -> C (C = 16 or 4) + BatchNorm + ReLU (segment.py:305-308).
 // Gather form: output (oy,ox) sees the 2x2 inputs with ky = (oy+1)%2 + {0,2}.
 // Weights [ky][kx][ci(CS)][co(C)], CS = storage stride of the input (pad rows are zero).
