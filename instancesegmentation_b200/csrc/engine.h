@@ -16,6 +16,17 @@ struct TensorD {
     int C, Cs, H, W;      // logical channels, storage stride, spatial size (per image)
     size_t off;           // byte offset in the workspace
     bool tap;             // exposed through isg_plan_tap_*
+    // storage variants of the fused bf16 path (engine_fk.cu):
+    //  layout 1: space-to-depth -- logical (c,y,x) lives at [(y/2)][(x/2)][((y&1)*2+(x&1))*Cs + c]
+    //  perm: logical channel -> storage channel (empty = identity)
+    int layout = 0;
+    std::vector<int> perm;
+    int storage_of(int c) const { return perm.empty() ? c : perm[c]; }
+    int logical_of(int s) const {
+        if (perm.empty()) return s < C ? s : -1;
+        for (int c = 0; c < C; ++c) if (perm[c] == s) return c;
+        return -1;
+    }
 };
 
 // host view of the caller's state_dict during isg_plan_load_weights
@@ -59,5 +70,6 @@ struct isg_plan {
 };
 
 namespace isg {
-int build_plan(isg_plan* p);  // engine_build.cu
+int build_plan(isg_plan* p);     // engine_build.cu
+void build_fk_plan(isg_plan* p);  // engine_fk.cu (ISG_MODE_BF16)
 }

@@ -1,29 +1,6 @@
 // Builder<T>::block_* -- the reference's residual blocks lowered to emit_* launches.
 // Included inside namespace isg::{anon}.  `p` is the state_dict prefix of the block.
 
-// ---- tensor-core lowering of a pointwise spec (bf16 mode); false -> caller uses emit_pw ----
-template <typename T>
-bool Builder<T>::try_tc_from_pw(const PwSpec& s) {
-    if (sizeof(T) != 2 || !P->use_tc) return false;
-    if (s.a.mode != SRC_DIRECT) return false;
-    if (s.b_kind == BR_GEMM && s.b.mode != SRC_DIRECT) return false;
-    if (s.b_kind != BR_NONE && s.act_a != ACT_NONE) return false;
-    TcSpec t;
-    t.name = s.name; t.kind = TC_PW; t.out = s.out;
-    auto add = [&](const Src& r, const std::string& conv, const std::string& bn, bool bias_only) {
-        int c0 = td(r.t0).C, c1 = r.t1 >= 0 ? td(r.t1).C : 0;
-        t.parts.push_back(TcPart{r.t0, conv, bn, bias_only, 0, c0 + c1});
-        if (r.t1 >= 0) t.parts.push_back(TcPart{r.t1, conv, bn, bias_only, c0, c0 + c1});
-    };
-    add(s.a, s.wa, s.bna, s.a_bias_only);
-    if (s.b_kind == BR_GEMM) add(s.b, s.wb, s.bnb, s.b_bias_only);
-    if (t.parts.size() > 3) return false;
-    if (s.b_kind == BR_NONE && s.act_out == ACT_NONE) { t.act = s.act_a; t.slope = s.slope_a; }
-    else { t.act = s.act_out; t.slope = s.slope_out; }
-    if (s.b_kind == BR_IDENTITY) { t.res = s.res; t.res_mode = tc::RES_DIRECT; }
-    return emit_tc(t);
-}
-
 template <typename T>
 void Builder<T>::emit_pool2(const std::string& name, int tin, int tout) {
     isg_plan* P = this->P;
@@ -40,7 +17,7 @@ void Builder<T>::emit_pool2(const std::string& name, int tin, int tout) {
     P->ops.push_back(op);
 }
 
-#define ISG_PW(spec) do { if (!try_tc_from_pw(spec)) emit_pw(spec); } while (0)
+#define ISG_PW(spec) emit_pw(spec)
 
 // BottleneckDown2 (segment.py:114-150): returns the block output; *keep = max-pooled input.
 template <typename T>
@@ -51,10 +28,7 @@ int Builder<T>::block_down(const std::string& p, int x, int mid, int cout, int* 
     int m1 = tensor(p + ".m1", mid, h, w), m2 = tensor(p + ".m2", mid, h, w);
     *keep = tensor(p + ".keep", tx.C, h, w, true);
     int out = tensor(tapname, cout, h, w, true);
-    TcSpec c0;
-    c0.name = p + ".convs.0"; c0.kind = TC_S2D; c0.out = m1; c0.act = ACT_PRELU; c0.slope = p + ".convs.0.act.weight";
-    c0.parts.push_back(TcPart{x, p + ".convs.0.conv", p + ".convs.0.bn", false, 0, tx.C});
-    if (!emit_tc(c0)) emit_convk(p + ".convs.0", p + ".convs.0", x, m1, 0, mid, 2, 2, 2, 0, ACT_PRELU);
+    emit_convk(p + ".convs.0", p + ".convs.0", x, m1, 0, mid, 2, 2, 2, 0, ACT_PRELU);
     emit_dw(p + ".convs.1", p + ".convs.1.conv", p + ".convs.1.bn", p + ".convs.1.act.weight", m1, m2, 3, 3, 1,
             ACT_PRELU);
     PwSpec s;
@@ -63,14 +37,6 @@ int Builder<T>::block_down(const std::string& p, int x, int mid, int cout, int* 
     s.b_kind = BR_GEMM; s.b.t0 = x; s.b.mode = SRC_POOL2; s.wb = p + ".convm.0.conv"; s.bnb = p + ".convm.0.bn";
     s.act_out = ACT_PRELU; s.slope_out = p + ".prelu.weight";
     s.out = out; s.pool_out = *keep;
-    if (sizeof(T) == 2 && P->use_tc) {
-        // tensor-core path: materialise the pooled map once, then one GEMM over (m2 | pooled)
-        emit_pool2(p + ".maxpool2", x, *keep);
-        PwSpec t = s;
-        t.b.t0 = *keep; t.b.mode = SRC_DIRECT; t.pool_out = -1;
-        if (try_tc_from_pw(t)) return out;
-        P->ops.pop_back();  // not feasible on tensor cores: drop the pool launch, use the fused CUDA-core op
-    }
     emit_pw(s);
     return out;
 }
@@ -154,10 +120,7 @@ int Builder<T>::block_plain(const std::string& p, int x, int mid) {
     a.name = p + ".convs.0";
     a.a.t0 = x; a.wa = p + ".convs.0.conv"; a.bna = p + ".convs.0.bn"; a.act_a = ACT_RELU; a.out = m1;
     ISG_PW(a);
-    TcSpec c1;
-    c1.name = p + ".convs.1"; c1.kind = TC_C3X3; c1.out = m2; c1.act = ACT_RELU;
-    c1.parts.push_back(TcPart{m1, p + ".convs.1.conv", p + ".convs.1.bn", false, 0, mid});
-    if (!emit_tc(c1)) emit_convk(p + ".convs.1", p + ".convs.1", m1, m2, 0, mid, 3, 3, 1, 1, ACT_RELU);
+    emit_convk(p + ".convs.1", p + ".convs.1", m1, m2, 0, mid, 3, 3, 1, 1, ACT_RELU);
     PwSpec c;
     c.name = p + ".convs.2+res+relu";
     c.a.t0 = m2; c.wa = p + ".convs.2.conv"; c.bna = p + ".convs.2.bn";
@@ -182,21 +145,6 @@ int Builder<T>::block_up(const std::string& p, int x, int skip, int mid, int cou
     r.name = p + ".conv2";
     r.a.t0 = x; r.wa = p + ".conv2.0.conv"; r.bna = p + ".conv2.0.bn"; r.out = r0;
     ISG_PW(r);
-    if (sizeof(T) == 2 && P->use_tc) {
-        // nearest-x2 followed by a 1x1 conv == the 1x1 conv followed by nearest-x2 (exact per pixel):
-        // run uppool.1 at low resolution and add it in the consumer's epilogue with index >> 1
-        int r1 = tensor(p + ".r1", cout, h, w);
-        PwSpec u;
-        u.name = p + ".uppool.1 (low res)";
-        u.a.t0 = r0; u.a.t1 = skip; u.wa = p + ".uppool.1"; u.a_bias_only = true; u.out = r1;
-        ISG_PW(u);
-        TcSpec f;
-        f.name = p + ".convs.4+up2(res)+relu"; f.kind = TC_PW; f.out = out; f.act = ACT_RELU;
-        f.parts.push_back(TcPart{m2, p + ".convs.4.conv", p + ".convs.4.bn", false, 0, mid});
-        f.res = r1; f.res_mode = tc::RES_UP2;
-        if (emit_tc(f)) return out;
-        P->ops.pop_back();
-    }
     PwSpec c;
     c.name = p + ".convs.4+uppool+relu";
     c.a.t0 = m2; c.wa = p + ".convs.4.conv"; c.bna = p + ".convs.4.bn";

@@ -10,8 +10,6 @@
 #include "kernels_cc.cuh"
 #include "kernels_misc.cuh"
 #include "kernels_pw.cuh"
-#include "tc_conv.cuh"
-#include "tc_host.h"
 
 namespace isg {
 namespace {
@@ -112,14 +110,6 @@ struct Builder {
         int out = -1; int pool_out = -1;
     };
     void emit_pw(const PwSpec& s);
-    enum TcKind { TC_PW = 0, TC_S2D = 1, TC_C3X3 = 2 };
-    struct TcPart { int tensor; std::string conv, bn; bool bias_only; int cin_off, cin_total; };
-    struct TcSpec {
-        std::string name; int kind = TC_PW; std::vector<TcPart> parts;
-        int act = ACT_NONE; std::string slope; int res = -1; int res_mode = 0; int out = -1;
-    };
-    bool emit_tc(const TcSpec& s);
-    bool try_tc_from_pw(const PwSpec& s);
     void emit_pool2(const std::string& name, int tin, int tout);
     void emit_convt4(const std::string& name, const std::string& prefix, int tin, int tout);
     void emit_tail(int tin);
@@ -134,14 +124,16 @@ struct Builder {
 };
 
 #include "engine_emit.inl"
-#include "engine_tc.inl"
 #include "engine_blocks.inl"
 
 }  // namespace
 
 int build_plan(isg_plan* p) {
+    // bf16 mode = fused tcgen05 block kernels (engine_fk.cu); ISG_NO_TC=1 keeps the CUDA-core
+    // kernels with bf16 storage, which exist only as a debugging cross-check
     p->use_tc = p->mode == ISG_MODE_BF16 && !getenv("ISG_NO_TC");
-    if (p->mode == ISG_MODE_BF16) Builder<bf16>(p).build();
+    if (p->use_tc) build_fk_plan(p);
+    else if (p->mode == ISG_MODE_BF16) Builder<bf16>(p).build();
     else Builder<float>(p).build();
     return 0;
 }

@@ -1,0 +1,1146 @@
+// ISG_MODE_BF16 plan: Segment.forward (model/segment.py:466-508) lowered to fused block
+// kernels (fk.cuh).  Every residual block is one or two launches; BatchNorm is folded into
+// bf16 weights + fp32 shift, activations into the epilogue, torch.cat into concatenated K
+// slices, depthwise convs into the consumer's prologue, the next block's first 1x1 conv
+// into the producer's second GEMM, nearest-x2 + 1x1 into a low-resolution GEMM whose result
+// is the pixel-shuffled consumer's residual, and bottle6_1 o bottle6_2 into one composed
+// transposed convolution.
+#include <algorithm>
+#include <cstdlib>
+#include <memory>
+
+#include "engine.h"
+#include "fk.cuh"
+#include "kernels_misc.cuh"
+#include "pack_util.h"
+#include "tc_host.h"
+
+namespace isg {
+namespace {
+
+// ---------------------------------------------------------------------------------
+// CUDA-core helpers of the fused path
+// ---------------------------------------------------------------------------------
+// network input NCHW fp32 -> X2 [B,H/2,W/2,Cs2] bf16, channel (ry*2+rx)*Cin + c (space-to-depth
+// of the stride-2 stem conv, segment.py:23-24), plus max_pool2d(x,4,4) (segment.py:29) into
+// channels [16,16+Cin) of init_down.  One thread = one 4x4 input patch.
+template <int CIN>
+__global__ void __launch_bounds__(128)
+prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, bf16* __restrict__ init,
+            int Cs_init, int total) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int W4 = W >> 2, H4 = H >> 2;
+    const int x4 = i % W4, y4 = (i / W4) % H4, b = i / (W4 * H4);
+    float v[CIN][4][4];
+#pragma unroll
+    for (int c = 0; c < CIN; ++c)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(
+                x + (((size_t)b * CIN + c) * H + 4 * y4 + r) * W + 4 * x4));
+            v[c][r][0] = q.x; v[c][r][1] = q.y; v[c][r][2] = q.z; v[c][r][3] = q.w;
+        }
+    // four space-to-depth pixels (sy, sx) = (2*y4 + a, 2*x4 + bb)
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int bb = 0; bb < 2; ++bb) {
+            float f[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) f[k] = 0.f;
+#pragma unroll
+            for (int ry = 0; ry < 2; ++ry)
+#pragma unroll
+                for (int rx = 0; rx < 2; ++rx)
+#pragma unroll
+                    for (int c = 0; c < CIN; ++c) f[(ry * 2 + rx) * CIN + c] = v[c][2 * a + ry][2 * bb + rx];
+            bf16* d = x2 + (((size_t)b * (H >> 1) + 2 * y4 + a) * (W >> 1) + 2 * x4 + bb) * Cs2;
+            fk::st_global_16(d, make_uint4(fk::pack_bf16(f[0], f[1]), fk::pack_bf16(f[2], f[3]),
+                                           fk::pack_bf16(f[4], f[5]), fk::pack_bf16(f[6], f[7])));
+            fk::st_global_16(d + 8, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
+                                               fk::pack_bf16(f[12], f[13]), fk::pack_bf16(f[14], f[15])));
+        }
+    float m[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) m[k] = 0.f;
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) {
+        float mx = v[c][0][0];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) mx = fmaxf(mx, v[c][r][q]);
+        m[c] = mx;
+    }
+    bf16* d = init + (((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16;
+    fk::st_global_16(d, make_uint4(fk::pack_bf16(m[0], m[1]), fk::pack_bf16(m[2], m[3]), fk::pack_bf16(m[4], m[5]),
+                                   fk::pack_bf16(m[6], m[7])));
+    fk::st_global_16(d + 8, make_uint4(0, 0, 0, 0));
+}
+
+// generic (any Cin) variant: one thread = one (patch, channel)
+__global__ void __launch_bounds__(128)
+prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __restrict__ x2, int Cs2,
+                    bf16* __restrict__ init, int Cs_init, int total) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int W4 = W >> 2, H4 = H >> 2;
+    const int x4 = i % W4, y4 = (i / W4) % H4, c = (i / (W4 * H4)) % Cin, b = i / (W4 * H4 * Cin);
+    float mx = -INFINITY;
+    for (int r = 0; r < 4; ++r) {
+        const float4 q = __ldg(reinterpret_cast<const float4*>(x + (((size_t)b * Cin + c) * H + 4 * y4 + r) * W + 4 * x4));
+        const float f[4] = {q.x, q.y, q.z, q.w};
+        for (int k = 0; k < 4; ++k) {
+            mx = fmaxf(mx, f[k]);
+            const int sy = 2 * y4 + (r >> 1), sx = 2 * x4 + (k >> 1);
+            x2[(((size_t)b * (H >> 1) + sy) * (W >> 1) + sx) * Cs2 + ((r & 1) * 2 + (k & 1)) * Cin + c] =
+                __float2bfloat16_rn(f[k]);
+        }
+    }
+    init[(((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16 + c] = __float2bfloat16_rn(mx);
+}
+
+// The composed tail GEMM treats the transposed conv's output as if it extended one pixel
+// beyond the image; the reference zero-pads it there (Conv2d padding=1, segment.py:437).
+// This kernel subtracts, for the border ring of the logits, the contributions of those
+// outside positions.  One thread = one border pixel.
+struct TailFixParams {
+    const bf16* in; int Hq, Wq, Cs;    // [B,Hq,Wq,16]
+    float* logits;                     // [B,4Hq,4Wq]
+    const float* wt;                   // [ky(8)][kx(8)][ci(16)][co(4)]
+    const float* bt;                   // [4]
+    const float* w3;                   // [ky(3)][kx(3)][ci(4)]
+    int total;                         // B * ring
+};
+__device__ __forceinline__ int floordiv4(int a) { return a >= 0 ? a >> 2 : -((3 - a) >> 2); }
+__global__ void __launch_bounds__(128) tail_fix_kernel(TailFixParams p) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.total) return;
+    const int H = 4 * p.Hq, W = 4 * p.Wq, ring = 2 * W + 2 * (H - 2);
+    const int b = i / ring;
+    int j = i - b * ring, oy, ox;
+    if (j < W) { oy = 0; ox = j; }
+    else if (j < 2 * W) { oy = H - 1; ox = j - W; }
+    else { j -= 2 * W; oy = 1 + (j >> 1); ox = (j & 1) ? W - 1 : 0; }
+    float corr = 0.f;
+    for (int dy = -1; dy <= 1; ++dy)
+        for (int dx = -1; dx <= 1; ++dx) {
+            const int ty = oy + dy, tx = ox + dx;
+            if (ty >= 0 && ty < H && tx >= 0 && tx < W) continue;
+            float t[4] = {p.bt[0], p.bt[1], p.bt[2], p.bt[3]};
+            const int iy1 = floordiv4(ty + 2), ix1 = floordiv4(tx + 2);
+            for (int iy = iy1 - 1; iy <= iy1; ++iy) {
+                const int ky = ty + 2 - 4 * iy;
+                if (iy < 0 || iy >= p.Hq || ky < 0 || ky > 7) continue;
+                for (int ix = ix1 - 1; ix <= ix1; ++ix) {
+                    const int kx = tx + 2 - 4 * ix;
+                    if (ix < 0 || ix >= p.Wq || kx < 0 || kx > 7) continue;
+                    const bf16* src = p.in + (((size_t)b * p.Hq + iy) * p.Wq + ix) * p.Cs;
+                    const float4* w = reinterpret_cast<const float4*>(p.wt) + (ky * 8 + kx) * 16;
+                    for (int c = 0; c < 16; ++c) {
+                        const float v = __bfloat162float(src[c]);
+                        const float4 ww = __ldg(w + c);
+                        t[0] = fmaf(v, ww.x, t[0]); t[1] = fmaf(v, ww.y, t[1]);
+                        t[2] = fmaf(v, ww.z, t[2]); t[3] = fmaf(v, ww.w, t[3]);
+                    }
+                }
+            }
+            const float* w3 = p.w3 + ((dy + 1) * 3 + dx + 1) * 4;
+            corr += t[0] * w3[0] + t[1] * w3[1] + t[2] * w3[2] + t[3] * w3[3];
+        }
+    p.logits[((size_t)b * H + oy) * W + ox] -= corr;
+}
+
+// ---------------------------------------------------------------------------------
+// specification of one fused launch
+// ---------------------------------------------------------------------------------
+struct LoadSpec { int tensor; int chunk0 = 0; int nchunks = -1; int halo = 0; bool s2d = false; };
+enum PartKind { PART_LOAD = 0, PART_STENCIL = 1, PART_PREV = 2 };
+struct Part { int kind; int load; };
+typedef std::function<void(const HostWeights&, float* B, float* shift, float* slope)> StageFill;
+typedef std::function<void(const HostWeights&, float* w, float* shift, float* slope, float* bw)> StencilFill;
+struct StageSpec {
+    std::vector<Part> parts;
+    bool taps9 = false;
+    int N = 0;
+    StageFill fill;                 // B[tap][K][N] (zeroed), shift[N] (zeroed), slope[N] (ones)
+    int res_load = -1, res_mod = 0;
+    int out_mode = fk::OUT_STAGE, out_tensor = -1, out_chunk0 = 0;
+    bool store = true;
+    int shuf = 1, Cp = 0;
+    bool to_logits = false;
+};
+struct StencilSpec { int kind = 0; int load = -1; int dil = 1; StencilFill fill; };  // 1 dw3x3, 2 sep5
+struct Spec {
+    std::string name;
+    int qH = 0, qW = 0;             // q-pixel grid of one image
+    std::vector<LoadSpec> loads;
+    StencilSpec st;
+    std::vector<StageSpec> stages;
+};
+
+struct Lay {
+    int TH = 0, TW = 0, pitch = 0, n_mt = 0, cols = 0;
+    size_t smem = 0;
+    int load_off[fk::MAX_LOADS], load_plane[fk::MAX_LOADS], load_planes[fk::MAX_LOADS];
+    int st_out_off = 0, st_out_plane = 0, st_in_pitch = 0;
+    int stage_off[2] = {0, 0}, stage_plane[2] = {0, 0}, stage_compact[2] = {1, 1};
+    int K[2] = {0, 0};
+    int b_off[2] = {0, 0}, vec_off[2] = {0, 0}, stw_off = 0, stvec_off = 0, blob_off = 0, blob_bytes = 0, bar_off = 0;
+    uint32_t tx = 0;
+    double score = -1;
+};
+
+inline int r128(int v) { return (v + 127) / 128 * 128; }
+
+struct FkMaps { CUtensorMap in[4], out[2]; };
+
+struct FkBuilder {
+    isg_plan* P;
+    explicit FkBuilder(isg_plan* p) : P(p) {}
+
+    int tensor(const std::string& name, int C, int H, int W, bool tap = false) {
+        TensorD t{name, C, round_up(C, 16), H, W, P->ws_bytes, tap};
+        size_t bytes = (size_t)P->max_batch * H * W * t.Cs * 2;
+        P->ws_bytes += (bytes + 255) / 256 * 256;
+        P->tensors.push_back(t);
+        if (tap) P->taps.push_back((int)P->tensors.size() - 1);
+        return (int)P->tensors.size() - 1;
+    }
+    int view(const std::string& name, int of, int C, int Cs, int H, int W, bool tap, int layout) {
+        TensorD t{name, C, Cs, H, W, P->tensors[of].off, tap};
+        t.layout = layout;
+        P->tensors.push_back(t);
+        if (tap) P->taps.push_back((int)P->tensors.size() - 1);
+        return (int)P->tensors.size() - 1;
+    }
+    const TensorD& td(int id) const { return P->tensors[id]; }
+    size_t arena(size_t nfloats) {
+        P->arena_floats = (P->arena_floats + 63) / 64 * 64;  // 256-byte aligned blobs
+        size_t o = P->arena_floats;
+        P->arena_floats += nfloats;
+        return o;
+    }
+    void macs(int64_t cout, int64_t cin_g, int kh, int kw, int Ho, int Wo) {
+        P->macs_per_image += cout * cin_g * kh * kw * Ho * Wo;
+    }
+
+    // ---- layout of one candidate tile ----
+    bool layout(const Spec& s, int TH, int TW, Lay& L) const {
+        const int hx = s.stages[0].taps9 ? 1 : 0;
+        L.TH = TH; L.TW = TW; L.pitch = TW + 2 * hx;
+        const int mrows = TH * L.pitch;
+        L.n_mt = cdiv(mrows, 128);
+        int maxN = 0;
+        for (auto& st : s.stages) maxN = std::max(maxN, st.N);
+        L.cols = L.n_mt * maxN;
+        if (L.cols > 512) return false;
+        const int a_rows = L.n_mt * 128 + (hx ? 2 * L.pitch + 2 : 0);
+        const int npix = TH * TW;
+        const bool chained = s.stages.size() > 1;
+        int off = 0;
+        L.tx = 0;
+        for (size_t i = 0; i < s.loads.size(); ++i) {
+            const LoadSpec& l = s.loads[i];
+            const TensorD& t = td(l.tensor);
+            int bw, bh, planes;
+            if (l.s2d) { bw = TW; bh = TH; planes = 4 * t.Cs / 8; }
+            else { bw = TW + 2 * l.halo; bh = TH + 2 * l.halo; planes = l.nchunks < 0 ? t.Cs / 8 : l.nchunks; }
+            if (bw > 256 || bh > 256 || planes > 256) return false;
+            L.load_off[i] = off; L.load_plane[i] = bw * bh * 16; L.load_planes[i] = planes;
+            bool is_a0 = false;
+            for (auto& pt : s.stages[0].parts) is_a0 |= pt.kind == PART_LOAD && pt.load == (int)i;
+            if (is_a0 && hx && l.halo != 1) return false;
+            if (is_a0 && !hx && l.halo != 0) return false;
+            int slack = 0;
+            if (is_a0) slack = std::max(0, a_rows * 16 - L.load_plane[i]);
+            if ((int)i == s.stages[0].res_load && chained) slack = std::max(slack, L.n_mt * 128 * 16 - L.load_plane[i]);
+            L.tx += (uint32_t)planes * L.load_plane[i];
+            off = r128(off + planes * L.load_plane[i] + slack);
+        }
+        if (s.st.kind) {
+            const LoadSpec& l = s.loads[s.st.load];
+            const int nch = l.nchunks < 0 ? td(l.tensor).Cs / 8 : l.nchunks;
+            L.st_in_pitch = TW + 2 * l.halo;
+            L.st_out_off = off; L.st_out_plane = npix * 16;
+            off = r128(off + nch * L.st_out_plane + std::max(0, L.n_mt * 128 * 16 - L.st_out_plane));
+        }
+        for (size_t k = 0; k < s.stages.size(); ++k) {
+            const StageSpec& st = s.stages[k];
+            int K = 0;
+            for (auto& pt : st.parts) {
+                if (pt.kind == PART_LOAD) K += L.load_planes[pt.load] * 8;
+                else if (pt.kind == PART_STENCIL) K += (s.loads[s.st.load].nchunks < 0 ? td(s.loads[s.st.load].tensor).Cs / 8
+                                                                                         : s.loads[s.st.load].nchunks) * 8;
+                else K += s.stages[0].N;
+            }
+            L.K[k] = K;
+            if (K % 16 || K / 16 > fk::MAX_KS) return false;
+            if (st.out_mode != fk::OUT_STAGE) continue;
+            const bool is_chain_src = k == 0 && chained;
+            L.stage_compact[k] = (hx == 0) || !is_chain_src;
+            if (!L.stage_compact[k] && st.store) return false;
+            const int pix = L.stage_compact[k] ? npix : L.n_mt * 128;
+            L.stage_plane[k] = pix * 16;
+            const bool alias = st.res_load >= 0 && st.res_mod == 0 && L.stage_compact[k] &&
+                               L.load_planes[st.res_load] == st.N / 8 && s.loads[st.res_load].halo == 0;
+            if (alias) { L.stage_off[k] = L.load_off[st.res_load]; continue; }
+            L.stage_off[k] = off;
+            int slack = is_chain_src ? std::max(0, L.n_mt * 128 * 16 - L.stage_plane[k]) : 0;
+            off = r128(off + (st.N / 8) * L.stage_plane[k] + slack);
+        }
+        // constants blob
+        L.blob_off = off;
+        int rel = 0;
+        for (size_t k = 0; k < s.stages.size(); ++k) {
+            L.b_off[k] = rel;
+            rel = r128(rel + (s.stages[k].taps9 ? 9 : 1) * (L.K[k] / 16) * s.stages[k].N * 32);
+        }
+        for (size_t k = 0; k < s.stages.size(); ++k) { L.vec_off[k] = rel; rel = r128(rel + 2 * s.stages[k].N * 4); }
+        if (s.st.kind) {
+            const LoadSpec& l = s.loads[s.st.load];
+            const int C = (l.nchunks < 0 ? td(l.tensor).Cs / 8 : l.nchunks) * 8;
+            const int ntaps = s.st.kind == 2 ? 25 : 9;
+            L.stw_off = rel; rel = r128(rel + ntaps * C * 4);
+            L.stvec_off = rel; rel = r128(rel + (s.st.kind == 2 ? 7 : 2) * C * 4);
+        }
+        L.blob_bytes = rel;
+        L.tx += rel;
+        off = r128(off + rel);
+        L.bar_off = off;
+        L.smem = (size_t)off + 64;
+        return L.smem <= 224 * 1024;
+    }
+
+    Lay choose(const Spec& s) const {
+        const int hx = s.stages[0].taps9 ? 1 : 0;
+        int max_halo = hx;
+        for (auto& l : s.loads) max_halo = std::max(max_halo, l.halo);
+        // tile width: the image width split evenly so that every TMA box fits 256 columns
+        int nx = 1;
+        while (cdiv(s.qW, nx) + 2 * max_halo > 256) ++nx;
+        const int TW = cdiv(s.qW, nx);
+        Lay best;
+        const char* cap_env = getenv("ISG_FK_MAX_MT");
+        const int mt_cap = cap_env ? atoi(cap_env) : 16;
+        for (int pass = 0; pass < 2 && best.score < 0; ++pass) {
+            for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
+                Lay L;
+                if (!layout(s, TH, TW, L)) continue;
+                if (L.n_mt > mt_cap && TH > 1) continue;
+                if (pass == 0 && (L.cols > 256 || L.smem > 112 * 1024)) continue;
+                const int tiles_y = cdiv(s.qH, TH);
+                const double eff_m = (double)(TH * TW) / (L.n_mt * 128);
+                const double eff_tail = (double)s.qH / (tiles_y * TH);
+                const double eff_halo = (double)TH / (TH + 2 * max_halo);
+                L.score = eff_m * eff_tail * (0.5 + 0.5 * eff_halo) + 1e-4 * TH;
+                if (L.score > best.score) best = L;
+            }
+        }
+        return best;
+    }
+
+    // ---- emit one fused launch ----
+    void emit(const Spec& s) {
+        isg_plan* P = this->P;
+        Lay L = choose(s);
+        if (L.score < 0) {
+            fprintf(stderr, "libisg: no feasible tile for %s\n", s.name.c_str());
+            abort();
+        }
+        if (getenv("ISG_FK_VERBOSE"))
+            fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d\n", s.name.c_str(),
+                    s.qH, s.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1]);
+        fk::Params q;
+        std::memset(&q, 0, sizeof q);
+        q.TH = L.TH; q.TW = L.TW; q.H = s.qH; q.W = s.qW;
+        q.tiles_x = cdiv(s.qW, L.TW); q.tiles_y = cdiv(s.qH, L.TH);
+        q.n_mt = L.n_mt; q.tmem_cols = tc::tmem_cols_pow2(L.cols);
+        q.nloads = (int)s.loads.size();
+        for (int i = 0; i < q.nloads; ++i) {
+            const LoadSpec& l = s.loads[i];
+            fk::Load& d = q.loads[i];
+            d.map = i; d.smem_off = L.load_off[i]; d.dx = -l.halo; d.dy = -l.halo; d.chunk0 = l.chunk0;
+            d.folded = l.s2d ? 1 : 0; d.rows_per_img = s.qH; d.step = 1;
+        }
+        q.tx_bytes = L.tx; q.blob_off = L.blob_off; q.blob_bytes = L.blob_bytes; q.bar_off = L.bar_off;
+        int st_C = 0;
+        if (s.st.kind) {
+            const LoadSpec& l = s.loads[s.st.load];
+            fk::Stencil& t = q.st;
+            t.on = 1; t.in_off = L.load_off[s.st.load]; t.in_pitch = L.st_in_pitch;
+            t.in_plane_bytes = L.load_plane[s.st.load]; t.halo = l.halo; t.nchunks = L.load_planes[s.st.load];
+            st_C = t.nchunks * 8;
+            if (s.st.kind == 1) {
+                t.ntaps = 9;
+                for (int k = 0; k < 9; ++k) t.tap_off[k] = ((k / 3) - 1) * s.st.dil * t.in_pitch + ((k % 3) - 1) * s.st.dil;
+            } else {
+                t.ntaps = 25; t.sep5 = 1;
+                for (int k = 0; k < 25; ++k) t.tap_off[k] = ((k / 5) - 2) * t.in_pitch + ((k % 5) - 2);
+            }
+            t.w_off = L.blob_off + L.stw_off; t.vec_off = L.blob_off + L.stvec_off;
+            t.out_off = L.st_out_off; t.out_plane_bytes = L.st_out_plane;
+        }
+        q.nstages = (int)s.stages.size();
+        for (int k = 0; k < q.nstages; ++k) {
+            const StageSpec& st = s.stages[k];
+            fk::Stage& d = q.stage[k];
+            d.N = st.N; d.ntaps = st.taps9 ? 9 : 1; d.pitch = L.pitch;
+            for (int t = 0; t < d.ntaps; ++t) d.tap_off[t] = st.taps9 ? (t / 3) * L.pitch + (t % 3) : 0;
+            int nks = 0;
+            for (auto& pt : st.parts) {
+                int base, plane, planes;
+                if (pt.kind == PART_LOAD) { base = L.load_off[pt.load]; plane = L.load_plane[pt.load]; planes = L.load_planes[pt.load]; }
+                else if (pt.kind == PART_STENCIL) { base = L.st_out_off; plane = L.st_out_plane; planes = st_C / 8; }
+                else { base = L.stage_off[0]; plane = L.stage_plane[0]; planes = s.stages[0].N / 8; }
+                for (int j = 0; j < planes / 2; ++j) { d.ks_off[nks] = base + 2 * j * plane; d.ks_lbo[nks] = plane; ++nks; }
+            }
+            d.nks = nks;
+            d.w_off = L.blob_off + L.b_off[k]; d.vec_off = L.blob_off + L.vec_off[k];
+            if (st.res_load >= 0) {
+                d.res_on = 1; d.res_off = L.load_off[st.res_load]; d.res_plane_bytes = L.load_plane[st.res_load];
+                d.res_mod = st.res_mod;
+            }
+            d.out_mode = st.out_mode; d.stage_off = L.stage_off[k]; d.stage_plane_bytes = L.stage_plane[k];
+            d.stage_compact = L.stage_compact[k]; d.store = st.store && st.out_mode == fk::OUT_STAGE;
+            d.store_chunk0 = st.out_chunk0; d.shuf = st.shuf; d.Cp = st.Cp;
+            if (st.out_tensor >= 0) d.Cs_out = td(st.out_tensor).Cs;
+        }
+        // constants blob in the arena
+        const size_t blob = arena((size_t)L.blob_bytes / 4);
+        const Spec sp = s;
+        Op op;
+        op.name = s.name + " [fk]";
+        op.pack = [=](const HostWeights& w, float* A) {
+            uint8_t* base = reinterpret_cast<uint8_t*>(A + blob);
+            std::memset(base, 0, L.blob_bytes);
+            for (size_t k = 0; k < sp.stages.size(); ++k) {
+                const StageSpec& st = sp.stages[k];
+                const int ntaps = st.taps9 ? 9 : 1, K = L.K[k], N = st.N, nks = K / 16;
+                std::vector<float> B((size_t)ntaps * K * N, 0.f), shift(N, 0.f), slope(N, 1.f);
+                st.fill(w, B.data(), shift.data(), slope.data());
+                uint16_t* wb = reinterpret_cast<uint16_t*>(base + L.b_off[k]);
+                for (int t = 0; t < ntaps; ++t)
+                    for (int kk = 0; kk < K; ++kk)
+                        for (int n = 0; n < N; ++n) {
+                            const size_t blk = (size_t)t * nks + kk / 16;
+                            const size_t idx = blk * (size_t)N * 16 + (size_t)((kk % 16) / 8) * N * 8 + (size_t)n * 8 + (kk % 8);
+                            wb[idx] = tc::f2bf(B[((size_t)t * K + kk) * N + n]);
+                        }
+                float* v = reinterpret_cast<float*>(base + L.vec_off[k]);
+                std::memcpy(v, shift.data(), sizeof(float) * N);
+                std::memcpy(v + N, slope.data(), sizeof(float) * N);
+            }
+            if (sp.st.kind) {
+                const int C = st_C, ntaps = sp.st.kind == 2 ? 25 : 9;
+                std::vector<float> wt((size_t)ntaps * C, 0.f), shift(C, 0.f), slope(C, 1.f), bw(5 * (size_t)C, 0.f);
+                sp.st.fill(w, wt.data(), shift.data(), slope.data(), bw.data());
+                std::memcpy(base + L.stw_off, wt.data(), sizeof(float) * wt.size());
+                float* v = reinterpret_cast<float*>(base + L.stvec_off);
+                std::memcpy(v, shift.data(), sizeof(float) * C);
+                std::memcpy(v + C, slope.data(), sizeof(float) * C);
+                if (sp.st.kind == 2) std::memcpy(v + 2 * C, bw.data(), sizeof(float) * 5 * C);
+            }
+        };
+        auto maps = std::make_shared<FkMaps>();
+        const int maxB = P->max_batch;
+        P->finalizers.push_back([=]() -> int {
+            for (size_t i = 0; i < sp.loads.size(); ++i) {
+                const LoadSpec& l = sp.loads[i];
+                const TensorD& t = P->tensors[l.tensor];
+                int rc;
+                if (l.s2d) rc = tc::make_s2d_map(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH, sp.name.c_str());
+                else rc = tc::make_act_map_chunks(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW + 2 * l.halo,
+                                                  L.TH + 2 * l.halo, L.load_planes[i], sp.name.c_str());
+                if (rc) return rc;
+            }
+            for (size_t i = sp.loads.size(); i < 4; ++i) maps->in[i] = maps->in[0];
+            for (size_t k = 0; k < 2; ++k) {
+                if (k < sp.stages.size() && sp.stages[k].out_mode == fk::OUT_STAGE && sp.stages[k].store) {
+                    const TensorD& t = P->tensors[sp.stages[k].out_tensor];
+                    int rc = tc::make_act_map_chunks(&maps->out[k], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH,
+                                                     sp.stages[k].N / 8, sp.name.c_str());
+                    if (rc) return rc;
+                } else maps->out[k] = maps->in[0];
+            }
+            return 0;
+        });
+        cudaFuncSetAttribute(fk::fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        const size_t smem = L.smem;
+        const int tiles = q.tiles_x * q.tiles_y;
+        op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
+            fk::Params p = q;
+            p.blob = P->arena + blob;
+            for (int k = 0; k < p.nstages; ++k) {
+                const StageSpec& st = sp.stages[k];
+                if (st.to_logits) p.stage[k].gptr = logits;
+                else if (st.out_mode != fk::OUT_STAGE) p.stage[k].gptr = P->ws + P->tensors[st.out_tensor].off;
+            }
+            fk::fk_kernel<<<n * tiles, fk::THREADS, smem, stream>>>(maps->in[0], maps->in[1], maps->in[2], maps->in[3],
+                                                                   maps->out[0], maps->out[1], p);
+            return cudaGetLastError();
+        };
+        P->ops.push_back(op);
+    }
+
+    // ---- plain CUDA-core launches ----
+    void emit_prep(int t_x2, int t_init) {
+        isg_plan* P = this->P;
+        const int cin = P->cin, H = P->H, W = P->W;
+        const TensorD x2 = td(t_x2), init = td(t_init);
+        Op op;
+        op.name = "prep: NCHW fp32 -> space-to-depth bf16 + max_pool4";
+        op.pack = [](const HostWeights&, float*) {};
+        op.launch = [=](int n, const float* x, float*, cudaStream_t st) {
+            bf16* px2 = reinterpret_cast<bf16*>(P->ws + x2.off);
+            bf16* pin = reinterpret_cast<bf16*>(P->ws + init.off);
+            if (cin == 3) {
+                const int total = n * (H / 4) * (W / 4);
+                prep_kernel<3><<<cdiv(total, 128), 128, 0, st>>>(x, H, W, px2, x2.Cs, pin, init.Cs, total);
+            } else {
+                const int total = n * cin * (H / 4) * (W / 4);
+                prep_generic_kernel<<<cdiv(total, 128), 128, 0, st>>>(x, cin, H, W, px2, x2.Cs, pin, init.Cs, total);
+            }
+            return cudaGetLastError();
+        };
+        P->ops.push_back(op);
+    }
+    void emit_pool2(const std::string& name, int tin, int tout) {
+        isg_plan* P = this->P;
+        const TensorD ti = td(tin), to = td(tout);
+        Op op;
+        op.name = name;
+        op.pack = [](const HostWeights&, float*) {};
+        op.launch = [=](int n, const float*, float*, cudaStream_t st) {
+            int total = n * to.H * to.W * (to.Cs / 4);
+            pool2_kernel<bf16><<<cdiv(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(P->ws + ti.off),
+                                                                reinterpret_cast<bf16*>(P->ws + to.off), to.H, to.W,
+                                                                to.Cs, total);
+            return cudaGetLastError();
+        };
+        P->ops.push_back(op);
+    }
+
+    // ---- fill helpers ----
+    // 1x1 conv weights Wt[Cout][cin_total] (columns cin_off.. of the logical input) times
+    // scale[o] into rows [k0, k0 + 8*nchunks) (storage channels of tensor t) and columns
+    // [n0, n0 + Cout) of B[K][N]
+    static void put_pw(float* B, int N, int k0, const TensorD& t, int chunk0, int nchunks, const float* Wt,
+                       int cin_total, int cin_off, const float* scale, int Cout, int n0) {
+        for (int j = 0; j < nchunks * 8; ++j) {
+            const int l = t.logical_of(chunk0 * 8 + j);
+            if (l < 0) continue;
+            for (int o = 0; o < Cout; ++o)
+                B[(size_t)(k0 + j) * N + n0 + o] = Wt[(size_t)o * cin_total + cin_off + l] * (scale ? scale[o] : 1.f);
+        }
+    }
+
+    // next block's first 1x1 conv (Conv wrapper `unit`) as a chained stage over the producer's staging
+    struct Next { bool on = false; std::string unit; int mid = 0; int act = ACT_PRELU; int out = -1; };
+    StageSpec chain_stage(const Next& nx, int Cprev /*logical channels of staging*/, int Nprev) {
+        StageSpec st;
+        st.parts = {Part{PART_PREV, -1}};
+        st.N = round_up(nx.mid, 16);
+        st.out_tensor = nx.out;
+        const std::string unit = nx.unit;
+        const int mid = nx.mid, act = nx.act, N = st.N;
+        (void)Nprev;
+        st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(mid), sh(mid);
+            fold_unit(w, unit + ".conv", unit + ".bn", mid, sc.data(), sh.data());
+            const float* Wt = w.get(unit + ".conv.weight");  // [mid][Cprev]
+            for (int k = 0; k < Cprev; ++k)
+                for (int o = 0; o < mid; ++o) B[(size_t)k * N + o] = Wt[(size_t)o * Cprev + k] * sc[o];
+            for (int o = 0; o < mid; ++o) {
+                shift[o] = sh[o];
+                slope[o] = act == ACT_PRELU ? w.get(unit + ".act.weight")[o] : 0.f;
+            }
+        };
+        return st;
+    }
+    Next next_of(const std::string& unit, int mid, int act, int H, int W) {
+        Next n;
+        n.on = true; n.unit = unit; n.mid = mid; n.act = act;
+        n.out = tensor(unit + ".out", mid, H, W);
+        return n;
+    }
+
+    StencilSpec dw3_stencil(const std::string& unit, int load, int mid, int dil) {
+        StencilSpec s;
+        s.kind = 1; s.load = load; s.dil = dil;
+        s.fill = [=](const HostWeights& w, float* wt, float* shift, float* slope, float*) {
+            const int C = round_up(mid, 16);
+            std::vector<float> sc(mid), sh(mid);
+            fold_unit(w, unit + ".conv", unit + ".bn", mid, sc.data(), sh.data());
+            const float* k = w.get(unit + ".conv.weight");  // [mid][1][3][3]
+            for (int c = 0; c < mid; ++c) {
+                for (int t = 0; t < 9; ++t) wt[(size_t)t * C + c] = k[(size_t)c * 9 + t] * sc[c];
+                shift[c] = sh[c];
+                slope[c] = w.get(unit + ".act.weight")[c];
+            }
+        };
+        return s;
+    }
+    // Bottleneck5x5 (segment.py:91-97): bare depthwise (5,1) + bias, then (1,5) + BN + PReLU
+    StencilSpec sep5_stencil(const std::string& p, int load, int mid) {
+        StencilSpec s;
+        s.kind = 2; s.load = load;
+        s.fill = [=](const HostWeights& w, float* wt, float* shift, float* slope, float* bw) {
+            const int C = round_up(mid, 16);
+            std::vector<float> sc(mid), sh(mid);
+            fold_unit(w, p + ".convs.2.conv", p + ".convs.2.bn", mid, sc.data(), sh.data());
+            const float* w1 = w.get(p + ".convs.1.weight");        // [mid][1][5][1]
+            const float* b1 = w.get(p + ".convs.1.bias");
+            const float* w2 = w.get(p + ".convs.2.conv.weight");   // [mid][1][1][5]
+            for (int c = 0; c < mid; ++c) {
+                for (int ky = 0; ky < 5; ++ky)
+                    for (int kx = 0; kx < 5; ++kx)
+                        wt[(size_t)(ky * 5 + kx) * C + c] = sc[c] * w2[c * 5 + kx] * w1[c * 5 + ky];
+                for (int kx = 0; kx < 5; ++kx) bw[(size_t)kx * C + c] = sc[c] * w2[c * 5 + kx] * b1[c];
+                shift[c] = sh[c];
+                slope[c] = w.get(p + ".convs.2.act.weight")[c];
+            }
+        };
+        return s;
+    }
+
+    // standalone 1x1 Conv wrapper over the concat of `srcs`
+    int pw_unit(const std::string& unit, const std::vector<int>& srcs, int cout, int act, const std::string& outname) {
+        const TensorD t0 = td(srcs[0]);
+        Spec s;
+        s.name = unit;
+        s.qH = t0.H; s.qW = t0.W;
+        StageSpec st;
+        std::vector<TensorD> tin;
+        int cin_total = 0;
+        for (size_t i = 0; i < srcs.size(); ++i) {
+            s.loads.push_back(LoadSpec{srcs[i]});
+            st.parts.push_back(Part{PART_LOAD, (int)i});
+            tin.push_back(td(srcs[i]));
+            cin_total += td(srcs[i]).C;
+        }
+        st.N = round_up(cout, 16);
+        const int out = tensor(outname, cout, t0.H, t0.W);
+        st.out_tensor = out;
+        macs(cout, cin_total, 1, 1, t0.H, t0.W);
+        const int N = st.N;
+        st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(cout), sh(cout);
+            fold_unit(w, unit + ".conv", unit + ".bn", cout, sc.data(), sh.data());
+            int k0 = 0, c0 = 0;
+            for (auto& t : tin) {
+                put_pw(B, N, k0, t, 0, t.Cs / 8, w.get(unit + ".conv.weight"), cin_total, c0, sc.data(), cout, 0);
+                k0 += t.Cs; c0 += t.C;
+            }
+            for (int o = 0; o < cout; ++o) {
+                shift[o] = sh[o];
+                slope[o] = act == ACT_PRELU ? w.get(unit + ".act.weight")[o] : (act == ACT_RELU ? 0.f : 1.f);
+            }
+        };
+        s.stages.push_back(st);
+        emit(s);
+        return out;
+    }
+
+    // Bottleneck3x3 / Bottleneck5x5 (segment.py:52-111) given the block's first conv output m1
+    int block_res(const std::string& p, int x, int m1, int mid, int dil, bool five, const Next& nx,
+                  const std::string& outname, bool tap) {
+        const TensorD tx = td(x);
+        const int C = tx.C;
+        const std::string last = five ? p + ".convs.3" : p + ".convs.2";
+        Spec s;
+        s.name = p;
+        s.qH = tx.H; s.qW = tx.W;
+        s.loads.push_back(LoadSpec{m1, 0, -1, five ? 2 : dil});
+        s.loads.push_back(LoadSpec{x});
+        s.st = five ? sep5_stencil(p, 0, mid) : dw3_stencil(p + ".convs.1", 0, mid, dil);
+        if (five) { macs(mid, 1, 5, 1, tx.H, tx.W); macs(mid, 1, 1, 5, tx.H, tx.W); }
+        else macs(mid, 1, 3, 3, tx.H, tx.W);
+        macs(C, mid, 1, 1, tx.H, tx.W);
+        StageSpec st;
+        st.parts = {Part{PART_STENCIL, -1}};
+        st.N = tx.Cs;
+        st.res_load = 1;
+        const int out = tensor(outname, C, tx.H, tx.W, tap);
+        st.out_tensor = out;
+        const int N = st.N;
+        st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(C), sh(C);
+            fold_unit(w, last + ".conv", last + ".bn", C, sc.data(), sh.data());
+            const float* Wt = w.get(last + ".conv.weight");  // [C][mid]
+            for (int k = 0; k < mid; ++k)
+                for (int o = 0; o < C; ++o) B[(size_t)k * N + o] = Wt[(size_t)o * mid + k] * sc[o];
+            for (int o = 0; o < C; ++o) { shift[o] = sh[o]; slope[o] = w.get(p + ".prelu.weight")[o]; }
+        };
+        s.stages.push_back(st);
+        if (nx.on) {
+            s.stages.push_back(chain_stage(nx, C, N));
+            macs(nx.mid, C, 1, 1, tx.H, tx.W);
+        }
+        emit(s);
+        return out;
+    }
+
+    // BottleneckDown2 (segment.py:114-150)
+    int block_down(const std::string& p, int x, int mid, int cout, int* keep, const std::string& outname,
+                   const std::string& keepname, const Next& nx) {
+        const TensorD tx = td(x);
+        const int h = tx.H / 2, w = tx.W / 2;
+        // convs.0: 2x2 stride-2 conv as a GEMM over the space-to-depth view
+        const int m1 = tensor(p + ".m1", mid, h, w);
+        {
+            Spec s;
+            s.name = p + ".convs.0 (2x2 s2)";
+            s.qH = h; s.qW = w;
+            LoadSpec l{x};
+            l.s2d = true;
+            s.loads.push_back(l);
+            StageSpec st;
+            st.parts = {Part{PART_LOAD, 0}};
+            st.N = round_up(mid, 16);
+            st.out_tensor = m1;
+            macs(mid, tx.C, 2, 2, h, w);
+            const int N = st.N, Cs = tx.Cs, Cin = tx.C;
+            const std::string unit = p + ".convs.0";
+            const TensorD txc = tx;
+            st.fill = [=](const HostWeights& wv, float* B, float* shift, float* slope) {
+                std::vector<float> sc(mid), sh(mid);
+                fold_unit(wv, unit + ".conv", unit + ".bn", mid, sc.data(), sh.data());
+                const float* Wt = wv.get(unit + ".conv.weight");  // [mid][Cin][2][2]
+                for (int a = 0; a < 2; ++a)
+                    for (int bb = 0; bb < 2; ++bb)
+                        for (int sidx = 0; sidx < Cs; ++sidx) {
+                            const int l = txc.logical_of(sidx);
+                            if (l < 0) continue;
+                            const int k = a * 2 * Cs + bb * Cs + sidx;
+                            for (int o = 0; o < mid; ++o)
+                                B[(size_t)k * N + o] = Wt[(((size_t)o * Cin + l) * 2 + a) * 2 + bb] * sc[o];
+                        }
+                for (int o = 0; o < mid; ++o) { shift[o] = sh[o]; slope[o] = wv.get(unit + ".act.weight")[o]; }
+            };
+            s.stages.push_back(st);
+            emit(s);
+        }
+        // residual_1 = max_pool2d(x) (segment.py:145): also the decoder's skip
+        *keep = tensor(keepname, tx.C, h, w, true);
+        P->tensors[*keep].perm = tx.perm;
+        emit_pool2(p + ".maxpool2", x, *keep);
+        // dw3x3 -> [convs.2 | convm] -> +, PReLU  (-> next block's first conv)
+        const TensorD tk = td(*keep);
+        Spec s;
+        s.name = p + ".dw+convs.2+convm";
+        s.qH = h; s.qW = w;
+        s.loads.push_back(LoadSpec{m1, 0, -1, 1});
+        s.loads.push_back(LoadSpec{*keep});
+        s.st = dw3_stencil(p + ".convs.1", 0, mid, 1);
+        macs(mid, 1, 3, 3, h, w);
+        macs(cout, mid, 1, 1, h, w);
+        macs(cout, tx.C, 1, 1, h, w);
+        StageSpec st;
+        st.parts = {Part{PART_STENCIL, -1}, Part{PART_LOAD, 1}};
+        st.N = round_up(cout, 16);
+        const int out = tensor(outname, cout, h, w, true);
+        st.out_tensor = out;
+        const int N = st.N, midp = round_up(mid, 16), Cin = tx.C;
+        st.fill = [=](const HostWeights& wv, float* B, float* shift, float* slope) {
+            std::vector<float> sc(cout), sh(cout), scm(cout), shm(cout);
+            fold_unit(wv, p + ".convs.2.conv", p + ".convs.2.bn", cout, sc.data(), sh.data());
+            fold_unit(wv, p + ".convm.0.conv", p + ".convm.0.bn", cout, scm.data(), shm.data());
+            const float* W2 = wv.get(p + ".convs.2.conv.weight");  // [cout][mid]
+            for (int k = 0; k < mid; ++k)
+                for (int o = 0; o < cout; ++o) B[(size_t)k * N + o] = W2[(size_t)o * mid + k] * sc[o];
+            put_pw(B, N, midp, tk, 0, tk.Cs / 8, wv.get(p + ".convm.0.conv.weight"), Cin, 0, scm.data(), cout, 0);
+            for (int o = 0; o < cout; ++o) { shift[o] = sh[o] + shm[o]; slope[o] = wv.get(p + ".prelu.weight")[o]; }
+        };
+        s.stages.push_back(st);
+        if (nx.on) {
+            s.stages.push_back(chain_stage(nx, cout, N));
+            macs(nx.mid, cout, 1, 1, h, w);
+        }
+        emit(s);
+        return out;
+    }
+
+    // BottleneckDim_Res (segment.py:153-209) on cat(x0, x1); m1 = convs.0 output
+    int block_proj(const std::string& p, int x0, int x1, int m1, int mid, int cout, bool last_prelu, const Next& nx) {
+        const TensorD t0 = td(x0), t1 = td(x1);
+        Spec s;
+        s.name = p + ".dw+convs.2+resconv";
+        s.qH = t0.H; s.qW = t0.W;
+        s.loads.push_back(LoadSpec{m1, 0, -1, 1});
+        s.loads.push_back(LoadSpec{x0});
+        s.loads.push_back(LoadSpec{x1});
+        s.st = dw3_stencil(p + ".convs.1", 0, mid, 1);
+        const int Cin = t0.C + t1.C;
+        macs(mid, 1, 3, 3, t0.H, t0.W);
+        macs(cout, mid, 1, 1, t0.H, t0.W);
+        macs(cout, Cin, 1, 1, t0.H, t0.W);
+        StageSpec st;
+        st.parts = {Part{PART_STENCIL, -1}, Part{PART_LOAD, 1}, Part{PART_LOAD, 2}};
+        st.N = round_up(cout, 16);
+        const int out = tensor(p, cout, t0.H, t0.W, true);
+        st.out_tensor = out;
+        const int N = st.N, midp = round_up(mid, 16);
+        st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(cout), sh(cout), scr(cout), shr(cout);
+            fold_unit(w, p + ".convs.2.conv", p + ".convs.2.bn", cout, sc.data(), sh.data());
+            fold_unit(w, p + ".resconv.0.conv", p + ".resconv.0.bn", cout, scr.data(), shr.data());
+            const float* W2 = w.get(p + ".convs.2.conv.weight");
+            for (int k = 0; k < mid; ++k)
+                for (int o = 0; o < cout; ++o) B[(size_t)k * N + o] = W2[(size_t)o * mid + k] * sc[o];
+            const float* Wr = w.get(p + ".resconv.0.conv.weight");  // [cout][Cin]
+            put_pw(B, N, midp, t0, 0, t0.Cs / 8, Wr, Cin, 0, scr.data(), cout, 0);
+            put_pw(B, N, midp + t0.Cs, t1, 0, t1.Cs / 8, Wr, Cin, t0.C, scr.data(), cout, 0);
+            for (int o = 0; o < cout; ++o) {
+                shift[o] = sh[o] + shr[o];
+                slope[o] = last_prelu ? w.get(p + ".prelu.weight")[o] : 0.f;
+            }
+        };
+        s.stages.push_back(st);
+        if (nx.on) {
+            s.stages.push_back(chain_stage(nx, cout, N));
+            macs(nx.mid, cout, 1, 1, t0.H, t0.W);
+        }
+        emit(s);
+        return out;
+    }
+
+    // BottleneckDim(usePrelu=False) (segment.py:232-261): dense 3x3 then 1x1 + x, ReLU; m1 = convs.0 output
+    int block_plain(const std::string& p, int x, int m1, int mid) {
+        const TensorD tx = td(x);
+        const int C = tx.C;
+        Spec s;
+        s.name = p + ".convs.1(3x3)+convs.2+res";
+        s.qH = tx.H; s.qW = tx.W;
+        s.loads.push_back(LoadSpec{m1, 0, -1, 1});
+        s.loads.push_back(LoadSpec{x});
+        macs(mid, mid, 3, 3, tx.H, tx.W);
+        macs(C, mid, 1, 1, tx.H, tx.W);
+        StageSpec a;
+        a.parts = {Part{PART_LOAD, 0}};
+        a.taps9 = true;
+        a.N = round_up(mid, 16);
+        a.store = false;
+        const int Na = a.N, Ka = td(m1).Cs;
+        a.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(mid), sh(mid);
+            fold_unit(w, p + ".convs.1.conv", p + ".convs.1.bn", mid, sc.data(), sh.data());
+            const float* Wt = w.get(p + ".convs.1.conv.weight");  // [mid][mid][3][3]
+            for (int t = 0; t < 9; ++t)
+                for (int k = 0; k < mid; ++k)
+                    for (int o = 0; o < mid; ++o)
+                        B[((size_t)t * Ka + k) * Na + o] = Wt[((size_t)o * mid + k) * 9 + t] * sc[o];
+            for (int o = 0; o < mid; ++o) { shift[o] = sh[o]; slope[o] = 0.f; }
+        };
+        s.stages.push_back(a);
+        StageSpec b;
+        b.parts = {Part{PART_PREV, -1}};
+        b.N = tx.Cs;
+        b.res_load = 1;
+        const int out = tensor(p, C, tx.H, tx.W, true);
+        b.out_tensor = out;
+        const int Nb = b.N;
+        b.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(C), sh(C);
+            fold_unit(w, p + ".convs.2.conv", p + ".convs.2.bn", C, sc.data(), sh.data());
+            const float* Wt = w.get(p + ".convs.2.conv.weight");  // [C][mid]
+            for (int k = 0; k < mid; ++k)
+                for (int o = 0; o < C; ++o) B[(size_t)k * Nb + o] = Wt[(size_t)o * mid + k] * sc[o];
+            for (int o = 0; o < C; ++o) { shift[o] = sh[o]; slope[o] = 0.f; }
+        };
+        s.stages.push_back(b);
+        emit(s);
+        return out;
+    }
+
+    // BottleneckUp_Res / _Other (segment.py:296-344)
+    int block_up(const std::string& p, int x, int skip, int mid, int cout, const std::string& outname) {
+        const TensorD tx = td(x), ts = td(skip);
+        const int h = tx.H, w = tx.W;
+        // (a) one GEMM over (x | skip): columns [0,16) = convs.0 (+BN, ReLU); columns [16,16+cout) =
+        //     uppool.1(cat(conv2(x), skip)) evaluated at LOW resolution (nearest-x2 commutes with a 1x1 conv)
+        const int u = tensor(p + ".u", 16 + cout, h, w);
+        {
+            Spec s;
+            s.name = p + ".convs.0|uppool(conv2|skip)";
+            s.qH = h; s.qW = w;
+            s.loads.push_back(LoadSpec{x});
+            s.loads.push_back(LoadSpec{skip});
+            StageSpec st;
+            st.parts = {Part{PART_LOAD, 0}, Part{PART_LOAD, 1}};
+            st.N = 16 + round_up(cout, 16);
+            st.out_tensor = u;
+            macs(mid, tx.C, 1, 1, h, w);
+            macs(cout, tx.C, 1, 1, h, w);
+            macs(cout, cout + ts.C, 1, 1, 2 * h, 2 * w);
+            const int N = st.N, Cx = tx.C, Cskip = ts.C;
+            st.fill = [=](const HostWeights& wv, float* B, float* shift, float* slope) {
+                std::vector<float> s0(mid), h0(mid), s2(cout), h2(cout);
+                fold_unit(wv, p + ".convs.0.conv", p + ".convs.0.bn", mid, s0.data(), h0.data());
+                fold_unit(wv, p + ".conv2.0.conv", p + ".conv2.0.bn", cout, s2.data(), h2.data());
+                put_pw(B, N, 0, tx, 0, tx.Cs / 8, wv.get(p + ".convs.0.conv.weight"), Cx, 0, s0.data(), mid, 0);
+                for (int o = 0; o < mid; ++o) { shift[o] = h0[o]; slope[o] = 0.f; }
+                for (int o = mid; o < 16; ++o) slope[o] = 0.f;
+                const float* Wu = wv.get(p + ".uppool.1.weight");   // [cout][cout + Cskip]
+                const float* bu = wv.get(p + ".uppool.1.bias");
+                const float* Wc = wv.get(p + ".conv2.0.conv.weight");  // [cout][Cx]
+                const int cu = cout + Cskip;
+                std::vector<float> comp((size_t)cout * Cx);
+                for (int o = 0; o < cout; ++o)
+                    for (int k = 0; k < Cx; ++k) {
+                        double a = 0;
+                        for (int j = 0; j < cout; ++j) a += (double)Wu[(size_t)o * cu + j] * s2[j] * Wc[(size_t)j * Cx + k];
+                        comp[(size_t)o * Cx + k] = (float)a;
+                    }
+                put_pw(B, N, 0, tx, 0, tx.Cs / 8, comp.data(), Cx, 0, nullptr, cout, 16);
+                put_pw(B, N, tx.Cs, ts, 0, ts.Cs / 8, Wu, cu, cout, nullptr, cout, 16);
+                for (int o = 0; o < cout; ++o) {
+                    double a = bu[o];
+                    for (int j = 0; j < cout; ++j) a += (double)Wu[(size_t)o * cu + j] * h2[j];
+                    shift[16 + o] = (float)a;
+                    slope[16 + o] = 1.f;
+                }
+            };
+            s.stages.push_back(st);
+            emit(s);
+        }
+        // (b) ConvTranspose2d k4 s2 p1 (+BN, ReLU) as a 9-tap GEMM with 4 output phases in N, then the
+        //     block-diagonal convs.4 (+BN), + low-res side branch, ReLU, pixel-shuffle store
+        const int Cp1 = mid <= 8 ? 8 : 16, Cp2 = round_up(cout, 16);
+        Spec s;
+        s.name = p + ".convT4+convs.4+side";
+        s.qH = h; s.qW = w;
+        s.loads.push_back(LoadSpec{u, 0, 2, 1});
+        s.loads.push_back(LoadSpec{u, 2, Cp2 / 8, 0});
+        macs(mid, mid, 4, 4, h, w);
+        macs(cout, mid, 1, 1, 2 * h, 2 * w);
+        StageSpec a;
+        a.parts = {Part{PART_LOAD, 0}};
+        a.taps9 = true;
+        a.N = 4 * Cp1;
+        a.store = false;
+        const int Na = a.N;
+        a.fill = [=](const HostWeights& wv, float* B, float* shift, float* slope) {
+            std::vector<float> sc(mid), sh(mid);
+            fold_unit(wv, p + ".convs.1", p + ".convs.2", mid, sc.data(), sh.data());
+            const float* Wt = wv.get(p + ".convs.1.weight");  // [mid(in)][mid(out)][4][4]
+            for (int t = 0; t < 9; ++t) {
+                const int dy = t / 3 - 1, dx = t % 3 - 1;
+                for (int ph = 0; ph < 4; ++ph) {
+                    const int ky = (ph >> 1) - 2 * dy + 1, kx = (ph & 1) - 2 * dx + 1;
+                    if (ky < 0 || ky > 3 || kx < 0 || kx > 3) continue;
+                    for (int k = 0; k < mid; ++k)
+                        for (int c = 0; c < mid; ++c)
+                            B[((size_t)t * 16 + k) * Na + ph * Cp1 + c] = Wt[(((size_t)k * mid + c) * 4 + ky) * 4 + kx] * sc[c];
+                }
+            }
+            for (int ph = 0; ph < 4; ++ph)
+                for (int c = 0; c < Cp1; ++c) {
+                    shift[ph * Cp1 + c] = c < mid ? sh[c] : 0.f;
+                    slope[ph * Cp1 + c] = 0.f;
+                }
+        };
+        s.stages.push_back(a);
+        StageSpec b;
+        b.parts = {Part{PART_PREV, -1}};
+        b.N = 4 * Cp2;
+        b.res_load = 1; b.res_mod = Cp2;
+        b.out_mode = fk::OUT_SHUF_BF16; b.shuf = 2; b.Cp = Cp2;
+        const int out = tensor(outname, cout, 2 * h, 2 * w, true);
+        b.out_tensor = out;
+        const int Nb = b.N;
+        b.fill = [=](const HostWeights& wv, float* B, float* shift, float* slope) {
+            std::vector<float> sc(cout), sh(cout);
+            fold_unit(wv, p + ".convs.4.conv", p + ".convs.4.bn", cout, sc.data(), sh.data());
+            const float* Wt = wv.get(p + ".convs.4.conv.weight");  // [cout][mid]
+            for (int ph = 0; ph < 4; ++ph)
+                for (int c = 0; c < mid; ++c)
+                    for (int o = 0; o < cout; ++o)
+                        B[(size_t)(ph * Cp1 + c) * Nb + ph * Cp2 + o] = Wt[(size_t)o * mid + c] * sc[o];
+            for (int ph = 0; ph < 4; ++ph)
+                for (int o = 0; o < Cp2; ++o) {
+                    shift[ph * Cp2 + o] = o < cout ? sh[o] : 0.f;
+                    slope[ph * Cp2 + o] = 0.f;
+                }
+        };
+        s.stages.push_back(b);
+        emit(s);
+        return out;
+    }
+
+    // 5x5 stride-2 pad-2 Conv wrapper as a 9-tap GEMM over a space-to-depth input (segment.py:23-26)
+    void stem_conv(const std::string& unit, int src, int cin, int out_tensor, int out_mode, int qH, int qW) {
+        Spec s;
+        s.name = unit + " (5x5 s2 via space-to-depth)";
+        s.qH = qH; s.qW = qW;
+        s.loads.push_back(LoadSpec{src, 0, -1, 1});
+        StageSpec st;
+        st.parts = {Part{PART_LOAD, 0}};
+        st.taps9 = true;
+        st.N = 16;
+        st.out_mode = out_mode;
+        st.out_tensor = out_tensor;
+        macs(16, cin, 5, 5, qH, qW);
+        const int K = td(src).Cs;
+        st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(16), sh(16);
+            fold_unit(w, unit + ".conv", unit + ".bn", 16, sc.data(), sh.data());
+            const float* Wt = w.get(unit + ".conv.weight");  // [16][cin][5][5]
+            for (int t = 0; t < 9; ++t)
+                for (int ph = 0; ph < 4; ++ph) {
+                    const int ky = 2 * (t / 3) + (ph >> 1), kx = 2 * (t % 3) + (ph & 1);
+                    if (ky > 4 || kx > 4) continue;
+                    for (int c = 0; c < cin; ++c)
+                        for (int o = 0; o < 16; ++o)
+                            B[((size_t)t * K + ph * cin + c) * 16 + o] = Wt[(((size_t)o * cin + c) * 5 + ky) * 5 + kx] * sc[o];
+                }
+            for (int o = 0; o < 16; ++o) { shift[o] = sh[o]; slope[o] = w.get(unit + ".act.weight")[o]; }
+        };
+        s.stages.push_back(st);
+        emit(s);
+    }
+
+    // bottle6_1 (ConvTranspose2d k8 s4 p2, 16->4) composed with bottle6_2 (Conv2d 3x3 p1, 4->1):
+    // no activation in between (segment.py:504-505), so the pair is one 16->1 transposed conv with a
+    // 10x10 kernel, stride 4: a 9-tap GEMM with the 16 output phases in N + a border correction
+    void tail(int y) {
+        isg_plan* P = this->P;
+        const TensorD ty = td(y);
+        macs(4, 16, 8, 8, ty.H, ty.W);
+        macs(1, 4, 3, 3, 4 * ty.H, 4 * ty.W);
+        Spec s;
+        s.name = "bottle6_1*bottle6_2 (composed k10 s4 transposed conv)";
+        s.qH = ty.H; s.qW = ty.W;
+        s.loads.push_back(LoadSpec{y, 0, -1, 1});
+        StageSpec st;
+        st.parts = {Part{PART_LOAD, 0}};
+        st.taps9 = true;
+        st.N = 16;
+        st.out_mode = fk::OUT_SHUF4_F32;
+        st.to_logits = true;
+        st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            const float* W1 = w.get("bottle6_1.weight");  // [16][4][8][8]
+            const float* b1 = w.get("bottle6_1.bias");
+            const float* W3 = w.get("bottle6_2.weight");  // [1][4][3][3]
+            const float b3 = w.get("bottle6_2.bias")[0];
+            std::vector<double> Wc(16 * 100, 0.0);        // [ci][ku][kv]
+            for (int ci = 0; ci < 16; ++ci)
+                for (int ku = 0; ku < 10; ++ku)
+                    for (int kv = 0; kv < 10; ++kv) {
+                        double a = 0;
+                        for (int c = 0; c < 4; ++c)
+                            for (int dy = -1; dy <= 1; ++dy)
+                                for (int dx = -1; dx <= 1; ++dx) {
+                                    const int ky = ku - 1 + dy, kx = kv - 1 + dx;
+                                    if (ky < 0 || ky > 7 || kx < 0 || kx > 7) continue;
+                                    a += (double)W3[c * 9 + (dy + 1) * 3 + dx + 1] * W1[(((size_t)ci * 4 + c) * 8 + ky) * 8 + kx];
+                                }
+                        Wc[(ci * 10 + ku) * 10 + kv] = a;
+                    }
+            for (int t = 0; t < 9; ++t) {
+                const int dy = t / 3 - 1, dx = t % 3 - 1;
+                for (int ph = 0; ph < 16; ++ph) {
+                    const int ku = (ph >> 2) - 4 * dy + 3, kv = (ph & 3) - 4 * dx + 3;
+                    if (ku < 0 || ku > 9 || kv < 0 || kv > 9) continue;
+                    for (int ci = 0; ci < 16; ++ci) B[((size_t)t * 16 + ci) * 16 + ph] = (float)Wc[(ci * 10 + ku) * 10 + kv];
+                }
+            }
+            double bias = b3;
+            for (int c = 0; c < 4; ++c)
+                for (int k = 0; k < 9; ++k) bias += (double)W3[c * 9 + k] * b1[c];
+            for (int ph = 0; ph < 16; ++ph) { shift[ph] = (float)bias; slope[ph] = 1.f; }
+        };
+        s.stages.push_back(st);
+        emit(s);
+        // border correction (fp32 weights in the reference layouts)
+        const size_t owt = arena(64 * 16 * 4), ow3 = arena(36), ob = arena(4);
+        Op op;
+        op.name = "logits border correction";
+        op.pack = [=](const HostWeights& w, float* A) {
+            const float* W1 = w.get("bottle6_1.weight");
+            for (int ci = 0; ci < 16; ++ci)
+                for (int co = 0; co < 4; ++co)
+                    for (int t = 0; t < 64; ++t) A[owt + ((size_t)t * 16 + ci) * 4 + co] = W1[((size_t)ci * 4 + co) * 64 + t];
+            const float* w3 = w.get("bottle6_2.weight");
+            for (int c = 0; c < 4; ++c)
+                for (int t = 0; t < 9; ++t) A[ow3 + t * 4 + c] = w3[c * 9 + t];
+            std::memcpy(A + ob, w.get("bottle6_1.bias"), 4 * sizeof(float));
+        };
+        op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
+            TailFixParams p;
+            p.in = reinterpret_cast<const bf16*>(P->ws + ty.off); p.Hq = ty.H; p.Wq = ty.W; p.Cs = ty.Cs;
+            p.logits = logits; p.wt = P->arena + owt; p.bt = P->arena + ob; p.w3 = P->arena + ow3;
+            const int H = 4 * ty.H, W = 4 * ty.W;
+            p.total = n * (2 * W + 2 * (H - 2));
+            tail_fix_kernel<<<cdiv(p.total, 128), 128, 0, stream>>>(p);
+            return cudaGetLastError();
+        };
+        P->ops.push_back(op);
+    }
+
+    // Segment.forward (segment.py:466-508)
+    void build() {
+        const int H = P->H, W = P->W, cin = P->cin;
+        // stem (init_head_s4, segment.py:19-31)
+        const int x2 = tensor("x2", 4 * cin, H / 2, W / 2);
+        const int s1 = tensor("stem1.s2d", 64, H / 4, W / 4);          // layer1 output, space-to-depth storage
+        view("stem1", s1, 16, 16, H / 2, W / 2, true, 1);
+        const int init = tensor("init_down", 16 + cin, H / 4, W / 4, true);
+        {
+            std::vector<int> perm(16 + cin);                            // logical: pooled input first (segment.py:31)
+            for (int c = 0; c < cin; ++c) perm[c] = 16 + c;
+            for (int c = 0; c < 16; ++c) perm[cin + c] = c;
+            P->tensors[init].perm = perm;
+        }
+        emit_prep(x2, init);
+        stem_conv("init_conv.layer1", x2, cin, s1, fk::OUT_S2D, H / 2, W / 2);
+        stem_conv("init_conv.layer2", s1, 16, init, fk::OUT_STAGE, H / 4, W / 4);
+
+        const int h8 = H / 8, w8 = W / 8, h16 = H / 16, w16 = W / 16;
+        int keep1, keep2;
+        Next nx = next_of("bottle1_x.0.convs.0", 16, ACT_PRELU, h8, w8);
+        const int d1 = block_down("bottle1_1", init, 16, 48, &keep1, "bottle1_down", "keep1", nx);
+        int y = d1, m1 = nx.out;
+        for (int i = 0; i < 4; ++i) {
+            const std::string p = "bottle1_x." + std::to_string(i);
+            Next n2;
+            if (i < 3) n2 = next_of("bottle1_x." + std::to_string(i + 1) + ".convs.0", 16, ACT_PRELU, h8, w8);
+            y = block_res(p, y, m1, 16, 1, false, n2, i == 3 ? "bottle1_5" : p, i == 3);
+            m1 = n2.out;
+        }
+        nx = next_of("bottle2_x.0.convs.0", 48, ACT_PRELU, h16, w16);
+        const int d2 = block_down("bottle2_1", y, 16, 128, &keep2, "bottle2_down", "keep2", nx);
+        const int dils[4] = {1, 2, 1, 4};
+        auto wide = [&](const std::string& pre, int t, int m, const Next& after, const char* outname) {
+            for (int i = 0; i < 5; ++i) {
+                const std::string p = pre + "." + std::to_string(i);
+                Next n2 = after;
+                if (i < 4) n2 = next_of(pre + "." + std::to_string(i + 1) + ".convs.0", 48, ACT_PRELU, h16, w16);
+                t = block_res(p, t, m, 48, i < 4 ? dils[i] : 1, i == 4, n2, i == 4 ? outname : p, i == 4);
+                m = n2.out;
+            }
+            return t;
+        };
+        y = wide("bottle2_x", d2, nx.out, Next(), "bottle2_8");
+        m1 = pw_unit("bottle3_1.convs.0", {y, d2}, 48, ACT_PRELU, "bottle3_1.m1");
+        nx = next_of("bottle3_x.0.convs.0", 48, ACT_PRELU, h16, w16);
+        y = block_proj("bottle3_1", y, d2, m1, 48, 128, true, nx);
+        y = wide("bottle3_x", y, nx.out, Next(), "bottle3_8");
+        y = block_up("bottle4_1up", y, keep2, 16, 48, "bottle4_1");
+        m1 = pw_unit("bottle4_2.convs.0", {d1, y}, 16, ACT_PRELU, "bottle4_2.m1");
+        nx = next_of("bottle4_3.convs.0", 16, ACT_RELU, h8, w8);
+        y = block_proj("bottle4_2", d1, y, m1, 16, 48, false, nx);
+        y = block_plain("bottle4_3", y, nx.out, 16);
+        y = block_up("bottle5_1up", y, keep1, 4, 16, "bottle5_1");
+        m1 = pw_unit("bottle5_2.convs.0", {y}, 4, ACT_RELU, "bottle5_2.m1");
+        y = block_plain("bottle5_2", y, m1, 4);
+        tail(y);
+    }
+};
+
+}  // namespace
+
+void build_fk_plan(isg_plan* p) { FkBuilder(p).build(); }
+
+}  // namespace isg

@@ -1,6 +1,8 @@
 // C ABI of libisg (include/isg.h): network description, plan lifetime, forward, test taps.
+#include <cstring>
 #include <map>
 #include <mutex>
+#include <vector>
 
 #include "engine.h"
 
@@ -16,13 +18,13 @@ const StateSpec& spec_for(int cin) {
     return it->second;
 }
 
-// NHWC (storage T, stride Cs) -> NCHW fp32, used only by the tap reader
-template <typename T>
-__global__ void tap_to_nchw(const T* in, float* out, int C, int Cs, int H, int W, int total) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    int x = i % W, y = (i / W) % H, c = (i / (W * H)) % C, b = i / (W * H * C);
-    out[i] = ld1(in + (((size_t)b * H + y) * W + x) * Cs + c);
+// storage element -> float, used only by the tap reader
+inline float raw_to_float(const void* raw, size_t i, bool is_bf16) {
+    if (!is_bf16) return static_cast<const float*>(raw)[i];
+    uint32_t u = (uint32_t)static_cast<const uint16_t*>(raw)[i] << 16;
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
 }
 }  // namespace
 
@@ -148,20 +150,25 @@ int isg_plan_tap_read(isg_plan* plan, int index, int n, float* out_host) {
         return fail(ISG_ERR_ARG, "isg_plan_tap_read: bad argument");
     if (n < 1 || n > plan->max_batch) return fail(ISG_ERR_ARG, "tap read of %d images (max_batch %d)", n, plan->max_batch);
     const TensorD& t = plan->tensors[plan->taps[index]];
-    const int total = n * t.C * t.H * t.W;
-    float* tmp = nullptr;
+    const bool is_bf16 = plan->mode == ISG_MODE_BF16;
+    const size_t per_img = (size_t)t.H * t.W * t.Cs, es = is_bf16 ? 2 : 4;
+    std::vector<uint8_t> raw(per_img * n * es);
     ISG_CUDA(cudaSetDevice(plan->device));
     ISG_CUDA(cudaDeviceSynchronize());
-    ISG_CUDA(cudaMalloc(&tmp, (size_t)total * sizeof(float)));
-    if (plan->mode == ISG_MODE_BF16)
-        tap_to_nchw<bf16><<<cdiv(total, 256), 256>>>(reinterpret_cast<const bf16*>(plan->ws + t.off), tmp, t.C, t.Cs,
-                                                     t.H, t.W, total);
-    else
-        tap_to_nchw<float><<<cdiv(total, 256), 256>>>(reinterpret_cast<const float*>(plan->ws + t.off), tmp, t.C,
-                                                      t.Cs, t.H, t.W, total);
-    cudaError_t e = cudaMemcpy(out_host, tmp, (size_t)total * sizeof(float), cudaMemcpyDeviceToHost);
-    cudaFree(tmp);
-    if (e != cudaSuccess) return fail(ISG_ERR_CUDA, "tap copy failed: %s", cudaGetErrorString(e));
+    ISG_CUDA(cudaMemcpy(raw.data(), plan->ws + t.off, raw.size(), cudaMemcpyDeviceToHost));
+    for (int b = 0; b < n; ++b)
+        for (int c = 0; c < t.C; ++c) {
+            const int sc = t.storage_of(c);
+            for (int y = 0; y < t.H; ++y)
+                for (int x = 0; x < t.W; ++x) {
+                    size_t i;
+                    if (t.layout == 1)
+                        i = (((size_t)(y >> 1) * (t.W >> 1)) + (x >> 1)) * (4 * (size_t)t.Cs) + ((y & 1) * 2 + (x & 1)) * t.Cs + sc;
+                    else
+                        i = ((size_t)y * t.W + x) * t.Cs + sc;
+                    out_host[(((size_t)b * t.C + c) * t.H + y) * t.W + x] = raw_to_float(raw.data(), b * per_img + i, is_bf16);
+                }
+        }
     return ISG_OK;
 }
 

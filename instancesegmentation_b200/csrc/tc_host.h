@@ -58,6 +58,16 @@ inline int make_act_map(CUtensorMap* out, void* base, int B, int H, int W, int C
     return make_map5(out, base, dims, st, box, what);
 }
 
+// same view, but the box covers only `nchunks` 8-channel chunks (channel subsets, e.g. the conv half
+// of init_down or the two halves of an up block's low-resolution tensor)
+inline int make_act_map_chunks(CUtensorMap* out, void* base, int B, int H, int W, int Cs, int bw, int bh, int nchunks,
+                               const char* what) {
+    const uint64_t dims[5] = {8, (uint64_t)W, (uint64_t)H, (uint64_t)Cs / 8, (uint64_t)B};
+    const uint64_t st[4] = {(uint64_t)Cs * 2, (uint64_t)W * Cs * 2, 16, (uint64_t)H * W * Cs * 2};
+    const uint32_t box[5] = {8, (uint32_t)bw, (uint32_t)bh, (uint32_t)nchunks, 1};
+    return make_map5(out, base, dims, st, box, what);
+}
+
 // 2x2 stride-2 patches of [B,H,W,Cs] (segment.py:121): (8ch, ox, b*Ho+oy, chunk of the pixel PAIR, row a)
 inline int make_s2d_map(CUtensorMap* out, void* base, int B, int H, int W, int Cs, int bw, int bh, const char* what) {
     const uint64_t dims[5] = {8, (uint64_t)W / 2, (uint64_t)B * (H / 2), (uint64_t)2 * Cs / 8, 2};
