@@ -196,6 +196,40 @@ inline int r128(int v) { return (v + 127) / 128 * 128; }
 
 struct FkMaps { CUtensorMap in[4], out[2]; };
 
+// debug (ISG_FK_PROF=1): run one launch with per-CTA phase stamps and print their means
+inline cudaError_t launch_profiled(const std::string& name, fk::Params p, int grid, size_t smem, const FkMaps& m,
+                                   cudaStream_t stream) {
+    long long* d = nullptr;
+    cudaMalloc(&d, (size_t)grid * 16 * sizeof(long long));
+    cudaMemset(d, 0, (size_t)grid * 16 * sizeof(long long));
+    p.prof = d;
+    cudaStreamSynchronize(stream);
+    fk::fk_kernel<<<grid, fk::THREADS, smem, stream>>>(m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+    cudaError_t e = cudaStreamSynchronize(stream);
+    std::vector<long long> h((size_t)grid * 16);
+    cudaMemcpy(h.data(), d, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    double ph[9] = {0};
+    long long t0 = h[14], t1 = h[15];
+    double life = 0;
+    for (int b = 0; b < grid; ++b) {
+        const long long* r = &h[(size_t)b * 16];
+        long long prev = r[0];
+        for (int k = 1; k <= 8; ++k) {
+            if (r[k] == 0) continue;
+            ph[k] += (double)(r[k] - prev);
+            prev = r[k];
+        }
+        t0 = std::min(t0, r[14]); t1 = std::max(t1, r[15]);
+        life += (double)(r[15] - r[14]);
+    }
+    fprintf(stderr, "prof %-40s grid %5d span %7.1f us  cta life %6.2f us | cycles: alloc %6.0f load %6.0f stencil %6.0f "
+            "mma0 %6.0f epi0 %6.0f mma1 %6.0f epi1 %6.0f store %6.0f\n", name.c_str(), grid, (t1 - t0) * 1e-3,
+            life / grid * 1e-3, ph[1] / grid, ph[2] / grid, ph[3] / grid, ph[4] / grid, ph[5] / grid, ph[6] / grid,
+            ph[7] / grid, ph[8] / grid);
+    return e;
+}
+
 struct FkBuilder {
     isg_plan* P;
     explicit FkBuilder(isg_plan* p) : P(p) {}
@@ -372,13 +406,8 @@ struct FkBuilder {
             t.on = 1; t.in_off = L.load_off[s.st.load]; t.in_pitch = L.st_in_pitch;
             t.in_plane_bytes = L.load_plane[s.st.load]; t.halo = l.halo; t.nchunks = L.load_planes[s.st.load];
             st_C = t.nchunks * 8;
-            if (s.st.kind == 1) {
-                t.ntaps = 9;
-                for (int k = 0; k < 9; ++k) t.tap_off[k] = ((k / 3) - 1) * s.st.dil * t.in_pitch + ((k % 3) - 1) * s.st.dil;
-            } else {
-                t.ntaps = 25; t.sep5 = 1;
-                for (int k = 0; k < 25; ++k) t.tap_off[k] = ((k / 5) - 2) * t.in_pitch + ((k % 5) - 2);
-            }
+            t.dil = s.st.kind == 1 ? s.st.dil : 1;
+            t.sep5 = s.st.kind == 2 ? 1 : 0;
             t.w_off = L.blob_off + L.stw_off; t.vec_off = L.blob_off + L.stvec_off;
             t.out_off = L.st_out_off; t.out_plane_bytes = L.st_out_plane;
         }
@@ -394,10 +423,11 @@ struct FkBuilder {
                 if (pt.kind == PART_LOAD) { base = L.load_off[pt.load]; plane = L.load_plane[pt.load]; planes = L.load_planes[pt.load]; }
                 else if (pt.kind == PART_STENCIL) { base = L.st_out_off; plane = L.st_out_plane; planes = st_C / 8; }
                 else { base = L.stage_off[0]; plane = L.stage_plane[0]; planes = s.stages[0].N / 8; }
-                for (int j = 0; j < planes / 2; ++j) { d.ks_off[nks] = base + 2 * j * plane; d.ks_lbo[nks] = plane; ++nks; }
+                for (int j = 0; j < planes / 2; ++j) d.a_desc[nks++] = tc::umma_smem_desc(base + 2 * j * plane, plane, 128);
             }
             d.nks = nks;
-            d.w_off = L.blob_off + L.b_off[k]; d.vec_off = L.blob_off + L.vec_off[k];
+            d.b_desc = tc::umma_smem_desc(L.blob_off + L.b_off[k], st.N * 16, 128);
+            d.vec_off = L.blob_off + L.vec_off[k];
             if (st.res_load >= 0) {
                 d.res_on = 1; d.res_off = L.load_off[st.res_load]; d.res_plane_bytes = L.load_plane[st.res_load];
                 d.res_mod = st.res_mod;
@@ -477,6 +507,8 @@ struct FkBuilder {
                 if (st.to_logits) p.stage[k].gptr = logits;
                 else if (st.out_mode != fk::OUT_STAGE) p.stage[k].gptr = P->ws + P->tensors[st.out_tensor].off;
             }
+            static const bool prof_on = getenv("ISG_FK_PROF") != nullptr;
+            if (prof_on) return launch_profiled(sp.name, p, n * tiles, smem, *maps, stream);
             fk::fk_kernel<<<n * tiles, fk::THREADS, smem, stream>>>(maps->in[0], maps->in[1], maps->in[2], maps->in[3],
                                                                    maps->out[0], maps->out[1], p);
             return cudaGetLastError();

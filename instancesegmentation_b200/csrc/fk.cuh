@@ -47,9 +47,9 @@ struct Load {
 struct Stage {
     int N, ntaps, nks;
     int tap_off[MAX_MMA_TAPS];     // pixel offsets dy*pitch + dx
-    int ks_off[MAX_KS];            // smem offset of the first plane of K slice (16 channels = 2 planes)
-    int ks_lbo[MAX_KS];            // plane stride of that slice
-    int w_off;                     // packed B: [tap][ks][2][N][8] bf16
+    uint64_t a_desc[MAX_KS];       // UMMA descriptor of K slice ks (16 channels = 2 planes) relative to the
+                                   // dynamic shared memory base: the kernel adds (base + row offset) >> 4
+    uint64_t b_desc;               // descriptor of the first packed B block [tap][ks][2][N][8] bf16
     int vec_off;                   // fp32 shift[N], slope[N]
     int pitch;                     // pitch of the M index space (TW + 2*halo of the tap planes)
     int res_on, res_off, res_plane_bytes, res_mod;
@@ -63,8 +63,7 @@ struct Stage {
 struct Stencil {
     int on;
     int in_off, in_pitch, in_plane_bytes, halo;
-    int nchunks, ntaps;
-    int tap_off[MAX_ST_TAPS];      // (dy*in_pitch + dx) pixel offsets relative to the centre
+    int nchunks, dil;
     int w_off;                     // fp32 [tap][C]
     int vec_off;                   // fp32 shift[C], slope[C], then bw[5][C] when sep5
     int sep5;
@@ -80,7 +79,15 @@ struct Params {
     Stencil st;
     int nstages; Stage stage[2];
     int bar_off;                   // 3 mbarriers + tmem slot
+    long long* prof;               // debug (ISG_FK_PROF=1): per-CTA phase time stamps, else null
 };
+
+__device__ __forceinline__ long long globaltimer_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define FK_STAMP(i) do { if (p.prof && threadIdx.x == 0) p.prof[(size_t)blockIdx.x * 16 + (i)] = clock64(); } while (0)
 
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -103,155 +110,219 @@ __device__ __forceinline__ void unpack8(uint4 q, float* f) {
     }
 }
 
+// packed fp32x2 FMA (Blackwell FFMA2): d = a * b + c on both halves
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long ra = *reinterpret_cast<unsigned long long*>(&a), rb = *reinterpret_cast<unsigned long long*>(&b),
+                       rc = *reinterpret_cast<unsigned long long*>(&c), rd;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    return *reinterpret_cast<float2*>(&rd);
+}
+__device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
+    return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+
 // ---- depthwise stencil: haloed input planes -> A operand planes ----
+// SEP5 = false: 3x3 with dilation; SEP5 = true: the composed (5,1)x(1,5) pair (25 taps)
+template <bool SEP5>
 __device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int x0) {
     const Stencil& s = p.st;
+    constexpr int KS = SEP5 ? 5 : 3;
     const int npix = p.TH * p.TW, C = s.nchunks * 8;
+    const int dil = SEP5 ? 1 : s.dil, pitch = s.in_pitch;
     const float* wt = reinterpret_cast<const float*>(smem + s.w_off);
     const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
-    for (int i = threadIdx.x; i < s.nchunks * npix; i += THREADS) {
-        const int k = i / npix, pix = i - k * npix;
-        const int r = pix / p.TW, c = pix - r * p.TW;
-        const uint8_t* in = smem + s.in_off + (size_t)k * s.in_plane_bytes +
-                            (size_t)((r + s.halo) * s.in_pitch + c + s.halo) * 16;
-        float acc[8];
+    for (int k = 0; k < s.nchunks; ++k) {
+        const uint8_t* plane = smem + s.in_off + (size_t)k * s.in_plane_bytes;
+        const float* wk = wt + k * 8;
+        for (int pix = threadIdx.x; pix < npix; pix += THREADS) {
+            const int r = pix / p.TW, c = pix - r * p.TW;
+            // top-left tap of this pixel
+            const uint8_t* in = plane + (size_t)((r + s.halo - (KS / 2) * dil) * pitch + c + s.halo - (KS / 2) * dil) * 16;
+            float2 acc[4];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-        for (int t = 0; t < s.ntaps; ++t) {
-            float v[8];
-            unpack8(*reinterpret_cast<const uint4*>(in + s.tap_off[t] * 16), v);
-            const float4 w0 = *reinterpret_cast<const float4*>(wt + t * C + k * 8);
-            const float4 w1 = *reinterpret_cast<const float4*>(wt + t * C + k * 8 + 4);
-            acc[0] = fmaf(v[0], w0.x, acc[0]); acc[1] = fmaf(v[1], w0.y, acc[1]);
-            acc[2] = fmaf(v[2], w0.z, acc[2]); acc[3] = fmaf(v[3], w0.w, acc[3]);
-            acc[4] = fmaf(v[4], w1.x, acc[4]); acc[5] = fmaf(v[5], w1.y, acc[5]);
-            acc[6] = fmaf(v[6], w1.z, acc[6]); acc[7] = fmaf(v[7], w1.w, acc[7]);
-        }
-        float sh[8], sl[8];
+            for (int e = 0; e < 4; ++e) acc[e] = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { sh[e] = vec[k * 8 + e]; sl[e] = vec[C + k * 8 + e]; }
-        if (s.sep5) {
-            // bias of the bare (5,1) conv seen through the (1,5) conv: only taps inside the image
-            const int xa = x0 + c;
+            for (int ty = 0; ty < KS; ++ty) {
+                uint4 q[KS];
 #pragma unroll
-            for (int kx = 0; kx < 5; ++kx) {
-                const int xx = xa + kx - 2;
-                if (xx >= 0 && xx < p.W) {
+                for (int tx = 0; tx < KS; ++tx)
+                    q[tx] = *reinterpret_cast<const uint4*>(in + (size_t)(ty * dil * pitch + tx * dil) * 16);
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) sh[e] += vec[(2 + kx) * C + k * 8 + e];
+                for (int tx = 0; tx < KS; ++tx) {
+                    const float4 w0 = *reinterpret_cast<const float4*>(wk + (ty * KS + tx) * C);
+                    const float4 w1 = *reinterpret_cast<const float4*>(wk + (ty * KS + tx) * C + 4);
+                    acc[0] = ffma2(bf2_to_f2(q[tx].x), make_float2(w0.x, w0.y), acc[0]);
+                    acc[1] = ffma2(bf2_to_f2(q[tx].y), make_float2(w0.z, w0.w), acc[1]);
+                    acc[2] = ffma2(bf2_to_f2(q[tx].z), make_float2(w1.x, w1.y), acc[2]);
+                    acc[3] = ffma2(bf2_to_f2(q[tx].w), make_float2(w1.z, w1.w), acc[3]);
                 }
             }
-        }
-        uint32_t o[4];
+            float4 sh0 = *reinterpret_cast<const float4*>(vec + k * 8), sh1 = *reinterpret_cast<const float4*>(vec + k * 8 + 4);
+            const float4 sl0 = *reinterpret_cast<const float4*>(vec + C + k * 8);
+            const float4 sl1 = *reinterpret_cast<const float4*>(vec + C + k * 8 + 4);
+            if (SEP5) {
+                // bias of the bare (5,1) conv seen through the (1,5) conv: only taps inside the image
+                const int xa = x0 + c;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            float a = acc[2 * e] + sh[2 * e], b = acc[2 * e + 1] + sh[2 * e + 1];
-            a = a >= 0.f ? a : a * sl[2 * e];
-            b = b >= 0.f ? b : b * sl[2 * e + 1];
-            o[e] = pack_bf16(a, b);
+                for (int kx = 0; kx < 5; ++kx) {
+                    const int xx = xa + kx - 2;
+                    if (xx >= 0 && xx < p.W) {
+                        const float4 b0 = *reinterpret_cast<const float4*>(vec + (2 + kx) * C + k * 8);
+                        const float4 b1 = *reinterpret_cast<const float4*>(vec + (2 + kx) * C + k * 8 + 4);
+                        sh0.x += b0.x; sh0.y += b0.y; sh0.z += b0.z; sh0.w += b0.w;
+                        sh1.x += b1.x; sh1.y += b1.y; sh1.z += b1.z; sh1.w += b1.w;
+                    }
+                }
+            }
+            float a0 = acc[0].x + sh0.x, a1 = acc[0].y + sh0.y, a2 = acc[1].x + sh0.z, a3 = acc[1].y + sh0.w;
+            float a4 = acc[2].x + sh1.x, a5 = acc[2].y + sh1.y, a6 = acc[3].x + sh1.z, a7 = acc[3].y + sh1.w;
+            a0 = a0 >= 0.f ? a0 : a0 * sl0.x; a1 = a1 >= 0.f ? a1 : a1 * sl0.y;
+            a2 = a2 >= 0.f ? a2 : a2 * sl0.z; a3 = a3 >= 0.f ? a3 : a3 * sl0.w;
+            a4 = a4 >= 0.f ? a4 : a4 * sl1.x; a5 = a5 >= 0.f ? a5 : a5 * sl1.y;
+            a6 = a6 >= 0.f ? a6 : a6 * sl1.z; a7 = a7 >= 0.f ? a7 : a7 * sl1.w;
+            *reinterpret_cast<uint4*>(smem + s.out_off + (size_t)k * s.out_plane_bytes + (size_t)pix * 16) =
+                make_uint4(pack_bf16(a0, a1), pack_bf16(a2, a3), pack_bf16(a4, a5), pack_bf16(a6, a7));
         }
-        *reinterpret_cast<uint4*>(smem + s.out_off + (size_t)k * s.out_plane_bytes + (size_t)pix * 16) =
-            make_uint4(o[0], o[1], o[2], o[3]);
     }
 }
 
-__device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, uint32_t smem_base, uint32_t tmem_base) {
+// MMAs of the M tiles mt = first, first + step, ...; called by ONE thread per issuing warp
+__device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, uint32_t smem_base, uint32_t tmem_base,
+                                          int first, int step) {
     const uint32_t idesc = tc::umma_idesc_bf16(128, s.N);
-    const uint32_t b_block = (uint32_t)s.N * 32;
-    for (int mt = 0; mt < p.n_mt; ++mt) {
+    const uint64_t base16 = smem_base >> 4;
+    const uint64_t bd0 = s.b_desc + base16;
+    const uint32_t b_step = (uint32_t)s.N * 2;  // 16-byte units per [2][N][8] block
+    for (int mt = first; mt < p.n_mt; mt += step) {
         uint32_t acc = 0;
+        uint64_t bd = bd0;
         for (int t = 0; t < s.ntaps; ++t) {
-            const uint32_t a_shift = (uint32_t)(mt * 128 + s.tap_off[t]) * 16;
+            const uint64_t a_row = base16 + (uint64_t)(mt * 128 + s.tap_off[t]);
+#pragma unroll 4
             for (int ks = 0; ks < s.nks; ++ks) {
-                const uint64_t ad = tc::umma_smem_desc(smem_base + s.ks_off[ks] + a_shift, s.ks_lbo[ks], 128);
-                const uint64_t bd = tc::umma_smem_desc(smem_base + s.w_off + (uint32_t)(t * s.nks + ks) * b_block,
-                                                       s.N * 16, 128);
-                tc::umma_bf16(tmem_base + mt * s.N, ad, bd, idesc, acc);
+                tc::umma_bf16(tmem_base + mt * s.N, s.a_desc[ks] + a_row, bd, idesc, acc);
                 acc = 1;
+                bd += b_step;
             }
         }
     }
 }
 
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// epilogue of one (M tile, 16-column chunk): raw accumulators -> shift/residual/activation -> output
+__device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const Stage& s, const uint32_t (&raw)[16],
+                                         int mt, int cc, int quad, int lane, int b, int x0, int y0) {
+    const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
+    const int m = mt * 128 + quad * 32 + lane;
+    const int r = m / s.pitch, c = m - r * s.pitch;
+    const bool geom = r < p.TH && c < p.TW;
+    const int y = y0 + r, x = x0 + c;
+    const bool inimg = geom && y < p.H && x < p.W;
+    const int pc = r * p.TW + c;
+    const int col0 = cc * 16;
+    float v[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[i]);
+    if (s.res_on && geom) {
+        const int ch0 = s.res_mod ? col0 % s.res_mod : col0;
+        const uint8_t* rp = smem + s.res_off + (size_t)(ch0 >> 3) * s.res_plane_bytes + (size_t)pc * 16;
+        float f[16];
+        unpack8(*reinterpret_cast<const uint4*>(rp), f);
+        unpack8(*reinterpret_cast<const uint4*>(rp + s.res_plane_bytes), f + 8);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] += f[i];
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float4 sh = *reinterpret_cast<const float4*>(vec + col0 + 4 * j);
+        const float4 sl = *reinterpret_cast<const float4*>(vec + s.N + col0 + 4 * j);
+        float a;
+        a = v[4 * j + 0] + sh.x; v[4 * j + 0] = a >= 0.f ? a : a * sl.x;
+        a = v[4 * j + 1] + sh.y; v[4 * j + 1] = a >= 0.f ? a : a * sl.y;
+        a = v[4 * j + 2] + sh.z; v[4 * j + 2] = a >= 0.f ? a : a * sl.z;
+        a = v[4 * j + 3] + sh.w; v[4 * j + 3] = a >= 0.f ? a : a * sl.w;
+    }
+    if (s.out_mode == OUT_SHUF4_F32) {
+        if (inimg) {
+            float* g = static_cast<float*>(s.gptr) + ((size_t)b * 4 * p.H + 4 * y) * (4 * (size_t)p.W) + 4 * x;
+#pragma unroll
+            for (int ry = 0; ry < 4; ++ry)
+                *reinterpret_cast<float4*>(g + (size_t)ry * 4 * p.W) =
+                    make_float4(v[4 * ry], v[4 * ry + 1], v[4 * ry + 2], v[4 * ry + 3]);
+        }
+        return;
+    }
+    const uint4 q0 = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+    const uint4 q1 = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
+                                pack_bf16(v[14], v[15]));
+    if (s.out_mode == OUT_STAGE) {
+        if (s.stage_compact && !geom) return;
+        const int si = s.stage_compact ? pc : m;
+        uint8_t* d = smem + s.stage_off + (size_t)(col0 >> 3) * s.stage_plane_bytes + (size_t)si * 16;
+        *reinterpret_cast<uint4*>(d) = q0;
+        *reinterpret_cast<uint4*>(d + s.stage_plane_bytes) = q1;
+    } else if (s.out_mode == OUT_S2D) {
+        if (inimg) {
+            bf16* g = static_cast<bf16*>(s.gptr) +
+                      (((size_t)b * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1)) * (4 * (size_t)s.N) +
+                      ((y & 1) * 2 + (x & 1)) * s.N + col0;
+            st_global_16(g, q0);
+            st_global_16(g + 8, q1);
+        }
+    } else {  // OUT_SHUF_BF16
+        if (inimg) {
+            const int phase = col0 / s.Cp, ch = col0 - phase * s.Cp;
+            const int py = phase / s.shuf, px = phase - py * s.shuf;
+            bf16* g = static_cast<bf16*>(s.gptr) +
+                      (((size_t)b * p.H * s.shuf + (size_t)y * s.shuf + py) * ((size_t)p.W * s.shuf) +
+                       (size_t)x * s.shuf + px) * s.Cs_out + ch;
+            st_global_16(g, q0);
+            st_global_16(g + 8, q1);
+        }
+    }
+}
+
+// warps 0-3 and 4-7 are two groups that alternate over the (M tile, column chunk) items; warp w may
+// only touch TMEM lanes [32*(w%4), +32).  The TMEM load of the next item is in flight while the
+// current one is processed.
 __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, const Stage& s, uint32_t tmem_base,
                                              int b, int x0, int y0) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int quad = warp & 3, grp = warp >> 2;
-    const int ncc = s.N >> 4;
-    const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
-    for (int item = grp; item < p.n_mt * ncc; item += 2) {
-        const int mt = item / ncc, cc = item - mt * ncc;
-        const int m = mt * 128 + quad * 32 + lane;
-        const int r = m / s.pitch, c = m - r * s.pitch;
-        const bool geom = r < p.TH && c < p.TW;
-        const int y = y0 + r, x = x0 + c;
-        const bool inimg = geom && y < p.H && x < p.W;
-        const int pc = r * p.TW + c;
-        float v[16];
+    const int ncc = s.N >> 4, nitems = p.n_mt * ncc;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
+    uint32_t ra[16], rb[16];
+    int item = grp;
+    if (item >= nitems) return;
+    __syncwarp();
+    tmem_ld16_nowait(lane_base + item * 16, ra);   // column of item = mt*N + cc*16 = item*16
+    while (true) {
         __syncwarp();
-        tc::tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + mt * s.N + cc * 16, v);
-        const int col0 = cc * 16;
-        if (s.res_on && geom) {
-            const int ch0 = s.res_mod ? col0 % s.res_mod : col0;
-            const uint8_t* rp = smem + s.res_off + (size_t)(ch0 >> 3) * s.res_plane_bytes + (size_t)pc * 16;
-            float f[16];
-            unpack8(*reinterpret_cast<const uint4*>(rp), f);
-            unpack8(*reinterpret_cast<const uint4*>(rp + s.res_plane_bytes), f + 8);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] += f[i];
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float4 sh = *reinterpret_cast<const float4*>(vec + col0 + 4 * j);
-            const float4 sl = *reinterpret_cast<const float4*>(vec + s.N + col0 + 4 * j);
-            float a;
-            a = v[4 * j + 0] + sh.x; v[4 * j + 0] = a >= 0.f ? a : a * sl.x;
-            a = v[4 * j + 1] + sh.y; v[4 * j + 1] = a >= 0.f ? a : a * sl.y;
-            a = v[4 * j + 2] + sh.z; v[4 * j + 2] = a >= 0.f ? a : a * sl.z;
-            a = v[4 * j + 3] + sh.w; v[4 * j + 3] = a >= 0.f ? a : a * sl.w;
-        }
-        if (s.out_mode == OUT_SHUF4_F32) {
-            if (inimg) {
-                float* g = static_cast<float*>(s.gptr) + ((size_t)b * 4 * p.H + 4 * y) * (4 * (size_t)p.W) + 4 * x;
-#pragma unroll
-                for (int ry = 0; ry < 4; ++ry)
-                    *reinterpret_cast<float4*>(g + (size_t)ry * 4 * p.W) =
-                        make_float4(v[4 * ry], v[4 * ry + 1], v[4 * ry + 2], v[4 * ry + 3]);
-            }
-            continue;
-        }
-        uint4 q0 = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-        uint4 q1 = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
-                              pack_bf16(v[14], v[15]));
-        if (s.out_mode == OUT_STAGE) {
-            if (s.stage_compact && !geom) continue;
-            const int si = s.stage_compact ? pc : m;
-            uint8_t* d = smem + s.stage_off + (size_t)(col0 >> 3) * s.stage_plane_bytes + (size_t)si * 16;
-            *reinterpret_cast<uint4*>(d) = q0;
-            *reinterpret_cast<uint4*>(d + s.stage_plane_bytes) = q1;
-        } else if (s.out_mode == OUT_S2D) {
-            if (inimg) {
-                bf16* g = static_cast<bf16*>(s.gptr) +
-                          (((size_t)b * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1)) * (4 * (size_t)s.N) +
-                          ((y & 1) * 2 + (x & 1)) * s.N + col0;
-                st_global_16(g, q0);
-                st_global_16(g + 8, q1);
-            }
-        } else {  // OUT_SHUF_BF16
-            if (inimg) {
-                const int phase = col0 / s.Cp, ch = col0 - phase * s.Cp;
-                const int py = phase / s.shuf, px = phase - py * s.shuf;
-                bf16* g = static_cast<bf16*>(s.gptr) +
-                          (((size_t)b * p.H * s.shuf + (size_t)y * s.shuf + py) * ((size_t)p.W * s.shuf) +
-                           (size_t)x * s.shuf + px) * s.Cs_out + ch;
-                st_global_16(g, q0);
-                st_global_16(g + 8, q1);
-            }
-        }
+        tmem_ld_wait();
+        const int n1 = item + 2;
+        if (n1 < nitems) tmem_ld16_nowait(lane_base + n1 * 16, rb);
+        epi_item(smem, p, s, ra, item / ncc, item % ncc, quad, lane, b, x0, y0);
+        if (n1 >= nitems) break;
+        __syncwarp();
+        tmem_ld_wait();
+        const int n2 = item + 4;
+        if (n2 < nitems) tmem_ld16_nowait(lane_base + n2 * 16, ra);
+        epi_item(smem, p, s, rb, n1 / ncc, n1 % ncc, quad, lane, b, x0, y0);
+        if (n2 >= nitems) break;
+        item = n2;
     }
 }
 
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(THREADS, 2)
 fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtensorMap m1,
           const __grid_constant__ CUtensorMap m2, const __grid_constant__ CUtensorMap m3,
           const __grid_constant__ CUtensorMap mo0, const __grid_constant__ CUtensorMap mo1,
@@ -266,10 +337,13 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     const int b = bid / p.tiles_y;
     const int x0 = tx * p.TW, y0 = ty * p.TH;
 
+    if (p.prof && tid == 0) p.prof[(size_t)blockIdx.x * 16 + 14] = globaltimer_ns();
+    FK_STAMP(0);
+    const int n_issuers = p.n_mt < 8 ? p.n_mt : 8;   // warp w issues the MMAs of M tiles w, w+8, ...
     if (tid == 0) {
         tc::mbar_init(&bars[0], 1);
-        tc::mbar_init(&bars[1], 1);
-        tc::mbar_init(&bars[2], 1);
+        tc::mbar_init(&bars[1], n_issuers);
+        tc::mbar_init(&bars[2], n_issuers);
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, p.tmem_cols);
@@ -277,6 +351,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     __syncthreads();
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    FK_STAMP(1);
 
     if (tid == 0) {
         tc::mbar_expect_tx(&bars[0], p.tx_bytes);
@@ -290,48 +365,57 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         bulk_g2s(smem + p.blob_off, p.blob, p.blob_bytes, &bars[0]);
     }
     tc::mbar_wait(&bars[0], 0);
+    FK_STAMP(2);
 
     if (p.st.on) {
-        run_stencil(smem, p, x0);
+        if (p.st.sep5) run_stencil<true>(smem, p, x0);
+        else run_stencil<false>(smem, p, x0);
         tc::fence_proxy_async();
         __syncthreads();
     }
+    FK_STAMP(3);
     const uint32_t smem_base = tc::smem_u32(smem);
-    if (tid == 0) {
+    if ((tid & 31) == 0 && warp < n_issuers) {
         tc::tc_fence_after();
-        issue_mma(p, p.stage[0], smem_base, tmem_base);
+        issue_mma(p, p.stage[0], smem_base, tmem_base, warp, 8);
         tc::umma_commit(&bars[1]);
     }
     __syncwarp();
     tc::mbar_wait(&bars[1], 0);
+    FK_STAMP(4);
     tc::tc_fence_after();
     run_epilogue(smem, p, p.stage[0], tmem_base, b, x0, y0);
     tc::fence_proxy_async();
     tc::tc_fence_before();
     __syncthreads();
+    FK_STAMP(5);
     if (tid == 0 && p.stage[0].out_mode == OUT_STAGE && p.stage[0].store) {
         tc::tma_store_5d(&mo0, smem + p.stage[0].stage_off, 0, x0, y0, p.stage[0].store_chunk0, b);
         tc::tma_store_commit();
     }
     if (p.nstages > 1) {
-        if (tid == 0) {
+        if ((tid & 31) == 0 && warp < n_issuers) {
             tc::tc_fence_after();
-            issue_mma(p, p.stage[1], smem_base, tmem_base);
+            issue_mma(p, p.stage[1], smem_base, tmem_base, warp, 8);
             tc::umma_commit(&bars[2]);
         }
         __syncwarp();
         tc::mbar_wait(&bars[2], 0);
+        FK_STAMP(6);
         tc::tc_fence_after();
         run_epilogue(smem, p, p.stage[1], tmem_base, b, x0, y0);
         tc::fence_proxy_async();
         tc::tc_fence_before();
         __syncthreads();
+        FK_STAMP(7);
         if (tid == 0 && p.stage[1].out_mode == OUT_STAGE && p.stage[1].store) {
             tc::tma_store_5d(&mo1, smem + p.stage[1].stage_off, 0, x0, y0, p.stage[1].store_chunk0, b);
             tc::tma_store_commit();
         }
     }
-    if (tid == 0) tc::tma_store_wait_all();
+    if (tid == 0) tc::tma_store_wait_read();
+    FK_STAMP(8);
+    if (p.prof && tid == 0) p.prof[(size_t)blockIdx.x * 16 + 15] = globaltimer_ns();
     if (warp == 1) {
         tc::tc_fence_after();
         tc::tmem_dealloc(tmem_base, p.tmem_cols);
