@@ -185,6 +185,7 @@ struct Lay {
     size_t smem = 0;
     int load_off[fk::MAX_LOADS], load_plane[fk::MAX_LOADS], load_planes[fk::MAX_LOADS];
     int st_out_off = 0, st_out_plane = 0, st_in_pitch = 0;
+    int lbuf_stride = 0, stage_in_load[2] = {0, 0};
     int stage_off[2] = {0, 0}, stage_plane[2] = {0, 0}, stage_compact[2] = {1, 1};
     int K[2] = {0, 0};
     int b_off[2] = {0, 0}, vec_off[2] = {0, 0}, stw_off = 0, stvec_off = 0, blob_off = 0, blob_bytes = 0, bar_off = 0;
@@ -293,6 +294,9 @@ struct FkBuilder {
             L.tx += (uint32_t)planes * L.load_plane[i];
             off = r128(off + planes * L.load_plane[i] + slack);
         }
+        // persistent CTAs double-buffer the whole load area: tile i+1 streams in while tile i computes
+        L.lbuf_stride = off;
+        off *= 2;
         if (s.st.kind) {
             const LoadSpec& l = s.loads[s.st.load];
             const int nch = l.nchunks < 0 ? td(l.tensor).Cs / 8 : l.nchunks;
@@ -319,6 +323,7 @@ struct FkBuilder {
             L.stage_plane[k] = pix * 16;
             const bool alias = st.res_load >= 0 && st.res_mod == 0 && L.stage_compact[k] &&
                                L.load_planes[st.res_load] == st.N / 8 && s.loads[st.res_load].halo == 0;
+            L.stage_in_load[k] = alias ? 1 : 0;
             if (alias) { L.stage_off[k] = L.load_off[st.res_load]; continue; }
             L.stage_off[k] = off;
             int slack = is_chain_src ? std::max(0, L.n_mt * 128 * 16 - L.stage_plane[k]) : 0;
@@ -340,10 +345,9 @@ struct FkBuilder {
             L.stvec_off = rel; rel = r128(rel + (s.st.kind == 2 ? 7 : 2) * C * 4);
         }
         L.blob_bytes = rel;
-        L.tx += rel;
         off = r128(off + rel);
         L.bar_off = off;
-        L.smem = (size_t)off + 64;
+        L.smem = (size_t)off + 128;
         return L.smem <= 224 * 1024;
     }
 
@@ -358,19 +362,21 @@ struct FkBuilder {
         Lay best;
         const char* cap_env = getenv("ISG_FK_MAX_MT");
         const int mt_cap = cap_env ? atoi(cap_env) : 16;
-        for (int pass = 0; pass < 2 && best.score < 0; ++pass) {
-            for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
-                Lay L;
-                if (!layout(s, TH, TW, L)) continue;
-                if (L.n_mt > mt_cap && TH > 1) continue;
-                if (pass == 0 && (L.cols > 256 || L.smem > 112 * 1024)) continue;
-                const int tiles_y = cdiv(s.qH, TH);
-                const double eff_m = (double)(TH * TW) / (L.n_mt * 128);
-                const double eff_tail = (double)s.qH / (tiles_y * TH);
-                const double eff_halo = (double)TH / (TH + 2 * max_halo);
-                L.score = eff_m * eff_tail * (0.5 + 0.5 * eff_halo) + 1e-4 * TH;
-                if (L.score > best.score) best = L;
-            }
+        const char* w1 = getenv("ISG_FK_OCC1_WEIGHT");
+        const double occ1 = w1 ? atof(w1) : 0.75;   // relative value of a tile that leaves room for one CTA per SM only
+        for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
+            Lay L;
+            if (!layout(s, TH, TW, L)) continue;
+            if (L.n_mt > mt_cap && TH > 1) continue;
+            const bool two = true;   // one 512-thread CTA per SM: nothing to gain from small footprints
+            const int tiles_y = cdiv(s.qH, TH);
+            const double eff_m = (double)(TH * TW) / (L.n_mt * 128);
+            const double eff_tail = (double)s.qH / (tiles_y * TH);
+            const double eff_halo = (double)TH / (TH + 2 * max_halo);
+            const long total = (long)P->max_batch * tiles_y * cdiv(s.qW, TW);
+            const double eff_wave = (double)total / (double)(cdiv((int)total, 148) * 148L);
+            L.score = eff_m * eff_tail * (0.5 + 0.5 * eff_halo) * (two ? 1.0 : occ1) * (0.3 + 0.7 * eff_wave) + 1e-4 * TH;
+            if (L.score > best.score) best = L;
         }
         return best;
     }
@@ -398,6 +404,7 @@ struct FkBuilder {
             d.map = i; d.smem_off = L.load_off[i]; d.dx = -l.halo; d.dy = -l.halo; d.chunk0 = l.chunk0;
             d.folded = l.s2d ? 1 : 0; d.rows_per_img = s.qH; d.step = 1;
         }
+        q.lbuf_stride = L.lbuf_stride;
         q.tx_bytes = L.tx; q.blob_off = L.blob_off; q.blob_bytes = L.blob_bytes; q.bar_off = L.bar_off;
         int st_C = 0;
         if (s.st.kind) {
@@ -420,11 +427,16 @@ struct FkBuilder {
             int nks = 0;
             for (auto& pt : st.parts) {
                 int base, plane, planes;
-                if (pt.kind == PART_LOAD) { base = L.load_off[pt.load]; plane = L.load_plane[pt.load]; planes = L.load_planes[pt.load]; }
+                bool in_load = false;
+                if (pt.kind == PART_LOAD) { base = L.load_off[pt.load]; plane = L.load_plane[pt.load]; planes = L.load_planes[pt.load]; in_load = true; }
                 else if (pt.kind == PART_STENCIL) { base = L.st_out_off; plane = L.st_out_plane; planes = st_C / 8; }
-                else { base = L.stage_off[0]; plane = L.stage_plane[0]; planes = s.stages[0].N / 8; }
-                for (int j = 0; j < planes / 2; ++j) d.a_desc[nks++] = tc::umma_smem_desc(base + 2 * j * plane, plane, 128);
+                else { base = L.stage_off[0]; plane = L.stage_plane[0]; planes = s.stages[0].N / 8; in_load = L.stage_in_load[0]; }
+                for (int j = 0; j < planes / 2; ++j) {
+                    if (in_load) d.a_buf_mask |= 1u << nks;
+                    d.a_desc[nks++] = tc::umma_smem_desc(base + 2 * j * plane, plane, 128);
+                }
             }
+            d.stage_in_load = L.stage_in_load[k];
             d.nks = nks;
             d.b_desc = tc::umma_smem_desc(L.blob_off + L.b_off[k], st.N * 16, 128);
             d.vec_off = L.blob_off + L.vec_off[k];
@@ -499,6 +511,9 @@ struct FkBuilder {
         cudaFuncSetAttribute(fk::fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         const size_t smem = L.smem;
         const int tiles = q.tiles_x * q.tiles_y;
+        int num_sms = 148;
+        cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, P->device);
+        const int slots = num_sms;   // persistent: one 512-thread CTA per SM
         op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
             fk::Params p = q;
             p.blob = P->arena + blob;
@@ -507,9 +522,11 @@ struct FkBuilder {
                 if (st.to_logits) p.stage[k].gptr = logits;
                 else if (st.out_mode != fk::OUT_STAGE) p.stage[k].gptr = P->ws + P->tensors[st.out_tensor].off;
             }
+            p.total_tiles = n * tiles;
+            const int grid = std::min(p.total_tiles, slots);
             static const bool prof_on = getenv("ISG_FK_PROF") != nullptr;
-            if (prof_on) return launch_profiled(sp.name, p, n * tiles, smem, *maps, stream);
-            fk::fk_kernel<<<n * tiles, fk::THREADS, smem, stream>>>(maps->in[0], maps->in[1], maps->in[2], maps->in[3],
+            if (prof_on) return launch_profiled(sp.name, p, grid, smem, *maps, stream);
+            fk::fk_kernel<<<grid, fk::THREADS, smem, stream>>>(maps->in[0], maps->in[1], maps->in[2], maps->in[3],
                                                                    maps->out[0], maps->out[1], p);
             return cudaGetLastError();
         };

@@ -26,7 +26,8 @@
 namespace isg {
 namespace fk {
 
-constexpr int THREADS = 256;
+constexpr int THREADS = 512;
+constexpr int NWARPS = THREADS / 32, NGROUPS = THREADS / 128;
 constexpr int MAX_LOADS = 5;
 constexpr int MAX_KS = 20;      // K <= 320 per tap
 constexpr int MAX_MMA_TAPS = 9;
@@ -50,6 +51,8 @@ struct Stage {
     uint64_t a_desc[MAX_KS];       // UMMA descriptor of K slice ks (16 channels = 2 planes) relative to the
                                    // dynamic shared memory base: the kernel adds (base + row offset) >> 4
     uint64_t b_desc;               // descriptor of the first packed B block [tap][ks][2][N][8] bf16
+    uint32_t a_buf_mask;           // bit ks set: that K slice lives in the double-buffered load area
+    int stage_in_load;             // staging planes alias a load region (follow the load buffer)
     int vec_off;                   // fp32 shift[N], slope[N]
     int pitch;                     // pitch of the M index space (TW + 2*halo of the tap planes)
     int res_on, res_off, res_plane_bytes, res_mod;
@@ -74,7 +77,9 @@ struct Params {
     int TH, TW, H, W, tiles_x, tiles_y;
     int n_mt, tmem_cols;
     int nloads; Load loads[MAX_LOADS];
-    uint32_t tx_bytes;             // all TMA boxes + the constant blob
+    uint32_t tx_bytes;             // all TMA boxes of one tile
+    int lbuf_stride;               // byte distance between the two load buffers (persistent double buffering)
+    int total_tiles;               // batch * tiles_y * tiles_x of this launch
     const void* blob; int blob_off, blob_bytes;
     Stencil st;
     int nstages; Stage stage[2];
@@ -124,17 +129,18 @@ __device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
 // ---- depthwise stencil: haloed input planes -> A operand planes ----
 // SEP5 = false: 3x3 with dilation; SEP5 = true: the composed (5,1)x(1,5) pair (25 taps)
 template <bool SEP5>
-__device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int x0) {
+__device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int x0, int boff) {
     const Stencil& s = p.st;
     constexpr int KS = SEP5 ? 5 : 3;
     const int npix = p.TH * p.TW, C = s.nchunks * 8;
     const int dil = SEP5 ? 1 : s.dil, pitch = s.in_pitch;
     const float* wt = reinterpret_cast<const float*>(smem + s.w_off);
     const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
-    for (int k = 0; k < s.nchunks; ++k) {
-        const uint8_t* plane = smem + s.in_off + (size_t)k * s.in_plane_bytes;
-        const float* wk = wt + k * 8;
-        for (int pix = threadIdx.x; pix < npix; pix += THREADS) {
+    {
+        for (int item = threadIdx.x; item < npix * s.nchunks; item += THREADS) {
+            const int k = item / npix, pix = item - k * npix;
+            const uint8_t* plane = smem + s.in_off + boff + (size_t)k * s.in_plane_bytes;
+            const float* wk = wt + k * 8;
             const int r = pix / p.TW, c = pix - r * p.TW;
             // top-left tap of this pixel
             const uint8_t* in = plane + (size_t)((r + s.halo - (KS / 2) * dil) * pitch + c + s.halo - (KS / 2) * dil) * 16;
@@ -188,10 +194,11 @@ __device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int 
 
 // MMAs of the M tiles mt = first, first + step, ...; called by ONE thread per issuing warp
 __device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, uint32_t smem_base, uint32_t tmem_base,
-                                          int first, int step) {
+                                          int first, int step, int boff) {
     const uint32_t idesc = tc::umma_idesc_bf16(128, s.N);
     const uint64_t base16 = smem_base >> 4;
     const uint64_t bd0 = s.b_desc + base16;
+    const uint64_t boff16 = (uint64_t)(boff >> 4);
     const uint32_t b_step = (uint32_t)s.N * 2;  // 16-byte units per [2][N][8] block
     for (int mt = first; mt < p.n_mt; mt += step) {
         uint32_t acc = 0;
@@ -200,7 +207,8 @@ __device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, uint3
             const uint64_t a_row = base16 + (uint64_t)(mt * 128 + s.tap_off[t]);
 #pragma unroll 4
             for (int ks = 0; ks < s.nks; ++ks) {
-                tc::umma_bf16(tmem_base + mt * s.N, s.a_desc[ks] + a_row, bd, idesc, acc);
+                tc::umma_bf16(tmem_base + mt * s.N, s.a_desc[ks] + a_row + (((s.a_buf_mask >> ks) & 1u) ? boff16 : 0), bd,
+                              idesc, acc);
                 acc = 1;
                 bd += b_step;
             }
@@ -220,7 +228,7 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 // epilogue of one (M tile, 16-column chunk): raw accumulators -> shift/residual/activation -> output
 __device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const Stage& s, const uint32_t (&raw)[16],
-                                         int mt, int cc, int quad, int lane, int b, int x0, int y0) {
+                                         int mt, int cc, int quad, int lane, int b, int x0, int y0, int boff) {
     const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
     const int m = mt * 128 + quad * 32 + lane;
     const int r = m / s.pitch, c = m - r * s.pitch;
@@ -234,7 +242,7 @@ __device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const S
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[i]);
     if (s.res_on && geom) {
         const int ch0 = s.res_mod ? col0 % s.res_mod : col0;
-        const uint8_t* rp = smem + s.res_off + (size_t)(ch0 >> 3) * s.res_plane_bytes + (size_t)pc * 16;
+        const uint8_t* rp = smem + s.res_off + boff + (size_t)(ch0 >> 3) * s.res_plane_bytes + (size_t)pc * 16;
         float f[16];
         unpack8(*reinterpret_cast<const uint4*>(rp), f);
         unpack8(*reinterpret_cast<const uint4*>(rp + s.res_plane_bytes), f + 8);
@@ -267,7 +275,7 @@ __device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const S
     if (s.out_mode == OUT_STAGE) {
         if (s.stage_compact && !geom) return;
         const int si = s.stage_compact ? pc : m;
-        uint8_t* d = smem + s.stage_off + (size_t)(col0 >> 3) * s.stage_plane_bytes + (size_t)si * 16;
+        uint8_t* d = smem + s.stage_off + (s.stage_in_load ? boff : 0) + (size_t)(col0 >> 3) * s.stage_plane_bytes + (size_t)si * 16;
         *reinterpret_cast<uint4*>(d) = q0;
         *reinterpret_cast<uint4*>(d + s.stage_plane_bytes) = q1;
     } else if (s.out_mode == OUT_S2D) {
@@ -295,7 +303,7 @@ __device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const S
 // only touch TMEM lanes [32*(w%4), +32).  The TMEM load of the next item is in flight while the
 // current one is processed.
 __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, const Stage& s, uint32_t tmem_base,
-                                             int b, int x0, int y0) {
+                                             int b, int x0, int y0, int boff) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int quad = warp & 3, grp = warp >> 2;
     const int ncc = s.N >> 4, nitems = p.n_mt * ncc;
@@ -308,42 +316,41 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
     while (true) {
         __syncwarp();
         tmem_ld_wait();
-        const int n1 = item + 2;
+        const int n1 = item + NGROUPS;
         if (n1 < nitems) tmem_ld16_nowait(lane_base + n1 * 16, rb);
-        epi_item(smem, p, s, ra, item / ncc, item % ncc, quad, lane, b, x0, y0);
+        epi_item(smem, p, s, ra, item / ncc, item % ncc, quad, lane, b, x0, y0, boff);
         if (n1 >= nitems) break;
         __syncwarp();
         tmem_ld_wait();
-        const int n2 = item + 4;
+        const int n2 = item + 2 * NGROUPS;
         if (n2 < nitems) tmem_ld16_nowait(lane_base + n2 * 16, ra);
-        epi_item(smem, p, s, rb, n1 / ncc, n1 % ncc, quad, lane, b, x0, y0);
+        epi_item(smem, p, s, rb, n1 / ncc, n1 % ncc, quad, lane, b, x0, y0, boff);
         if (n2 >= nitems) break;
         item = n2;
     }
 }
 
-__global__ void __launch_bounds__(THREADS, 2)
+__global__ void __launch_bounds__(THREADS, 1)
 fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtensorMap m1,
           const __grid_constant__ CUtensorMap m2, const __grid_constant__ CUtensorMap m3,
           const __grid_constant__ CUtensorMap mo0, const __grid_constant__ CUtensorMap mo1,
           const __grid_constant__ Params p) {
     extern __shared__ __align__(1024) uint8_t smem[];
+    // bars: [0],[1] tile loads of buffer 0/1; [2],[3] MMAs of stage 0/1; [4] constants blob
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.bar_off);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
     const int tid = threadIdx.x, warp = tid >> 5;
-    int bid = blockIdx.x;
-    const int tx = bid % p.tiles_x; bid /= p.tiles_x;
-    const int ty = bid % p.tiles_y;
-    const int b = bid / p.tiles_y;
-    const int x0 = tx * p.TW, y0 = ty * p.TH;
+    const CUtensorMap* maps[4] = {&m0, &m1, &m2, &m3};
 
     if (p.prof && tid == 0) p.prof[(size_t)blockIdx.x * 16 + 14] = globaltimer_ns();
     FK_STAMP(0);
-    const int n_issuers = p.n_mt < 8 ? p.n_mt : 8;   // warp w issues the MMAs of M tiles w, w+8, ...
+    const int n_issuers = p.n_mt < NWARPS ? p.n_mt : NWARPS;   // warp w issues the MMAs of M tiles w, w+NWARPS, ...
     if (tid == 0) {
         tc::mbar_init(&bars[0], 1);
-        tc::mbar_init(&bars[1], n_issuers);
+        tc::mbar_init(&bars[1], 1);
         tc::mbar_init(&bars[2], n_issuers);
+        tc::mbar_init(&bars[3], n_issuers);
+        tc::mbar_init(&bars[4], 1);
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, p.tmem_cols);
@@ -351,66 +358,90 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     __syncthreads();
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    const uint32_t smem_base = tc::smem_u32(smem);
     FK_STAMP(1);
 
-    if (tid == 0) {
-        tc::mbar_expect_tx(&bars[0], p.tx_bytes);
-        const CUtensorMap* maps[4] = {&m0, &m1, &m2, &m3};
+    // one elected thread: TMA boxes of tile `t` into load buffer `buf`
+    auto issue_loads = [&](int t, int buf) {
+        const int txi = t % p.tiles_x, r1 = t / p.tiles_x;
+        const int tyi = r1 % p.tiles_y, bi = r1 / p.tiles_y;
+        tc::mbar_expect_tx(&bars[buf], p.tx_bytes);
         for (int i = 0; i < p.nloads; ++i) {
             const Load& l = p.loads[i];
-            const int cx = x0 * l.step + l.dx;
-            const int cy = y0 * l.step + l.dy + (l.folded ? b * l.rows_per_img : 0);
-            tc::tma_load_5d(smem + l.smem_off, maps[l.map], &bars[0], 0, cx, cy, l.chunk0, l.folded ? 0 : b);
+            const int cx = txi * p.TW * l.step + l.dx;
+            const int cy = tyi * p.TH * l.step + l.dy + (l.folded ? bi * l.rows_per_img : 0);
+            tc::tma_load_5d(smem + l.smem_off + buf * p.lbuf_stride, maps[l.map], &bars[buf], 0, cx, cy, l.chunk0,
+                            l.folded ? 0 : bi);
         }
-        bulk_g2s(smem + p.blob_off, p.blob, p.blob_bytes, &bars[0]);
+    };
+    if (tid == 0) {
+        tc::mbar_expect_tx(&bars[4], p.blob_bytes);
+        bulk_g2s(smem + p.blob_off, p.blob, p.blob_bytes, &bars[4]);
+        issue_loads(blockIdx.x, 0);
     }
-    tc::mbar_wait(&bars[0], 0);
-    FK_STAMP(2);
+    tc::mbar_wait(&bars[4], 0);
 
-    if (p.st.on) {
-        if (p.st.sep5) run_stencil<true>(smem, p, x0);
-        else run_stencil<false>(smem, p, x0);
-        tc::fence_proxy_async();
-        __syncthreads();
-    }
-    FK_STAMP(3);
-    const uint32_t smem_base = tc::smem_u32(smem);
-    if ((tid & 31) == 0 && warp < n_issuers) {
-        tc::tc_fence_after();
-        issue_mma(p, p.stage[0], smem_base, tmem_base, warp, 8);
-        tc::umma_commit(&bars[1]);
-    }
-    __syncwarp();
-    tc::mbar_wait(&bars[1], 0);
-    FK_STAMP(4);
-    tc::tc_fence_after();
-    run_epilogue(smem, p, p.stage[0], tmem_base, b, x0, y0);
-    tc::fence_proxy_async();
-    tc::tc_fence_before();
-    __syncthreads();
-    FK_STAMP(5);
-    if (tid == 0 && p.stage[0].out_mode == OUT_STAGE && p.stage[0].store) {
-        tc::tma_store_5d(&mo0, smem + p.stage[0].stage_off, 0, x0, y0, p.stage[0].store_chunk0, b);
-        tc::tma_store_commit();
-    }
-    if (p.nstages > 1) {
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1, boff = buf * p.lbuf_stride;
+        const int txi = tile % p.tiles_x, r1 = tile / p.tiles_x;
+        const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
+        const int x0 = txi * p.TW, y0 = tyi * p.TH;
+        if (tid == 0) {
+            // the other buffer (and the single-buffered staging planes) may still be read by the TMA
+            // stores of the previous tile
+            tc::tma_store_wait_read();
+            if (tile + (int)gridDim.x < p.total_tiles) issue_loads(tile + gridDim.x, buf ^ 1);
+        }
+        tc::mbar_wait(&bars[buf], (it >> 1) & 1);
+        if (it == 0) FK_STAMP(2);
+
+        if (p.st.on) {
+            if (p.st.sep5) run_stencil<true>(smem, p, x0, boff);
+            else run_stencil<false>(smem, p, x0, boff);
+            tc::fence_proxy_async();
+            __syncthreads();
+        }
+        if (it == 0) FK_STAMP(3);
         if ((tid & 31) == 0 && warp < n_issuers) {
             tc::tc_fence_after();
-            issue_mma(p, p.stage[1], smem_base, tmem_base, warp, 8);
+            issue_mma(p, p.stage[0], smem_base, tmem_base, warp, NWARPS, boff);
             tc::umma_commit(&bars[2]);
         }
         __syncwarp();
-        tc::mbar_wait(&bars[2], 0);
-        FK_STAMP(6);
+        tc::mbar_wait(&bars[2], it & 1);
+        if (it == 0) FK_STAMP(4);
         tc::tc_fence_after();
-        run_epilogue(smem, p, p.stage[1], tmem_base, b, x0, y0);
+        run_epilogue(smem, p, p.stage[0], tmem_base, b, x0, y0, boff);
         tc::fence_proxy_async();
         tc::tc_fence_before();
         __syncthreads();
-        FK_STAMP(7);
-        if (tid == 0 && p.stage[1].out_mode == OUT_STAGE && p.stage[1].store) {
-            tc::tma_store_5d(&mo1, smem + p.stage[1].stage_off, 0, x0, y0, p.stage[1].store_chunk0, b);
+        if (it == 0) FK_STAMP(5);
+        if (tid == 0 && p.stage[0].out_mode == OUT_STAGE && p.stage[0].store) {
+            tc::tma_store_5d(&mo0, smem + p.stage[0].stage_off + (p.stage[0].stage_in_load ? boff : 0), 0, x0, y0,
+                             p.stage[0].store_chunk0, b);
             tc::tma_store_commit();
+        }
+        if (p.nstages > 1) {
+            if ((tid & 31) == 0 && warp < n_issuers) {
+                tc::tc_fence_after();
+                issue_mma(p, p.stage[1], smem_base, tmem_base, warp, NWARPS, boff);
+                tc::umma_commit(&bars[3]);
+            }
+            __syncwarp();
+            tc::mbar_wait(&bars[3], it & 1);
+            if (it == 0) FK_STAMP(6);
+            tc::tc_fence_after();
+            run_epilogue(smem, p, p.stage[1], tmem_base, b, x0, y0, boff);
+            tc::fence_proxy_async();
+            tc::tc_fence_before();
+            __syncthreads();
+            if (it == 0) FK_STAMP(7);
+            if (tid == 0 && p.stage[1].out_mode == OUT_STAGE && p.stage[1].store) {
+                tc::tma_store_5d(&mo1, smem + p.stage[1].stage_off + (p.stage[1].stage_in_load ? boff : 0), 0, x0, y0,
+                                 p.stage[1].store_chunk0, b);
+                tc::tma_store_commit();
+            }
         }
     }
     if (tid == 0) tc::tma_store_wait_read();

@@ -122,10 +122,31 @@ int isg_forward(isg_plan* plan, const float* x_dev, int batch, float* logits_dev
     const size_t in_img = (size_t)plan->cin * plan->H * plan->W, out_img = (size_t)plan->H * plan->W;
     for (int b0 = 0; b0 < batch; b0 += plan->max_batch) {
         const int n = batch - b0 < plan->max_batch ? batch - b0 : plan->max_batch;
+        static const bool op_timing = getenv("ISG_OP_TIMING") != nullptr;   // debug: per-op device time
+        std::vector<cudaEvent_t> evs;
+        if (op_timing) {
+            evs.resize(plan->ops.size() + 1);
+            for (auto& e : evs) cudaEventCreate(&e);
+            cudaEventRecord(evs[0], st);
+        }
+        size_t oi = 0;
         for (auto& op : plan->ops) {
             cudaError_t e = op.launch(n, x_dev + b0 * in_img, logits_dev + b0 * out_img, st);
             if (e != cudaSuccess)
                 return fail(ISG_ERR_CUDA, "launch of %s failed: %s", op.name.c_str(), cudaGetErrorString(e));
+            if (op_timing) cudaEventRecord(evs[++oi], st);
+        }
+        if (op_timing) {
+            cudaStreamSynchronize(st);
+            float tot = 0;
+            for (size_t i = 0; i < plan->ops.size(); ++i) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, evs[i], evs[i + 1]);
+                tot += ms;
+                fprintf(stderr, "optime %7.1f us  %s\n", ms * 1e3, plan->ops[i].name.c_str());
+            }
+            fprintf(stderr, "optime total %.1f us\n", tot * 1e3);
+            for (auto& e : evs) cudaEventDestroy(e);
         }
         plan->last_n = n;
     }
