@@ -123,7 +123,7 @@ def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
 
     from instancesegmentation_b200 import Segment, synth
-    from instancesegmentation_b200.decode import decode_masks
+    from instancesegmentation_b200.decode import DecodePlan, decode_masks
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -145,10 +145,11 @@ def run_ours(args, rank, world, local_rank):
     xs = [h.to(dev) for h in host]
     boxes = np.tile(np.array([0, 0, S, S], np.int32), (B, 1))
     masks_buf = torch.empty(B * S * S, dtype=torch.uint8, device=dev)
+    dplan = DecodePlan(boxes, dev)      # box table / offsets uploaded once: a decode is one launch
 
     def step(x):
         with torch.no_grad():
-            return decode_masks(model(x), boxes, out=masks_buf)
+            return decode_masks(model(x), out=masks_buf, plan=dplan)
 
     def barrier():
         if world > 1:
@@ -169,7 +170,7 @@ def run_ours(args, rank, world, local_rank):
         with torch.no_grad():
             y = model(x)
         ev[3 * i + 1].record()          # forward | decode boundary
-        decode_masks(y, boxes, out=masks_buf)
+        decode_masks(y, out=masks_buf, plan=dplan)
         ev[3 * i + 2].record()
         ev[3 * i + 3].record()
     barrier()

@@ -4,106 +4,177 @@
 // mask stores, one atomic set per CTA.  Semantics: DESIGN.md section 3; sigmoid =
 // model/segment.py:534, soft byte = train_instance.py:398-399.
 #include <climits>
+#include <cmath>
 
 #include "decode_math.cuh"
 
 namespace isg {
 namespace {
 
-constexpr int DEC_THREADS = 256, DEC_ITERS = 4, DEC_PPB = DEC_THREADS * 4 * DEC_ITERS;
+constexpr int DEC_THREADS = 256, DEC_VEC = 8, DEC_ITERS = 4, DEC_PPB = DEC_THREADS * DEC_VEC * DEC_ITERS;
+constexpr int DEC_MAX_INST = 65536;
 
-__global__ void decode_init_kernel(int n_inst, int32_t* area, int32_t* bbox) {
-    int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= n_inst) return;
-    area[n] = 0;
-    bbox[4 * n] = INT_MAX; bbox[4 * n + 1] = INT_MAX; bbox[4 * n + 2] = -1; bbox[4 * n + 3] = -1;
+// Per-instance accumulators of the launch in flight: {area, enc(xmin), enc(ymin), xmax+1, ymax+1}
+// with enc(v) = INT_MAX - v, so that zero is the identity of every field (area: add, others: max)
+// and the last CTA of an instance can publish the result and hand the slot back zeroed -- no
+// init or finalize launch.  One decode per device may be in flight at a time (stream order).
+__device__ int g_dec_acc[DEC_MAX_INST][5];
+__device__ unsigned g_dec_ticket[DEC_MAX_INST];
+
+// rarely taken exact re-evaluations stay out of line: the hot loop must fit the instruction cache
+__device__ __noinline__ float exact_sigmoid_nl(float x) { return exact_sigmoid(x); }
+template <typename TL>
+__device__ __noinline__ float exact_prob_nl(const TL* L, int w, int y0, int y1, float ly0, float ly1, int ox, float sx) {
+    Tap ty; ty.i0 = y0; ty.i1 = y1; ty.l0 = ly0; ty.l1 = ly1;
+    Tap tx = make_tap(ox, w, sx);
+    return exact_prob(L, w, ty, tx);
 }
 
-__global__ void decode_finalize_kernel(int n_inst, const int32_t* boxes, const int32_t* area, int32_t* bbox) {
-    int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= n_inst) return;
-    if (area[n] == 0) {
-        bbox[4 * n] = bbox[4 * n + 1] = bbox[4 * n + 2] = bbox[4 * n + 3] = 0;
-    } else {
-        int x0 = boxes[4 * n], y0 = boxes[4 * n + 1];
-        bbox[4 * n] += x0; bbox[4 * n + 1] += y0; bbox[4 * n + 2] += x0 + 1; bbox[4 * n + 3] += y0 + 1;
-    }
-}
+struct DecAcc { int cnt, xmin, ymin, xmax, ymax; };
 
-// One CTA = DEC_PPB consecutive pixels of one instance's flat hk*wk mask.
-template <typename TL, bool SOFT>
-__global__ void __launch_bounds__(DEC_THREADS)
-decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restrict__ boxes,
-              const int64_t* __restrict__ mask_off, float thr, uint8_t* __restrict__ masks,
-              uint8_t* __restrict__ soft, int32_t* __restrict__ area, int32_t* __restrict__ bbox) {
-    const int n = blockIdx.y;
-    const int wk = boxes[4 * n + 2], hk = boxes[4 * n + 3];
-    const int npix = wk * hk;
-    const int start = blockIdx.x * DEC_PPB;
-    if (start >= npix) return;
-    const TL* L = logits + (size_t)n * h * w;
-    uint8_t* dst = masks + mask_off[n];
-    uint8_t* sdst = SOFT ? soft + mask_off[n] : nullptr;
-    const bool identity = (wk == w && hk == h);
-    const float sy = __fdiv_rn((float)h, (float)hk), sx = __fdiv_rn((float)w, (float)wk);
-
-    int cnt = 0, xmin = INT_MAX, ymin = INT_MAX, xmax = -1, ymax = -1;
+// pixels [idx, idx+nv) of one instance; IDENT: the mask has the size of the logit map
+template <typename TL, bool SOFT, bool IDENT>
+__device__ __forceinline__ void decode_run(const TL* __restrict__ L, int h, int w, int wk, int hk, int npix, int idx, int nv,
+                                           bool have, const float4& p0, const float4& p1, float thr, float thr_logit,
+                                           int use_logit_cmp, float sy, float sx, bool vec_out, uint8_t* dst,
+                                           uint8_t* sdst, DecAcc& A) {
+    int oy = idx / wk, ox = idx - oy * wk;
+    unsigned mb[2] = {0u, 0u}, sb[2] = {0u, 0u};
+    const float lv[DEC_VEC] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+    if (IDENT && !SOFT && have && use_logit_cmp && (wk & (DEC_VEC - 1)) == 0) {
+        // hot path: the 8 pixels share a row; decide on the logit, keep bits, update stats once
+        unsigned m8 = 0, u8 = 0;
 #pragma unroll
-    for (int it = 0; it < DEC_ITERS; ++it) {
-        const int idx = start + (it * DEC_THREADS + threadIdx.x) * 4;
-        if (idx >= npix) break;
-        const int nv = min(4, npix - idx);
-        int oy = idx / wk, ox = idx - oy * wk;
-        unsigned mbits = 0, sbits = 0;
-        float lv[4];
-        bool have = false;
-        if (identity && sizeof(TL) == 4 && nv == 4 && ((reinterpret_cast<uintptr_t>(L + idx) & 15) == 0)) {
-            float4 v = __ldcs(reinterpret_cast<const float4*>(L + idx));
-            lv[0] = v.x; lv[1] = v.y; lv[2] = v.z; lv[3] = v.w;
-            have = true;
+        for (int e = 0; e < DEC_VEC; ++e) {
+            const float d = lv[e] - thr_logit;
+            m8 |= (d > 0.f ? 1u : 0u) << e;
+            u8 |= (fabsf(d) <= 1e-3f ? 1u : 0u) << e;
         }
-        Tap ty = make_tap(oy, h, sy);
+        while (u8) {   // within 1e-3 of the boundary: the specification's exact sequence decides
+            const int e = __ffs(u8) - 1;
+            u8 &= u8 - 1;
+            const bool m = exact_sigmoid_nl(lv[e]) > thr;
+            m8 = (m8 & ~(1u << e)) | ((m ? 1u : 0u) << e);
+        }
+        if (m8) {
+            A.cnt += __popc(m8);
+            A.xmin = min(A.xmin, ox + __ffs(m8) - 1); A.xmax = max(A.xmax, ox + 31 - __clz(m8));
+            A.ymin = min(A.ymin, oy); A.ymax = max(A.ymax, oy);
+        }
+        const unsigned lo = ((m8 & 0xfu) * 0x00204081u) & 0x01010101u, hi = ((m8 >> 4) * 0x00204081u) & 0x01010101u;
+        if (vec_out) __stcs(reinterpret_cast<uint2*>(dst + idx), make_uint2(lo, hi));
+        else {
+            for (int e = 0; e < DEC_VEC; ++e) dst[idx + e] = (uint8_t)((m8 >> e) & 1u);
+        }
+        return;
+    }
+    Tap ty = make_tap(oy, h, sy);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            if (e < nv) {
-                float p;
-                bool decided = false, m = false;
-                if (identity) {
-                    float x = have ? lv[e] : ldl(L + idx + e);
-                    if (!SOFT) {
+    for (int e = 0; e < DEC_VEC; ++e) {
+        if (e < nv) {
+            float p = 0.f;
+            bool decided = false, m = false;
+            if (IDENT) {
+                const float x = have ? lv[e] : ldl(L + idx + e);
+                if (!SOFT) {
+                    // sigmoid is monotone: far from logit(thr) the comparison is made on the logit itself
+                    if (use_logit_cmp) {
+                        if (fabsf(x - thr_logit) > 1e-3f) { m = x > thr_logit; decided = true; }
+                    } else {
                         p = fast_sigmoid(x);
                         if (fabsf(p - thr) > DECIDE_MARGIN) { m = p > thr; decided = true; }
                     }
-                    if (!decided) { p = exact_sigmoid(x); m = p > thr; }
-                } else {
+                }
+                if (!decided) { p = exact_sigmoid_nl(x); m = p > thr; }
+            } else {
+                if (!SOFT) {
                     Tap tx = make_tap(ox, w, sx);
-                    if (!SOFT) {
-                        p = fast_prob(L, w, ty, tx);
-                        if (fabsf(p - thr) > DECIDE_MARGIN) { m = p > thr; decided = true; }
-                    }
-                    if (!decided) { p = exact_prob(L, w, ty, tx); m = p > thr; }
+                    p = fast_prob(L, w, ty, tx);
+                    if (fabsf(p - thr) > DECIDE_MARGIN) { m = p > thr; decided = true; }
                 }
-                if (m) {
-                    mbits |= 1u << (8 * e);
-                    ++cnt;
-                    xmin = min(xmin, ox); xmax = max(xmax, ox);
-                    ymin = min(ymin, oy); ymax = max(ymax, oy);
-                }
-                if (SOFT) sbits |= soft_byte(p) << (8 * e);
-                if (++ox == wk) { ox = 0; ++oy; ty = make_tap(oy, h, sy); }
+                if (!decided) { p = exact_prob_nl(L, w, ty.i0, ty.i1, ty.l0, ty.l1, ox, sx); m = p > thr; }
             }
-        }
-        if (nv == 4 && ((reinterpret_cast<uintptr_t>(dst + idx) & 3) == 0)) {
-            __stcs(reinterpret_cast<unsigned*>(dst + idx), mbits);
-            if (SOFT) __stcs(reinterpret_cast<unsigned*>(sdst + idx), sbits);
-        } else {
-            for (int e = 0; e < nv; ++e) {
-                dst[idx + e] = (uint8_t)((mbits >> (8 * e)) & 0xff);
-                if (SOFT) sdst[idx + e] = (uint8_t)((sbits >> (8 * e)) & 0xff);
+            if (m) {
+                mb[e >> 2] |= 1u << (8 * (e & 3));
+                ++A.cnt;
+                A.xmin = min(A.xmin, ox); A.xmax = max(A.xmax, ox);
+                A.ymin = min(A.ymin, oy); A.ymax = max(A.ymax, oy);
             }
+            if (SOFT) sb[e >> 2] |= soft_byte(p) << (8 * (e & 3));
+            if (++ox == wk) { ox = 0; ++oy; if (!IDENT) ty = make_tap(oy, h, sy); }
         }
     }
-    // warp reduction, then one set of atomics per CTA
+    if (nv == DEC_VEC && vec_out) {
+        __stcs(reinterpret_cast<uint2*>(dst + idx), make_uint2(mb[0], mb[1]));
+        if (SOFT) __stcs(reinterpret_cast<uint2*>(sdst + idx), make_uint2(sb[0], sb[1]));
+    } else {
+        for (int e = 0; e < nv; ++e) {
+            dst[idx + e] = (uint8_t)((mb[e >> 2] >> (8 * (e & 3))) & 0xff);
+            if (SOFT) sdst[idx + e] = (uint8_t)((sb[e >> 2] >> (8 * (e & 3))) & 0xff);
+        }
+    }
+}
+
+// One CTA = DEC_PPB consecutive pixels of one instance's flat hk*wk mask; one thread-iteration =
+// 8 consecutive pixels: two 16-byte logit loads in, one 8-byte mask store out.
+template <typename TL, bool SOFT>
+__global__ void __launch_bounds__(DEC_THREADS)
+decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restrict__ boxes,
+              const int64_t* __restrict__ mask_off, float thr, float thr_logit, int use_logit_cmp,
+              uint8_t* __restrict__ masks, uint8_t* __restrict__ soft, int32_t* __restrict__ area,
+              int32_t* __restrict__ bbox) {
+    const int n = blockIdx.y;
+    const int4 bx = __ldg(reinterpret_cast<const int4*>(boxes) + n);
+    const int wk = bx.z, hk = bx.w;
+    const int npix = wk * hk;
+    const int start = blockIdx.x * DEC_PPB;
+    if (npix <= 0 && blockIdx.x == 0 && threadIdx.x == 0) {   // degenerate box: empty result
+        area[n] = 0;
+        bbox[4 * n] = bbox[4 * n + 1] = bbox[4 * n + 2] = bbox[4 * n + 3] = 0;
+    }
+    if (start >= npix) return;
+    const TL* L = logits + (size_t)n * h * w;
+    const int64_t moff = mask_off[n];
+    uint8_t* dst = masks + moff;
+    uint8_t* sdst = SOFT ? soft + moff : nullptr;
+    const bool identity = (wk == w && hk == h);
+    const bool vec_in = identity && sizeof(TL) == 4 && ((reinterpret_cast<uintptr_t>(L) & 15) == 0);
+    const bool vec_out = ((reinterpret_cast<uintptr_t>(dst) & 7) == 0) && (!SOFT || (reinterpret_cast<uintptr_t>(sdst) & 7) == 0);
+    const float sy = __fdiv_rn((float)h, (float)hk), sx = __fdiv_rn((float)w, (float)wk);
+    DecAcc A = {0, INT_MAX, INT_MAX, -1, -1};
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (identity) {
+        // all loads of the thread are in flight before the first is consumed
+        float4 pre[DEC_ITERS][2];
+#pragma unroll
+        for (int it = 0; it < DEC_ITERS; ++it) {
+            const int idx = start + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
+            pre[it][0] = z4; pre[it][1] = z4;
+            if (vec_in && idx + DEC_VEC <= npix) {
+                pre[it][0] = __ldcs(reinterpret_cast<const float4*>(L + idx));
+                pre[it][1] = __ldcs(reinterpret_cast<const float4*>(L + idx) + 1);
+            }
+        }
+#pragma unroll
+        for (int it = 0; it < DEC_ITERS; ++it) {
+            const int idx = start + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
+            if (idx < npix) {
+                const int nv = min(DEC_VEC, npix - idx);
+                decode_run<TL, SOFT, true>(L, h, w, wk, hk, npix, idx, nv, vec_in && nv == DEC_VEC, pre[it][0], pre[it][1],
+                                           thr, thr_logit, use_logit_cmp, sy, sx, vec_out, dst, sdst, A);
+            }
+        }
+    } else {
+#pragma unroll 1
+        for (int it = 0; it < DEC_ITERS; ++it) {
+            const int idx = start + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
+            if (idx >= npix) break;
+            decode_run<TL, SOFT, false>(L, h, w, wk, hk, npix, idx, min(DEC_VEC, npix - idx), false, z4, z4, thr, thr_logit,
+                                        use_logit_cmp, sy, sx, vec_out, dst, sdst, A);
+        }
+    }
+    int cnt = A.cnt, xmin = A.xmin, ymin = A.ymin, xmax = A.xmax, ymax = A.ymax;
+    // warp reduction, one set of atomics per CTA, last CTA of the instance publishes
     cnt = __reduce_add_sync(0xffffffffu, cnt);
     xmin = __reduce_min_sync(0xffffffffu, xmin); ymin = __reduce_min_sync(0xffffffffu, ymin);
     xmax = __reduce_max_sync(0xffffffffu, xmax); ymax = __reduce_max_sync(0xffffffffu, ymax);
@@ -117,10 +188,26 @@ decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __rest
             xmin = min(xmin, red[i][1]); ymin = min(ymin, red[i][2]);
             xmax = max(xmax, red[i][3]); ymax = max(ymax, red[i][4]);
         }
+        int* acc = g_dec_acc[n];
         if (cnt) {
-            atomicAdd(area + n, cnt);
-            atomicMin(bbox + 4 * n, xmin); atomicMin(bbox + 4 * n + 1, ymin);
-            atomicMax(bbox + 4 * n + 2, xmax); atomicMax(bbox + 4 * n + 3, ymax);
+            atomicAdd(acc, cnt);
+            atomicMax(acc + 1, INT_MAX - xmin); atomicMax(acc + 2, INT_MAX - ymin);
+            atomicMax(acc + 3, xmax + 1); atomicMax(acc + 4, ymax + 1);
+        }
+        __threadfence();
+        const unsigned nblk = (unsigned)((npix + DEC_PPB - 1) / DEC_PPB);
+        if (atomicAdd(&g_dec_ticket[n], 1u) == nblk - 1) {
+            __threadfence();
+            const int a = atomicExch(acc, 0);
+            const int e1 = atomicExch(acc + 1, 0), e2 = atomicExch(acc + 2, 0);
+            const int e3 = atomicExch(acc + 3, 0), e4 = atomicExch(acc + 4, 0);
+            g_dec_ticket[n] = 0;
+            area[n] = a;
+            if (a == 0) { bbox[4 * n] = bbox[4 * n + 1] = bbox[4 * n + 2] = bbox[4 * n + 3] = 0; }
+            else {
+                bbox[4 * n] = INT_MAX - e1 + bx.x; bbox[4 * n + 1] = INT_MAX - e2 + bx.y;
+                bbox[4 * n + 2] = e3 + bx.x; bbox[4 * n + 3] = e4 + bx.y;
+            }
         }
     }
 }
@@ -197,16 +284,20 @@ int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int h, int w
         return fail(ISG_ERR_ARG, "isg_decode: bad sizes (n_inst=%d h=%d w=%d max box %dx%d)", n_inst, h, w, max_wk, max_hk);
     if ((int64_t)max_wk * max_hk > INT_MAX) return fail(ISG_ERR_ARG, "isg_decode: box too large");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    decode_init_kernel<<<cdiv(n_inst, 128), 128, 0, st>>>(n_inst, area_dev, bbox_dev);
+    // identity-size pixels far from the boundary are decided on the logit itself (sigmoid is monotone);
+    // only when thr is so close to 0/1 that 1e-3 in logit units is not well separated in probability we
+    // keep the probability-space test
+    const double t = threshold;
+    const int use_logit_cmp = (t > 1e-3 && t < 1.0 - 1e-3) ? 1 : 0;
+    const float thr_logit = use_logit_cmp ? (float)log(t / (1.0 - t)) : 0.f;
     dim3 grid(cdiv(max_wk * max_hk, DEC_PPB), n_inst);
 #define ISG_DEC(TL, SOFT)                                                                                     \
     decode_kernel<TL, SOFT><<<grid, DEC_THREADS, 0, st>>>(static_cast<const TL*>(logits_dev), h, w, boxes_dev, \
-                                                           mask_off_dev, threshold, masks_dev, soft_dev,      \
-                                                           area_dev, bbox_dev)
+                                                           mask_off_dev, threshold, thr_logit, use_logit_cmp,  \
+                                                           masks_dev, soft_dev, area_dev, bbox_dev)
     if (logits_bf16) { if (soft_dev) ISG_DEC(bf16, true); else ISG_DEC(bf16, false); }
     else { if (soft_dev) ISG_DEC(float, true); else ISG_DEC(float, false); }
 #undef ISG_DEC
-    decode_finalize_kernel<<<cdiv(n_inst, 128), 128, 0, st>>>(n_inst, boxes_dev, area_dev, bbox_dev);
     ISG_CUDA(cudaGetLastError());
     return ISG_OK;
 }

@@ -44,8 +44,29 @@ def mask_offsets(boxes, align=16):
     return off
 
 
+class DecodePlan:
+    """Device-resident geometry of a decode that is repeated with the same boxes (serving loop,
+    bench): box table, mask offsets and the area/bbox outputs are uploaded / allocated once, so a
+    call is exactly one kernel launch with no host<->device traffic."""
+
+    def __init__(self, boxes, device, align=16):
+        self.boxes = np.ascontiguousarray(np.asarray(boxes, np.int32).reshape(-1, 4))
+        if len(self.boxes) and (self.boxes[:, 2:] < 1).any():
+            raise ValueError("box width/height must be >= 1")
+        self.offsets = mask_offsets(self.boxes, align)
+        self.device = torch.device(device)
+        n = len(self.boxes)
+        self.boxes_d = torch.from_numpy(self.boxes).to(self.device)
+        self.off_d = torch.from_numpy(self.offsets[:-1].copy()).to(self.device)
+        self.area = torch.empty(max(n, 1), dtype=torch.int32, device=self.device)[:n]
+        self.bbox = torch.empty((max(n, 1), 4), dtype=torch.int32, device=self.device)[:n]
+        self.max_w = int(self.boxes[:, 2].max()) if n else 1
+        self.max_h = int(self.boxes[:, 3].max()) if n else 1
+        self.total = max(int(self.offsets[-1]), 1)
+
+
 def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=None, canvas=None,
-                 align=16, out=None):
+                 align=16, out=None, plan=None):
     """``logits``: CUDA fp32/bf16 [N,h,w] or [N,1,h,w].  ``boxes``: int32 [N,4] (x0,y0,wk,hk) on
     the host (None = identity: every map decoded at its own size at the canvas origin).
     ``img_first`` (int32 [n_img+1]) + ``canvas`` (Hs, Ws) additionally produce the id map."""
@@ -59,16 +80,14 @@ def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=N
         raise TypeError(f"logits must be float32 or bfloat16, got {logits.dtype}")
     logits = logits.contiguous()
     N, h, w = logits.shape
-    if boxes is None:
-        boxes = np.tile(np.array([0, 0, w, h], np.int32), (N, 1))
-    boxes = np.ascontiguousarray(np.asarray(boxes, np.int32).reshape(-1, 4))
+    dev = logits.device
+    if plan is None:
+        if boxes is None:
+            boxes = np.tile(np.array([0, 0, w, h], np.int32), (N, 1))
+        plan = DecodePlan(boxes, dev, align)
+    boxes, off, total = plan.boxes, plan.offsets, plan.total
     if len(boxes) != N:
         raise ValueError(f"{N} logit maps but {len(boxes)} boxes")
-    if N and (boxes[:, 2:] < 1).any():
-        raise ValueError("box width/height must be >= 1")
-    off = mask_offsets(boxes, align)
-    dev = logits.device
-    total = max(int(off[-1]), 1)
     l = _lib.lib()
     with torch.cuda.device(dev):
         st = torch.cuda.current_stream().cuda_stream
@@ -79,14 +98,11 @@ def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=N
         else:
             masks = torch.empty(total, dtype=torch.uint8, device=dev)
         soft = torch.empty(total, dtype=torch.uint8, device=dev) if want_soft else None
-        area = torch.empty(max(N, 1), dtype=torch.int32, device=dev)[:N]
-        bbox = torch.empty((max(N, 1), 4), dtype=torch.int32, device=dev)[:N]
-        boxes_d = torch.from_numpy(boxes).to(dev, non_blocking=False)
-        off_d = torch.from_numpy(off[:-1].copy()).to(dev)
+        area, bbox, boxes_d, off_d = plan.area, plan.bbox, plan.boxes_d, plan.off_d
         if N:
             _lib.check(l.isg_decode(logits.data_ptr(), int(logits.dtype == torch.bfloat16), N, h, w,
-                                    boxes_d.data_ptr(), off_d.data_ptr(), int(boxes[:, 2].max()),
-                                    int(boxes[:, 3].max()), float(threshold), masks.data_ptr(),
+                                    boxes_d.data_ptr(), off_d.data_ptr(), plan.max_w,
+                                    plan.max_h, float(threshold), masks.data_ptr(),
                                     soft.data_ptr() if want_soft else None, area.data_ptr(),
                                     bbox.data_ptr(), st))
         idmap = None
