@@ -1,0 +1,117 @@
+"""Multi-process host logic on CPU (gloo, world size 2): the flat gradient bucket of the training
+step and the contiguous batch shard of inference.  No kernels run here."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from instancesegmentation_b200 import Segment, synth
+from instancesegmentation_b200.train_step import FlatBucket
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def shard(n_items, rank, world):
+    """contiguous split used by bench.py / infer: rank r owns [lo, hi)"""
+    per = (n_items + world - 1) // world
+    return min(rank * per, n_items), min((rank + 1) * per, n_items)
+
+
+def test_shard_partition_is_exact():
+    for n in (0, 1, 7, 64, 512, 513):
+        for world in (1, 2, 4, 8):
+            spans = [shard(n, r, world) for r in range(world)]
+            covered = [i for lo, hi in spans for i in range(lo, hi)]
+            assert covered == list(range(n))
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)                      # identical replicas
+    model = Segment(3)
+    bucket = FlatBucket(model)
+    x = torch.from_numpy(synth.batch(4, 32, 32, seed=5))
+    y = (torch.from_numpy(synth.logits(4, 32, 32, seed=6)) > 0).float()[:, None]
+    lo, hi = shard(4, rank, world)
+    model.train()
+    loss = torch.nn.BCELoss()(model.train_batch(x[lo:hi]), y[lo:hi])
+    loss.backward()
+    bucket.pack_grads()
+    scale = bucket.allreduce()
+    if rank == 0:
+        out["grad"] = (bucket.grad * scale).clone().numpy()
+        out["numel"] = bucket.numel
+        out["unused"] = [n for n, p in model.named_parameters() if p.grad is None]
+    dist.destroy_process_group()
+
+
+def test_bucket_allreduce_matches_two_half_batches():
+    world, port = 2, _free_port()
+    with mp.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_worker, args=(world, port, out), nprocs=world, join=True)
+        got, numel, unused = out["grad"], out["numel"], list(out["unused"])
+    assert numel == 257145                       # parameters of Segment(3)
+    assert sorted(unused) == ["bottle4_2.prelu.weight", "bottle4_3.prelu.weight", "bottle5_2.prelu.weight"]
+    # single-process reference: mean of the two half-batch gradients (BatchNorm statistics are
+    # per rank in the reference -- it has no SyncBN -- so halves are evaluated separately)
+    torch.manual_seed(0)
+    model = Segment(3)
+    x = torch.from_numpy(synth.batch(4, 32, 32, seed=5))
+    y = (torch.from_numpy(synth.logits(4, 32, 32, seed=6)) > 0).float()[:, None]
+    acc = None
+    for r in range(world):
+        lo, hi = shard(4, r, world)
+        model.zero_grad(set_to_none=True)
+        model.train()
+        torch.nn.BCELoss()(model.train_batch(x[lo:hi]), y[lo:hi]).backward()
+        flat = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1)
+                          for _, p in model.named_parameters()])
+        acc = flat if acc is None else acc + flat
+    want = (acc / world).numpy()
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-7)
+
+
+def test_flat_views_keep_state_dict_keys():
+    model = Segment(3)
+    keys = list(model.state_dict().keys())
+    bucket = FlatBucket(model)
+    assert list(model.state_dict().keys()) == keys
+    with torch.no_grad():
+        bucket.flat.add_(1.0)                     # parameters are views of the flat tensor
+    assert torch.allclose(next(iter(model.parameters())).reshape(-1)[:4], bucket.flat[:4])
+
+
+@pytest.mark.gpu
+def test_adam_step_matches_torch_adam():
+    torch.manual_seed(1)
+    model = Segment(3).cuda()
+    ref = Segment(3).cuda()
+    ref.load_state_dict(model.state_dict())
+    bucket = FlatBucket(model)
+    opt = torch.optim.Adam(ref.parameters(), lr=1e-3)
+    x = torch.from_numpy(synth.batch(2, 32, 32, seed=5)).cuda()
+    y = (torch.from_numpy(synth.logits(2, 32, 32, seed=6)) > 0).float()[:, None].cuda()
+    for _ in range(3):
+        for m in (model, ref):
+            m.train()
+            m.zero_grad(set_to_none=True)
+            torch.nn.BCELoss()(m.train_batch(x), y).backward()
+        bucket.pack_grads()
+        bucket.adam_step(bucket.allreduce())
+        opt.step()
+    for (n, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
+        if b.grad is None:
+            continue
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6), n
