@@ -270,6 +270,8 @@ struct FkBuilder {
         int maxN = 0;
         for (auto& st : s.stages) maxN = std::max(maxN, st.N);
         L.cols = L.n_mt * maxN;
+        const bool pipelined = s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE");   // experimental, no gain measured
+        if (pipelined) L.cols *= 2;   // two accumulators: MMAs of tile i+1 overlap the epilogue of tile i
         if (L.cols > 512) return false;
         const int a_rows = L.n_mt * 128 + (hx ? 2 * L.pitch + 2 : 0);
         const int npix = TH * TW;
@@ -296,7 +298,9 @@ struct FkBuilder {
         }
         // persistent CTAs double-buffer the whole load area: tile i+1 streams in while tile i computes
         L.lbuf_stride = off;
-        off *= 2;
+        const char* nb_env = getenv("ISG_FK_NBUF");
+        const int ring = nb_env ? atoi(nb_env) : 3;
+        off *= pipelined ? ring : 2;   // pipelined launches keep a ring of load buffers
         if (s.st.kind) {
             const LoadSpec& l = s.loads[s.st.load];
             const int nch = l.nchunks < 0 ? td(l.tensor).Cs / 8 : l.nchunks;
@@ -347,7 +351,7 @@ struct FkBuilder {
         L.blob_bytes = rel;
         off = r128(off + rel);
         L.bar_off = off;
-        L.smem = (size_t)off + 128;
+        L.smem = (size_t)off + 128 + 2 * 3 * 40 * 8;   // barriers + A-descriptor tables
         return L.smem <= 224 * 1024;
     }
 
@@ -397,6 +401,11 @@ struct FkBuilder {
         q.TH = L.TH; q.TW = L.TW; q.H = s.qH; q.W = s.qW;
         q.tiles_x = cdiv(s.qW, L.TW); q.tiles_y = cdiv(s.qH, L.TH);
         q.n_mt = L.n_mt; q.tmem_cols = tc::tmem_cols_pow2(L.cols);
+        auto magic = [](int d) -> uint32_t { return d > 1 ? (uint32_t)(((1ull << 32) + d - 1) / d) : 0u; };
+        q.tw_magic = magic(L.TW); q.npix_magic = magic(L.TH * L.TW);
+        q.pipelined = (s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE")) ? 1 : 0;
+        q.acc_stride = L.cols / 2;
+        q.nbuf = getenv("ISG_FK_NBUF") ? atoi(getenv("ISG_FK_NBUF")) : 3;
         q.nloads = (int)s.loads.size();
         for (int i = 0; i < q.nloads; ++i) {
             const LoadSpec& l = s.loads[i];
@@ -422,7 +431,7 @@ struct FkBuilder {
         for (int k = 0; k < q.nstages; ++k) {
             const StageSpec& st = s.stages[k];
             fk::Stage& d = q.stage[k];
-            d.N = st.N; d.ntaps = st.taps9 ? 9 : 1; d.pitch = L.pitch;
+            d.N = st.N; d.ntaps = st.taps9 ? 9 : 1; d.pitch = L.pitch; d.pitch_magic = magic(L.pitch);
             for (int t = 0; t < d.ntaps; ++t) d.tap_off[t] = st.taps9 ? (t / 3) * L.pitch + (t % 3) : 0;
             int nks = 0;
             for (auto& pt : st.parts) {

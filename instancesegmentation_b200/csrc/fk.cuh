@@ -55,6 +55,7 @@ struct Stage {
     int stage_in_load;             // staging planes alias a load region (follow the load buffer)
     int vec_off;                   // fp32 shift[N], slope[N]
     int pitch;                     // pitch of the M index space (TW + 2*halo of the tap planes)
+    uint32_t pitch_magic;          // ceil(2^32 / pitch) (0 when pitch == 1): m / pitch = umulhi(m, magic)
     int res_on, res_off, res_plane_bytes, res_mod;
     int out_mode;
     int stage_off, stage_plane_bytes, stage_compact;
@@ -76,16 +77,25 @@ struct Stencil {
 struct Params {
     int TH, TW, H, W, tiles_x, tiles_y;
     int n_mt, tmem_cols;
+    uint32_t tw_magic, npix_magic; // ceil(2^32 / TW), ceil(2^32 / (TH*TW)) (0 when the divisor is 1)
     int nloads; Load loads[MAX_LOADS];
     uint32_t tx_bytes;             // all TMA boxes of one tile
     int lbuf_stride;               // byte distance between the two load buffers (persistent double buffering)
     int total_tiles;               // batch * tiles_y * tiles_x of this launch
+    int pipelined;                 // single-stage launch: two TMEM accumulators, MMAs of tile i+1 overlap epilogue i
+    int acc_stride;                // TMEM columns between the two accumulators
+    int nbuf;                      // load buffers in the ring of a pipelined launch (2 or 3)
     const void* blob; int blob_off, blob_bytes;
     Stencil st;
     int nstages; Stage stage[2];
     int bar_off;                   // 3 mbarriers + tmem slot
     long long* prof;               // debug (ISG_FK_PROF=1): per-CTA phase time stamps, else null
 };
+
+// x / d for x * d < 2^32 with magic = ceil(2^32 / d); magic == 0 encodes d == 1
+__device__ __forceinline__ int fastdiv(int x, uint32_t magic) {
+    return magic ? (int)__umulhi((uint32_t)x, magic) : x;
+}
 
 __device__ __forceinline__ long long globaltimer_ns() {
     long long t;
@@ -138,10 +148,10 @@ __device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int 
     const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
     {
         for (int item = threadIdx.x; item < npix * s.nchunks; item += THREADS) {
-            const int k = item / npix, pix = item - k * npix;
+            const int k = fastdiv(item, p.npix_magic), pix = item - k * npix;
             const uint8_t* plane = smem + s.in_off + boff + (size_t)k * s.in_plane_bytes;
             const float* wk = wt + k * 8;
-            const int r = pix / p.TW, c = pix - r * p.TW;
+            const int r = fastdiv(pix, p.tw_magic), c = pix - r * p.TW;
             // top-left tap of this pixel
             const uint8_t* in = plane + (size_t)((r + s.halo - (KS / 2) * dil) * pitch + c + s.halo - (KS / 2) * dil) * 16;
             float2 acc[4];
@@ -193,25 +203,38 @@ __device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int 
 }
 
 // MMAs of the M tiles mt = first, first + step, ...; called by ONE thread per issuing warp
-__device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, uint32_t smem_base, uint32_t tmem_base,
-                                          int first, int step, int boff) {
-    const uint32_t idesc = tc::umma_idesc_bf16(128, s.N);
+constexpr int TAB_N = 40;   // A descriptors per (stage, load buffer): ntaps * nks <= 40
+
+// A-descriptor table of one stage and one load buffer, built once per CTA in shared memory:
+// entry (t * nks + ks) = descriptor of K slice ks shifted by conv tap t, absolute shared address
+__device__ __forceinline__ void build_desc_table(const Params& p, uint64_t* tabs, uint32_t smem_base) {
     const uint64_t base16 = smem_base >> 4;
-    const uint64_t bd0 = s.b_desc + base16;
-    const uint64_t boff16 = (uint64_t)(boff >> 4);
+    for (int i = threadIdx.x; i < p.nstages * 3 * TAB_N; i += THREADS) {
+        const int k = i / (3 * TAB_N), r = i - k * 3 * TAB_N, buf = r / TAB_N, j = r - buf * TAB_N;
+        const Stage& s = p.stage[k];
+        if (j >= s.ntaps * s.nks) continue;
+        const int t = j / s.nks, ks = j - t * s.nks;
+        uint64_t d = s.a_desc[ks] + base16 + (uint64_t)(int64_t)s.tap_off[t];
+        if ((s.a_buf_mask >> ks) & 1u) d += (uint64_t)((buf * p.lbuf_stride) >> 4);
+        tabs[i] = d;
+    }
+}
+
+// MMAs of the M tiles mt = first, first + step, ...; called by ONE thread per issuing warp
+__device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, const uint64_t* tab, uint32_t smem_base,
+                                          uint32_t tmem_base, int first, int step) {
+    const uint32_t idesc = tc::umma_idesc_bf16(128, s.N);
+    const uint64_t bd0 = s.b_desc + (smem_base >> 4);
     const uint32_t b_step = (uint32_t)s.N * 2;  // 16-byte units per [2][N][8] block
+    const int n = s.ntaps * s.nks;
     for (int mt = first; mt < p.n_mt; mt += step) {
-        uint32_t acc = 0;
+        const uint64_t row = (uint64_t)(mt * 128);
         uint64_t bd = bd0;
-        for (int t = 0; t < s.ntaps; ++t) {
-            const uint64_t a_row = base16 + (uint64_t)(mt * 128 + s.tap_off[t]);
+        tc::umma_bf16(tmem_base + mt * s.N, tab[0] + row, bd, idesc, 0u);
 #pragma unroll 4
-            for (int ks = 0; ks < s.nks; ++ks) {
-                tc::umma_bf16(tmem_base + mt * s.N, s.a_desc[ks] + a_row + (((s.a_buf_mask >> ks) & 1u) ? boff16 : 0), bd,
-                              idesc, acc);
-                acc = 1;
-                bd += b_step;
-            }
+        for (int j = 1; j < n; ++j) {
+            bd += b_step;
+            tc::umma_bf16(tmem_base + mt * s.N, tab[j] + row, bd, idesc, 1u);
         }
     }
 }
@@ -231,7 +254,7 @@ __device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const S
                                          int mt, int cc, int quad, int lane, int b, int x0, int y0, int boff) {
     const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
     const int m = mt * 128 + quad * 32 + lane;
-    const int r = m / s.pitch, c = m - r * s.pitch;
+    const int r = fastdiv(m, s.pitch_magic), c = m - r * s.pitch;
     const bool geom = r < p.TH && c < p.TW;
     const int y = y0 + r, x = x0 + c;
     const bool inimg = geom && y < p.H && x < p.W;
@@ -338,7 +361,8 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     extern __shared__ __align__(1024) uint8_t smem[];
     // bars: [0],[1] tile loads of buffer 0/1; [2],[3] MMAs of stage 0/1; [4] constants blob
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.bar_off);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+    uint64_t* tabs = bars + 16;   // [stage][load buffer][TAB_N] A descriptors
     const int tid = threadIdx.x, warp = tid >> 5;
     const CUtensorMap* maps[4] = {&m0, &m1, &m2, &m3};
 
@@ -351,9 +375,13 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         tc::mbar_init(&bars[2], n_issuers);
         tc::mbar_init(&bars[3], n_issuers);
         tc::mbar_init(&bars[4], 1);
+        tc::mbar_init(&bars[8], 1);
+        tc::mbar_init(&bars[9], 1);
+        tc::mbar_init(&bars[10], 1);
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, p.tmem_cols);
+    build_desc_table(p, tabs, tc::smem_u32(smem));
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
@@ -381,6 +409,92 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     }
     tc::mbar_wait(&bars[4], 0);
 
+    if (p.pipelined) {
+        // single-stage launches: the MMAs of tile i+1 run while tile i is in its epilogue (two TMEM
+        // accumulators); loads run nbuf-1 tiles ahead in a ring of nbuf buffers (bars[8..8+nbuf))
+        const Stage& s0 = p.stage[0];
+        const int step = gridDim.x, nbuf = p.nbuf;
+        uint64_t* lbar = bars + 8;
+        const bool issuer = (tid & 31) == 0 && warp < n_issuers;
+        const bool store0 = s0.out_mode == OUT_STAGE && s0.store;
+        const bool buf_busy_in_epi = s0.res_on || s0.stage_in_load;   // the epilogue still needs the load buffer
+        auto issue_ring = [&](int t, int slot) {
+            const int txi = t % p.tiles_x, r1 = t / p.tiles_x;
+            const int tyi = r1 % p.tiles_y, bi = r1 / p.tiles_y;
+            tc::mbar_expect_tx(&lbar[slot], p.tx_bytes);
+            for (int i = 0; i < p.nloads; ++i) {
+                const Load& l = p.loads[i];
+                const int cx = txi * p.TW * l.step + l.dx;
+                const int cy = tyi * p.TH * l.step + l.dy + (l.folded ? bi * l.rows_per_img : 0);
+                tc::tma_load_5d(smem + l.smem_off + slot * p.lbuf_stride, maps[l.map], &lbar[slot], 0, cx, cy, l.chunk0,
+                                l.folded ? 0 : bi);
+            }
+        };
+        if (tid == 0)
+            for (int k = 1; k < nbuf; ++k)
+                if ((int)blockIdx.x + k * step < p.total_tiles) issue_ring(blockIdx.x + k * step, k);
+        tc::mbar_wait(&bars[0], 0);           // tile 0 came through the common prologue into slot 0
+        if (issuer) {
+            tc::tc_fence_after();
+            issue_mma(p, s0, tabs, smem_base, tmem_base, warp, NWARPS);
+            tc::umma_commit(&bars[2]);
+        }
+        FK_STAMP(2);
+        int it = 0, slot = 0, use0 = 0;      // use0: how often slot 0's ring barrier has completed (tile 0 used bars[0])
+        (void)use0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += step, ++it) {
+            const int acc = it & 1, next = tile + step;
+            const int nslot = slot + 1 == nbuf ? 0 : slot + 1;
+            const int txi = tile % p.tiles_x, r1 = tile / p.tiles_x;
+            const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
+            if (next < p.total_tiles) {
+                // tile it+1 is the ((it+1)/nbuf)-th user of its slot; slot 0's first user (tile 0) used bars[0]
+                const int uses = (it + 1) / nbuf - (nslot == 0 ? 1 : 0);
+                tc::mbar_wait(&lbar[nslot], uses & 1);
+                if (issuer) {
+                    tc::tc_fence_after();
+                    issue_mma(p, s0, tabs + nslot * TAB_N, smem_base, tmem_base + (acc ^ 1) * p.acc_stride, warp, NWARPS);
+                    tc::umma_commit(&bars[2 + (acc ^ 1)]);
+                }
+            }
+            __syncwarp();
+            tc::mbar_wait(&bars[2 + acc], (it >> 1) & 1);
+            tc::tc_fence_after();
+            const int refill = tile + nbuf * step;
+            if (!buf_busy_in_epi && tid == 0 && refill < p.total_tiles) issue_ring(refill, slot);
+            if (store0 && !s0.stage_in_load) {   // single-buffered staging: the previous store must have read it
+                if (tid == 0) tc::tma_store_wait_read();
+                __syncthreads();
+            }
+            run_epilogue(smem, p, s0, tmem_base + acc * p.acc_stride, b, txi * p.TW, tyi * p.TH, slot * p.lbuf_stride);
+            tc::fence_proxy_async();
+            tc::tc_fence_before();
+            __syncthreads();
+            if (tid == 0) {
+                if (store0) {
+                    tc::tma_store_5d(&mo0, smem + s0.stage_off + (s0.stage_in_load ? slot * p.lbuf_stride : 0), 0, txi * p.TW,
+                                     tyi * p.TH, s0.store_chunk0, b);
+                    tc::tma_store_commit();
+                }
+                if (buf_busy_in_epi && refill < p.total_tiles) {
+                    if (store0 && s0.stage_in_load) tc::tma_store_wait_read();   // the store reads from this load buffer
+                    issue_ring(refill, slot);
+                }
+            }
+            slot = nslot;
+        }
+        if (tid == 0) tc::tma_store_wait_read();
+        FK_STAMP(8);
+        if (p.prof && tid == 0) p.prof[(size_t)blockIdx.x * 16 + 15] = globaltimer_ns();
+        tc::tc_fence_before();
+        __syncthreads();
+        if (warp == 1) {
+            tc::tc_fence_after();
+            tc::tmem_dealloc(tmem_base, p.tmem_cols);
+        }
+        return;
+    }
+
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
         const int buf = it & 1, boff = buf * p.lbuf_stride;
@@ -405,7 +519,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         if (it == 0) FK_STAMP(3);
         if ((tid & 31) == 0 && warp < n_issuers) {
             tc::tc_fence_after();
-            issue_mma(p, p.stage[0], smem_base, tmem_base, warp, NWARPS, boff);
+            issue_mma(p, p.stage[0], tabs + buf * TAB_N, smem_base, tmem_base, warp, NWARPS);
             tc::umma_commit(&bars[2]);
         }
         __syncwarp();
@@ -425,7 +539,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         if (p.nstages > 1) {
             if ((tid & 31) == 0 && warp < n_issuers) {
                 tc::tc_fence_after();
-                issue_mma(p, p.stage[1], smem_base, tmem_base, warp, NWARPS, boff);
+                issue_mma(p, p.stage[1], tabs + (3 + buf) * TAB_N, smem_base, tmem_base, warp, NWARPS);
                 tc::umma_commit(&bars[3]);
             }
             __syncwarp();
