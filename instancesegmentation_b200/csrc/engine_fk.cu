@@ -182,6 +182,7 @@ struct Spec {
 
 struct Lay {
     int TH = 0, TW = 0, pitch = 0, n_mt = 0, cols = 0;
+    int ctas = 1, nlbuf = 2;   // CTAs per SM (1: 512 threads, 2: 256 threads), load buffers of the generic loop
     size_t smem = 0;
     int load_off[fk::MAX_LOADS], load_plane[fk::MAX_LOADS], load_planes[fk::MAX_LOADS];
     int st_out_off = 0, st_out_plane = 0, st_in_pitch = 0;
@@ -198,14 +199,31 @@ inline int r128(int v) { return (v + 127) / 128 * 128; }
 struct FkMaps { CUtensorMap in[4], out[2]; };
 
 // debug (ISG_FK_PROF=1): run one launch with per-CTA phase stamps and print their means
-inline cudaError_t launch_profiled(const std::string& name, fk::Params p, int grid, size_t smem, const FkMaps& m,
+// programmatic dependent launch: the grid may be scheduled (prologue + constants) while the previous
+// kernel of the stream drains; fk_kernel orders its activation traffic with griddepcontrol.wait
+inline cudaError_t launch_fk(int ctas, int grid, size_t smem, const FkMaps& m, const fk::Params& p, cudaStream_t stream) {
+    static const bool pdl = getenv("ISG_FK_NO_PDL") == nullptr;
+    cudaLaunchConfig_t cfg;
+    std::memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(ctas == 2 ? 256 : 512);
+    cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    if (ctas == 2)
+        return cudaLaunchKernelEx(&cfg, fk::fk_kernel<256>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+    return cudaLaunchKernelEx(&cfg, fk::fk_kernel<512>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+}
+
+inline cudaError_t launch_profiled(const std::string& name, fk::Params p, int ctas, int grid, size_t smem, const FkMaps& m,
                                    cudaStream_t stream) {
     long long* d = nullptr;
     cudaMalloc(&d, (size_t)grid * 16 * sizeof(long long));
     cudaMemset(d, 0, (size_t)grid * 16 * sizeof(long long));
     p.prof = d;
     cudaStreamSynchronize(stream);
-    fk::fk_kernel<<<grid, fk::THREADS, smem, stream>>>(m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+    launch_fk(ctas, grid, smem, m, p, stream);
     cudaError_t e = cudaStreamSynchronize(stream);
     std::vector<long long> h((size_t)grid * 16);
     cudaMemcpy(h.data(), d, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
@@ -262,9 +280,9 @@ struct FkBuilder {
     }
 
     // ---- layout of one candidate tile ----
-    bool layout(const Spec& s, int TH, int TW, Lay& L) const {
+    bool layout(const Spec& s, int TH, int TW, int ctas, int nlbuf, Lay& L) const {
         const int hx = s.stages[0].taps9 ? 1 : 0;
-        L.TH = TH; L.TW = TW; L.pitch = TW + 2 * hx;
+        L.TH = TH; L.TW = TW; L.pitch = TW + 2 * hx; L.ctas = ctas; L.nlbuf = nlbuf;
         const int mrows = TH * L.pitch;
         L.n_mt = cdiv(mrows, 128);
         int maxN = 0;
@@ -272,7 +290,7 @@ struct FkBuilder {
         L.cols = L.n_mt * maxN;
         const bool pipelined = s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE");   // experimental, no gain measured
         if (pipelined) L.cols *= 2;   // two accumulators: MMAs of tile i+1 overlap the epilogue of tile i
-        if (L.cols > 512) return false;
+        if (L.cols > 512 || (int)tc::tmem_cols_pow2(L.cols) > 512 / ctas) return false;
         const int a_rows = L.n_mt * 128 + (hx ? 2 * L.pitch + 2 : 0);
         const int npix = TH * TW;
         const bool chained = s.stages.size() > 1;
@@ -300,7 +318,7 @@ struct FkBuilder {
         L.lbuf_stride = off;
         const char* nb_env = getenv("ISG_FK_NBUF");
         const int ring = nb_env ? atoi(nb_env) : 3;
-        off *= pipelined ? ring : 2;   // pipelined launches keep a ring of load buffers
+        off *= pipelined ? ring : nlbuf;   // pipelined launches keep a ring of load buffers
         if (s.st.kind) {
             const LoadSpec& l = s.loads[s.st.load];
             const int nch = l.nchunks < 0 ? td(l.tensor).Cs / 8 : l.nchunks;
@@ -352,7 +370,7 @@ struct FkBuilder {
         off = r128(off + rel);
         L.bar_off = off;
         L.smem = (size_t)off + 128 + 2 * 3 * 40 * 8;   // barriers + A-descriptor tables
-        return L.smem <= 224 * 1024;
+        return L.smem <= (ctas == 2 ? 112 * 1024 : 224 * 1024);
     }
 
     Lay choose(const Spec& s) const {
@@ -366,21 +384,26 @@ struct FkBuilder {
         Lay best;
         const char* cap_env = getenv("ISG_FK_MAX_MT");
         const int mt_cap = cap_env ? atoi(cap_env) : 16;
-        const char* w1 = getenv("ISG_FK_OCC1_WEIGHT");
-        const double occ1 = w1 ? atof(w1) : 0.75;   // relative value of a tile that leaves room for one CTA per SM only
-        for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
-            Lay L;
-            if (!layout(s, TH, TW, L)) continue;
-            if (L.n_mt > mt_cap && TH > 1) continue;
-            const bool two = true;   // one 512-thread CTA per SM: nothing to gain from small footprints
-            const int tiles_y = cdiv(s.qH, TH);
-            const double eff_m = (double)(TH * TW) / (L.n_mt * 128);
-            const double eff_tail = (double)s.qH / (tiles_y * TH);
-            const double eff_halo = (double)TH / (TH + 2 * max_halo);
-            const long total = (long)P->max_batch * tiles_y * cdiv(s.qW, TW);
-            const double eff_wave = (double)total / (double)(cdiv((int)total, 148) * 148L);
-            L.score = eff_m * eff_tail * (0.5 + 0.5 * eff_halo) * (two ? 1.0 : occ1) * (0.3 + 0.7 * eff_wave) + 1e-4 * TH;
-            if (L.score > best.score) best = L;
+        static const int env_ctas = getenv("ISG_FK_CTAS") ? atoi(getenv("ISG_FK_CTAS")) : 1;
+        static const int env_lbuf = getenv("ISG_FK_LBUF") ? atoi(getenv("ISG_FK_LBUF")) : 2;
+        const bool pipelined = s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE");
+        const int ctas = pipelined ? 1 : env_ctas, nlbuf = pipelined ? 2 : env_lbuf;
+        for (int pass = 0; pass < 2 && best.score < 0; ++pass) {
+            const int c = pass ? 1 : ctas, nb = pass ? 2 : nlbuf;   // fall back to one double-buffered CTA per SM
+            const int slots = 148 * c;
+            for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
+                Lay L;
+                if (!layout(s, TH, TW, c, nb, L)) continue;
+                if (L.n_mt > mt_cap && TH > 1) continue;
+                const int tiles_y = cdiv(s.qH, TH);
+                const double eff_m = (double)(TH * TW) / (L.n_mt * 128);
+                const double eff_tail = (double)s.qH / (tiles_y * TH);
+                const double eff_halo = (double)TH / (TH + 2 * max_halo);
+                const long total = (long)P->max_batch * tiles_y * cdiv(s.qW, TW);
+                const double eff_wave = (double)total / (double)(cdiv((int)total, slots) * (long)slots);
+                L.score = eff_m * eff_tail * (0.5 + 0.5 * eff_halo) * (0.3 + 0.7 * eff_wave) + 1e-4 * TH;
+                if (L.score > best.score) best = L;
+            }
         }
         return best;
     }
@@ -394,8 +417,8 @@ struct FkBuilder {
             abort();
         }
         if (getenv("ISG_FK_VERBOSE"))
-            fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d\n", s.name.c_str(),
-                    s.qH, s.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1]);
+            fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d ctas %d lbuf %d\n",
+                    s.name.c_str(), s.qH, s.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1], L.ctas, L.nlbuf);
         fk::Params q;
         std::memset(&q, 0, sizeof q);
         q.TH = L.TH; q.TW = L.TW; q.H = s.qH; q.W = s.qW;
@@ -406,6 +429,7 @@ struct FkBuilder {
         q.pipelined = (s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE")) ? 1 : 0;
         q.acc_stride = L.cols / 2;
         q.nbuf = getenv("ISG_FK_NBUF") ? atoi(getenv("ISG_FK_NBUF")) : 3;
+        q.nlbuf = L.nlbuf;
         q.nloads = (int)s.loads.size();
         for (int i = 0; i < q.nloads; ++i) {
             const LoadSpec& l = s.loads[i];
@@ -458,6 +482,10 @@ struct FkBuilder {
             d.store_chunk0 = st.out_chunk0; d.shuf = st.shuf; d.Cp = st.Cp;
             if (st.out_tensor >= 0) d.Cs_out = td(st.out_tensor).Cs;
         }
+        // single load buffer: may the next tile's boxes be issued as soon as the stage-0 MMAs completed?
+        q.early_load = 1;
+        for (int k = 0; k < q.nstages; ++k)
+            if (q.stage[k].res_on || q.stage[k].stage_in_load || (k > 0 && q.stage[k].a_buf_mask)) q.early_load = 0;
         // constants blob in the arena
         const size_t blob = arena((size_t)L.blob_bytes / 4);
         const Spec sp = s;
@@ -517,12 +545,14 @@ struct FkBuilder {
             }
             return 0;
         });
-        cudaFuncSetAttribute(fk::fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaFuncSetAttribute(fk::fk_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaFuncSetAttribute(fk::fk_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024);
         const size_t smem = L.smem;
+        const int ctas = L.ctas;
         const int tiles = q.tiles_x * q.tiles_y;
         int num_sms = 148;
         cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, P->device);
-        const int slots = num_sms;   // persistent: one 512-thread CTA per SM
+        const int slots = num_sms * ctas;   // persistent: one 512-thread CTA or two 256-thread CTAs per SM
         op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
             fk::Params p = q;
             p.blob = P->arena + blob;
@@ -534,10 +564,8 @@ struct FkBuilder {
             p.total_tiles = n * tiles;
             const int grid = std::min(p.total_tiles, slots);
             static const bool prof_on = getenv("ISG_FK_PROF") != nullptr;
-            if (prof_on) return launch_profiled(sp.name, p, grid, smem, *maps, stream);
-            fk::fk_kernel<<<grid, fk::THREADS, smem, stream>>>(maps->in[0], maps->in[1], maps->in[2], maps->in[3],
-                                                                   maps->out[0], maps->out[1], p);
-            return cudaGetLastError();
+            if (prof_on) return launch_profiled(sp.name, p, ctas, grid, smem, *maps, stream);
+            return launch_fk(ctas, grid, smem, *maps, p, stream);
         };
         P->ops.push_back(op);
     }

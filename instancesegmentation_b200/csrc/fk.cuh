@@ -26,8 +26,7 @@
 namespace isg {
 namespace fk {
 
-constexpr int THREADS = 512;
-constexpr int NWARPS = THREADS / 32, NGROUPS = THREADS / 128;
+constexpr int THREADS = 512;    // one CTA per SM; the 256-thread instantiation runs two CTAs per SM
 constexpr int MAX_LOADS = 5;
 constexpr int MAX_KS = 20;      // K <= 320 per tap
 constexpr int MAX_MMA_TAPS = 9;
@@ -85,6 +84,9 @@ struct Params {
     int pipelined;                 // single-stage launch: two TMEM accumulators, MMAs of tile i+1 overlap epilogue i
     int acc_stride;                // TMEM columns between the two accumulators
     int nbuf;                      // load buffers in the ring of a pipelined launch (2 or 3)
+    int nlbuf;                     // load buffers of the generic loop: 2 = double buffered; 1 = the co-resident
+                                   // CTA hides the load latency instead (two 256-thread CTAs per SM)
+    int early_load;                // nlbuf == 1: the load buffer is dead once the stage-0 MMAs completed
     const void* blob; int blob_off, blob_bytes;
     Stencil st;
     int nstages; Stage stage[2];
@@ -138,7 +140,7 @@ __device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
 
 // ---- depthwise stencil: haloed input planes -> A operand planes ----
 // SEP5 = false: 3x3 with dilation; SEP5 = true: the composed (5,1)x(1,5) pair (25 taps)
-template <bool SEP5>
+template <bool SEP5, int NT>
 __device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int x0, int boff) {
     const Stencil& s = p.st;
     constexpr int KS = SEP5 ? 5 : 3;
@@ -147,7 +149,7 @@ __device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int 
     const float* wt = reinterpret_cast<const float*>(smem + s.w_off);
     const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
     {
-        for (int item = threadIdx.x; item < npix * s.nchunks; item += THREADS) {
+        for (int item = threadIdx.x; item < npix * s.nchunks; item += NT) {
             const int k = fastdiv(item, p.npix_magic), pix = item - k * npix;
             const uint8_t* plane = smem + s.in_off + boff + (size_t)k * s.in_plane_bytes;
             const float* wk = wt + k * 8;
@@ -207,9 +209,10 @@ constexpr int TAB_N = 40;   // A descriptors per (stage, load buffer): ntaps * n
 
 // A-descriptor table of one stage and one load buffer, built once per CTA in shared memory:
 // entry (t * nks + ks) = descriptor of K slice ks shifted by conv tap t, absolute shared address
+template <int NT>
 __device__ __forceinline__ void build_desc_table(const Params& p, uint64_t* tabs, uint32_t smem_base) {
     const uint64_t base16 = smem_base >> 4;
-    for (int i = threadIdx.x; i < p.nstages * 3 * TAB_N; i += THREADS) {
+    for (int i = threadIdx.x; i < p.nstages * 3 * TAB_N; i += NT) {
         const int k = i / (3 * TAB_N), r = i - k * 3 * TAB_N, buf = r / TAB_N, j = r - buf * TAB_N;
         const Stage& s = p.stage[k];
         if (j >= s.ntaps * s.nks) continue;
@@ -325,8 +328,10 @@ __device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const S
 // warps 0-3 and 4-7 are two groups that alternate over the (M tile, column chunk) items; warp w may
 // only touch TMEM lanes [32*(w%4), +32).  The TMEM load of the next item is in flight while the
 // current one is processed.
+template <int NT>
 __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, const Stage& s, uint32_t tmem_base,
                                              int b, int x0, int y0, int boff) {
+    constexpr int NGROUPS = NT / 128;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int quad = warp & 3, grp = warp >> 2;
     const int ncc = s.N >> 4, nitems = p.n_mt * ncc;
@@ -353,7 +358,8 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
     }
 }
 
-__global__ void __launch_bounds__(THREADS, 1)
+template <int NT>
+__global__ void __launch_bounds__(NT, NT == 512 ? 1 : 2)
 fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtensorMap m1,
           const __grid_constant__ CUtensorMap m2, const __grid_constant__ CUtensorMap m3,
           const __grid_constant__ CUtensorMap mo0, const __grid_constant__ CUtensorMap mo1,
@@ -363,6 +369,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.bar_off);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
     uint64_t* tabs = bars + 16;   // [stage][load buffer][TAB_N] A descriptors
+    constexpr int NWARPS = NT / 32;
     const int tid = threadIdx.x, warp = tid >> 5;
     const CUtensorMap* maps[4] = {&m0, &m1, &m2, &m3};
 
@@ -381,7 +388,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, p.tmem_cols);
-    build_desc_table(p, tabs, tc::smem_u32(smem));
+    build_desc_table<NT>(p, tabs, tc::smem_u32(smem));
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
@@ -402,11 +409,16 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
                             l.folded ? 0 : bi);
         }
     };
+    // programmatic dependent launch: this grid may have been scheduled while its predecessor in the
+    // stream still runs; everything above (barriers, TMEM, descriptor tables) and the constants blob do
+    // not depend on it.  Activations are only touched after griddepcontrol.wait.
     if (tid == 0) {
         tc::mbar_expect_tx(&bars[4], p.blob_bytes);
         bulk_g2s(smem + p.blob_off, p.blob, p.blob_bytes, &bars[4]);
-        issue_loads(blockIdx.x, 0);
     }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (tid == 0) issue_loads(blockIdx.x, 0);
     tc::mbar_wait(&bars[4], 0);
 
     if (p.pipelined) {
@@ -466,7 +478,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
                 if (tid == 0) tc::tma_store_wait_read();
                 __syncthreads();
             }
-            run_epilogue(smem, p, s0, tmem_base + acc * p.acc_stride, b, txi * p.TW, tyi * p.TH, slot * p.lbuf_stride);
+            run_epilogue<NT>(smem, p, s0, tmem_base + acc * p.acc_stride, b, txi * p.TW, tyi * p.TH, slot * p.lbuf_stride);
             tc::fence_proxy_async();
             tc::tc_fence_before();
             __syncthreads();
@@ -496,23 +508,25 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     }
 
     int it = 0;
+    const bool dbl = p.nlbuf == 2;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-        const int buf = it & 1, boff = buf * p.lbuf_stride;
+        const int buf = dbl ? (it & 1) : 0, boff = buf * p.lbuf_stride;
         const int txi = tile % p.tiles_x, r1 = tile / p.tiles_x;
         const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
         const int x0 = txi * p.TW, y0 = tyi * p.TH;
-        if (tid == 0) {
+        const int next = tile + (int)gridDim.x;
+        if (tid == 0 && dbl) {
             // the other buffer (and the single-buffered staging planes) may still be read by the TMA
             // stores of the previous tile
             tc::tma_store_wait_read();
-            if (tile + (int)gridDim.x < p.total_tiles) issue_loads(tile + gridDim.x, buf ^ 1);
+            if (next < p.total_tiles) issue_loads(next, buf ^ 1);
         }
-        tc::mbar_wait(&bars[buf], (it >> 1) & 1);
+        tc::mbar_wait(&bars[buf], (dbl ? (it >> 1) : it) & 1);
         if (it == 0) FK_STAMP(2);
 
         if (p.st.on) {
-            if (p.st.sep5) run_stencil<true>(smem, p, x0, boff);
-            else run_stencil<false>(smem, p, x0, boff);
+            if (p.st.sep5) run_stencil<true, NT>(smem, p, x0, boff);
+            else run_stencil<false, NT>(smem, p, x0, boff);
             tc::fence_proxy_async();
             __syncthreads();
         }
@@ -526,7 +540,8 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         tc::mbar_wait(&bars[2], it & 1);
         if (it == 0) FK_STAMP(4);
         tc::tc_fence_after();
-        run_epilogue(smem, p, p.stage[0], tmem_base, b, x0, y0, boff);
+        if (tid == 0 && !dbl && p.early_load && next < p.total_tiles) issue_loads(next, 0);
+        run_epilogue<NT>(smem, p, p.stage[0], tmem_base, b, x0, y0, boff);
         tc::fence_proxy_async();
         tc::tc_fence_before();
         __syncthreads();
@@ -546,7 +561,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             tc::mbar_wait(&bars[3], it & 1);
             if (it == 0) FK_STAMP(6);
             tc::tc_fence_after();
-            run_epilogue(smem, p, p.stage[1], tmem_base, b, x0, y0, boff);
+            run_epilogue<NT>(smem, p, p.stage[1], tmem_base, b, x0, y0, boff);
             tc::fence_proxy_async();
             tc::tc_fence_before();
             __syncthreads();
@@ -556,6 +571,12 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
                                  p.stage[1].store_chunk0, b);
                 tc::tma_store_commit();
             }
+        }
+        if (tid == 0 && !dbl) {
+            // single load buffer: every reader of this tile is done (the __syncthreads above); staging
+            // planes (which may alias the load buffer) must have left through their TMA stores
+            tc::tma_store_wait_read();
+            if (!p.early_load && next < p.total_tiles) issue_loads(next, 0);
         }
     }
     if (tid == 0) tc::tma_store_wait_read();
