@@ -28,6 +28,9 @@ template <int CIN>
 __global__ void __launch_bounds__(128)
 prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, bf16* __restrict__ init,
             int Cs_init, int total) {
+    // launched with programmatic stream serialization: x2 / init_down may still be read by the
+    // previous forward's kernels until the wait returns
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
     const int W4 = W >> 2, H4 = H >> 2;
@@ -83,6 +86,7 @@ prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, in
 __global__ void __launch_bounds__(128)
 prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __restrict__ x2, int Cs2,
                     bf16* __restrict__ init, int Cs_init, int total) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
     const int W4 = W >> 2, H4 = H >> 2;
@@ -108,13 +112,13 @@ prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __
 struct TailFixParams {
     const bf16* in; int Hq, Wq, Cs;    // [B,Hq,Wq,16]
     float* logits;                     // [B,4Hq,4Wq]
-    const float* wt;                   // [ky(8)][kx(8)][ci(16)][co(4)]
-    const float* bt;                   // [4]
-    const float* w3;                   // [ky(3)][kx(3)][ci(4)]
+    const float* g;                    // [ky(8)][kx(8)][d(9)][ci(16)]: transposed-conv tap (ky,kx) seen through 3x3 tap d
+    const float* gb;                   // [d(9)]: the transposed conv's bias seen through 3x3 tap d
     int total;                         // B * ring
 };
 __device__ __forceinline__ int floordiv4(int a) { return a >= 0 ? a >> 2 : -((3 - a) >> 2); }
 __global__ void __launch_bounds__(128) tail_fix_kernel(TailFixParams p) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.total) return;
     const int H = 4 * p.Hq, W = 4 * p.Wq, ring = 2 * W + 2 * (H - 2);
@@ -124,31 +128,35 @@ __global__ void __launch_bounds__(128) tail_fix_kernel(TailFixParams p) {
     else if (j < 2 * W) { oy = H - 1; ox = j - W; }
     else { j -= 2 * W; oy = 1 + (j >> 1); ox = (j & 1) ? W - 1 : 0; }
     float corr = 0.f;
-    for (int dy = -1; dy <= 1; ++dy)
-        for (int dx = -1; dx <= 1; ++dx) {
-            const int ty = oy + dy, tx = ox + dx;
-            if (ty >= 0 && ty < H && tx >= 0 && tx < W) continue;
-            float t[4] = {p.bt[0], p.bt[1], p.bt[2], p.bt[3]};
-            const int iy1 = floordiv4(ty + 2), ix1 = floordiv4(tx + 2);
-            for (int iy = iy1 - 1; iy <= iy1; ++iy) {
-                const int ky = ty + 2 - 4 * iy;
-                if (iy < 0 || iy >= p.Hq || ky < 0 || ky > 7) continue;
-                for (int ix = ix1 - 1; ix <= ix1; ++ix) {
-                    const int kx = tx + 2 - 4 * ix;
-                    if (ix < 0 || ix >= p.Wq || kx < 0 || kx > 7) continue;
-                    const bf16* src = p.in + (((size_t)b * p.Hq + iy) * p.Wq + ix) * p.Cs;
-                    const float4* w = reinterpret_cast<const float4*>(p.wt) + (ky * 8 + kx) * 16;
-                    for (int c = 0; c < 16; ++c) {
-                        const float v = __bfloat162float(src[c]);
-                        const float4 ww = __ldg(w + c);
-                        t[0] = fmaf(v, ww.x, t[0]); t[1] = fmaf(v, ww.y, t[1]);
-                        t[2] = fmaf(v, ww.z, t[2]); t[3] = fmaf(v, ww.w, t[3]);
-                    }
+#pragma unroll
+    for (int d = 0; d < 9; ++d) {
+        const int ty = oy + d / 3 - 1, tx = ox + d % 3 - 1;
+        if (ty >= 0 && ty < H && tx >= 0 && tx < W) continue;
+        corr += __ldg(p.gb + d);
+        // transposed conv k8 s4 p2 (segment.py:436): output t gets input i through tap k = t + 2 - 4 i
+        const int iy1 = floordiv4(ty + 2), ix1 = floordiv4(tx + 2);
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+            const int iy = iy1 - 1 + a, ky = ty + 2 - 4 * iy;
+            if (iy < 0 || iy >= p.Hq) continue;
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int ix = ix1 - 1 + e, kx = tx + 2 - 4 * ix;
+                if (ix < 0 || ix >= p.Wq) continue;
+                const uint4* src = reinterpret_cast<const uint4*>(p.in + (((size_t)b * p.Hq + iy) * p.Wq + ix) * p.Cs);
+                const float4* g = reinterpret_cast<const float4*>(p.g + ((size_t)(ky * 8 + kx) * 9 + d) * 16);
+                float f[16];
+                fk::unpack8(__ldg(src), f);
+                fk::unpack8(__ldg(src + 1), f + 8);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 w = __ldg(g + q);
+                    corr = fmaf(f[4 * q], w.x, corr); corr = fmaf(f[4 * q + 1], w.y, corr);
+                    corr = fmaf(f[4 * q + 2], w.z, corr); corr = fmaf(f[4 * q + 3], w.w, corr);
                 }
             }
-            const float* w3 = p.w3 + ((dy + 1) * 3 + dx + 1) * 4;
-            corr += t[0] * w3[0] + t[1] * w3[1] + t[2] * w3[2] + t[3] * w3[3];
         }
+    }
     p.logits[((size_t)b * H + oy) * W + ox] -= corr;
 }
 
@@ -199,6 +207,19 @@ inline int r128(int v) { return (v + 127) / 128 * 128; }
 struct FkMaps { CUtensorMap in[4], out[2]; };
 
 // debug (ISG_FK_PROF=1): run one launch with per-CTA phase stamps and print their means
+// plain kernels: launched with programmatic stream serialization (they start with griddepcontrol.wait)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg;
+    std::memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // programmatic dependent launch: the grid may be scheduled (prologue + constants) while the previous
 // kernel of the stream drains; fk_kernel orders its activation traffic with griddepcontrol.wait
 inline cudaError_t launch_fk(int ctas, int grid, size_t smem, const FkMaps& m, const fk::Params& p, cudaStream_t stream) {
@@ -583,12 +604,10 @@ struct FkBuilder {
             bf16* pin = reinterpret_cast<bf16*>(P->ws + init.off);
             if (cin == 3) {
                 const int total = n * (H / 4) * (W / 4);
-                prep_kernel<3><<<cdiv(total, 128), 128, 0, st>>>(x, H, W, px2, x2.Cs, pin, init.Cs, total);
-            } else {
-                const int total = n * cin * (H / 4) * (W / 4);
-                prep_generic_kernel<<<cdiv(total, 128), 128, 0, st>>>(x, cin, H, W, px2, x2.Cs, pin, init.Cs, total);
+                return launch_pdl(prep_kernel<3>, cdiv(total, 128), 128, st, x, H, W, px2, x2.Cs, pin, init.Cs, total);
             }
-            return cudaGetLastError();
+            const int total = n * cin * (H / 4) * (W / 4);
+            return launch_pdl(prep_generic_kernel, cdiv(total, 128), 128, st, x, cin, H, W, px2, x2.Cs, pin, init.Cs, total);
         };
         P->ops.push_back(op);
     }
@@ -600,10 +619,8 @@ struct FkBuilder {
         op.pack = [](const HostWeights&, float*) {};
         op.launch = [=](int n, const float*, float*, cudaStream_t st) {
             int total = n * to.H * to.W * (to.Cs / 4);
-            pool2_kernel<bf16><<<cdiv(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(P->ws + ti.off),
-                                                                reinterpret_cast<bf16*>(P->ws + to.off), to.H, to.W,
-                                                                to.Cs, total);
-            return cudaGetLastError();
+            return launch_pdl(pool2_kernel<bf16>, cdiv(total, 256), 256, st, reinterpret_cast<const bf16*>(P->ws + ti.off),
+                              reinterpret_cast<bf16*>(P->ws + to.off), to.H, to.W, to.Cs, total);
         };
         P->ops.push_back(op);
     }
@@ -1139,28 +1156,34 @@ struct FkBuilder {
         };
         s.stages.push_back(st);
         emit(s);
-        // border correction (fp32 weights in the reference layouts)
-        const size_t owt = arena(64 * 16 * 4), ow3 = arena(36), ob = arena(4);
+        // border correction: fp32 tables composed on the host
+        const size_t og = arena(64 * 9 * 16), ogb = arena(12);
         Op op;
         op.name = "logits border correction";
         op.pack = [=](const HostWeights& w, float* A) {
-            const float* W1 = w.get("bottle6_1.weight");
-            for (int ci = 0; ci < 16; ++ci)
-                for (int co = 0; co < 4; ++co)
-                    for (int t = 0; t < 64; ++t) A[owt + ((size_t)t * 16 + ci) * 4 + co] = W1[((size_t)ci * 4 + co) * 64 + t];
-            const float* w3 = w.get("bottle6_2.weight");
-            for (int c = 0; c < 4; ++c)
-                for (int t = 0; t < 9; ++t) A[ow3 + t * 4 + c] = w3[c * 9 + t];
-            std::memcpy(A + ob, w.get("bottle6_1.bias"), 4 * sizeof(float));
+            const float* W1 = w.get("bottle6_1.weight");   // [ci(16)][co(4)][8][8]
+            const float* w3 = w.get("bottle6_2.weight");   // [1][c(4)][3][3]
+            const float* b1 = w.get("bottle6_1.bias");
+            for (int t = 0; t < 64; ++t)
+                for (int d = 0; d < 9; ++d)
+                    for (int ci = 0; ci < 16; ++ci) {
+                        double a = 0;
+                        for (int co = 0; co < 4; ++co) a += (double)W1[((size_t)ci * 4 + co) * 64 + t] * w3[co * 9 + d];
+                        A[og + ((size_t)t * 9 + d) * 16 + ci] = (float)a;
+                    }
+            for (int d = 0; d < 9; ++d) {
+                double a = 0;
+                for (int co = 0; co < 4; ++co) a += (double)b1[co] * w3[co * 9 + d];
+                A[ogb + d] = (float)a;
+            }
         };
         op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
             TailFixParams p;
             p.in = reinterpret_cast<const bf16*>(P->ws + ty.off); p.Hq = ty.H; p.Wq = ty.W; p.Cs = ty.Cs;
-            p.logits = logits; p.wt = P->arena + owt; p.bt = P->arena + ob; p.w3 = P->arena + ow3;
+            p.logits = logits; p.g = P->arena + og; p.gb = P->arena + ogb;
             const int H = 4 * ty.H, W = 4 * ty.W;
             p.total = n * (2 * W + 2 * (H - 2));
-            tail_fix_kernel<<<cdiv(p.total, 128), 128, 0, stream>>>(p);
-            return cudaGetLastError();
+            return launch_pdl(tail_fix_kernel, cdiv(p.total, 128), 128, stream, p);
         };
         P->ops.push_back(op);
     }

@@ -54,6 +54,7 @@ __global__ void __launch_bounds__(256) dw_kernel(DwParams p) {
 template <typename T>
 __global__ void __launch_bounds__(256) pool2_kernel(const T* __restrict__ in, T* __restrict__ out, int Ho, int Wo,
                                                     int Cs, int total /* B*Ho*Wo*(Cs/4) */) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // no-op unless launched with programmatic serialization
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
     const int cg = Cs >> 2, c = (i % cg) * 4, pix = i / cg;
