@@ -64,6 +64,9 @@ struct isg_plan {
     std::vector<int> taps;     // tensor ids
     bool use_tc = false;       // bf16 mode: GEMM-shaped convs on tcgen05 (ISG_NO_TC=1 disables)
     std::vector<std::function<int()>> finalizers;  // run once after the workspace is allocated (tensor maps)
+    // run once after the finalizers: each fused launch times its candidate tilings on the device
+    // (scratch logits buffer of max_batch images, stream) and keeps the fastest
+    std::vector<std::function<int(float*, cudaStream_t)>> tuners;
 
     size_t esize() const { return mode == ISG_MODE_BF16 ? 2 : 4; }
     void* tptr(int id) const { return ws + tensors[id].off; }

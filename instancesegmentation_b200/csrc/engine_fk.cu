@@ -267,6 +267,13 @@ inline cudaError_t launch_profiled(const std::string& name, fk::Params p, int ct
             "mma0 %6.0f epi0 %6.0f mma1 %6.0f epi1 %6.0f store %6.0f\n", name.c_str(), grid, (t1 - t0) * 1e-3,
             life / grid * 1e-3, ph[1] / grid, ph[2] / grid, ph[3] / grid, ph[4] / grid, ph[5] / grid, ph[6] / grid,
             ph[7] / grid, ph[8] / grid);
+    double ss[5] = {0};
+    for (int b = 0; b < grid; ++b)
+        for (int k = 0; k < 5; ++k) ss[k] += (double)h[(size_t)b * 16 + 9 + k];
+    const double nt = std::max(1, p.total_tiles - grid);
+    fprintf(stderr, "     steady state per tile (%d tiles, %.1f per CTA): wait+stencil %6.0f mma0 %6.0f epi0 %6.0f mma1 %6.0f "
+            "epi1 %6.0f | sum %6.0f cycles\n", p.total_tiles, (double)p.total_tiles / grid, ss[0] / nt, ss[1] / nt,
+            ss[2] / nt, ss[3] / nt, ss[4] / nt, (ss[0] + ss[1] + ss[2] + ss[3] + ss[4]) / nt);
     return e;
 }
 
@@ -394,7 +401,9 @@ struct FkBuilder {
         return L.smem <= (ctas == 2 ? 112 * 1024 : 224 * 1024);
     }
 
-    Lay choose(const Spec& s) const {
+    // candidate layouts, best heuristic score first.  The plan times them on the device
+    // (autotune) unless ISG_FK_NO_TUNE is set; ISG_FK_CTAS / ISG_FK_LBUF pin the mode.
+    std::vector<Lay> candidates(const Spec& s) const {
         const int hx = s.stages[0].taps9 ? 1 : 0;
         int max_halo = hx;
         for (auto& l : s.loads) max_halo = std::max(max_halo, l.halo);
@@ -402,16 +411,22 @@ struct FkBuilder {
         int nx = 1;
         while (cdiv(s.qW, nx) + 2 * max_halo > 256) ++nx;
         const int TW = cdiv(s.qW, nx);
-        Lay best;
         const char* cap_env = getenv("ISG_FK_MAX_MT");
         const int mt_cap = cap_env ? atoi(cap_env) : 16;
-        static const int env_ctas = getenv("ISG_FK_CTAS") ? atoi(getenv("ISG_FK_CTAS")) : 1;
-        static const int env_lbuf = getenv("ISG_FK_LBUF") ? atoi(getenv("ISG_FK_LBUF")) : 2;
         const bool pipelined = s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE");
-        const int ctas = pipelined ? 1 : env_ctas, nlbuf = pipelined ? 2 : env_lbuf;
-        for (int pass = 0; pass < 2 && best.score < 0; ++pass) {
-            const int c = pass ? 1 : ctas, nb = pass ? 2 : nlbuf;   // fall back to one double-buffered CTA per SM
+        const bool tune = !getenv("ISG_FK_NO_TUNE") && !pipelined;
+        const int env_ctas = getenv("ISG_FK_CTAS") ? atoi(getenv("ISG_FK_CTAS")) : 0;
+        const int env_lbuf = getenv("ISG_FK_LBUF") ? atoi(getenv("ISG_FK_LBUF")) : 0;
+        const int per_mode = getenv("ISG_FK_TUNE_TOP") ? atoi(getenv("ISG_FK_TUNE_TOP")) : 3;
+        std::vector<Lay> out;
+        for (int mode = 0; mode < 4; ++mode) {
+            const int c = mode & 1 ? 2 : 1, nb = mode & 2 ? 1 : 2;   // mode 0 = one double-buffered CTA per SM
+            if (pipelined && mode) break;
+            if (!tune && mode && !(env_ctas || env_lbuf)) break;
+            if (env_ctas && c != env_ctas) continue;
+            if (env_lbuf && nb != env_lbuf) continue;
             const int slots = 148 * c;
+            std::vector<Lay> found;
             for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
                 Lay L;
                 if (!layout(s, TH, TW, c, nb, L)) continue;
@@ -423,23 +438,26 @@ struct FkBuilder {
                 const long total = (long)P->max_batch * tiles_y * cdiv(s.qW, TW);
                 const double eff_wave = (double)total / (double)(cdiv((int)total, slots) * (long)slots);
                 L.score = eff_m * eff_tail * (0.5 + 0.5 * eff_halo) * (0.3 + 0.7 * eff_wave) + 1e-4 * TH;
-                if (L.score > best.score) best = L;
+                found.push_back(L);
+            }
+            std::stable_sort(found.begin(), found.end(), [](const Lay& a, const Lay& b) { return a.score > b.score; });
+            const int keep = tune ? per_mode : 1;
+            for (int i = 0; i < (int)found.size() && i < keep; ++i) out.push_back(found[i]);
+        }
+        if (out.empty() && (env_ctas || env_lbuf)) {   // pinned mode infeasible for this launch: default mode
+            for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
+                Lay L;
+                if (!layout(s, TH, TW, 1, 2, L)) continue;
+                L.score = (double)(TH * TW) / (L.n_mt * 128) + 1e-4 * TH;
+                if (out.empty() || L.score > out[0].score) { out.clear(); out.push_back(L); }
             }
         }
-        return best;
+        // the heuristic's favourite of the default mode stays first (it is what runs without tuning)
+        return out;
     }
 
-    // ---- emit one fused launch ----
-    void emit(const Spec& s) {
-        isg_plan* P = this->P;
-        Lay L = choose(s);
-        if (L.score < 0) {
-            fprintf(stderr, "libisg: no feasible tile for %s\n", s.name.c_str());
-            abort();
-        }
-        if (getenv("ISG_FK_VERBOSE"))
-            fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d ctas %d lbuf %d\n",
-                    s.name.c_str(), s.qH, s.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1], L.ctas, L.nlbuf);
+    // ---- kernel parameters of one layout ----
+    fk::Params make_params(const Spec& s, const Lay& L, int& st_C) const {
         fk::Params q;
         std::memset(&q, 0, sizeof q);
         q.TH = L.TH; q.TW = L.TW; q.H = s.qH; q.W = s.qW;
@@ -460,7 +478,7 @@ struct FkBuilder {
         }
         q.lbuf_stride = L.lbuf_stride;
         q.tx_bytes = L.tx; q.blob_off = L.blob_off; q.blob_bytes = L.blob_bytes; q.bar_off = L.bar_off;
-        int st_C = 0;
+        st_C = 0;
         if (s.st.kind) {
             const LoadSpec& l = s.loads[s.st.load];
             fk::Stencil& t = q.st;
@@ -507,6 +525,25 @@ struct FkBuilder {
         q.early_load = 1;
         for (int k = 0; k < q.nstages; ++k)
             if (q.stage[k].res_on || q.stage[k].stage_in_load || (k > 0 && q.stage[k].a_buf_mask)) q.early_load = 0;
+        return q;
+    }
+
+    // one way to run a fused launch: tile, CTAs per SM, load buffering
+    struct Variant { Lay L; fk::Params q; std::shared_ptr<FkMaps> maps; };
+
+    // ---- emit one fused launch ----
+    void emit(const Spec& s) {
+        isg_plan* P = this->P;
+        std::vector<Lay> cands = candidates(s);
+        if (cands.empty()) {
+            fprintf(stderr, "libisg: no feasible tile for %s\n", s.name.c_str());
+            abort();
+        }
+        auto vars = std::make_shared<std::vector<Variant>>();
+        int st_C = 0;
+        for (const Lay& c : cands) vars->push_back(Variant{c, make_params(s, c, st_C), std::make_shared<FkMaps>()});
+        const Lay L = cands[0];   // blob layout (tile independent)
+        auto chosen = std::make_shared<int>(0);
         // constants blob in the arena
         const size_t blob = arena((size_t)L.blob_bytes / 4);
         const Spec sp = s;
@@ -543,51 +580,84 @@ struct FkBuilder {
                 if (sp.st.kind == 2) std::memcpy(v + 2 * C, bw.data(), sizeof(float) * 5 * C);
             }
         };
-        auto maps = std::make_shared<FkMaps>();
         const int maxB = P->max_batch;
         P->finalizers.push_back([=]() -> int {
-            for (size_t i = 0; i < sp.loads.size(); ++i) {
-                const LoadSpec& l = sp.loads[i];
-                const TensorD& t = P->tensors[l.tensor];
-                int rc;
-                if (l.s2d) rc = tc::make_s2d_map(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH, sp.name.c_str());
-                else rc = tc::make_act_map_chunks(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW + 2 * l.halo,
-                                                  L.TH + 2 * l.halo, L.load_planes[i], sp.name.c_str());
-                if (rc) return rc;
-            }
-            for (size_t i = sp.loads.size(); i < 4; ++i) maps->in[i] = maps->in[0];
-            for (size_t k = 0; k < 2; ++k) {
-                if (k < sp.stages.size() && sp.stages[k].out_mode == fk::OUT_STAGE && sp.stages[k].store) {
-                    const TensorD& t = P->tensors[sp.stages[k].out_tensor];
-                    int rc = tc::make_act_map_chunks(&maps->out[k], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH,
-                                                     sp.stages[k].N / 8, sp.name.c_str());
+            for (Variant& v : *vars) {
+                const Lay& L = v.L;
+                FkMaps* maps = v.maps.get();
+                for (size_t i = 0; i < sp.loads.size(); ++i) {
+                    const LoadSpec& l = sp.loads[i];
+                    const TensorD& t = P->tensors[l.tensor];
+                    int rc;
+                    if (l.s2d) rc = tc::make_s2d_map(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH, sp.name.c_str());
+                    else rc = tc::make_act_map_chunks(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW + 2 * l.halo,
+                                                      L.TH + 2 * l.halo, L.load_planes[i], sp.name.c_str());
                     if (rc) return rc;
-                } else maps->out[k] = maps->in[0];
+                }
+                for (size_t i = sp.loads.size(); i < 4; ++i) maps->in[i] = maps->in[0];
+                for (size_t k = 0; k < 2; ++k) {
+                    if (k < sp.stages.size() && sp.stages[k].out_mode == fk::OUT_STAGE && sp.stages[k].store) {
+                        const TensorD& t = P->tensors[sp.stages[k].out_tensor];
+                        int rc = tc::make_act_map_chunks(&maps->out[k], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH,
+                                                         sp.stages[k].N / 8, sp.name.c_str());
+                        if (rc) return rc;
+                    } else maps->out[k] = maps->in[0];
+                }
             }
             return 0;
         });
         cudaFuncSetAttribute(fk::fk_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         cudaFuncSetAttribute(fk::fk_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024);
-        const size_t smem = L.smem;
-        const int ctas = L.ctas;
-        const int tiles = q.tiles_x * q.tiles_y;
         int num_sms = 148;
         cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, P->device);
-        const int slots = num_sms * ctas;   // persistent: one 512-thread CTA or two 256-thread CTAs per SM
-        op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
-            fk::Params p = q;
+        auto run = [=](int which, int n, float* logits, cudaStream_t stream, bool prof) -> cudaError_t {
+            const Variant& v = (*vars)[which];
+            fk::Params p = v.q;
             p.blob = P->arena + blob;
             for (int k = 0; k < p.nstages; ++k) {
                 const StageSpec& st = sp.stages[k];
                 if (st.to_logits) p.stage[k].gptr = logits;
                 else if (st.out_mode != fk::OUT_STAGE) p.stage[k].gptr = P->ws + P->tensors[st.out_tensor].off;
             }
-            p.total_tiles = n * tiles;
-            const int grid = std::min(p.total_tiles, slots);
-            static const bool prof_on = getenv("ISG_FK_PROF") != nullptr;
-            if (prof_on) return launch_profiled(sp.name, p, ctas, grid, smem, *maps, stream);
-            return launch_fk(ctas, grid, smem, *maps, p, stream);
+            p.total_tiles = n * p.tiles_x * p.tiles_y;
+            // persistent: one 512-thread CTA or two 256-thread CTAs per SM
+            const int grid = std::min(p.total_tiles, num_sms * v.L.ctas);
+            if (prof) return launch_profiled(sp.name, p, v.L.ctas, grid, v.L.smem, *v.maps, stream);
+            return launch_fk(v.L.ctas, grid, v.L.smem, *v.maps, p, stream);
         };
+        op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
+            static const bool prof_on = getenv("ISG_FK_PROF") != nullptr;
+            return run(*chosen, n, logits, stream, prof_on);
+        };
+        // autotune: time every variant at the plan's batch size on the device, keep the fastest
+        P->tuners.push_back([=](float* logits, cudaStream_t stream) -> int {
+            const bool verbose = getenv("ISG_FK_VERBOSE") != nullptr;
+            float best = 1e30f;
+            cudaEvent_t e0, e1;
+            cudaEventCreate(&e0); cudaEventCreate(&e1);
+            for (int i = 0; i < (int)vars->size() && vars->size() > 1; ++i) {
+                const int reps = 3;
+                if (run(i, maxB, logits, stream, false) != cudaSuccess) return ISG_ERR_CUDA;
+                cudaEventRecord(e0, stream);
+                for (int r = 0; r < reps; ++r) run(i, maxB, logits, stream, false);
+                cudaEventRecord(e1, stream);
+                if (cudaEventSynchronize(e1) != cudaSuccess) return ISG_ERR_CUDA;
+                float ms = 0;
+                cudaEventElapsedTime(&ms, e0, e1);
+                ms /= reps;
+                const Lay& L = (*vars)[i].L;
+                if (verbose)
+                    fprintf(stderr, "tune %-40s tile %3dx%-3d n_mt %2d ctas %d lbuf %d smem %6zu: %7.1f us\n", sp.name.c_str(),
+                            L.TH, L.TW, L.n_mt, L.ctas, L.nlbuf, L.smem, ms * 1e3);
+                if (ms < best) { best = ms; *chosen = i; }
+            }
+            cudaEventDestroy(e0); cudaEventDestroy(e1);
+            const Lay& L = (*vars)[*chosen].L;
+            if (verbose)
+                fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d ctas %d lbuf %d\n",
+                        sp.name.c_str(), sp.qH, sp.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1], L.ctas, L.nlbuf);
+            return 0;
+        });
         P->ops.push_back(op);
     }
 

@@ -105,6 +105,9 @@ __device__ __forceinline__ long long globaltimer_ns() {
     return t;
 }
 #define FK_STAMP(i) do { if (p.prof && threadIdx.x == 0) p.prof[(size_t)blockIdx.x * 16 + (i)] = clock64(); } while (0)
+// steady state (tiles after the first): per-CTA sums of phase cycles in slots 9..13
+#define FK_ACC(i) do { if (p.prof && threadIdx.x == 0 && it > 0) { const long long t_ = clock64(); \
+    p.prof[(size_t)blockIdx.x * 16 + (i)] += t_ - tprev; tprev = t_; } } while (0)
 
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -508,6 +511,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     }
 
     int it = 0;
+    long long tprev = 0;
     const bool dbl = p.nlbuf == 2;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
         const int buf = dbl ? (it & 1) : 0, boff = buf * p.lbuf_stride;
@@ -515,6 +519,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
         const int x0 = txi * p.TW, y0 = tyi * p.TH;
         const int next = tile + (int)gridDim.x;
+        if (p.prof) tprev = clock64();
         if (tid == 0 && dbl) {
             // the other buffer (and the single-buffered staging planes) may still be read by the TMA
             // stores of the previous tile
@@ -531,6 +536,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             __syncthreads();
         }
         if (it == 0) FK_STAMP(3);
+        FK_ACC(9);
         if ((tid & 31) == 0 && warp < n_issuers) {
             tc::tc_fence_after();
             issue_mma(p, p.stage[0], tabs + buf * TAB_N, smem_base, tmem_base, warp, NWARPS);
@@ -539,6 +545,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         __syncwarp();
         tc::mbar_wait(&bars[2], it & 1);
         if (it == 0) FK_STAMP(4);
+        FK_ACC(10);
         tc::tc_fence_after();
         if (tid == 0 && !dbl && p.early_load && next < p.total_tiles) issue_loads(next, 0);
         run_epilogue<NT>(smem, p, p.stage[0], tmem_base, b, x0, y0, boff);
@@ -546,6 +553,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         tc::tc_fence_before();
         __syncthreads();
         if (it == 0) FK_STAMP(5);
+        FK_ACC(11);
         if (tid == 0 && p.stage[0].out_mode == OUT_STAGE && p.stage[0].store) {
             tc::tma_store_5d(&mo0, smem + p.stage[0].stage_off + (p.stage[0].stage_in_load ? boff : 0), 0, x0, y0,
                              p.stage[0].store_chunk0, b);
@@ -560,12 +568,14 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             __syncwarp();
             tc::mbar_wait(&bars[3], it & 1);
             if (it == 0) FK_STAMP(6);
+            FK_ACC(12);
             tc::tc_fence_after();
             run_epilogue<NT>(smem, p, p.stage[1], tmem_base, b, x0, y0, boff);
             tc::fence_proxy_async();
             tc::tc_fence_before();
             __syncthreads();
             if (it == 0) FK_STAMP(7);
+            FK_ACC(13);
             if (tid == 0 && p.stage[1].out_mode == OUT_STAGE && p.stage[1].store) {
                 tc::tma_store_5d(&mo1, smem + p.stage[1].stage_off + (p.stage[1].stage_in_load ? boff : 0), 0, x0, y0,
                                  p.stage[1].store_chunk0, b);

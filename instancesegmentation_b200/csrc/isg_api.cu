@@ -70,10 +70,23 @@ int isg_plan_create(int device, int in_channel, int height, int width, int max_b
     ISG_CUDA(cudaMalloc(&p->ws, p->ws_bytes));
     ISG_CUDA(cudaMemset(p->ws, 0, p->ws_bytes));  // pad channels stay zero for the plan's lifetime
     ISG_CUDA(cudaMalloc(&p->arena, p->arena_floats * sizeof(float)));
+    ISG_CUDA(cudaMemset(p->arena, 0, p->arena_floats * sizeof(float)));
     p->arena_host.assign(p->arena_floats, 0.f);
     for (auto& fin : p->finalizers) {
         int rc = fin();
         if (rc) { cudaFree(p->ws); cudaFree(p->arena); return rc; }
+    }
+    if (!p->tuners.empty()) {
+        // autotune on all-zero activations and constants: the timing of TMA, tcgen05 and the CUDA-core
+        // phases does not depend on the data, and the workspace (pad channels included) stays zero
+        float* scratch = nullptr;
+        ISG_CUDA(cudaMalloc(&scratch, (size_t)max_batch * height * width * sizeof(float)));
+        int rc = 0;
+        for (auto& tune : p->tuners)
+            if ((rc = tune(scratch, nullptr))) break;
+        cudaDeviceSynchronize();
+        cudaFree(scratch);
+        if (rc) { cudaFree(p->ws); cudaFree(p->arena); return fail(rc, "autotune launch failed: %s", cudaGetErrorString(cudaGetLastError())); }
     }
     ISG_CUDA(cudaDeviceSynchronize());
     *out = p.release();
