@@ -316,8 +316,6 @@ struct FkBuilder {
         int maxN = 0;
         for (auto& st : s.stages) maxN = std::max(maxN, st.N);
         L.cols = L.n_mt * maxN;
-        const bool pipelined = s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE");   // experimental, no gain measured
-        if (pipelined) L.cols *= 2;   // two accumulators: MMAs of tile i+1 overlap the epilogue of tile i
         if (L.cols > 512 || (int)tc::tmem_cols_pow2(L.cols) > 512 / ctas) return false;
         const int a_rows = L.n_mt * 128 + (hx ? 2 * L.pitch + 2 : 0);
         const int npix = TH * TW;
@@ -344,9 +342,7 @@ struct FkBuilder {
         }
         // persistent CTAs double-buffer the whole load area: tile i+1 streams in while tile i computes
         L.lbuf_stride = off;
-        const char* nb_env = getenv("ISG_FK_NBUF");
-        const int ring = nb_env ? atoi(nb_env) : 3;
-        off *= pipelined ? ring : nlbuf;   // pipelined launches keep a ring of load buffers
+        off *= nlbuf;
         if (s.st.kind) {
             const LoadSpec& l = s.loads[s.st.load];
             const int nch = l.nchunks < 0 ? td(l.tensor).Cs / 8 : l.nchunks;
@@ -413,15 +409,13 @@ struct FkBuilder {
         const int TW = cdiv(s.qW, nx);
         const char* cap_env = getenv("ISG_FK_MAX_MT");
         const int mt_cap = cap_env ? atoi(cap_env) : 16;
-        const bool pipelined = s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE");
-        const bool tune = !getenv("ISG_FK_NO_TUNE") && !pipelined;
+        const bool tune = !getenv("ISG_FK_NO_TUNE");
         const int env_ctas = getenv("ISG_FK_CTAS") ? atoi(getenv("ISG_FK_CTAS")) : 0;
         const int env_lbuf = getenv("ISG_FK_LBUF") ? atoi(getenv("ISG_FK_LBUF")) : 0;
         const int per_mode = getenv("ISG_FK_TUNE_TOP") ? atoi(getenv("ISG_FK_TUNE_TOP")) : 3;
         std::vector<Lay> out;
         for (int mode = 0; mode < 4; ++mode) {
             const int c = mode & 1 ? 2 : 1, nb = mode & 2 ? 1 : 2;   // mode 0 = one double-buffered CTA per SM
-            if (pipelined && mode) break;
             if (!tune && mode && !(env_ctas || env_lbuf)) break;
             if (env_ctas && c != env_ctas) continue;
             if (env_lbuf && nb != env_lbuf) continue;
@@ -465,9 +459,6 @@ struct FkBuilder {
         q.n_mt = L.n_mt; q.tmem_cols = tc::tmem_cols_pow2(L.cols);
         auto magic = [](int d) -> uint32_t { return d > 1 ? (uint32_t)(((1ull << 32) + d - 1) / d) : 0u; };
         q.tw_magic = magic(L.TW); q.npix_magic = magic(L.TH * L.TW);
-        q.pipelined = (s.stages.size() == 1 && !s.st.kind && getenv("ISG_FK_PIPE")) ? 1 : 0;
-        q.acc_stride = L.cols / 2;
-        q.nbuf = getenv("ISG_FK_NBUF") ? atoi(getenv("ISG_FK_NBUF")) : 3;
         q.nlbuf = L.nlbuf;
         q.nloads = (int)s.loads.size();
         for (int i = 0; i < q.nloads; ++i) {

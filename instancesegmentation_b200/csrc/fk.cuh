@@ -81,9 +81,6 @@ struct Params {
     uint32_t tx_bytes;             // all TMA boxes of one tile
     int lbuf_stride;               // byte distance between the two load buffers (persistent double buffering)
     int total_tiles;               // batch * tiles_y * tiles_x of this launch
-    int pipelined;                 // single-stage launch: two TMEM accumulators, MMAs of tile i+1 overlap epilogue i
-    int acc_stride;                // TMEM columns between the two accumulators
-    int nbuf;                      // load buffers in the ring of a pipelined launch (2 or 3)
     int nlbuf;                     // load buffers of the generic loop: 2 = double buffered; 1 = the co-resident
                                    // CTA hides the load latency instead (two 256-thread CTAs per SM)
     int early_load;                // nlbuf == 1: the load buffer is dead once the stage-0 MMAs completed
@@ -254,6 +251,15 @@ __device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t (&r)[1
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// wait for the TMEM loads in flight; the registers they fill pass through the statement so that no use
+// of them can be scheduled before it
+__device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&r)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                   "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :
+                 : "memory");
+}
 
 // epilogue of one (M tile, 16-column chunk): raw accumulators -> shift/residual/activation -> output
 __device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const Stage& s, const uint32_t (&raw)[16],
@@ -344,20 +350,18 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
     if (item >= nitems) return;
     __syncwarp();
     tmem_ld16_nowait(lane_base + item * 16, ra);   // column of item = mt*N + cc*16 = item*16
+    tmem_ld_wait_dep(ra);
     while (true) {
+        const int nxt = item + NGROUPS;
         __syncwarp();
-        tmem_ld_wait();
-        const int n1 = item + NGROUPS;
-        if (n1 < nitems) tmem_ld16_nowait(lane_base + n1 * 16, rb);
+        if (nxt < nitems) tmem_ld16_nowait(lane_base + nxt * 16, rb);   // in flight during this item
         epi_item(smem, p, s, ra, item / ncc, item % ncc, quad, lane, b, x0, y0, boff);
-        if (n1 >= nitems) break;
+        if (nxt >= nitems) break;
+        item = nxt;
         __syncwarp();
-        tmem_ld_wait();
-        const int n2 = item + 2 * NGROUPS;
-        if (n2 < nitems) tmem_ld16_nowait(lane_base + n2 * 16, ra);
-        epi_item(smem, p, s, rb, n1 / ncc, n1 % ncc, quad, lane, b, x0, y0, boff);
-        if (n2 >= nitems) break;
-        item = n2;
+        tmem_ld_wait_dep(rb);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) ra[i] = rb[i];
     }
 }
 
@@ -424,92 +428,6 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     if (tid == 0) issue_loads(blockIdx.x, 0);
     tc::mbar_wait(&bars[4], 0);
 
-    if (p.pipelined) {
-        // single-stage launches: the MMAs of tile i+1 run while tile i is in its epilogue (two TMEM
-        // accumulators); loads run nbuf-1 tiles ahead in a ring of nbuf buffers (bars[8..8+nbuf))
-        const Stage& s0 = p.stage[0];
-        const int step = gridDim.x, nbuf = p.nbuf;
-        uint64_t* lbar = bars + 8;
-        const bool issuer = (tid & 31) == 0 && warp < n_issuers;
-        const bool store0 = s0.out_mode == OUT_STAGE && s0.store;
-        const bool buf_busy_in_epi = s0.res_on || s0.stage_in_load;   // the epilogue still needs the load buffer
-        auto issue_ring = [&](int t, int slot) {
-            const int txi = t % p.tiles_x, r1 = t / p.tiles_x;
-            const int tyi = r1 % p.tiles_y, bi = r1 / p.tiles_y;
-            tc::mbar_expect_tx(&lbar[slot], p.tx_bytes);
-            for (int i = 0; i < p.nloads; ++i) {
-                const Load& l = p.loads[i];
-                const int cx = txi * p.TW * l.step + l.dx;
-                const int cy = tyi * p.TH * l.step + l.dy + (l.folded ? bi * l.rows_per_img : 0);
-                tc::tma_load_5d(smem + l.smem_off + slot * p.lbuf_stride, maps[l.map], &lbar[slot], 0, cx, cy, l.chunk0,
-                                l.folded ? 0 : bi);
-            }
-        };
-        if (tid == 0)
-            for (int k = 1; k < nbuf; ++k)
-                if ((int)blockIdx.x + k * step < p.total_tiles) issue_ring(blockIdx.x + k * step, k);
-        tc::mbar_wait(&bars[0], 0);           // tile 0 came through the common prologue into slot 0
-        if (issuer) {
-            tc::tc_fence_after();
-            issue_mma(p, s0, tabs, smem_base, tmem_base, warp, NWARPS);
-            tc::umma_commit(&bars[2]);
-        }
-        FK_STAMP(2);
-        int it = 0, slot = 0, use0 = 0;      // use0: how often slot 0's ring barrier has completed (tile 0 used bars[0])
-        (void)use0;
-        for (int tile = blockIdx.x; tile < p.total_tiles; tile += step, ++it) {
-            const int acc = it & 1, next = tile + step;
-            const int nslot = slot + 1 == nbuf ? 0 : slot + 1;
-            const int txi = tile % p.tiles_x, r1 = tile / p.tiles_x;
-            const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
-            if (next < p.total_tiles) {
-                // tile it+1 is the ((it+1)/nbuf)-th user of its slot; slot 0's first user (tile 0) used bars[0]
-                const int uses = (it + 1) / nbuf - (nslot == 0 ? 1 : 0);
-                tc::mbar_wait(&lbar[nslot], uses & 1);
-                if (issuer) {
-                    tc::tc_fence_after();
-                    issue_mma(p, s0, tabs + nslot * TAB_N, smem_base, tmem_base + (acc ^ 1) * p.acc_stride, warp, NWARPS);
-                    tc::umma_commit(&bars[2 + (acc ^ 1)]);
-                }
-            }
-            __syncwarp();
-            tc::mbar_wait(&bars[2 + acc], (it >> 1) & 1);
-            tc::tc_fence_after();
-            const int refill = tile + nbuf * step;
-            if (!buf_busy_in_epi && tid == 0 && refill < p.total_tiles) issue_ring(refill, slot);
-            if (store0 && !s0.stage_in_load) {   // single-buffered staging: the previous store must have read it
-                if (tid == 0) tc::tma_store_wait_read();
-                __syncthreads();
-            }
-            run_epilogue<NT>(smem, p, s0, tmem_base + acc * p.acc_stride, b, txi * p.TW, tyi * p.TH, slot * p.lbuf_stride);
-            tc::fence_proxy_async();
-            tc::tc_fence_before();
-            __syncthreads();
-            if (tid == 0) {
-                if (store0) {
-                    tc::tma_store_5d(&mo0, smem + s0.stage_off + (s0.stage_in_load ? slot * p.lbuf_stride : 0), 0, txi * p.TW,
-                                     tyi * p.TH, s0.store_chunk0, b);
-                    tc::tma_store_commit();
-                }
-                if (buf_busy_in_epi && refill < p.total_tiles) {
-                    if (store0 && s0.stage_in_load) tc::tma_store_wait_read();   // the store reads from this load buffer
-                    issue_ring(refill, slot);
-                }
-            }
-            slot = nslot;
-        }
-        if (tid == 0) tc::tma_store_wait_read();
-        FK_STAMP(8);
-        if (p.prof && tid == 0) p.prof[(size_t)blockIdx.x * 16 + 15] = globaltimer_ns();
-        tc::tc_fence_before();
-        __syncthreads();
-        if (warp == 1) {
-            tc::tc_fence_after();
-            tc::tmem_dealloc(tmem_base, p.tmem_cols);
-        }
-        return;
-    }
-
     int it = 0;
     long long tprev = 0;
     const bool dbl = p.nlbuf == 2;
@@ -537,48 +455,27 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         }
         if (it == 0) FK_STAMP(3);
         FK_ACC(9);
-        if ((tid & 31) == 0 && warp < n_issuers) {
-            tc::tc_fence_after();
-            issue_mma(p, p.stage[0], tabs + buf * TAB_N, smem_base, tmem_base, warp, NWARPS);
-            tc::umma_commit(&bars[2]);
-        }
-        __syncwarp();
-        tc::mbar_wait(&bars[2], it & 1);
-        if (it == 0) FK_STAMP(4);
-        FK_ACC(10);
-        tc::tc_fence_after();
-        if (tid == 0 && !dbl && p.early_load && next < p.total_tiles) issue_loads(next, 0);
-        run_epilogue<NT>(smem, p, p.stage[0], tmem_base, b, x0, y0, boff);
-        tc::fence_proxy_async();
-        tc::tc_fence_before();
-        __syncthreads();
-        if (it == 0) FK_STAMP(5);
-        FK_ACC(11);
-        if (tid == 0 && p.stage[0].out_mode == OUT_STAGE && p.stage[0].store) {
-            tc::tma_store_5d(&mo0, smem + p.stage[0].stage_off + (p.stage[0].stage_in_load ? boff : 0), 0, x0, y0,
-                             p.stage[0].store_chunk0, b);
-            tc::tma_store_commit();
-        }
-        if (p.nstages > 1) {
+        for (int k = 0; k < p.nstages; ++k) {
+            const Stage& s = p.stage[k];
             if ((tid & 31) == 0 && warp < n_issuers) {
                 tc::tc_fence_after();
-                issue_mma(p, p.stage[1], tabs + (3 + buf) * TAB_N, smem_base, tmem_base, warp, NWARPS);
-                tc::umma_commit(&bars[3]);
+                issue_mma(p, s, tabs + (3 * k + buf) * TAB_N, smem_base, tmem_base, warp, NWARPS);
+                tc::umma_commit(&bars[2 + k]);
             }
             __syncwarp();
-            tc::mbar_wait(&bars[3], it & 1);
-            if (it == 0) FK_STAMP(6);
-            FK_ACC(12);
+            tc::mbar_wait(&bars[2 + k], it & 1);
+            if (it == 0) FK_STAMP(4 + 2 * k);
+            FK_ACC(10 + 2 * k);
             tc::tc_fence_after();
-            run_epilogue<NT>(smem, p, p.stage[1], tmem_base, b, x0, y0, boff);
+            if (k == 0 && tid == 0 && !dbl && p.early_load && next < p.total_tiles) issue_loads(next, 0);
+            run_epilogue<NT>(smem, p, s, tmem_base, b, x0, y0, boff);
             tc::fence_proxy_async();
             tc::tc_fence_before();
             __syncthreads();
-            if (it == 0) FK_STAMP(7);
-            FK_ACC(13);
-            if (tid == 0 && p.stage[1].out_mode == OUT_STAGE && p.stage[1].store) {
-                tc::tma_store_5d(&mo1, smem + p.stage[1].stage_off + (p.stage[1].stage_in_load ? boff : 0), 0, x0, y0,
-                                 p.stage[1].store_chunk0, b);
+            if (it == 0) FK_STAMP(5 + 2 * k);
+            FK_ACC(11 + 2 * k);
+            if (tid == 0 && s.out_mode == OUT_STAGE && s.store) {
+                tc::tma_store_5d(k ? &mo1 : &mo0, smem + s.stage_off + (s.stage_in_load ? boff : 0), 0, x0, y0, s.store_chunk0, b);
                 tc::tma_store_commit();
             }
         }
