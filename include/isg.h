@@ -75,6 +75,13 @@ ISG_API int isg_plan_load_weights(isg_plan* plan, const void* const* tensors_hos
  * size is accepted; it is processed in groups of max_batch. */
 ISG_API int isg_forward(isg_plan* plan, const float* x_dev, int batch, float* logits_dev, void* stream);
 
+/* the same forward from what an image decoder produces: x_u8_dev is uint8 NHWC [batch,H,W,in_channel];
+ * ToTensor + Normalize(mean, std) of the reference's data path (train_instance.py:80-85:
+ * (v / 255 - mean[c]) / std[c], fp32, IEEE division) run inside the first kernel, so a batch costs a
+ * quarter of the PCIe bytes of the fp32 tensor.  mean_host / std_host: in_channel floats on the host. */
+ISG_API int isg_forward_u8(isg_plan* plan, const uint8_t* x_u8_dev, int batch, const float* mean_host,
+                           const float* std_host, float* logits_dev, void* stream);
+
 /* number of kernels isg_forward launches per group of <= max_batch images */
 ISG_API int isg_plan_launches_per_forward(const isg_plan* plan);
 /* conv/convT multiply-accumulates per image of the reference graph (SURVEY 8d constant) */

@@ -23,6 +23,7 @@ SIGNATURES = {
     "isg_plan_workspace_bytes": (C.c_size_t, [_vp]),
     "isg_plan_load_weights": (_i, [_vp, C.POINTER(_vp), C.POINTER(_i64), _i]),
     "isg_forward": (_i, [_vp, _vp, _i, _vp, _vp]),
+    "isg_forward_u8": (_i, [_vp, _vp, _i, C.POINTER(_f), C.POINTER(_f), _vp, _vp]),
     "isg_plan_launches_per_forward": (_i, [_vp]),
     "isg_plan_macs_per_image": (_i64, [_vp]),
     "isg_plan_tap_count": (_i, [_vp]),

@@ -62,6 +62,11 @@ struct isg_plan {
     int64_t macs_per_image = 0;
     int last_n = 0;
     std::vector<int> taps;     // tensor ids
+    // isg_forward_u8: uint8 NHWC source of the running forward (null: fp32 NCHW input) and its
+    // normalisation; the bf16 plan's first kernel reads it directly, the fp32 plan converts into u8_scratch
+    const uint8_t* u8_src = nullptr;
+    float u8_mean[8] = {0}, u8_std[8] = {1, 1, 1, 1, 1, 1, 1, 1};
+    float* u8_scratch = nullptr;
     bool use_tc = false;       // bf16 mode: GEMM-shaped convs on tcgen05 (ISG_NO_TC=1 disables)
     std::vector<std::function<int()>> finalizers;  // run once after the workspace is allocated (tensor maps)
     // run once after the finalizers: each fused launch times its candidate tilings on the device

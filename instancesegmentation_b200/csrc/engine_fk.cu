@@ -82,6 +82,63 @@ prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, in
     fk::st_global_16(d + 8, make_uint4(0, 0, 0, 0));
 }
 
+// the same from uint8 NHWC [B,H,W,3] (isg_forward_u8): ToTensor + Normalize of the reference's data
+// path (train_instance.py:80-85) in fp32 with IEEE division, then exactly prep_kernel<3>.
+// One thread = one 4x4 patch = four 12-byte rows.
+struct NormU8 { float mean[3], std[3]; };
+__global__ void __launch_bounds__(128)
+prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, bf16* __restrict__ init,
+               int Cs_init, int total, NormU8 nm) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int W4 = W >> 2, H4 = H >> 2;
+    const int x4 = i % W4, y4 = (i / W4) % H4, b = i / (W4 * H4);
+    float v[3][4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(x + (((size_t)b * H + 4 * y4 + r) * W + 4 * x4) * 3);
+        const uint32_t w[3] = {__ldg(src), __ldg(src + 1), __ldg(src + 2)};
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+            const float u = (float)((w[k >> 2] >> (8 * (k & 3))) & 0xffu);
+            v[k % 3][r][k / 3] = __fdiv_rn(__fdiv_rn(u, 255.f) - nm.mean[k % 3], nm.std[k % 3]);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int bb = 0; bb < 2; ++bb) {
+            float f[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) f[k] = 0.f;
+#pragma unroll
+            for (int ry = 0; ry < 2; ++ry)
+#pragma unroll
+                for (int rx = 0; rx < 2; ++rx)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) f[(ry * 2 + rx) * 3 + c] = v[c][2 * a + ry][2 * bb + rx];
+            bf16* d = x2 + (((size_t)b * (H >> 1) + 2 * y4 + a) * (W >> 1) + 2 * x4 + bb) * Cs2;
+            fk::st_global_16(d, make_uint4(fk::pack_bf16(f[0], f[1]), fk::pack_bf16(f[2], f[3]),
+                                           fk::pack_bf16(f[4], f[5]), fk::pack_bf16(f[6], f[7])));
+            fk::st_global_16(d + 8, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
+                                               fk::pack_bf16(f[12], f[13]), fk::pack_bf16(f[14], f[15])));
+        }
+    float m[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float mx = v[c][0][0];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) mx = fmaxf(mx, v[c][r][q]);
+        m[c] = mx;
+    }
+    bf16* d = init + (((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16;
+    fk::st_global_16(d, make_uint4(fk::pack_bf16(m[0], m[1]), fk::pack_bf16(m[2], 0.f), 0, 0));
+    fk::st_global_16(d + 8, make_uint4(0, 0, 0, 0));
+}
+
 // generic (any Cin) variant: one thread = one (patch, channel)
 __global__ void __launch_bounds__(128)
 prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __restrict__ x2, int Cs2,
@@ -663,6 +720,12 @@ struct FkBuilder {
         op.launch = [=](int n, const float* x, float*, cudaStream_t st) {
             bf16* px2 = reinterpret_cast<bf16*>(P->ws + x2.off);
             bf16* pin = reinterpret_cast<bf16*>(P->ws + init.off);
+            if (cin == 3 && P->u8_src) {
+                NormU8 nm;
+                for (int c = 0; c < 3; ++c) { nm.mean[c] = P->u8_mean[c]; nm.std[c] = P->u8_std[c]; }
+                const int total = n * (H / 4) * (W / 4);
+                return launch_pdl(prep_u8_kernel, cdiv(total, 128), 128, st, P->u8_src, H, W, px2, x2.Cs, pin, init.Cs, total, nm);
+            }
             if (cin == 3) {
                 const int total = n * (H / 4) * (W / 4);
                 return launch_pdl(prep_kernel<3>, cdiv(total, 128), 128, st, x, H, W, px2, x2.Cs, pin, init.Cs, total);

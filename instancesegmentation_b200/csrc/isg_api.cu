@@ -98,6 +98,7 @@ int isg_plan_destroy(isg_plan* plan) {
     cudaSetDevice(plan->device);
     cudaFree(plan->ws);
     cudaFree(plan->arena);
+    cudaFree(plan->u8_scratch);
     delete plan;
     return ISG_OK;
 }
@@ -127,6 +128,58 @@ int isg_plan_load_weights(isg_plan* plan, const void* const* tensors_host, const
     return ISG_OK;
 }
 
+namespace {
+
+// uint8 NHWC -> fp32 NCHW with ToTensor + Normalize (generic path of isg_forward_u8)
+__global__ void __launch_bounds__(256) u8_to_f32_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, int C,
+                                                        int HW, int total, const float* __restrict__ mean_std) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;   // (b, pixel)
+    if (i >= total) return;
+    const int b = i / HW, pix = i - b * HW;
+    for (int c = 0; c < C; ++c) {
+        const float v = __fdiv_rn((float)src[(size_t)i * C + c], 255.f);
+        dst[((size_t)b * C + c) * HW + pix] = __fdiv_rn(v - mean_std[c], mean_std[8 + c]);
+    }
+}
+
+// one group of <= max_batch images through the plan's launches
+int run_group(isg_plan* plan, const float* x, const uint8_t* u8, int n, float* logits, cudaStream_t st) {
+    static const bool op_timing = getenv("ISG_OP_TIMING") != nullptr;   // debug: per-op device time
+    std::vector<cudaEvent_t> evs;
+    if (op_timing) {
+        evs.resize(plan->ops.size() + 1);
+        for (auto& e : evs) cudaEventCreate(&e);
+        cudaEventRecord(evs[0], st);
+    }
+    plan->u8_src = u8;
+    size_t oi = 0;
+    for (auto& op : plan->ops) {
+        cudaError_t e = op.launch(n, x, logits, st);
+        if (e != cudaSuccess) {
+            plan->u8_src = nullptr;
+            return fail(ISG_ERR_CUDA, "launch of %s failed: %s", op.name.c_str(), cudaGetErrorString(e));
+        }
+        if (op_timing) cudaEventRecord(evs[++oi], st);
+    }
+    plan->u8_src = nullptr;
+    if (op_timing) {
+        cudaStreamSynchronize(st);
+        float tot = 0;
+        for (size_t i = 0; i < plan->ops.size(); ++i) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, evs[i], evs[i + 1]);
+            tot += ms;
+            fprintf(stderr, "optime %7.1f us  %s\n", ms * 1e3, plan->ops[i].name.c_str());
+        }
+        fprintf(stderr, "optime total %.1f us\n", tot * 1e3);
+        for (auto& e : evs) cudaEventDestroy(e);
+    }
+    plan->last_n = n;
+    return ISG_OK;
+}
+
+}  // namespace
+
 int isg_forward(isg_plan* plan, const float* x_dev, int batch, float* logits_dev, void* stream) {
     if (!plan || !x_dev || !logits_dev) return fail(ISG_ERR_ARG, "isg_forward: null argument");
     if (!plan->weights_loaded) return fail(ISG_ERR_STATE, "isg_forward before isg_plan_load_weights");
@@ -135,33 +188,49 @@ int isg_forward(isg_plan* plan, const float* x_dev, int batch, float* logits_dev
     const size_t in_img = (size_t)plan->cin * plan->H * plan->W, out_img = (size_t)plan->H * plan->W;
     for (int b0 = 0; b0 < batch; b0 += plan->max_batch) {
         const int n = batch - b0 < plan->max_batch ? batch - b0 : plan->max_batch;
-        static const bool op_timing = getenv("ISG_OP_TIMING") != nullptr;   // debug: per-op device time
-        std::vector<cudaEvent_t> evs;
-        if (op_timing) {
-            evs.resize(plan->ops.size() + 1);
-            for (auto& e : evs) cudaEventCreate(&e);
-            cudaEventRecord(evs[0], st);
+        int rc = run_group(plan, x_dev + b0 * in_img, nullptr, n, logits_dev + b0 * out_img, st);
+        if (rc) return rc;
+    }
+    return ISG_OK;
+}
+
+int isg_forward_u8(isg_plan* plan, const uint8_t* x_u8_dev, int batch, const float* mean_host, const float* std_host,
+                   float* logits_dev, void* stream) {
+    if (!plan || !x_u8_dev || !logits_dev || !mean_host || !std_host)
+        return fail(ISG_ERR_ARG, "isg_forward_u8: null argument");
+    if (!plan->weights_loaded) return fail(ISG_ERR_STATE, "isg_forward_u8 before isg_plan_load_weights");
+    if (batch < 0) return fail(ISG_ERR_ARG, "negative batch");
+    if (plan->cin > 8) return fail(ISG_ERR_ARG, "isg_forward_u8: at most 8 input channels");
+    for (int c = 0; c < plan->cin; ++c) {
+        if (!(std_host[c] != 0.f)) return fail(ISG_ERR_ARG, "isg_forward_u8: std[%d] is zero", c);
+        plan->u8_mean[c] = mean_host[c];
+        plan->u8_std[c] = std_host[c];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t in_img = (size_t)plan->cin * plan->H * plan->W, out_img = (size_t)plan->H * plan->W;
+    const bool direct = plan->use_tc && plan->cin == 3;   // the bf16 plan's first kernel reads uint8 itself
+    if (!direct && !plan->u8_scratch) {
+        ISG_CUDA(cudaMalloc(&plan->u8_scratch, ((size_t)plan->max_batch * in_img + 16) * sizeof(float)));
+    }
+    for (int b0 = 0; b0 < batch; b0 += plan->max_batch) {
+        const int n = batch - b0 < plan->max_batch ? batch - b0 : plan->max_batch;
+        const uint8_t* src = x_u8_dev + b0 * in_img;
+        int rc;
+        if (direct) {
+            rc = run_group(plan, nullptr, src, n, logits_dev + b0 * out_img, st);
+        } else {
+            // mean / std ride at the end of the scratch buffer (stream ordered)
+            float ms[16];
+            for (int c = 0; c < 8; ++c) { ms[c] = plan->u8_mean[c]; ms[8 + c] = plan->u8_std[c]; }
+            float* msd = plan->u8_scratch + (size_t)plan->max_batch * in_img;
+            ISG_CUDA(cudaMemcpyAsync(msd, ms, sizeof ms, cudaMemcpyHostToDevice, st));
+            const int total = n * plan->H * plan->W;
+            u8_to_f32_kernel<<<(total + 255) / 256, 256, 0, st>>>(src, plan->u8_scratch, plan->cin, plan->H * plan->W,
+                                                                  total, msd);
+            ISG_CUDA(cudaGetLastError());
+            rc = run_group(plan, plan->u8_scratch, nullptr, n, logits_dev + b0 * out_img, st);
         }
-        size_t oi = 0;
-        for (auto& op : plan->ops) {
-            cudaError_t e = op.launch(n, x_dev + b0 * in_img, logits_dev + b0 * out_img, st);
-            if (e != cudaSuccess)
-                return fail(ISG_ERR_CUDA, "launch of %s failed: %s", op.name.c_str(), cudaGetErrorString(e));
-            if (op_timing) cudaEventRecord(evs[++oi], st);
-        }
-        if (op_timing) {
-            cudaStreamSynchronize(st);
-            float tot = 0;
-            for (size_t i = 0; i < plan->ops.size(); ++i) {
-                float ms = 0;
-                cudaEventElapsedTime(&ms, evs[i], evs[i + 1]);
-                tot += ms;
-                fprintf(stderr, "optime %7.1f us  %s\n", ms * 1e3, plan->ops[i].name.c_str());
-            }
-            fprintf(stderr, "optime total %.1f us\n", tot * 1e3);
-            for (auto& e : evs) cudaEventDestroy(e);
-        }
-        plan->last_n = n;
+        if (rc) return rc;
     }
     return ISG_OK;
 }

@@ -70,6 +70,26 @@ class SegmentEngine:
             _lib.check(self._l.isg_forward(self._h, x.data_ptr(), B, out.data_ptr(), st))
         return out
 
+    def forward_u8(self, x, mean, std, out=None):
+        """``x``: CUDA uint8 [B,H,W,C] (what an image decoder produces); ToTensor + Normalize(mean, std)
+        of the reference's data path (train_instance.py:80-85) run inside the first kernel."""
+        if not (x.is_cuda and x.dtype == torch.uint8 and x.dim() == 4):
+            raise TypeError("SegmentEngine.forward_u8: x must be a CUDA uint8 [B,H,W,C] tensor")
+        if tuple(x.shape[1:]) != (self.H, self.W, self.in_channel):
+            raise ValueError(f"plan is for [B,{self.H},{self.W},{self.in_channel}], got {tuple(x.shape)}")
+        if len(mean) != self.in_channel or len(std) != self.in_channel:
+            raise ValueError("mean / std need one value per input channel")
+        x = x.contiguous()
+        B = x.shape[0]
+        if out is None:
+            out = torch.empty((B, 1, self.H, self.W), device=x.device, dtype=torch.float32)
+        m = (C.c_float * self.in_channel)(*[float(v) for v in mean])
+        s = (C.c_float * self.in_channel)(*[float(v) for v in std])
+        with torch.cuda.device(x.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(self._l.isg_forward_u8(self._h, x.data_ptr(), B, m, s, out.data_ptr(), st))
+        return out
+
     # ---- introspection ----
     @property
     def workspace_bytes(self):

@@ -264,8 +264,19 @@ class Segment(nn.Module):
         t = self.bottle5_2(self.bottle5_1up(t, keep1))
         return self.bottle6_2(self.bottle6_1(t))
 
+    def forward_u8(self, x, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5)):
+        """Eval-mode forward from uint8 NHWC images [B,H,W,C] on the device: the reference's
+        ``ToTensor`` + ``Normalize(mean, std)`` (train_instance.py:80-85) run inside the engine's first
+        kernel.  Equals ``forward(((x / 255 - mean) / std).permute(0, 3, 1, 2))``."""
+        if x.dim() != 4 or x.shape[3] != self.in_channel:
+            raise ValueError(f"Segment: expected uint8 [B,H,W,{self.in_channel}], got {tuple(x.shape)}")
+        self.check_size(x.shape[1], x.shape[2])
+        if not x.is_cuda:
+            raise RuntimeError("Segment.forward_u8 runs only in the sm_100a CUDA engine (libisg.so)")
+        eng = self._engine_for(x.device, x.shape[0], x.shape[1], x.shape[2])
+        return eng.forward_u8(x, mean, std)
+
     def _forward_engine(self, x):
-        from .engine import SegmentEngine
         if not x.is_cuda:
             raise RuntimeError(
                 "Segment: eval-mode forward runs only in the sm_100a CUDA engine (libisg.so); "
@@ -273,16 +284,20 @@ class Segment(nn.Module):
         if x.dtype != torch.float32:
             raise TypeError(f"Segment: input must be float32, got {x.dtype}")
         B, _, H, W = x.shape
-        key = (x.device.index, H, W, self.precision, min(self.max_batch, max(B, 1)))
+        return self._engine_for(x.device, B, H, W).forward(x)
+
+    def _engine_for(self, device, B, H, W):
+        from .engine import SegmentEngine
+        key = (device.index, H, W, self.precision, min(self.max_batch, max(B, 1)))
         eng = self._engines.get(key)
         if eng is None or eng.max_batch < min(B, self.max_batch):
-            eng = SegmentEngine(x.device, self.in_channel, H, W,
+            eng = SegmentEngine(device, self.in_channel, H, W,
                                 min(self.max_batch, max(B, 1)), self.precision)
             self._engines[key] = eng
         if eng.weights_epoch != self._weights_epoch:
             eng.load_state_dict(self.state_dict())
             eng.weights_epoch = self._weights_epoch
-        return eng.forward(x)
+        return eng
 
     def train_batch(self, x, heatmaps=None):
         """sigmoid(forward(cat([x, heatmaps], 1))) -- segment.py:531-534; ``heatmaps``

@@ -165,3 +165,90 @@ def test_bf16_mode_error_is_reported_and_bounded(golden_state):
           f"{theirs.max():.3e} mean {theirs.mean():.3e}")
     assert float(ours.mean()) <= max(float(theirs.mean()), 0.1)
     assert float(ours.max()) <= max(float(theirs.max()), 1.5)
+
+
+def _u8_batch(B, H, W, seed):
+    rng = np.random.default_rng(seed)
+    return torch.from_numpy(rng.integers(0, 256, size=(B, H, W, 3), dtype=np.uint8))
+
+
+def _normalize_like_reference(u8, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5)):
+    """ToTensor + Normalize of train_instance.py:80-85 on the host in fp32."""
+    x = u8.permute(0, 3, 1, 2).float().div(255.0)
+    m = torch.tensor(mean).view(1, 3, 1, 1)
+    s = torch.tensor(std).view(1, 3, 1, 1)
+    return x.sub(m).div(s).contiguous()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_forward_u8_equals_forward_of_normalized_input(golden_state, precision):
+    """isg_forward_u8 (uint8 NHWC in, Normalize on the device) must give exactly the logits of
+    isg_forward on the host-normalised fp32 tensor: the normalisation is the same IEEE sequence."""
+    u8 = _u8_batch(3, 64, 96, seed=5)
+    x = _normalize_like_reference(u8, (0.4, 0.5, 0.6), (0.5, 0.25, 0.2))
+    m = _model(golden_state, precision=precision)
+    with torch.no_grad():
+        want = m(x.cuda()).cpu()
+        got = m.forward_u8(u8.cuda(), (0.4, 0.5, 0.6), (0.5, 0.25, 0.2)).cpu()
+    assert torch.equal(got, want), float((got - want).abs().max())
+    if precision == "fp32":
+        _fp32_check(golden_state, x, got, "u8 64x96")
+
+
+_MODE_SCRIPT = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, sys.argv[1])
+from instancesegmentation_b200 import Segment, synth
+z = np.load(sys.argv[2])
+m = Segment(3); m.load_state_dict({k: torch.from_numpy(z[k]) for k in z.files}); m.precision, m.max_batch = "bf16", 4
+m = m.cuda().eval()
+x = torch.from_numpy(synth.batch(4, 128, 192, seed=3)).cuda()
+with torch.no_grad():
+    y = m(x)
+torch.cuda.synchronize()
+np.save(sys.argv[3], y.cpu().numpy())
+"""
+
+
+def test_bf16_launch_variants_are_bitwise_identical(tmp_path):
+    """Every way the autotuner may run a fused launch (tile, CTAs per SM, load buffering) computes each
+    pixel with the same instruction sequence: logits must not depend on the choice."""
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "run.py"
+    script.write_text(_MODE_SCRIPT)
+    outs = []
+    for i, env in enumerate([{"ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "1"},
+                             {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "2"}, {"ISG_FK_CTAS": "1", "ISG_FK_LBUF": "1"}]):
+        out = tmp_path / f"y{i}.npy"
+        e = dict(os.environ, **env)
+        subprocess.run([sys.executable, str(script), root, os.path.join(GOLDEN, "segment3_state.npz"), str(out)],
+                       check=True, env=e, timeout=600)
+        outs.append(np.load(out))
+    for i in range(1, len(outs)):
+        assert np.array_equal(outs[0], outs[i]), (i, float(np.abs(outs[0] - outs[i]).max()))
+
+
+def test_pipeline_matches_direct_calls(golden_state):
+    """Three-stream serving pipeline (fp32 and uint8 batches): same masks / stats as plain calls."""
+    from instancesegmentation_b200.decode import decode_masks
+    from instancesegmentation_b200.pipeline import Pipeline, identity_boxes
+    B, H, W = 4, 64, 64
+    m = _model(golden_state, precision="bf16", max_batch=B)
+    pipe = Pipeline(m, identity_boxes(B, H, W), depth=2)
+    batches = [_u8_batch(B, H, W, seed=s).pin_memory() for s in range(3)]
+    batches += [_normalize_like_reference(b).pin_memory() for b in batches[:2]]
+    outs = [(torch.empty(B * H * W, dtype=torch.uint8).pin_memory(), torch.empty(B, dtype=torch.int32).pin_memory(),
+             torch.empty((B, 4), dtype=torch.int32).pin_memory()) for _ in batches]
+    for hb, (mh, ah, bh) in zip(batches, outs):
+        pipe.submit(hb, mh, (ah, bh))
+    pipe.finish()
+    torch.cuda.synchronize()
+    for hb, (mh, ah, bh) in zip(batches, outs):
+        with torch.no_grad():
+            logits = m.forward_u8(hb.cuda()) if hb.dtype == torch.uint8 else m(hb.cuda())
+            r = decode_masks(logits)
+        assert torch.equal(mh, r.masks.cpu()[:B * H * W])
+        assert torch.equal(ah, r.area.cpu()) and torch.equal(bh, r.bbox.cpu())
+    # uint8 and host-normalised fp32 batches of the same images agree
+    assert torch.equal(outs[0][0], outs[3][0]) and torch.equal(outs[1][0], outs[4][0])
