@@ -1,8 +1,9 @@
 """Inference CLI with the reference's call surface (reference infer.py:12-36): flags
 ``-i/--test-image-dir``, ``-o/--output-dir``, ``--continue-test`` and ``path_decompose``.
 The reference's loop body stops after ``path_decompose``; here it is completed: load ->
-resize to the network size -> Normalize(0.5, 0.5) (train_instance.py:80-85) -> Segment
-forward (libisg) -> mask decode back to the source resolution (libisg) -> ``<name>.png``.
+resize to the network size -> uint8 NHWC batch to the device -> ToTensor + Normalize(0.5, 0.5)
+(train_instance.py:80-85) inside the first kernel -> Segment forward (libisg) -> mask decode back to
+the source resolution (libisg) -> ``<name>.png``.
 """
 import argparse
 import glob
@@ -65,11 +66,11 @@ def run(args):
             if bgr is None:
                 raise IOError(f"cannot read {path}")
             boxes.append((0, 0, bgr.shape[1], bgr.shape[0]))
-            rgb = cv2.cvtColor(cv2.resize(bgr, (S, S)), cv2.COLOR_BGR2RGB)
-            imgs.append((rgb.transpose(2, 0, 1).astype(np.float32) / 255.0 - 0.5) / 0.5)
-        x = torch.from_numpy(np.stack(imgs)).pin_memory().to(dev, non_blocking=True)
+            imgs.append(cv2.cvtColor(cv2.resize(bgr, (S, S)), cv2.COLOR_BGR2RGB))
+        x = torch.from_numpy(np.stack(imgs)).pin_memory().to(dev, non_blocking=True)   # uint8 [B,S,S,3]
         with torch.no_grad():
-            res = decode_masks(model(x), np.array(boxes, np.int32), want_soft=args.soft)
+            res = decode_masks(model.forward_u8(x, (0.5, 0.5, 0.5), (0.5, 0.5, 0.5)), np.array(boxes, np.int32),
+                               want_soft=args.soft)
         for n, (_, dst) in enumerate(chunk):
             cv2.imwrite(dst, res.mask(n).cpu().numpy() * 255)
             if args.soft:
