@@ -3,6 +3,7 @@
 // and the per-image id map.  Memory-bound by design: coalesced 16-byte logit loads, 4-byte
 // mask stores, one atomic set per CTA.  Semantics: DESIGN.md section 3; sigmoid =
 // model/segment.py:534, soft byte = train_instance.py:398-399.
+#include <algorithm>
 #include <climits>
 #include <cmath>
 
@@ -11,7 +12,7 @@
 namespace isg {
 namespace {
 
-constexpr int DEC_THREADS = 256, DEC_VEC = 8, DEC_ITERS = 4, DEC_PPB = DEC_THREADS * DEC_VEC * DEC_ITERS;
+constexpr int DEC_THREADS = 256, DEC_VEC = 8, DEC_ITERS = 2, DEC_PPB = DEC_THREADS * DEC_VEC * DEC_ITERS;
 constexpr int DEC_MAX_INST = 65536;
 
 // Per-instance accumulators of the launch in flight: {area, enc(xmin), enc(ymin), xmax+1, ymax+1}
@@ -115,24 +116,94 @@ __device__ __forceinline__ void decode_run(const TL* __restrict__ L, int h, int 
     }
 }
 
-// One CTA = DEC_PPB consecutive pixels of one instance's flat hk*wk mask; one thread-iteration =
-// 8 consecutive pixels: two 16-byte logit loads in, one 8-byte mask store out.
+// ---- lean path: identity size, fp32 logits, 0/1 masks only, rows and pointers 8-pixel aligned ----
+// exact decision of 8 pixels (specification sequence), out of line: taken only near the boundary
+__device__ __noinline__ unsigned exact_m8(float4 a, float4 b, float thr) {
+    const float lv[DEC_VEC] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    unsigned m8 = 0;
+#pragma unroll
+    for (int e = 0; e < DEC_VEC; ++e) m8 |= (exact_sigmoid(lv[e]) > thr ? 1u : 0u) << e;
+    return m8;
+}
+
+// 8 pixels of one row: decide on the logit (sigmoid is monotone; `margin` in logit units covers the
+// rounding of the exact sequence and of thr_logit), keep bits, update the statistics once
+__device__ __forceinline__ void lean_item(const float4& p0, const float4& p1, int idx, int oy, int ox, float thr,
+                                          float thr_logit, float margin, uint8_t* dst, DecAcc& A) {
+    const float lv[DEC_VEC] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+    unsigned m8 = 0;
+    float near = 3.0e38f;
+#pragma unroll
+    for (int e = 0; e < DEC_VEC; ++e) {
+        const float d = lv[e] - thr_logit;
+        m8 |= (d > 0.f ? 1u : 0u) << e;
+        near = fminf(near, fabsf(d));     // NaN logits drop out here and give 0 above, as the exact sequence does
+    }
+    if (near <= margin) m8 = exact_m8(p0, p1, thr);
+    if (m8) {
+        A.cnt += __popc(m8);
+        A.xmin = min(A.xmin, ox + __ffs(m8) - 1); A.xmax = max(A.xmax, ox + 31 - __clz(m8));
+        A.ymin = min(A.ymin, oy); A.ymax = max(A.ymax, oy);
+    }
+    const unsigned lo = ((m8 & 0xfu) * 0x00204081u) & 0x01010101u, hi = ((m8 >> 4) * 0x00204081u) & 0x01010101u;
+    __stcs(reinterpret_cast<uint2*>(dst + idx), make_uint2(lo, hi));
+}
+
+__device__ __forceinline__ void decode_lean(const float* __restrict__ L, int wk, int npix, int ngroups, float thr,
+                                            float thr_logit, float margin, uint8_t* dst, DecAcc& A) {
+    static_assert(DEC_ITERS == 2, "lean path is written for two items per group");
+    constexpr int HALF = DEC_THREADS * DEC_VEC;
+    int q = blockIdx.x;
+    int idx = q * DEC_PPB + threadIdx.x * DEC_VEC;
+    // (row, column) of the thread's item follow the two strides of its walk without further divisions
+    int oy = idx / wk, ox = idx - oy * wk;
+    const int dq1 = HALF / wk, dr1 = HALF - dq1 * wk;
+    const int step2 = (int)gridDim.x * DEC_PPB - HALF;
+    const int dq2 = step2 / wk, dr2 = step2 - dq2 * wk;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 c0 = z4, c1 = z4, c2 = z4, c3 = z4, n0 = z4, n1 = z4, n2 = z4, n3 = z4;
+    if (idx < npix) { c0 = __ldcs(reinterpret_cast<const float4*>(L + idx)); c1 = __ldcs(reinterpret_cast<const float4*>(L + idx) + 1); }
+    if (idx + HALF < npix) { c2 = __ldcs(reinterpret_cast<const float4*>(L + idx + HALF)); c3 = __ldcs(reinterpret_cast<const float4*>(L + idx + HALF) + 1); }
+    while (true) {
+        const int qn = q + gridDim.x;
+        const bool more = qn < ngroups;
+        const int idn = qn * DEC_PPB + threadIdx.x * DEC_VEC;
+        if (more) {   // the next group's loads are in flight while this one is decided
+            if (idn < npix) { n0 = __ldcs(reinterpret_cast<const float4*>(L + idn)); n1 = __ldcs(reinterpret_cast<const float4*>(L + idn) + 1); }
+            if (idn + HALF < npix) { n2 = __ldcs(reinterpret_cast<const float4*>(L + idn + HALF)); n3 = __ldcs(reinterpret_cast<const float4*>(L + idn + HALF) + 1); }
+        }
+        if (idx < npix) lean_item(c0, c1, idx, oy, ox, thr, thr_logit, margin, dst, A);
+        ox += dr1; oy += dq1;
+        if (ox >= wk) { ox -= wk; ++oy; }
+        if (idx + HALF < npix) lean_item(c2, c3, idx + HALF, oy, ox, thr, thr_logit, margin, dst, A);
+        if (!more) break;
+        ox += dr2; oy += dq2;
+        if (ox >= wk) { ox -= wk; ++oy; }
+        q = qn; idx = idn;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    }
+}
+
+// gridDim.x CTAs share one instance's flat hk*wk mask in groups of DEC_PPB consecutive pixels
+// (group q = blockIdx.x, blockIdx.x + gridDim.x, ...); one thread-iteration = 8 consecutive pixels:
+// two 16-byte logit loads in, one 8-byte mask store out.  The loads of the next group are in flight
+// while the current one is decided.
 template <typename TL, bool SOFT>
 __global__ void __launch_bounds__(DEC_THREADS)
 decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restrict__ boxes,
-              const int64_t* __restrict__ mask_off, float thr, float thr_logit, int use_logit_cmp,
+              const int64_t* __restrict__ mask_off, float thr, float thr_logit, float margin, int use_logit_cmp,
               uint8_t* __restrict__ masks, uint8_t* __restrict__ soft, int32_t* __restrict__ area,
               int32_t* __restrict__ bbox) {
     const int n = blockIdx.y;
     const int4 bx = __ldg(reinterpret_cast<const int4*>(boxes) + n);
     const int wk = bx.z, hk = bx.w;
     const int npix = wk * hk;
-    const int start = blockIdx.x * DEC_PPB;
     if (npix <= 0 && blockIdx.x == 0 && threadIdx.x == 0) {   // degenerate box: empty result
         area[n] = 0;
         bbox[4 * n] = bbox[4 * n + 1] = bbox[4 * n + 2] = bbox[4 * n + 3] = 0;
     }
-    if (start >= npix) return;
+    const int ngroups = (npix + DEC_PPB - 1) / DEC_PPB;
+    if ((int)blockIdx.x >= ngroups) return;
     const TL* L = logits + (size_t)n * h * w;
     const int64_t moff = mask_off[n];
     uint8_t* dst = masks + moff;
@@ -143,34 +214,50 @@ decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __rest
     const float sy = __fdiv_rn((float)h, (float)hk), sx = __fdiv_rn((float)w, (float)wk);
     DecAcc A = {0, INT_MAX, INT_MAX, -1, -1};
     const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (identity) {
-        // all loads of the thread are in flight before the first is consumed
-        float4 pre[DEC_ITERS][2];
+    if (!SOFT && sizeof(TL) == 4 && vec_in && vec_out && use_logit_cmp && (wk & (DEC_VEC - 1)) == 0) {
+        decode_lean(reinterpret_cast<const float*>(L), wk, npix, ngroups, thr, thr_logit, margin, dst, A);
+    } else if (identity) {
+        float4 cur[DEC_ITERS][2], nxt[DEC_ITERS][2];
+        auto load = [&](float4 (&buf)[DEC_ITERS][2], int q) {
 #pragma unroll
-        for (int it = 0; it < DEC_ITERS; ++it) {
-            const int idx = start + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
-            pre[it][0] = z4; pre[it][1] = z4;
-            if (vec_in && idx + DEC_VEC <= npix) {
-                pre[it][0] = __ldcs(reinterpret_cast<const float4*>(L + idx));
-                pre[it][1] = __ldcs(reinterpret_cast<const float4*>(L + idx) + 1);
+            for (int it = 0; it < DEC_ITERS; ++it) {
+                const int idx = q * DEC_PPB + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
+                buf[it][0] = z4; buf[it][1] = z4;
+                if (vec_in && idx + DEC_VEC <= npix) {
+                    buf[it][0] = __ldcs(reinterpret_cast<const float4*>(L + idx));
+                    buf[it][1] = __ldcs(reinterpret_cast<const float4*>(L + idx) + 1);
+                }
             }
-        }
+        };
+        int q = blockIdx.x;
+        load(cur, q);
+        while (true) {
+            const int qn = q + gridDim.x;
+            const bool more = qn < ngroups;
+            if (more) load(nxt, qn);
 #pragma unroll
-        for (int it = 0; it < DEC_ITERS; ++it) {
-            const int idx = start + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
-            if (idx < npix) {
-                const int nv = min(DEC_VEC, npix - idx);
-                decode_run<TL, SOFT, true>(L, h, w, wk, hk, npix, idx, nv, vec_in && nv == DEC_VEC, pre[it][0], pre[it][1],
-                                           thr, thr_logit, use_logit_cmp, sy, sx, vec_out, dst, sdst, A);
+            for (int it = 0; it < DEC_ITERS; ++it) {
+                const int idx = q * DEC_PPB + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
+                if (idx < npix) {
+                    const int nv = min(DEC_VEC, npix - idx);
+                    decode_run<TL, SOFT, true>(L, h, w, wk, hk, npix, idx, nv, vec_in && nv == DEC_VEC, cur[it][0], cur[it][1],
+                                               thr, thr_logit, use_logit_cmp, sy, sx, vec_out, dst, sdst, A);
+                }
             }
+            if (!more) break;
+            q = qn;
+#pragma unroll
+            for (int it = 0; it < DEC_ITERS; ++it) { cur[it][0] = nxt[it][0]; cur[it][1] = nxt[it][1]; }
         }
     } else {
+        for (int q = blockIdx.x; q < ngroups; q += gridDim.x) {
 #pragma unroll 1
-        for (int it = 0; it < DEC_ITERS; ++it) {
-            const int idx = start + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
-            if (idx >= npix) break;
-            decode_run<TL, SOFT, false>(L, h, w, wk, hk, npix, idx, min(DEC_VEC, npix - idx), false, z4, z4, thr, thr_logit,
-                                        use_logit_cmp, sy, sx, vec_out, dst, sdst, A);
+            for (int it = 0; it < DEC_ITERS; ++it) {
+                const int idx = q * DEC_PPB + (it * DEC_THREADS + threadIdx.x) * DEC_VEC;
+                if (idx >= npix) break;
+                decode_run<TL, SOFT, false>(L, h, w, wk, hk, npix, idx, min(DEC_VEC, npix - idx), false, z4, z4, thr,
+                                            thr_logit, use_logit_cmp, sy, sx, vec_out, dst, sdst, A);
+            }
         }
     }
     int cnt = A.cnt, xmin = A.xmin, ymin = A.ymin, xmax = A.xmax, ymax = A.ymax;
@@ -195,7 +282,7 @@ decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __rest
             atomicMax(acc + 3, xmax + 1); atomicMax(acc + 4, ymax + 1);
         }
         __threadfence();
-        const unsigned nblk = (unsigned)((npix + DEC_PPB - 1) / DEC_PPB);
+        const unsigned nblk = (unsigned)min((int)gridDim.x, ngroups);   // CTAs of this instance that take part
         if (atomicAdd(&g_dec_ticket[n], 1u) == nblk - 1) {
             __threadfence();
             const int a = atomicExch(acc, 0);
@@ -290,10 +377,33 @@ int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int h, int w
     const double t = threshold;
     const int use_logit_cmp = (t > 1e-3 && t < 1.0 - 1e-3) ? 1 : 0;
     const float thr_logit = use_logit_cmp ? (float)log(t / (1.0 - t)) : 0.f;
-    dim3 grid(cdiv(max_wk * max_hk, DEC_PPB), n_inst);
+    // lean path: |logit - thr_logit| beyond this is decided on the logit.  The exact sequence is within
+    // 3e-7 of the true sigmoid (Cephes expf, two roundings), i.e. 3e-7 / (t (1 - t)) in logit units, and
+    // thr_logit carries one rounding (<= 5e-7): six-fold cover
+    const float margin = use_logit_cmp ? (float)(2e-6 / (t * (1.0 - t)) + 2e-6) : 0.f;
+    // one resident wave: as many CTAs as fit on the device at once, shared evenly by the instances
+    // (more would queue behind the first wave; env ISG_DEC_SLOTS overrides)
+    static int slots_tab[4] = {0, 0, 0, 0};
+    int& slots = slots_tab[(logits_bf16 ? 2 : 0) + (soft_dev ? 1 : 0)];
+    if (!slots) {
+        int dev = 0, sms = 148, occ = 2;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (logits_bf16) {
+            if (soft_dev) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel<bf16, true>, DEC_THREADS, 0);
+            else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel<bf16, false>, DEC_THREADS, 0);
+        } else {
+            if (soft_dev) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel<float, true>, DEC_THREADS, 0);
+            else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_kernel<float, false>, DEC_THREADS, 0);
+        }
+        slots = getenv("ISG_DEC_SLOTS") ? atoi(getenv("ISG_DEC_SLOTS")) : sms * std::max(occ, 1);
+    }
+    const int groups = cdiv(max_wk * max_hk, DEC_PPB);
+    dim3 grid(std::max(1, std::min(groups, slots / n_inst)), n_inst);
 #define ISG_DEC(TL, SOFT)                                                                                     \
     decode_kernel<TL, SOFT><<<grid, DEC_THREADS, 0, st>>>(static_cast<const TL*>(logits_dev), h, w, boxes_dev, \
-                                                           mask_off_dev, threshold, thr_logit, use_logit_cmp,  \
+                                                           mask_off_dev, threshold, thr_logit, margin,         \
+                                                           use_logit_cmp,                                      \
                                                            masks_dev, soft_dev, area_dev, bbox_dev)
     if (logits_bf16) { if (soft_dev) ISG_DEC(bf16, true); else ISG_DEC(bf16, false); }
     else { if (soft_dev) ISG_DEC(float, true); else ISG_DEC(float, false); }
