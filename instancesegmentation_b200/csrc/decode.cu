@@ -189,7 +189,7 @@ __device__ __forceinline__ void decode_lean(const float* __restrict__ L, int wk,
 // two 16-byte logit loads in, one 8-byte mask store out.  The loads of the next group are in flight
 // while the current one is decided.
 template <typename TL, bool SOFT>
-__global__ void __launch_bounds__(DEC_THREADS)
+__global__ void __launch_bounds__(DEC_THREADS, 4)
 decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restrict__ boxes,
               const int64_t* __restrict__ mask_off, float thr, float thr_logit, float margin, int use_logit_cmp,
               uint8_t* __restrict__ masks, uint8_t* __restrict__ soft, int32_t* __restrict__ area,
