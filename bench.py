@@ -106,7 +106,7 @@ def run_reference(args, rank, world):
     B = 8  # bounded sample of the 64-image workload (the CPU path is ~4 orders slower)
     ips, t, threads = cpu_reference_arm(B, args.size, max(args.steps, 1), min(args.warmup, 2))
     sample = f"{B} of {args.batch} images per step, fp32, torch CPU conv + scalar C decode"
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": "images/sec", "value": ips, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -253,13 +253,30 @@ def run_ours(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": threads, "kind": "port",
                                     "sample": f"8 of {B} images per step x 3 steps, fp32 torch-CPU forward "
                                               f"(oracle restatement, bit-equal to the reference) + scalar C decode"}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def emit(obj):
+    """The one JSON line goes to the process's ORIGINAL stdout; everything libraries print at fd 1
+    (e.g. NCCL's version banner) was redirected to stderr in main()."""
+    data = (json.dumps(obj) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    global _RESULT_FD
     args = parse()
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -270,7 +287,7 @@ def main():
         import subprocess
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29511", os.path.abspath(__file__)] + sys.argv[1:]
-        sys.exit(subprocess.call(cmd))
+        sys.exit(subprocess.call(cmd, stdout=_RESULT_FD))
     run_ours(args, rank, world, local_rank)
 
 
