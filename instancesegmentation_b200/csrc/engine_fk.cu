@@ -243,6 +243,7 @@ struct Spec {
     std::vector<LoadSpec> loads;
     StencilSpec st;
     std::vector<StageSpec> stages;
+    int pool_tensor = -1;           // single-stage launch over a folded s2d load: also emit max_pool2d(x, 2, 2) here
 };
 
 struct Lay {
@@ -252,6 +253,7 @@ struct Lay {
     int load_off[fk::MAX_LOADS], load_plane[fk::MAX_LOADS], load_planes[fk::MAX_LOADS];
     int st_out_off = 0, st_out_plane = 0, st_in_pitch = 0;
     int lbuf_stride = 0, stage_in_load[2] = {0, 0};
+    int pool_off = 0, pool_plane = 0;
     int stage_off[2] = {0, 0}, stage_plane[2] = {0, 0}, stage_compact[2] = {1, 1};
     int K[2] = {0, 0};
     int b_off[2] = {0, 0}, vec_off[2] = {0, 0}, stw_off = 0, stvec_off = 0, blob_off = 0, blob_bytes = 0, bar_off = 0;
@@ -432,6 +434,10 @@ struct FkBuilder {
             int slack = is_chain_src ? std::max(0, L.n_mt * 128 * 16 - L.stage_plane[k]) : 0;
             off = r128(off + (st.N / 8) * L.stage_plane[k] + slack);
         }
+        if (s.pool_tensor >= 0) {
+            L.pool_off = off; L.pool_plane = npix * 16;
+            off = r128(off + (td(s.pool_tensor).Cs / 8) * L.pool_plane);
+        }
         // constants blob
         L.blob_off = off;
         int rel = 0;
@@ -569,8 +575,12 @@ struct FkBuilder {
             d.store_chunk0 = st.out_chunk0; d.shuf = st.shuf; d.Cp = st.Cp;
             if (st.out_tensor >= 0) d.Cs_out = td(st.out_tensor).Cs;
         }
+        if (s.pool_tensor >= 0) {
+            q.pool_on = 1; q.pool_in_off = L.load_off[0]; q.pool_in_plane_bytes = L.load_plane[0];
+            q.pool_nchunks = td(s.pool_tensor).Cs / 8; q.pool_off = L.pool_off; q.pool_plane_bytes = L.pool_plane;
+        }
         // single load buffer: may the next tile's boxes be issued as soon as the stage-0 MMAs completed?
-        q.early_load = 1;
+        q.early_load = s.pool_tensor >= 0 ? 0 : 1;
         for (int k = 0; k < q.nstages; ++k)
             if (q.stage[k].res_on || q.stage[k].stage_in_load || (k > 0 && q.stage[k].a_buf_mask)) q.early_load = 0;
         return q;
@@ -650,6 +660,12 @@ struct FkBuilder {
                                                          sp.stages[k].N / 8, sp.name.c_str());
                         if (rc) return rc;
                     } else maps->out[k] = maps->in[0];
+                }
+                if (sp.pool_tensor >= 0) {
+                    const TensorD& t = P->tensors[sp.pool_tensor];
+                    int rc = tc::make_act_map_chunks(&maps->out[1], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH, t.Cs / 8,
+                                                     sp.name.c_str());
+                    if (rc) return rc;
                 }
             }
             return 0;
@@ -916,9 +932,14 @@ struct FkBuilder {
         const int h = tx.H / 2, w = tx.W / 2;
         // convs.0: 2x2 stride-2 conv as a GEMM over the space-to-depth view
         const int m1 = tensor(p + ".m1", mid, h, w);
+        // residual_1 = max_pool2d(x) (segment.py:145), also the decoder's skip: pooled in the same launch
+        // from the sub-pixel planes the 2x2 conv already holds in shared memory
+        *keep = tensor(keepname, tx.C, h, w, true);
+        P->tensors[*keep].perm = tx.perm;
         {
             Spec s;
-            s.name = p + ".convs.0 (2x2 s2)";
+            s.name = p + ".convs.0 (2x2 s2) + maxpool2";
+            s.pool_tensor = *keep;
             s.qH = h; s.qW = w;
             LoadSpec l{x};
             l.s2d = true;
@@ -949,10 +970,6 @@ struct FkBuilder {
             s.stages.push_back(st);
             emit(s);
         }
-        // residual_1 = max_pool2d(x) (segment.py:145): also the decoder's skip
-        *keep = tensor(keepname, tx.C, h, w, true);
-        P->tensors[*keep].perm = tx.perm;
-        emit_pool2(p + ".maxpool2", x, *keep);
         // dw3x3 -> [convs.2 | convm] -> +, PReLU  (-> next block's first conv)
         const TensorD tk = td(*keep);
         Spec s;

@@ -86,6 +86,9 @@ struct Params {
     int early_load;                // nlbuf == 1: the load buffer is dead once the stage-0 MMAs completed
     const void* blob; int blob_off, blob_bytes;
     Stencil st;
+    // optional 2x2 max-pool of a folded space-to-depth load (BottleneckDown2's residual, segment.py:145):
+    // max over the four sub-pixel plane groups -> pool planes -> TMA store through the second out map
+    int pool_on, pool_in_off, pool_in_plane_bytes, pool_nchunks, pool_off, pool_plane_bytes;
     int nstages; Stage stage[2];
     int bar_off;                   // 3 mbarriers + tmem slot
     long long* prof;               // debug (ISG_FK_PROF=1): per-CTA phase time stamps, else null
@@ -201,6 +204,29 @@ __device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int 
             *reinterpret_cast<uint4*>(smem + s.out_off + (size_t)k * s.out_plane_bytes + (size_t)pix * 16) =
                 make_uint4(pack_bf16(a0, a1), pack_bf16(a2, a3), pack_bf16(a4, a5), pack_bf16(a6, a7));
         }
+    }
+}
+
+__device__ __forceinline__ uint32_t bf2max(uint32_t a, uint32_t b) {
+    __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+    return *reinterpret_cast<uint32_t*>(&r);
+}
+__device__ __forceinline__ uint4 bf8max(uint4 a, uint4 b) {
+    return make_uint4(bf2max(a.x, b.x), bf2max(a.y, b.y), bf2max(a.z, b.z), bf2max(a.w, b.w));
+}
+
+// 2x2 max-pool from the four sub-pixel plane groups of a folded space-to-depth load
+template <int NT>
+__device__ __forceinline__ void run_pool(uint8_t* smem, const Params& p, int boff) {
+    const int npix = p.TH * p.TW;
+    const size_t grp = (size_t)p.pool_nchunks * p.pool_in_plane_bytes;
+    for (int item = threadIdx.x; item < npix * p.pool_nchunks; item += NT) {
+        const int k = fastdiv(item, p.npix_magic), pix = item - k * npix;
+        const uint8_t* src = smem + p.pool_in_off + boff + (size_t)k * p.pool_in_plane_bytes + (size_t)pix * 16;
+        const uint4 a = *reinterpret_cast<const uint4*>(src), b = *reinterpret_cast<const uint4*>(src + grp);
+        const uint4 c = *reinterpret_cast<const uint4*>(src + 2 * grp), d = *reinterpret_cast<const uint4*>(src + 3 * grp);
+        *reinterpret_cast<uint4*>(smem + p.pool_off + (size_t)k * p.pool_plane_bytes + (size_t)pix * 16) =
+            bf8max(bf8max(a, b), bf8max(c, d));
     }
 }
 
@@ -467,6 +493,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             if (it == 0) FK_STAMP(4 + 2 * k);
             FK_ACC(10 + 2 * k);
             tc::tc_fence_after();
+            if (k == 0 && p.pool_on) run_pool<NT>(smem, p, boff);   // before the load buffer may be refilled
             if (k == 0 && tid == 0 && !dbl && p.early_load && next < p.total_tiles) issue_loads(next, 0);
             run_epilogue<NT>(smem, p, s, tmem_base, b, x0, y0, boff);
             tc::fence_proxy_async();
@@ -476,6 +503,10 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             FK_ACC(11 + 2 * k);
             if (tid == 0 && s.out_mode == OUT_STAGE && s.store) {
                 tc::tma_store_5d(k ? &mo1 : &mo0, smem + s.stage_off + (s.stage_in_load ? boff : 0), 0, x0, y0, s.store_chunk0, b);
+                tc::tma_store_commit();
+            }
+            if (k == 0 && tid == 0 && p.pool_on) {
+                tc::tma_store_5d(&mo1, smem + p.pool_off, 0, x0, y0, 0, b);
                 tc::tma_store_commit();
             }
         }
