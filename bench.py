@@ -245,7 +245,7 @@ def run_ours(args, rank, world, local_rank):
             "e2e_u8": {"value": imgs / (e2e_u8_ms * 1e-3), "unit": "images/s",
                        "h2d_bytes_per_step": B * 3 * S * S, "d2h_bytes_per_step": B * S * S + B * 20,
                        "what": "same pipeline fed uint8 NHWC images (infer.py path, Normalize on the device)"},
-            "gpu_launches": K * (eng.launches_per_forward + 3),
+            "gpu_launches": K * (eng.launches_per_forward + 1),   # forward launches + one decode launch per step
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -89,6 +89,13 @@ struct NormU8 { float mean[3], std[3]; };
 __global__ void __launch_bounds__(128)
 prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, bf16* __restrict__ init,
                int Cs_init, int total, NormU8 nm) {
+    // a byte has 256 values: the IEEE sequence is evaluated once per (channel, value) and CTA
+    __shared__ float lut[3][256];
+    for (int e = threadIdx.x; e < 768; e += blockDim.x) {
+        const int c = e >> 8;
+        lut[c][e & 255] = __fdiv_rn(__fdiv_rn((float)(e & 255), 255.f) - nm.mean[c], nm.std[c]);
+    }
+    __syncthreads();
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
@@ -100,10 +107,7 @@ prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x
         const uint32_t* src = reinterpret_cast<const uint32_t*>(x + (((size_t)b * H + 4 * y4 + r) * W + 4 * x4) * 3);
         const uint32_t w[3] = {__ldg(src), __ldg(src + 1), __ldg(src + 2)};
 #pragma unroll
-        for (int k = 0; k < 12; ++k) {
-            const float u = (float)((w[k >> 2] >> (8 * (k & 3))) & 0xffu);
-            v[k % 3][r][k / 3] = __fdiv_rn(__fdiv_rn(u, 255.f) - nm.mean[k % 3], nm.std[k % 3]);
-        }
+        for (int k = 0; k < 12; ++k) v[k % 3][r][k / 3] = lut[k % 3][(w[k >> 2] >> (8 * (k & 3))) & 0xffu];
     }
 #pragma unroll
     for (int a = 0; a < 2; ++a)
