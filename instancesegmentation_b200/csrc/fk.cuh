@@ -287,82 +287,24 @@ __device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&r)[16]) {
                  : "memory");
 }
 
-// epilogue of one (M tile, 16-column chunk): raw accumulators -> shift/residual/activation -> output
-__device__ __forceinline__ void epi_item(uint8_t* smem, const Params& p, const Stage& s, const uint32_t (&raw)[16],
-                                         int mt, int cc, int quad, int lane, int b, int x0, int y0, int boff) {
-    const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
-    const int m = mt * 128 + quad * 32 + lane;
-    const int r = fastdiv(m, s.pitch_magic), c = m - r * s.pitch;
-    const bool geom = r < p.TH && c < p.TW;
-    const int y = y0 + r, x = x0 + c;
-    const bool inimg = geom && y < p.H && x < p.W;
-    const int pc = r * p.TW + c;
-    const int col0 = cc * 16;
-    float v[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[i]);
-    if (s.res_on && geom) {
-        const int ch0 = s.res_mod ? col0 % s.res_mod : col0;
-        const uint8_t* rp = smem + s.res_off + boff + (size_t)(ch0 >> 3) * s.res_plane_bytes + (size_t)pc * 16;
-        float f[16];
-        unpack8(*reinterpret_cast<const uint4*>(rp), f);
-        unpack8(*reinterpret_cast<const uint4*>(rp + s.res_plane_bytes), f + 8);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] += f[i];
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const float4 sh = *reinterpret_cast<const float4*>(vec + col0 + 4 * j);
-        const float4 sl = *reinterpret_cast<const float4*>(vec + s.N + col0 + 4 * j);
-        float a;
-        a = v[4 * j + 0] + sh.x; v[4 * j + 0] = a >= 0.f ? a : a * sl.x;
-        a = v[4 * j + 1] + sh.y; v[4 * j + 1] = a >= 0.f ? a : a * sl.y;
-        a = v[4 * j + 2] + sh.z; v[4 * j + 2] = a >= 0.f ? a : a * sl.z;
-        a = v[4 * j + 3] + sh.w; v[4 * j + 3] = a >= 0.f ? a : a * sl.w;
-    }
-    if (s.out_mode == OUT_SHUF4_F32) {
-        if (inimg) {
-            float* g = static_cast<float*>(s.gptr) + ((size_t)b * 4 * p.H + 4 * y) * (4 * (size_t)p.W) + 4 * x;
-#pragma unroll
-            for (int ry = 0; ry < 4; ++ry)
-                *reinterpret_cast<float4*>(g + (size_t)ry * 4 * p.W) =
-                    make_float4(v[4 * ry], v[4 * ry + 1], v[4 * ry + 2], v[4 * ry + 3]);
-        }
-        return;
-    }
-    const uint4 q0 = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-    const uint4 q1 = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
-                                pack_bf16(v[14], v[15]));
-    if (s.out_mode == OUT_STAGE) {
-        if (s.stage_compact && !geom) return;
-        const int si = s.stage_compact ? pc : m;
-        uint8_t* d = smem + s.stage_off + (s.stage_in_load ? boff : 0) + (size_t)(col0 >> 3) * s.stage_plane_bytes + (size_t)si * 16;
-        *reinterpret_cast<uint4*>(d) = q0;
-        *reinterpret_cast<uint4*>(d + s.stage_plane_bytes) = q1;
-    } else if (s.out_mode == OUT_S2D) {
-        if (inimg) {
-            bf16* g = static_cast<bf16*>(s.gptr) +
-                      (((size_t)b * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1)) * (4 * (size_t)s.N) +
-                      ((y & 1) * 2 + (x & 1)) * s.N + col0;
-            st_global_16(g, q0);
-            st_global_16(g + 8, q1);
-        }
-    } else {  // OUT_SHUF_BF16
-        if (inimg) {
-            const int phase = col0 / s.Cp, ch = col0 - phase * s.Cp;
-            const int py = phase / s.shuf, px = phase - py * s.shuf;
-            bf16* g = static_cast<bf16*>(s.gptr) +
-                      (((size_t)b * p.H * s.shuf + (size_t)y * s.shuf + py) * ((size_t)p.W * s.shuf) +
-                       (size_t)x * s.shuf + px) * s.Cs_out + ch;
-            st_global_16(g, q0);
-            st_global_16(g + 8, q1);
-        }
-    }
+// ---- epilogue of one stage: TMEM accumulators -> + shift (+ residual) -> activation -> output ----
+// Warp w may only touch TMEM lanes [32*(w%4), +32): the NT/128 warp groups alternate over the
+// (M tile, 16-column chunk) items.  Everything that depends on the tile only (image base pointers) is
+// computed once per call, everything that depends on the M tile only (pixel geometry) once per M tile;
+// the TMEM load of the next item is issued as soon as the current accumulators have been consumed.
+struct EpiGeom { int r, c, y, x, pc, m; bool geom, inimg; };
+
+__device__ __forceinline__ EpiGeom epi_geom(const Params& p, const Stage& s, int mt, int quad, int lane, int x0, int y0) {
+    EpiGeom g;
+    g.m = mt * 128 + quad * 32 + lane;
+    g.r = fastdiv(g.m, s.pitch_magic); g.c = g.m - g.r * s.pitch;
+    g.geom = g.r < p.TH && g.c < p.TW;
+    g.y = y0 + g.r; g.x = x0 + g.c;
+    g.inimg = g.geom && g.y < p.H && g.x < p.W;
+    g.pc = g.r * p.TW + g.c;
+    return g;
 }
 
-// warps 0-3 and 4-7 are two groups that alternate over the (M tile, column chunk) items; warp w may
-// only touch TMEM lanes [32*(w%4), +32).  The TMEM load of the next item is in flight while the
-// current one is processed.
 template <int NT>
 __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, const Stage& s, uint32_t tmem_base,
                                              int b, int x0, int y0, int boff) {
@@ -370,24 +312,90 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int quad = warp & 3, grp = warp >> 2;
     const int ncc = s.N >> 4, nitems = p.n_mt * ncc;
-    const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
-    uint32_t ra[16], rb[16];
     int item = grp;
     if (item >= nitems) return;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
+    const int out_mode = s.out_mode, N = s.N;
+    // per-tile bases: one 64-bit product per call, 32-bit offsets inside the image afterwards
+    uint8_t* gimg = static_cast<uint8_t*>(s.gptr);
+    if (out_mode == OUT_S2D) gimg += (size_t)b * (p.H >> 1) * (p.W >> 1) * (4 * N) * sizeof(bf16);
+    else if (out_mode == OUT_SHUF_BF16) gimg += (size_t)b * p.H * p.W * (s.shuf * s.shuf * s.Cs_out) * sizeof(bf16);
+    else if (out_mode == OUT_SHUF4_F32) gimg += (size_t)b * p.H * p.W * 16 * sizeof(float);
+    uint8_t* stage = smem + s.stage_off + (s.stage_in_load ? boff : 0);
+    const uint8_t* res = smem + s.res_off + boff;
+    int mt = 0, cc = item;
+    while (cc >= ncc) { cc -= ncc; ++mt; }
+    int mt_geom = -1;
+    EpiGeom g = {};
+    uint32_t ra[16];
     __syncwarp();
     tmem_ld16_nowait(lane_base + item * 16, ra);   // column of item = mt*N + cc*16 = item*16
-    tmem_ld_wait_dep(ra);
     while (true) {
+        tmem_ld_wait_dep(ra);
+        if (mt != mt_geom) { g = epi_geom(p, s, mt, quad, lane, x0, y0); mt_geom = mt; }
+        const int col0 = cc * 16;
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(ra[i]);
+        // the accumulators are in v: the next item's TMEM load overlaps the arithmetic below
         const int nxt = item + NGROUPS;
         __syncwarp();
-        if (nxt < nitems) tmem_ld16_nowait(lane_base + nxt * 16, rb);   // in flight during this item
-        epi_item(smem, p, s, ra, item / ncc, item % ncc, quad, lane, b, x0, y0, boff);
+        if (nxt < nitems) tmem_ld16_nowait(lane_base + nxt * 16, ra);
+        if (s.res_on && g.geom) {
+            const int ch0 = s.res_mod ? col0 % s.res_mod : col0;
+            const uint8_t* rp = res + (size_t)(ch0 >> 3) * s.res_plane_bytes + (size_t)g.pc * 16;
+            float f[16];
+            unpack8(*reinterpret_cast<const uint4*>(rp), f);
+            unpack8(*reinterpret_cast<const uint4*>(rp + s.res_plane_bytes), f + 8);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += f[i];
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float4 sh = *reinterpret_cast<const float4*>(vec + col0 + 4 * j);
+            const float4 sl = *reinterpret_cast<const float4*>(vec + N + col0 + 4 * j);
+            float a;
+            a = v[4 * j + 0] + sh.x; v[4 * j + 0] = a >= 0.f ? a : a * sl.x;
+            a = v[4 * j + 1] + sh.y; v[4 * j + 1] = a >= 0.f ? a : a * sl.y;
+            a = v[4 * j + 2] + sh.z; v[4 * j + 2] = a >= 0.f ? a : a * sl.z;
+            a = v[4 * j + 3] + sh.w; v[4 * j + 3] = a >= 0.f ? a : a * sl.w;
+        }
+        if (out_mode == OUT_SHUF4_F32) {
+            if (g.inimg) {   // 16 columns = the 4x4 sub-pixels of this q pixel, fp32 logits
+                float* o = reinterpret_cast<float*>(gimg) + (4 * g.y) * (4 * p.W) + 4 * g.x;
+#pragma unroll
+                for (int ry = 0; ry < 4; ++ry)
+                    *reinterpret_cast<float4*>(o + ry * 4 * p.W) = make_float4(v[4 * ry], v[4 * ry + 1], v[4 * ry + 2], v[4 * ry + 3]);
+            }
+        } else {
+            const uint4 q0 = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+            const uint4 q1 = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
+                                        pack_bf16(v[14], v[15]));
+            if (out_mode == OUT_STAGE) {
+                if (!s.stage_compact || g.geom) {
+                    uint8_t* d = stage + (size_t)(col0 >> 3) * s.stage_plane_bytes + (size_t)(s.stage_compact ? g.pc : g.m) * 16;
+                    *reinterpret_cast<uint4*>(d) = q0;
+                    *reinterpret_cast<uint4*>(d + s.stage_plane_bytes) = q1;
+                }
+            } else if (g.inimg) {
+                bf16* o;
+                if (out_mode == OUT_S2D) {
+                    o = reinterpret_cast<bf16*>(gimg) + ((g.y >> 1) * (p.W >> 1) + (g.x >> 1)) * (4 * N) +
+                        ((g.y & 1) * 2 + (g.x & 1)) * N + col0;
+                } else {  // OUT_SHUF_BF16: column = phase * Cp + channel, phase = (py, px) of the x`shuf` upsampling
+                    const int phase = col0 / s.Cp, ch = col0 - phase * s.Cp;
+                    const int py = phase / s.shuf, px = phase - py * s.shuf;
+                    o = reinterpret_cast<bf16*>(gimg) + ((g.y * s.shuf + py) * (p.W * s.shuf) + g.x * s.shuf + px) * s.Cs_out + ch;
+                }
+                st_global_16(o, q0);
+                st_global_16(o + 8, q1);
+            }
+        }
         if (nxt >= nitems) break;
         item = nxt;
-        __syncwarp();
-        tmem_ld_wait_dep(rb);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) ra[i] = rb[i];
+        cc += NGROUPS;
+        while (cc >= ncc) { cc -= ncc; ++mt; }
     }
 }
 
