@@ -573,10 +573,16 @@ struct FkBuilder {
             if (st.res_load >= 0) {
                 d.res_on = 1; d.res_off = L.load_off[st.res_load]; d.res_plane_bytes = L.load_plane[st.res_load];
                 d.res_mod = st.res_mod;
+                if (st.res_mod % 16) { fprintf(stderr, "libisg: res_mod must be a multiple of 16\n"); abort(); }
+                d.res_magic = magic(st.res_mod / 16);
             }
             d.out_mode = st.out_mode; d.stage_off = L.stage_off[k]; d.stage_plane_bytes = L.stage_plane[k];
             d.stage_compact = L.stage_compact[k]; d.store = st.store && st.out_mode == fk::OUT_STAGE;
             d.store_chunk0 = st.out_chunk0; d.shuf = st.shuf; d.Cp = st.Cp;
+            if (st.out_mode == fk::OUT_SHUF_BF16) {
+                if (st.shuf != 2 || st.Cp % 16) { fprintf(stderr, "libisg: pixel shuffle needs shuf 2, Cp %% 16 == 0\n"); abort(); }
+                d.cp_magic = magic(st.Cp / 16);
+            }
             if (st.out_tensor >= 0) d.Cs_out = td(st.out_tensor).Cs;
         }
         if (s.pool_tensor >= 0) {

@@ -61,6 +61,8 @@ struct Stage {
     int store;                     // 1: TMA-store the staging planes through the stage's out map
     int store_chunk0;
     void* gptr; int Cs_out, shuf, Cp;   // direct-store modes
+    // 16-column chunk cc -> (cc / (res_mod/16), cc / (Cp/16)) by magic multiplication (0: divisor 1 or unused)
+    uint32_t res_magic, cp_magic;
 };
 
 struct Stencil {
@@ -343,7 +345,7 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
         __syncwarp();
         if (nxt < nitems) tmem_ld16_nowait(lane_base + nxt * 16, ra);
         if (s.res_on && g.geom) {
-            const int ch0 = s.res_mod ? col0 % s.res_mod : col0;
+            const int ch0 = s.res_mod ? col0 - fastdiv(cc, s.res_magic) * s.res_mod : col0;
             const uint8_t* rp = res + (size_t)(ch0 >> 3) * s.res_plane_bytes + (size_t)g.pc * 16;
             float f[16];
             unpack8(*reinterpret_cast<const uint4*>(rp), f);
@@ -384,8 +386,8 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
                     o = reinterpret_cast<bf16*>(gimg) + ((g.y >> 1) * (p.W >> 1) + (g.x >> 1)) * (4 * N) +
                         ((g.y & 1) * 2 + (g.x & 1)) * N + col0;
                 } else {  // OUT_SHUF_BF16: column = phase * Cp + channel, phase = (py, px) of the x`shuf` upsampling
-                    const int phase = col0 / s.Cp, ch = col0 - phase * s.Cp;
-                    const int py = phase / s.shuf, px = phase - py * s.shuf;
+                    const int phase = fastdiv(cc, s.cp_magic), ch = col0 - phase * s.Cp;
+                    const int py = phase >> 1, px = phase & 1;   // shuf == 2 (ConvT k4 s2)
                     o = reinterpret_cast<bf16*>(gimg) + ((g.y * s.shuf + py) * (p.W * s.shuf) + g.x * s.shuf + px) * s.Cs_out + ch;
                 }
                 st_global_16(o, q0);
