@@ -11,6 +11,7 @@
 
 #include "engine.h"
 #include "fk.cuh"
+#include "mega.cuh"
 #include "kernels_misc.cuh"
 #include "pack_util.h"
 #include "tc_host.h"
@@ -918,14 +919,7 @@ struct FkBuilder {
         const int out = tensor(outname, C, tx.H, tx.W, tap);
         st.out_tensor = out;
         const int N = st.N;
-        st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
-            std::vector<float> sc(C), sh(C);
-            fold_unit(w, last + ".conv", last + ".bn", C, sc.data(), sh.data());
-            const float* Wt = w.get(last + ".conv.weight");  // [C][mid]
-            for (int k = 0; k < mid; ++k)
-                for (int o = 0; o < C; ++o) B[(size_t)k * N + o] = Wt[(size_t)o * mid + k] * sc[o];
-            for (int o = 0; o < C; ++o) { shift[o] = sh[o]; slope[o] = w.get(p + ".prelu.weight")[o]; }
-        };
+        st.fill = res_out_fill(p, last, C, mid, N);
         s.stages.push_back(st);
         if (nx.on) {
             s.stages.push_back(chain_stage(nx, C, N));
@@ -934,6 +928,160 @@ struct FkBuilder {
         emit(s);
         return out;
     }
+    // last 1x1 conv + BN of a residual bottleneck and the block's PReLU: B[K = mid][N], shift, slope
+    static StageFill res_out_fill(const std::string& p, const std::string& last, int C, int mid, int N) {
+        return [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(C), sh(C);
+            fold_unit(w, last + ".conv", last + ".bn", C, sc.data(), sh.data());
+            const float* Wt = w.get(last + ".conv.weight");  // [C][mid]
+            for (int k = 0; k < mid; ++k)
+                for (int o = 0; o < C; ++o) B[(size_t)k * N + o] = Wt[(size_t)o * mid + k] * sc[o];
+            for (int o = 0; o < C; ++o) { shift[o] = sh[o]; slope[o] = w.get(p + ".prelu.weight")[o]; }
+        };
+    }
+
+    // ---- a run of residual bottlenecks as ONE cluster launch (csrc/mega.cuh) ----
+    struct MegaLay { mega::Params q; size_t smem = 0; bool ok = false; };
+    MegaLay mega_layout(int H, int W, int C, int mid, int nblocks) const {
+        MegaLay L;
+        mega::Params& q = L.q;
+        std::memset(&q, 0, sizeof q);
+        if (getenv("ISG_FK_NO_MEGA") || nblocks > mega::MAX_BLOCKS || H % mega::CLUSTER) return L;
+        q.H = H; q.W = W; q.R = H / mega::CLUSTER;
+        q.Cs = round_up(C, 16); q.Cm = round_up(mid, 16);
+        q.npx = q.R * W;
+        if (q.npx % 128 || q.R < mega::HALO || W + 2 * mega::HALO > 256 || q.R > 256) return L;
+        q.n_mt = q.npx / 128;
+        q.pitch = W + 2 * mega::HALO; q.rows_p = q.R + 2 * mega::HALO;
+        auto magic = [](int d) -> uint32_t { return d > 1 ? (uint32_t)(((1ull << 32) + d - 1) / d) : 0u; };
+        q.w_magic = magic(W); q.npx_magic = magic(q.npx);
+        q.nblocks = nblocks;
+        const int cols = q.n_mt * std::max(q.Cs, q.Cm);
+        if (cols > 512) return L;
+        q.tmem_cols = tc::tmem_cols_pow2(cols);
+        int rel = 0;
+        q.w0_off = rel; rel = r128(rel + q.Cs * q.Cm * 2);
+        q.v0_off = rel; rel = r128(rel + 2 * q.Cm * 4);
+        q.dw_off = rel; rel = r128(rel + 25 * q.Cm * 4);
+        q.dv_off = rel; rel = r128(rel + 7 * q.Cm * 4);
+        q.w2_off = rel; rel = r128(rel + q.Cm * q.Cs * 2);
+        q.v2_off = rel; rel = r128(rel + 2 * q.Cs * 4);
+        q.blob_bytes = rel; q.blob_stride = rel;
+        int off = 0;
+        q.x_off = off; off = r128(off + (q.Cs / 8) * q.npx * 16);
+        q.m1_off = off; off = r128(off + (q.Cm / 8) * q.rows_p * q.pitch * 16);
+        q.d_off = off; off = r128(off + (q.Cm / 8) * q.npx * 16);
+        q.wbuf_off[0] = off; off = r128(off + rel);
+        q.wbuf_off[1] = off; off = r128(off + rel);
+        q.bar_off = off; off += 128;
+        L.smem = off;
+        L.ok = L.smem <= 227 * 1024;
+        return L;
+    }
+    struct MegaBlock { std::string p; int dil; bool five; };
+    int mega_run(const std::string& name, int x, int mid, const std::vector<MegaBlock>& blocks, const std::string& outname) {
+        isg_plan* P = this->P;
+        const TensorD tx = td(x);
+        const int C = tx.C;
+        MegaLay L = mega_layout(tx.H, tx.W, C, mid, (int)blocks.size());
+        mega::Params q = L.q;
+        const int out = tensor(outname, C, tx.H, tx.W, true);
+        struct Fills { StageFill f0, f2; StencilFill fs; };
+        auto fills = std::make_shared<std::vector<Fills>>();
+        for (size_t i = 0; i < blocks.size(); ++i) {
+            const MegaBlock& b = blocks[i];
+            q.blk[i].dil = b.five ? 1 : b.dil; q.blk[i].sep5 = b.five ? 1 : 0;
+            Next n0; n0.on = true; n0.unit = b.p + ".convs.0"; n0.mid = mid; n0.act = ACT_PRELU;
+            Fills f;
+            f.f0 = chain_stage(n0, C, q.Cs).fill;
+            f.fs = b.five ? sep5_stencil(b.p, 0, mid).fill : dw3_stencil(b.p + ".convs.1", 0, mid, b.dil).fill;
+            f.f2 = res_out_fill(b.p, b.five ? b.p + ".convs.3" : b.p + ".convs.2", C, mid, q.Cs);
+            fills->push_back(f);
+            macs(mid, C, 1, 1, tx.H, tx.W);
+            if (b.five) { macs(mid, 1, 5, 1, tx.H, tx.W); macs(mid, 1, 1, 5, tx.H, tx.W); }
+            else macs(mid, 1, 3, 3, tx.H, tx.W);
+            macs(C, mid, 1, 1, tx.H, tx.W);
+        }
+        const size_t blob = arena((size_t)q.blob_stride * blocks.size() / 4);
+        Op op;
+        op.name = name + " (" + std::to_string(blocks.size()) + " residual bottlenecks, cluster-resident) [mega]";
+        const int nb = (int)blocks.size();
+        op.pack = [=](const HostWeights& w, float* A) {
+            auto pack_b = [](uint16_t* wb, const float* B, int K, int N) {   // B[K][N] -> blocked [k16][2][N][8] bf16
+                for (int kk = 0; kk < K; ++kk)
+                    for (int n = 0; n < N; ++n)
+                        wb[(size_t)(kk / 16) * N * 16 + (size_t)((kk % 16) / 8) * N * 8 + (size_t)n * 8 + (kk % 8)] =
+                            tc::f2bf(B[(size_t)kk * N + n]);
+            };
+            for (int i = 0; i < nb; ++i) {
+                uint8_t* base = reinterpret_cast<uint8_t*>(A + blob) + (size_t)i * q.blob_stride;
+                std::memset(base, 0, q.blob_bytes);
+                const Fills& f = (*fills)[i];
+                {
+                    std::vector<float> B((size_t)q.Cs * q.Cm, 0.f), sh(q.Cm, 0.f), sl(q.Cm, 1.f);
+                    f.f0(w, B.data(), sh.data(), sl.data());
+                    pack_b(reinterpret_cast<uint16_t*>(base + q.w0_off), B.data(), q.Cs, q.Cm);
+                    float* v = reinterpret_cast<float*>(base + q.v0_off);
+                    std::memcpy(v, sh.data(), 4 * q.Cm); std::memcpy(v + q.Cm, sl.data(), 4 * q.Cm);
+                }
+                {
+                    std::vector<float> wt((size_t)25 * q.Cm, 0.f), sh(q.Cm, 0.f), sl(q.Cm, 1.f), bw((size_t)5 * q.Cm, 0.f);
+                    f.fs(w, wt.data(), sh.data(), sl.data(), bw.data());
+                    std::memcpy(base + q.dw_off, wt.data(), 4 * wt.size());
+                    float* v = reinterpret_cast<float*>(base + q.dv_off);
+                    std::memcpy(v, sh.data(), 4 * q.Cm); std::memcpy(v + q.Cm, sl.data(), 4 * q.Cm);
+                    std::memcpy(v + 2 * q.Cm, bw.data(), 4 * bw.size());
+                }
+                {
+                    std::vector<float> B((size_t)q.Cm * q.Cs, 0.f), sh(q.Cs, 0.f), sl(q.Cs, 1.f);
+                    f.f2(w, B.data(), sh.data(), sl.data());
+                    pack_b(reinterpret_cast<uint16_t*>(base + q.w2_off), B.data(), q.Cm, q.Cs);
+                    float* v = reinterpret_cast<float*>(base + q.v2_off);
+                    std::memcpy(v, sh.data(), 4 * q.Cs); std::memcpy(v + q.Cs, sl.data(), 4 * q.Cs);
+                }
+            }
+        };
+        auto maps = std::make_shared<FkMaps>();
+        const int maxB = P->max_batch;
+        const TensorD to = td(out);
+        P->finalizers.push_back([=]() -> int {
+            int rc = tc::make_act_map_chunks(&maps->in[0], P->ws + tx.off, maxB, tx.H, tx.W, tx.Cs, tx.W, q.R, tx.Cs / 8, name.c_str());
+            if (rc) return rc;
+            return tc::make_act_map_chunks(&maps->out[0], P->ws + to.off, maxB, to.H, to.W, to.Cs, to.W, q.R, to.Cs / 8, name.c_str());
+        });
+        cudaFuncSetAttribute(mega::mega_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaFuncSetAttribute(mega::mega_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        const size_t smem = L.smem;
+        auto nclusters = std::make_shared<int>(0);
+        op.launch = [=](int n, const float*, float*, cudaStream_t stream) -> cudaError_t {
+            mega::Params p = q;
+            p.blob = reinterpret_cast<const uint8_t*>(P->arena + blob);
+            p.nimg = n;
+            cudaLaunchConfig_t cfg;
+            std::memset(&cfg, 0, sizeof cfg);
+            cfg.blockDim = dim3(mega::THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+            cudaLaunchAttribute at[2];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = mega::CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[1].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = 2;
+            if (*nclusters == 0) {   // co-resident clusters of this footprint (GPC boundaries matter): once
+                cfg.gridDim = dim3(mega::CLUSTER * 64);
+                int nc = 0;
+                cudaError_t e = cudaOccupancyMaxActiveClusters(&nc, mega::mega_kernel, &cfg);
+                if (e != cudaSuccess) return e;
+                if (nc < 1) return cudaErrorLaunchOutOfResources;
+                *nclusters = nc;
+                if (getenv("ISG_FK_VERBOSE")) fprintf(stderr, "mega %s: %d co-resident clusters of %d, smem %zu\n", name.c_str(), nc, mega::CLUSTER, smem);
+            }
+            cfg.gridDim = dim3(mega::CLUSTER * std::min(*nclusters, std::max(n, 1)));
+            return cudaLaunchKernelEx(&cfg, mega::mega_kernel, maps->in[0], maps->out[0], p);
+        };
+        P->ops.push_back(op);
+        return out;
+    }
+
 
     // BottleneckDown2 (segment.py:114-150)
     int block_down(const std::string& p, int x, int mid, int cout, int* keep, const std::string& outname,
@@ -1369,10 +1517,16 @@ struct FkBuilder {
             y = block_res(p, y, m1, 16, 1, false, n2, i == 3 ? "bottle1_5" : p, i == 3);
             m1 = n2.out;
         }
-        nx = next_of("bottle2_x.0.convs.0", 48, ACT_PRELU, h16, w16);
+        const bool mega16 = mega_layout(h16, w16, 128, 48, 5).ok;
+        nx = mega16 ? Next() : next_of("bottle2_x.0.convs.0", 48, ACT_PRELU, h16, w16);
         const int d2 = block_down("bottle2_1", y, 16, 128, &keep2, "bottle2_down", "keep2", nx);
         const int dils[4] = {1, 2, 1, 4};
         auto wide = [&](const std::string& pre, int t, int m, const Next& after, const char* outname) {
+            if (mega16) {
+                std::vector<MegaBlock> blocks;
+                for (int i = 0; i < 5; ++i) blocks.push_back(MegaBlock{pre + "." + std::to_string(i), i < 4 ? dils[i] : 1, i == 4});
+                return mega_run(pre, t, 48, blocks, outname);
+            }
             for (int i = 0; i < 5; ++i) {
                 const std::string p = pre + "." + std::to_string(i);
                 Next n2 = after;
@@ -1384,7 +1538,7 @@ struct FkBuilder {
         };
         y = wide("bottle2_x", d2, nx.out, Next(), "bottle2_8");
         m1 = pw_unit("bottle3_1.convs.0", {y, d2}, 48, ACT_PRELU, "bottle3_1.m1");
-        nx = next_of("bottle3_x.0.convs.0", 48, ACT_PRELU, h16, w16);
+        nx = mega16 ? Next() : next_of("bottle3_x.0.convs.0", 48, ACT_PRELU, h16, w16);
         y = block_proj("bottle3_1", y, d2, m1, 48, 128, true, nx);
         y = wide("bottle3_x", y, nx.out, Next(), "bottle3_8");
         y = block_up("bottle4_1up", y, keep2, 16, 48, "bottle4_1");

@@ -146,19 +146,19 @@ __device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
 // ---- depthwise stencil: haloed input planes -> A operand planes ----
 // SEP5 = false: 3x3 with dilation; SEP5 = true: the composed (5,1)x(1,5) pair (25 taps)
 template <bool SEP5, int NT>
-__device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int x0, int boff) {
-    const Stencil& s = p.st;
+__device__ __forceinline__ void run_stencil(uint8_t* smem, const Stencil& s, int TH, int TW, int Wimg, uint32_t npix_magic,
+                                            uint32_t tw_magic, int x0, int boff) {
     constexpr int KS = SEP5 ? 5 : 3;
-    const int npix = p.TH * p.TW, C = s.nchunks * 8;
+    const int npix = TH * TW, C = s.nchunks * 8;
     const int dil = SEP5 ? 1 : s.dil, pitch = s.in_pitch;
     const float* wt = reinterpret_cast<const float*>(smem + s.w_off);
     const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
     {
         for (int item = threadIdx.x; item < npix * s.nchunks; item += NT) {
-            const int k = fastdiv(item, p.npix_magic), pix = item - k * npix;
+            const int k = fastdiv(item, npix_magic), pix = item - k * npix;
             const uint8_t* plane = smem + s.in_off + boff + (size_t)k * s.in_plane_bytes;
             const float* wk = wt + k * 8;
-            const int r = fastdiv(pix, p.tw_magic), c = pix - r * p.TW;
+            const int r = fastdiv(pix, tw_magic), c = pix - r * TW;
             // top-left tap of this pixel
             const uint8_t* in = plane + (size_t)((r + s.halo - (KS / 2) * dil) * pitch + c + s.halo - (KS / 2) * dil) * 16;
             float2 acc[4];
@@ -189,7 +189,7 @@ __device__ __forceinline__ void run_stencil(uint8_t* smem, const Params& p, int 
 #pragma unroll
                 for (int kx = 0; kx < 5; ++kx) {
                     const int xx = xa + kx - 2;
-                    if (xx >= 0 && xx < p.W) {
+                    if (xx >= 0 && xx < Wimg) {
                         const float4 b0 = *reinterpret_cast<const float4*>(vec + (2 + kx) * C + k * 8);
                         const float4 b1 = *reinterpret_cast<const float4*>(vec + (2 + kx) * C + k * 8 + 4);
                         sh0.x += b0.x; sh0.y += b0.y; sh0.z += b0.z; sh0.w += b0.w;
@@ -484,8 +484,8 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         if (it == 0) FK_STAMP(2);
 
         if (p.st.on) {
-            if (p.st.sep5) run_stencil<true, NT>(smem, p, x0, boff);
-            else run_stencil<false, NT>(smem, p, x0, boff);
+            if (p.st.sep5) run_stencil<true, NT>(smem, p.st, p.TH, p.TW, p.W, p.npix_magic, p.tw_magic, x0, boff);
+            else run_stencil<false, NT>(smem, p.st, p.TH, p.TW, p.W, p.npix_magic, p.tw_magic, x0, boff);
             tc::fence_proxy_async();
             __syncthreads();
         }
