@@ -1507,10 +1507,16 @@ struct FkBuilder {
 
         const int h8 = H / 8, w8 = W / 8, h16 = H / 16, w16 = W / 16;
         int keep1, keep2;
-        Next nx = next_of("bottle1_x.0.convs.0", 16, ACT_PRELU, h8, w8);
+        const bool mega8 = mega_layout(h8, w8, 48, 16, 4).ok && !getenv("ISG_FK_NO_MEGA8");
+        Next nx = mega8 ? Next() : next_of("bottle1_x.0.convs.0", 16, ACT_PRELU, h8, w8);
         const int d1 = block_down("bottle1_1", init, 16, 48, &keep1, "bottle1_down", "keep1", nx);
         int y = d1, m1 = nx.out;
-        for (int i = 0; i < 4; ++i) {
+        if (mega8) {
+            std::vector<MegaBlock> blocks;
+            for (int i = 0; i < 4; ++i) blocks.push_back(MegaBlock{"bottle1_x." + std::to_string(i), 1, false});
+            y = mega_run("bottle1_x", d1, 16, blocks, "bottle1_5");
+        }
+        for (int i = 0; i < 4 && !mega8; ++i) {
             const std::string p = "bottle1_x." + std::to_string(i);
             Next n2;
             if (i < 3) n2 = next_of("bottle1_x." + std::to_string(i + 1) + ".convs.0", 16, ACT_PRELU, h8, w8);
