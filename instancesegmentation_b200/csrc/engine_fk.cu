@@ -235,6 +235,7 @@ struct StageSpec {
     bool taps9 = false;
     int N = 0;
     StageFill fill;                 // B[tap][K][N] (zeroed), shift[N] (zeroed), slope[N] (ones)
+    std::function<bool(int tap, int ks)> used;   // optional: false = that 16-row K slice of the tap is structurally zero
     int res_load = -1, res_mod = 0;
     int out_mode = fk::OUT_STAGE, out_tensor = -1, out_chunk0 = 0;
     bool store = true;
@@ -569,6 +570,13 @@ struct FkBuilder {
             }
             d.stage_in_load = L.stage_in_load[k];
             d.nks = nks;
+            d.nent = 0;
+            for (int t = 0; t < d.ntaps; ++t) {
+                d.tap_mask[t] = 0;
+                for (int ks = 0; ks < nks; ++ks)
+                    if (!st.used || st.used(t, ks)) { d.tap_mask[t] |= 1u << ks; ++d.nent; }
+            }
+            if (d.nent > fk::TAB_N) { fprintf(stderr, "libisg: %s: %d MMAs per M tile exceed the descriptor table\n", s.name.c_str(), d.nent); abort(); }
             d.b_desc = tc::umma_smem_desc(L.blob_off + L.b_off[k], st.N * 16, 128);
             d.vec_off = L.blob_off + L.vec_off[k];
             if (st.res_load >= 0) {
@@ -627,12 +635,23 @@ struct FkBuilder {
                 std::vector<float> B((size_t)ntaps * K * N, 0.f), shift(N, 0.f), slope(N, 1.f);
                 st.fill(w, B.data(), shift.data(), slope.data());
                 uint16_t* wb = reinterpret_cast<uint16_t*>(base + L.b_off[k]);
+                // blocks of structurally zero K slices are not stored: the kernel skips their MMAs
+                std::vector<int> slot((size_t)ntaps * nks, -1);
+                int nslot = 0;
+                for (int t = 0; t < ntaps; ++t)
+                    for (int ks = 0; ks < nks; ++ks)
+                        if (!st.used || st.used(t, ks)) slot[(size_t)t * nks + ks] = nslot++;
                 for (int t = 0; t < ntaps; ++t)
                     for (int kk = 0; kk < K; ++kk)
                         for (int n = 0; n < N; ++n) {
-                            const size_t blk = (size_t)t * nks + kk / 16;
-                            const size_t idx = blk * (size_t)N * 16 + (size_t)((kk % 16) / 8) * N * 8 + (size_t)n * 8 + (kk % 8);
-                            wb[idx] = tc::f2bf(B[((size_t)t * K + kk) * N + n]);
+                            const float v = B[((size_t)t * K + kk) * N + n];
+                            const int blk = slot[(size_t)t * nks + kk / 16];
+                            if (blk < 0) {
+                                if (v != 0.f) { fprintf(stderr, "libisg: %s: weight in a K slice declared unused\n", sp.name.c_str()); abort(); }
+                                continue;
+                            }
+                            const size_t idx = (size_t)blk * N * 16 + (size_t)((kk % 16) / 8) * N * 8 + (size_t)n * 8 + (kk % 8);
+                            wb[idx] = tc::f2bf(v);
                         }
                 float* v = reinterpret_cast<float*>(base + L.vec_off[k]);
                 std::memcpy(v, shift.data(), sizeof(float) * N);
@@ -1385,6 +1404,10 @@ struct FkBuilder {
         st.out_tensor = out_tensor;
         macs(16, cin, 5, 5, qH, qW);
         const int K = td(src).Cs;
+        // a K slice of 16 rows is one sub-pixel (ry, rx) of the space-to-depth input when cin == 16: the taps
+        // that would need kernel row / column 5 do not exist (25 of the 36 slices carry weights)
+        if (cin == 16)
+            st.used = [](int t, int ks) { return 2 * (t / 3) + (ks >> 1) <= 4 && 2 * (t % 3) + (ks & 1) <= 4; };
         st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
             std::vector<float> sc(16), sh(16);
             fold_unit(w, unit + ".conv", unit + ".bn", 16, sc.data(), sh.data());

@@ -47,6 +47,8 @@ struct Load {
 struct Stage {
     int N, ntaps, nks;
     int tap_off[MAX_MMA_TAPS];     // pixel offsets dy*pitch + dx
+    uint32_t tap_mask[MAX_MMA_TAPS];   // bit ks set: K slice ks of this tap has weights (structural zeros are skipped)
+    int nent;                      // MMAs per M tile = set bits; the packed B blocks follow the same order
     uint64_t a_desc[MAX_KS];       // UMMA descriptor of K slice ks (16 channels = 2 planes) relative to the
                                    // dynamic shared memory base: the kernel adds (base + row offset) >> 4
     uint64_t b_desc;               // descriptor of the first packed B block [tap][ks][2][N][8] bf16
@@ -240,14 +242,18 @@ constexpr int TAB_N = 40;   // A descriptors per (stage, load buffer): ntaps * n
 template <int NT>
 __device__ __forceinline__ void build_desc_table(const Params& p, uint64_t* tabs, uint32_t smem_base) {
     const uint64_t base16 = smem_base >> 4;
-    for (int i = threadIdx.x; i < p.nstages * 3 * TAB_N; i += NT) {
-        const int k = i / (3 * TAB_N), r = i - k * 3 * TAB_N, buf = r / TAB_N, j = r - buf * TAB_N;
+    for (int i = threadIdx.x; i < p.nstages * 3; i += NT) {   // one thread per (stage, load buffer) table
+        const int k = i / 3, buf = i - 3 * k;
         const Stage& s = p.stage[k];
-        if (j >= s.ntaps * s.nks) continue;
-        const int t = j / s.nks, ks = j - t * s.nks;
-        uint64_t d = s.a_desc[ks] + base16 + (uint64_t)(int64_t)s.tap_off[t];
-        if ((s.a_buf_mask >> ks) & 1u) d += (uint64_t)((buf * p.lbuf_stride) >> 4);
-        tabs[i] = d;
+        uint64_t* tab = tabs + i * TAB_N;
+        int j = 0;
+        for (int t = 0; t < s.ntaps; ++t)
+            for (int ks = 0; ks < s.nks; ++ks) {
+                if (!((s.tap_mask[t] >> ks) & 1u)) continue;
+                uint64_t d = s.a_desc[ks] + base16 + (uint64_t)(int64_t)s.tap_off[t];
+                if ((s.a_buf_mask >> ks) & 1u) d += (uint64_t)((buf * p.lbuf_stride) >> 4);
+                tab[j++] = d;
+            }
     }
 }
 
@@ -257,7 +263,7 @@ __device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, const
     const uint32_t idesc = tc::umma_idesc_bf16(128, s.N);
     const uint64_t bd0 = s.b_desc + (smem_base >> 4);
     const uint32_t b_step = (uint32_t)s.N * 2;  // 16-byte units per [2][N][8] block
-    const int n = s.ntaps * s.nks;
+    const int n = s.nent;
     for (int mt = first; mt < p.n_mt; mt += step) {
         const uint64_t row = (uint64_t)(mt * 128);
         uint64_t bd = bd0;

@@ -200,9 +200,10 @@ import sys, numpy as np, torch
 sys.path.insert(0, sys.argv[1])
 from instancesegmentation_b200 import Segment, synth
 z = np.load(sys.argv[2])
-m = Segment(3); m.load_state_dict({k: torch.from_numpy(z[k]) for k in z.files}); m.precision, m.max_batch = "bf16", 4
+B, H, W = (int(v) for v in sys.argv[4].split("x"))
+m = Segment(3); m.load_state_dict({k: torch.from_numpy(z[k]) for k in z.files}); m.precision, m.max_batch = "bf16", B
 m = m.cuda().eval()
-x = torch.from_numpy(synth.batch(4, 128, 192, seed=3)).cuda()
+x = torch.from_numpy(synth.batch(B, H, W, seed=3)).cuda()
 with torch.no_grad():
     y = m(x)
 torch.cuda.synchronize()
@@ -210,19 +211,25 @@ np.save(sys.argv[3], y.cpu().numpy())
 """
 
 
-def test_bf16_launch_variants_are_bitwise_identical(tmp_path):
-    """Every way the autotuner may run a fused launch (tile, CTAs per SM, load buffering) computes each
-    pixel with the same instruction sequence: logits must not depend on the choice."""
+@pytest.mark.parametrize("size,envs", [
+    ("4x128x192", [{"ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "1"},
+                   {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "2"}, {"ISG_FK_CTAS": "1", "ISG_FK_LBUF": "1"}]),
+    # 512x512: the residual-bottleneck runs go through the cluster-resident launch (csrc/mega.cuh)
+    ("3x512x512", [{"ISG_FK_NO_MEGA": "1", "ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_NO_MEGA8": "1"}]),
+])
+def test_bf16_launch_variants_are_bitwise_identical(tmp_path, size, envs):
+    """Every way a fused launch may run (tile, CTAs per SM, load buffering -- the autotuner's choices -- and
+    per-block launches vs one cluster launch per bottleneck run) computes each pixel with the same
+    instruction sequence: logits must not depend on the choice."""
     import subprocess, sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     script = tmp_path / "run.py"
     script.write_text(_MODE_SCRIPT)
     outs = []
-    for i, env in enumerate([{"ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "1"},
-                             {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "2"}, {"ISG_FK_CTAS": "1", "ISG_FK_LBUF": "1"}]):
+    for i, env in enumerate(envs):
         out = tmp_path / f"y{i}.npy"
         e = dict(os.environ, **env)
-        subprocess.run([sys.executable, str(script), root, os.path.join(GOLDEN, "segment3_state.npz"), str(out)],
+        subprocess.run([sys.executable, str(script), root, os.path.join(GOLDEN, "segment3_state.npz"), str(out), size],
                        check=True, env=e, timeout=600)
         outs.append(np.load(out))
     for i in range(1, len(outs)):
