@@ -1095,6 +1095,24 @@ struct FkBuilder {
                 if (getenv("ISG_FK_VERBOSE")) fprintf(stderr, "mega %s: %d co-resident clusters of %d, smem %zu\n", name.c_str(), nc, mega::CLUSTER, smem);
             }
             cfg.gridDim = dim3(mega::CLUSTER * std::min(*nclusters, std::max(n, 1)));
+            static const bool prof_on = getenv("ISG_MEGA_PROF") != nullptr;
+            if (prof_on) {   // debug: per-phase cycle sums of every CTA
+                const int grid = cfg.gridDim.x;
+                cudaMalloc(&p.prof, (size_t)grid * 8 * sizeof(long long));
+                cudaMemset(p.prof, 0, (size_t)grid * 8 * sizeof(long long));
+                cudaError_t e = cudaLaunchKernelEx(&cfg, mega::mega_kernel, maps->in[0], maps->out[0], p);
+                cudaStreamSynchronize(stream);
+                std::vector<long long> h((size_t)grid * 8);
+                cudaMemcpy(h.data(), p.prof, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+                cudaFree(p.prof);
+                double ph[8] = {0};
+                for (int b = 0; b < grid; ++b) for (int k = 0; k < 8; ++k) ph[k] += (double)h[(size_t)b * 8 + k];
+                const double steps = (double)n * nb * mega::CLUSTER;   // (image, block) steps summed over CTAs
+                fprintf(stderr, "megaprof %-12s cycles per block and CTA: wgt+gemm0 %6.0f epi_m1 %6.0f halo-barrier %6.0f stencil %6.0f "
+                        "gemm2 %6.0f epi_x %6.0f | x load per image %6.0f\n", name.c_str(), ph[1] / steps, ph[2] / steps,
+                        ph[3] / steps, ph[4] / steps, ph[5] / steps, ph[6] / steps, ph[0] / ((double)n * mega::CLUSTER));
+                return e;
+            }
             return cudaLaunchKernelEx(&cfg, mega::mega_kernel, maps->in[0], maps->out[0], p);
         };
         P->ops.push_back(op);

@@ -37,7 +37,10 @@ struct Params {
     int w0_off, v0_off, dw_off, dv_off, w2_off, v2_off;   // byte offsets inside one block's blob
     int x_off, m1_off, d_off, wbuf_off[2], bar_off;        // shared memory layout
     int tmem_cols;
+    long long* prof;              // debug (ISG_MEGA_PROF=1): per-CTA sums of phase cycles [8], else null
 };
+#define MEGA_ACC(i) do { if (p.prof && threadIdx.x == 0) { const long long t_ = clock64(); \
+    p.prof[(size_t)blockIdx.x * 8 + (i)] += t_ - tprev; tprev = t_; } } while (0)
 
 __device__ __forceinline__ uint32_t cluster_rank() {
     uint32_t r;
@@ -221,6 +224,7 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
 
     const int x_bytes = (p.Cs >> 3) * p.npx * 16;
     int seq = 0, mma_n = 0, it = 0;
+    long long tprev = p.prof ? clock64() : 0;
     bool pending2 = false;      // a cluster barrier arrival (m1 planes read) not yet waited for
     for (int img = cluster_id; img < p.nimg; img += nclusters, ++it) {
         if (tid == 0) {
@@ -229,6 +233,7 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
             tc::tma_load_5d(smem + p.x_off, &min, &bars[0], 0, 0, (int)rank * p.R, 0, img);
         }
         tc::mbar_wait(&bars[0], it & 1);
+        MEGA_ACC(0);   // x load
         for (int k = 0; k < p.nblocks; ++k, ++seq) {
             const int wbi = seq & 1;
             const uint8_t* wb = smem + p.wbuf_off[wbi];
@@ -244,11 +249,14 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
             __syncwarp();
             tc::mbar_wait(&bars[3], mma_n & 1); ++mma_n;
             tc::tc_fence_after();
+            MEGA_ACC(1);   // weights wait + first GEMM
             if (pending2) { cluster_wait(); pending2 = false; }   // neighbours have read their halo of the previous block
             epi_m1(smem, p, wb, tmem_base, blk.sep5 ? 2 : blk.dil, rank);
             tc::tc_fence_before();
+            MEGA_ACC(2);   // m1 epilogue (+ wait for the neighbours' previous reads)
             cluster_arrive();       // release: my rows (local and pushed) are written ...
             cluster_wait();         // ... acquire: so are the halo rows the neighbours pushed to me
+            MEGA_ACC(3);   // halo exchange barrier
             // ---- d = PReLU(dw(m1)) ----
             {
                 fk::Stencil st;
@@ -261,6 +269,7 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
             }
             tc::fence_proxy_async();
             __syncthreads();
+            MEGA_ACC(4);   // depthwise stencil
             cluster_arrive();       // my reads of the m1 planes are done (waited for before the next push)
             pending2 = true;
             // ---- x = PReLU(W2 . d + x) ----
@@ -273,10 +282,12 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
             __syncwarp();
             tc::mbar_wait(&bars[3], mma_n & 1); ++mma_n;
             tc::tc_fence_after();
+            MEGA_ACC(5);   // second GEMM
             epi_x(smem, p, wb, tmem_base);
             tc::fence_proxy_async();   // x planes: next read by tcgen05.mma / the TMA store
             tc::tc_fence_before();
             __syncthreads();
+            MEGA_ACC(6);   // x epilogue
             // this weight buffer is free: fetch the weights of step seq + 2
             if (tid == 0 && seq + 2 < total_seq) load_weights(seq + 2);
         }
