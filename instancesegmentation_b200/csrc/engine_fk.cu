@@ -255,6 +255,8 @@ struct Spec {
 struct Lay {
     int TH = 0, TW = 0, pitch = 0, n_mt = 0, cols = 0;
     int ctas = 1, nlbuf = 2;   // CTAs per SM (1: 512 threads, 2: 256 threads), load buffers of the generic loop
+    int pipe = 0;              // > 0: warp-specialised launch (fk_pipe_kernel) with this many load slots
+    int groups = 3;            // ... and this many epilogue warp groups (the other warps issue MMAs)
     size_t smem = 0;
     int load_off[fk::MAX_LOADS], load_plane[fk::MAX_LOADS], load_planes[fk::MAX_LOADS];
     int st_out_off = 0, st_out_plane = 0, st_in_pitch = 0;
@@ -288,6 +290,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, cud
 // programmatic dependent launch: the grid may be scheduled (prologue + constants) while the previous
 // kernel of the stream drains; fk_kernel orders its activation traffic with griddepcontrol.wait
 inline cudaError_t launch_fk(int ctas, int grid, size_t smem, const FkMaps& m, const fk::Params& p, cudaStream_t stream) {
+    if (p.pipe_slots) ctas = 1;
     static const bool pdl = getenv("ISG_FK_NO_PDL") == nullptr;
     cudaLaunchConfig_t cfg;
     std::memset(&cfg, 0, sizeof cfg);
@@ -297,6 +300,8 @@ inline cudaError_t launch_fk(int ctas, int grid, size_t smem, const FkMaps& m, c
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    if (p.pipe_slots)
+        return cudaLaunchKernelEx(&cfg, fk::fk_pipe_kernel, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
     if (ctas == 2)
         return cudaLaunchKernelEx(&cfg, fk::fk_kernel<256>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
     return cudaLaunchKernelEx(&cfg, fk::fk_kernel<512>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
@@ -373,14 +378,20 @@ struct FkBuilder {
     }
 
     // ---- layout of one candidate tile ----
-    bool layout(const Spec& s, int TH, int TW, int ctas, int nlbuf, Lay& L) const {
+    // single stage, no stencil / pooled output / residual: eligible for the warp-specialised kernel
+    static bool pipe_ok(const Spec& s) {
+        return s.stages.size() == 1 && !s.st.kind && s.pool_tensor < 0 && s.stages[0].res_load < 0 && !getenv("ISG_FK_NO_PIPE");
+    }
+    bool layout(const Spec& s, int TH, int TW, int ctas, int nlbuf, Lay& L, int pipe = 0) const {
         const int hx = s.stages[0].taps9 ? 1 : 0;
-        L.TH = TH; L.TW = TW; L.pitch = TW + 2 * hx; L.ctas = ctas; L.nlbuf = nlbuf;
+        L.TH = TH; L.TW = TW; L.pitch = TW + 2 * hx; L.ctas = ctas; L.nlbuf = nlbuf; L.pipe = pipe;
+        if (pipe) nlbuf = pipe;
         const int mrows = TH * L.pitch;
         L.n_mt = cdiv(mrows, 128);
         int maxN = 0;
         for (auto& st : s.stages) maxN = std::max(maxN, st.N);
         L.cols = L.n_mt * maxN;
+        if (pipe && 2 * L.cols > 512) return false;   // two accumulators
         if (L.cols > 512 || (int)tc::tmem_cols_pow2(L.cols) > 512 / ctas) return false;
         const int a_rows = L.n_mt * 128 + (hx ? 2 * L.pitch + 2 : 0);
         const int npix = TH * TW;
@@ -483,8 +494,13 @@ struct FkBuilder {
         const int env_lbuf = getenv("ISG_FK_LBUF") ? atoi(getenv("ISG_FK_LBUF")) : 0;
         const int per_mode = getenv("ISG_FK_TUNE_TOP") ? atoi(getenv("ISG_FK_TUNE_TOP")) : 3;
         std::vector<Lay> out;
-        for (int mode = 0; mode < 4; ++mode) {
-            const int c = mode & 1 ? 2 : 1, nb = mode & 2 ? 1 : 2;   // mode 0 = one double-buffered CTA per SM
+        for (int mode = 0; mode < 8; ++mode) {
+            // modes 0-3: generic kernel (mode 0 = one double-buffered CTA per SM); 4-7: warp-specialised,
+            // 2 / 3 load slots x 3 / 2 epilogue warp groups
+            const int pipe = mode >= 4 ? 2 + (mode & 1) : 0;
+            const int groups = mode >= 6 ? 2 : 3;
+            if (pipe && (!pipe_ok(s) || env_ctas || env_lbuf)) continue;
+            const int c = pipe ? 1 : (mode & 1 ? 2 : 1), nb = pipe ? 2 : (mode & 2 ? 1 : 2);
             if (!tune && mode && !(env_ctas || env_lbuf)) break;
             if (env_ctas && c != env_ctas) continue;
             if (env_lbuf && nb != env_lbuf) continue;
@@ -492,7 +508,8 @@ struct FkBuilder {
             std::vector<Lay> found;
             for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
                 Lay L;
-                if (!layout(s, TH, TW, c, nb, L)) continue;
+                if (!layout(s, TH, TW, c, nb, L, pipe)) continue;
+                L.groups = groups;
                 if (L.n_mt > mt_cap && TH > 1) continue;
                 const int tiles_y = cdiv(s.qH, TH);
                 const double eff_m = (double)(TH * TW) / (L.n_mt * 128);
@@ -525,7 +542,9 @@ struct FkBuilder {
         std::memset(&q, 0, sizeof q);
         q.TH = L.TH; q.TW = L.TW; q.H = s.qH; q.W = s.qW;
         q.tiles_x = cdiv(s.qW, L.TW); q.tiles_y = cdiv(s.qH, L.TH);
-        q.n_mt = L.n_mt; q.tmem_cols = tc::tmem_cols_pow2(L.cols);
+        q.n_mt = L.n_mt; q.tmem_cols = tc::tmem_cols_pow2(L.pipe ? 2 * L.cols : L.cols);
+        q.pipe_slots = L.pipe; q.acc_stride = L.cols;
+        q.pipe_groups = L.groups;
         auto magic = [](int d) -> uint32_t { return d > 1 ? (uint32_t)(((1ull << 32) + d - 1) / d) : 0u; };
         q.tw_magic = magic(L.TW); q.npix_magic = magic(L.TH * L.TW);
         q.nlbuf = L.nlbuf;
@@ -702,6 +721,7 @@ struct FkBuilder {
         });
         cudaFuncSetAttribute(fk::fk_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         cudaFuncSetAttribute(fk::fk_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024);
+        cudaFuncSetAttribute(fk::fk_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         int num_sms = 148;
         cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, P->device);
         auto run = [=](int which, int n, float* logits, cudaStream_t stream, bool prof) -> cudaError_t {
@@ -741,15 +761,15 @@ struct FkBuilder {
                 ms /= reps;
                 const Lay& L = (*vars)[i].L;
                 if (verbose)
-                    fprintf(stderr, "tune %-40s tile %3dx%-3d n_mt %2d ctas %d lbuf %d smem %6zu: %7.1f us\n", sp.name.c_str(),
-                            L.TH, L.TW, L.n_mt, L.ctas, L.nlbuf, L.smem, ms * 1e3);
+                    fprintf(stderr, "tune %-40s tile %3dx%-3d n_mt %2d ctas %d lbuf %d pipe %d smem %6zu: %7.1f us\n", sp.name.c_str(),
+                            L.TH, L.TW, L.n_mt, L.ctas, L.nlbuf, L.pipe * 10 + (L.pipe ? L.groups : 0), L.smem, ms * 1e3);
                 if (ms < best) { best = ms; *chosen = i; }
             }
             cudaEventDestroy(e0); cudaEventDestroy(e1);
             const Lay& L = (*vars)[*chosen].L;
             if (verbose)
-                fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d ctas %d lbuf %d\n",
-                        sp.name.c_str(), sp.qH, sp.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1], L.ctas, L.nlbuf);
+                fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d ctas %d lbuf %d pipe %d\n",
+                        sp.name.c_str(), sp.qH, sp.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1], L.ctas, L.nlbuf, L.pipe * 10 + (L.pipe ? L.groups : 0));
             return 0;
         });
         P->ops.push_back(op);

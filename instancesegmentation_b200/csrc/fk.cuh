@@ -85,6 +85,9 @@ struct Params {
     uint32_t tx_bytes;             // all TMA boxes of one tile
     int lbuf_stride;               // byte distance between the two load buffers (persistent double buffering)
     int total_tiles;               // batch * tiles_y * tiles_x of this launch
+    int pipe_slots;                // > 0: warp-specialised single-stage launch (fk_pipe_kernel) with this many load slots
+    int acc_stride;                // ... and two TMEM accumulators this many columns apart
+    int pipe_groups;               // ... and this many epilogue warp groups (of 4 warps); the rest issue MMAs
     int nlbuf;                     // load buffers of the generic loop: 2 = double buffered; 1 = the co-resident
                                    // CTA hides the load latency instead (two 256-thread CTAs per SM)
     int early_load;                // nlbuf == 1: the load buffer is dead once the stage-0 MMAs completed
@@ -313,12 +316,10 @@ __device__ __forceinline__ EpiGeom epi_geom(const Params& p, const Stage& s, int
     return g;
 }
 
-template <int NT>
 __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, const Stage& s, uint32_t tmem_base,
-                                             int b, int x0, int y0, int boff) {
-    constexpr int NGROUPS = NT / 128;
+                                             int b, int x0, int y0, int boff, int grp, int NGROUPS) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int quad = warp & 3, grp = warp >> 2;
+    const int quad = warp & 3;
     const int ncc = s.N >> 4, nitems = p.n_mt * ncc;
     int item = grp;
     if (item >= nitems) return;
@@ -511,7 +512,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             tc::tc_fence_after();
             if (k == 0 && p.pool_on) run_pool<NT>(smem, p, boff);   // before the load buffer may be refilled
             if (k == 0 && tid == 0 && !dbl && p.early_load && next < p.total_tiles) issue_loads(next, 0);
-            run_epilogue<NT>(smem, p, s, tmem_base, b, x0, y0, boff);
+            run_epilogue(smem, p, s, tmem_base, b, x0, y0, boff, warp >> 2, NT / 128);
             tc::fence_proxy_async();
             tc::tc_fence_before();
             __syncthreads();
@@ -536,6 +537,129 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
     if (tid == 0) tc::tma_store_wait_read();
     FK_STAMP(8);
     if (p.prof && tid == 0) p.prof[(size_t)blockIdx.x * 16 + 15] = globaltimer_ns();
+    if (warp == 1) {
+        tc::tc_fence_after();
+        tc::tmem_dealloc(tmem_base, p.tmem_cols);
+    }
+}
+
+// ---- warp-specialised variant for single-stage launches without stencil / residual ----
+// warps 0, 2, 3: MMA issuers (one lane each, M tiles interleaved -- a single thread cannot issue fast
+// enough to keep the tensor pipe busy); warp 1: TMA producer (one lane); warps 4..15: epilogue (three
+// groups of four TMEM lane quadrants).  Two TMEM accumulators and `pipe_slots` load slots: the tensor pipe works on
+// tile i+1 (and TMA on tile i+2) while the CUDA cores are in the epilogue of tile i.
+constexpr int PIPE_THREADS = 512;
+
+__device__ __forceinline__ void epi_bar_sync(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
+
+__global__ void __launch_bounds__(PIPE_THREADS, 1)
+fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtensorMap m1,
+               const __grid_constant__ CUtensorMap m2, const __grid_constant__ CUtensorMap m3,
+               const __grid_constant__ CUtensorMap mo0, const __grid_constant__ CUtensorMap mo1,
+               const __grid_constant__ Params p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    // bars: [0..2] slot full, [3..5] slot free, [6],[7] accumulator full, [8],[9] accumulator free, [10] blob
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.bar_off);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+    uint64_t* tabs = bars + 16;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const CUtensorMap* maps[4] = {&m0, &m1, &m2, &m3};
+    (void)mo1;
+    const Stage& s = p.stage[0];
+    const int nslots = p.pipe_slots;
+    // epilogue: the last 4 * pipe_groups warps; before them warp 1 produces, the others issue MMAs
+    const int PIPE_EPI_WARPS = 4 * p.pipe_groups, PIPE_EPI_WARP0 = PIPE_THREADS / 32 - PIPE_EPI_WARPS;
+    const int PIPE_ISSUERS = PIPE_EPI_WARP0 - 1;
+    if (tid == 0) {
+        for (int i = 0; i < 3; ++i) { tc::mbar_init(&bars[i], 1); tc::mbar_init(&bars[3 + i], PIPE_ISSUERS); }
+        tc::mbar_init(&bars[6], PIPE_ISSUERS); tc::mbar_init(&bars[7], PIPE_ISSUERS);
+        tc::mbar_init(&bars[8], PIPE_EPI_WARPS); tc::mbar_init(&bars[9], PIPE_EPI_WARPS);
+        tc::mbar_init(&bars[10], 1);
+        tc::fence_barrier_init();
+    }
+    if (warp == 1) tc::tmem_alloc(tmem_slot, p.tmem_cols);
+    build_desc_table<PIPE_THREADS>(p, tabs, tc::smem_u32(smem));
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t smem_base = tc::smem_u32(smem);
+    if (tid == 0) {
+        tc::mbar_expect_tx(&bars[10], p.blob_bytes);
+        bulk_g2s(smem + p.blob_off, p.blob, p.blob_bytes, &bars[10]);
+    }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int step = gridDim.x;
+
+    if (warp == 1) {
+        if (lane == 0) {   // ---- TMA producer ----
+            int it = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += step, ++it) {
+                const int slot = it % nslots, use = it / nslots;
+                if (use > 0) tc::mbar_wait(&bars[3 + slot], (use - 1) & 1);   // the MMAs that read this slot completed
+                const int txi = tile % p.tiles_x, r1 = tile / p.tiles_x;
+                const int tyi = r1 % p.tiles_y, bi = r1 / p.tiles_y;
+                tc::mbar_expect_tx(&bars[slot], p.tx_bytes);
+                for (int i = 0; i < p.nloads; ++i) {
+                    const Load& l = p.loads[i];
+                    const int cx = txi * p.TW * l.step + l.dx;
+                    const int cy = tyi * p.TH * l.step + l.dy + (l.folded ? bi * l.rows_per_img : 0);
+                    tc::tma_load_5d(smem + l.smem_off + slot * p.lbuf_stride, maps[l.map], &bars[slot], 0, cx, cy, l.chunk0,
+                                    l.folded ? 0 : bi);
+                }
+            }
+        }
+    } else if (warp < PIPE_EPI_WARP0) {
+        if (lane == 0) {   // ---- MMA issuers: M tiles first, first + PIPE_ISSUERS, ... ----
+            // (descriptors from the shared-memory table; a converged-warp variant with warp-uniform descriptor
+            // arithmetic was measured slower: ~19 dependent uniform-datapath instructions per MMA)
+            const int first = warp == 0 ? 0 : warp - 1;
+            tc::mbar_wait(&bars[10], 0);
+            int it = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += step, ++it) {
+                const int slot = it % nslots, use = it / nslots, acc = it & 1;
+                tc::mbar_wait(&bars[slot], use & 1);
+                if (it >= 2) tc::mbar_wait(&bars[8 + acc], ((it >> 1) - 1) & 1);   // the epilogue has drained this accumulator
+                tc::tc_fence_after();
+                issue_mma(p, s, tabs + slot * TAB_N, smem_base, tmem_base + acc * p.acc_stride, first, PIPE_ISSUERS);
+                tc::umma_commit(&bars[3 + slot]);
+                tc::umma_commit(&bars[6 + acc]);
+            }
+        }
+    } else if (warp >= PIPE_EPI_WARP0) {   // ---- epilogue ----
+        tc::mbar_wait(&bars[10], 0);
+        const bool stores = s.out_mode == OUT_STAGE && s.store;
+        const bool leader = tid == PIPE_EPI_WARP0 * 32;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += step, ++it) {
+            const int acc = it & 1;
+            const int txi = tile % p.tiles_x, r1 = tile / p.tiles_x;
+            const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
+            const int x0 = txi * p.TW, y0 = tyi * p.TH;
+            tc::mbar_wait(&bars[6 + acc], (it >> 1) & 1);
+            tc::tc_fence_after();
+            if (stores) {   // the previous tile's TMA store has read the (single) staging planes
+                if (leader) tc::tma_store_wait_read();
+                epi_bar_sync(PIPE_EPI_WARPS * 32);
+            }
+            run_epilogue(smem, p, s, tmem_base + acc * p.acc_stride, b, x0, y0, 0, (warp - PIPE_EPI_WARP0) >> 2, p.pipe_groups);
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&bars[8 + acc]);
+            if (stores) {
+                tc::fence_proxy_async();
+                epi_bar_sync(PIPE_EPI_WARPS * 32);
+                if (leader) {
+                    tc::tma_store_5d(&mo0, smem + s.stage_off, 0, x0, y0, s.store_chunk0, b);
+                    tc::tma_store_commit();
+                }
+            }
+        }
+        if (leader) tc::tma_store_wait_read();
+    }
+    tc::tc_fence_before();
+    __syncthreads();
     if (warp == 1) {
         tc::tc_fence_after();
         tc::tmem_dealloc(tmem_base, p.tmem_cols);
