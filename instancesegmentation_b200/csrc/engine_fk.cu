@@ -500,6 +500,7 @@ struct FkBuilder {
             const int pipe = mode >= 4 ? 2 + (mode & 1) : 0;
             const int groups = mode >= 6 ? 2 : 3;
             if (pipe && (!pipe_ok(s) || env_ctas || env_lbuf)) continue;
+            if (!pipe && getenv("ISG_FK_FORCE_PIPE") && pipe_ok(s)) continue;   // tests: every eligible launch warp-specialised
             const int c = pipe ? 1 : (mode & 1 ? 2 : 1), nb = pipe ? 2 : (mode & 2 ? 1 : 2);
             if (!tune && mode && !(env_ctas || env_lbuf)) break;
             if (env_ctas && c != env_ctas) continue;
