@@ -597,7 +597,7 @@ fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ C
             int it = 0;
             for (int tile = blockIdx.x; tile < p.total_tiles; tile += step, ++it) {
                 const int slot = it % nslots, use = it / nslots;
-                if (use > 0) tc::mbar_wait(&bars[3 + slot], (use - 1) & 1);   // the MMAs that read this slot completed
+                if (use > 0) tc::mbar_wait_backoff(&bars[3 + slot], (use - 1) & 1);   // the MMAs that read this slot completed
                 const int txi = tile % p.tiles_x, r1 = tile / p.tiles_x;
                 const int tyi = r1 % p.tiles_y, bi = r1 / p.tiles_y;
                 tc::mbar_expect_tx(&bars[slot], p.tx_bytes);
@@ -619,8 +619,8 @@ fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ C
             int it = 0;
             for (int tile = blockIdx.x; tile < p.total_tiles; tile += step, ++it) {
                 const int slot = it % nslots, use = it / nslots, acc = it & 1;
-                tc::mbar_wait(&bars[slot], use & 1);
-                if (it >= 2) tc::mbar_wait(&bars[8 + acc], ((it >> 1) - 1) & 1);   // the epilogue has drained this accumulator
+                tc::mbar_wait_backoff(&bars[slot], use & 1);
+                if (it >= 2) tc::mbar_wait_backoff(&bars[8 + acc], ((it >> 1) - 1) & 1);   // the epilogue has drained this accumulator
                 tc::tc_fence_after();
                 issue_mma(p, s, tabs + slot * TAB_N, smem_base, tmem_base + acc * p.acc_stride, first, PIPE_ISSUERS);
                 tc::umma_commit(&bars[3 + slot]);

@@ -46,6 +46,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
 }
 
+// the same for single-lane role threads (TMA producer, MMA issuer): back off between polls so that the
+// spinning lane does not take issue slots from the warps doing the arithmetic on the same scheduler
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "nanosleep.u32 40;\n\t"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+
 // ---------------- proxies / fences ----------------
 __device__ __forceinline__ void fence_proxy_async() {  // generic-proxy smem writes -> async proxy (TMA, UMMA)
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

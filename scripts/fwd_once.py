@@ -9,6 +9,10 @@ m = Segment(3); m.load_state_dict({k: torch.from_numpy(z[k]) for k in z.files});
 m = m.cuda().eval()
 x = torch.from_numpy(np.tile(synth.batch(4, S, S, seed=1), (B // 4, 1, 1, 1))).cuda()
 with torch.no_grad():
+    m(x)                                   # plan creation + autotune + first forward stay outside the capture
+    torch.cuda.synchronize()
+    torch.cuda.profiler.start()            # ncu --profile-from-start off
     y = m(x)
-torch.cuda.synchronize()
+    torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
 print("ok", float(y.abs().mean()))
