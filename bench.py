@@ -221,6 +221,12 @@ def run_ours(args, rank, world, local_rank):
         conv_tf = (B * K * flop_img) / (fwd_ms * 1e-3) / 1e12           # per GPU
         dec_bytes = B * (S * S * DECODE_BYTES_PER_PIXEL + 20)
         dec_gbs = dec_bytes * K / (dec_ms * 1e-3) / 1e9
+        # dram__bytes_read.sum + dram__bytes_write.sum from ncu at exactly this workload (bytes per forward of 64
+        # images summed over its 23 launches / per decode launch): profiles/r1f_dram_traffic_per_launch.txt,
+        # profiles/r1f_ncu_decode_kernel.txt.  Any other workload has no capture -> null.
+        cfg2 = (B == 64 and S == 512 and args.precision == "bf16")
+        conv_traffic = 1355.4e6 if cfg2 else None
+        dec_traffic = 69.74e6 if cfg2 else None
         line = {
             "metric": "images/sec", "value": imgs / (total_ms * 1e-3), "unit": "images/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
@@ -231,12 +237,12 @@ def run_ours(args, rank, world, local_rank):
                        "l2": f"inputs rotate over {NBUF} batches ({NBUF * B * 3 * S * S * 4 / 1e6:.0f} MB) and the "
                              f"activation workspace is {eng.workspace_bytes / 1e6:.0f} MB, both > 126 MB L2"},
             "roofline": {"bound": "tensor", "achieved": conv_tf, "peak": pk["tf_sust"] / 1e0, "unit": "TFLOP/s",
-                         "frac": conv_tf / pk["tf_sust"], "traffic": None,
+                         "frac": conv_tf / pk["tf_sust"], "traffic": conv_traffic,
                          "what": f"conv stack ({eng.launches_per_forward} launches/forward), algorithmic "
                                  f"{flop_img / 1e9:.4f} GFLOP/image, peak = sustained bf16 of {pk['src']}",
                          "ms_per_forward": fwd_ms / K},
             "roofline_decode": {"bound": "hbm", "achieved": dec_gbs, "peak": pk["hbm"], "unit": "GB/s",
-                                "frac": dec_gbs / pk["hbm"], "traffic": None, "bytes_per_launch": dec_bytes,
+                                "frac": dec_gbs / pk["hbm"], "traffic": dec_traffic, "bytes_per_launch": dec_bytes,
                                 "ms_per_decode": dec_ms / K},
             "e2e": {"value": imgs / (e2e_ms * 1e-3), "unit": "images/s",
                     "h2d_bytes_per_step": B * 3 * S * S * 4, "d2h_bytes_per_step": B * S * S + B * 20,
