@@ -4,7 +4,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libisg.so")
+# ISG_LIB: experiments only (an A/B build made by scripts/build_variant.sh); still a libisg build, never a fallback
+LIB_PATH = os.environ.get("ISG_LIB") or os.path.join(_HERE, "libisg.so")
 _lib = None
 
 MODE_FP32, MODE_BF16 = 0, 1

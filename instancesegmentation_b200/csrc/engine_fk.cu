@@ -486,7 +486,7 @@ struct FkBuilder {
         // tile width: the image width split evenly so that every TMA box fits 256 columns
         int nx = 1;
         while (cdiv(s.qW, nx) + 2 * max_halo > 256) ++nx;
-        const int TW = cdiv(s.qW, nx);
+        const int TW0 = cdiv(s.qW, nx);
         const char* cap_env = getenv("ISG_FK_MAX_MT");
         const int mt_cap = cap_env ? atoi(cap_env) : 16;
         const bool tune = !getenv("ISG_FK_NO_TUNE");
@@ -507,7 +507,11 @@ struct FkBuilder {
             if (env_lbuf && nb != env_lbuf) continue;
             const int slots = 148 * c;
             std::vector<Lay> found;
+            // half-width tiles trade halo columns for more rows per tile (better M-tile fill when few rows fit)
+            for (int split = 1; split <= (tune && !getenv("ISG_FK_NO_SPLIT") ? 2 : 1); ++split)
             for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
+                const int TW = cdiv(s.qW, nx * split);
+                if (split > 1 && TW < 32) continue;
                 Lay L;
                 if (!layout(s, TH, TW, c, nb, L, pipe)) continue;
                 L.groups = groups;
@@ -515,7 +519,7 @@ struct FkBuilder {
                 const int tiles_y = cdiv(s.qH, TH);
                 const double eff_m = (double)(TH * TW) / (L.n_mt * 128);
                 const double eff_tail = (double)s.qH / (tiles_y * TH);
-                const double eff_halo = (double)TH / (TH + 2 * max_halo);
+                const double eff_halo = (double)TH / (TH + 2 * max_halo) * TW / (TW + 2 * max_halo);
                 const long total = (long)P->max_batch * tiles_y * cdiv(s.qW, TW);
                 const double eff_wave = (double)total / (double)(cdiv((int)total, slots) * (long)slots);
                 L.score = eff_m * eff_tail * (0.5 + 0.5 * eff_halo) * (0.3 + 0.7 * eff_wave) + 1e-4 * TH;
@@ -528,8 +532,8 @@ struct FkBuilder {
         if (out.empty() && (env_ctas || env_lbuf)) {   // pinned mode infeasible for this launch: default mode
             for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
                 Lay L;
-                if (!layout(s, TH, TW, 1, 2, L)) continue;
-                L.score = (double)(TH * TW) / (L.n_mt * 128) + 1e-4 * TH;
+                if (!layout(s, TH, TW0, 1, 2, L)) continue;
+                L.score = (double)(TH * TW0) / (L.n_mt * 128) + 1e-4 * TH;
                 if (out.empty() || L.score > out[0].score) { out.clear(); out.push_back(L); }
             }
         }
@@ -768,9 +772,17 @@ struct FkBuilder {
             }
             cudaEventDestroy(e0); cudaEventDestroy(e1);
             const Lay& L = (*vars)[*chosen].L;
-            if (verbose)
-                fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d ctas %d lbuf %d pipe %d\n",
-                        sp.name.c_str(), sp.qH, sp.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1], L.ctas, L.nlbuf, L.pipe * 10 + (L.pipe ? L.groups : 0));
+            if (verbose) {
+                // issue floor: every MMA of this shape costs >= 32 clk (4 KB A operand from shared memory)
+                const fk::Params& q = (*vars)[*chosen].q;
+                long mma = 0;
+                for (int k = 0; k < q.nstages; ++k) mma += (long)q.stage[k].nent * q.n_mt;
+                mma *= (long)maxB * q.tiles_x * q.tiles_y;
+                fprintf(stderr, "fk %-34s q %4dx%-4d tile %3dx%-3d n_mt %2d cols %3d smem %6zu K %d,%d ctas %d lbuf %d pipe %d"
+                        "  best %6.1f us  mma %ld (floor %.1f us)\n",
+                        sp.name.c_str(), sp.qH, sp.qW, L.TH, L.TW, L.n_mt, L.cols, L.smem, L.K[0], L.K[1], L.ctas, L.nlbuf,
+                        L.pipe * 10 + (L.pipe ? L.groups : 0), best * 1e3, mma, mma * 32.0 / 148 / 1965.0);
+            }
             return 0;
         });
         P->ops.push_back(op);
@@ -1031,6 +1043,7 @@ struct FkBuilder {
         for (size_t i = 0; i < blocks.size(); ++i) {
             const MegaBlock& b = blocks[i];
             q.blk[i].dil = b.five ? 1 : b.dil; q.blk[i].sep5 = b.five ? 1 : 0;
+            q.blk[i].sr = 4 * q.blk[i].dil <= q.R ? 4 : 2;   // stencil strip height (rows `dil` apart) within the CTA's rows
             Next n0; n0.on = true; n0.unit = b.p + ".convs.0"; n0.mid = mid; n0.act = ACT_PRELU;
             Fills f;
             f.f0 = chain_stage(n0, C, q.Cs).fill;
@@ -1129,9 +1142,13 @@ struct FkBuilder {
                 double ph[8] = {0};
                 for (int b = 0; b < grid; ++b) for (int k = 0; k < 8; ++k) ph[k] += (double)h[(size_t)b * 8 + k];
                 const double steps = (double)n * nb * mega::CLUSTER;   // (image, block) steps summed over CTAs
-                fprintf(stderr, "megaprof %-12s cycles per block and CTA: wgt+gemm0 %6.0f epi_m1 %6.0f halo-barrier %6.0f stencil %6.0f "
-                        "gemm2 %6.0f epi_x %6.0f | x load per image %6.0f\n", name.c_str(), ph[1] / steps, ph[2] / steps,
-                        ph[3] / steps, ph[4] / steps, ph[5] / steps, ph[6] / steps, ph[0] / ((double)n * mega::CLUSTER));
+                int n5 = 0;
+                for (int k = 0; k < nb; ++k) n5 += p.blk[k].sep5;
+                const double s3 = steps * (nb - n5) / nb, s5 = steps * n5 / nb;
+                fprintf(stderr, "megaprof %-12s cycles per block and CTA: wgt+gemm0 %6.0f epi_m1 %6.0f halo-barrier %6.0f stencil 3x3 %6.0f "
+                        "5x5 %6.0f gemm2 %6.0f epi_x %6.0f | x load per image %6.0f\n", name.c_str(), ph[1] / steps, ph[2] / steps,
+                        ph[3] / steps, s3 > 0 ? ph[4] / s3 : 0.0, s5 > 0 ? ph[7] / s5 : 0.0, ph[5] / steps, ph[6] / steps,
+                        ph[0] / ((double)n * mega::CLUSTER));
                 return e;
             }
             return cudaLaunchKernelEx(&cfg, mega::mega_kernel, maps->in[0], maps->out[0], p);

@@ -149,69 +149,92 @@ __device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
 }
 
 // ---- depthwise stencil: haloed input planes -> A operand planes ----
-// SEP5 = false: 3x3 with dilation; SEP5 = true: the composed (5,1)x(1,5) pair (25 taps)
-template <bool SEP5, int NT>
-__device__ __forceinline__ void run_stencil(uint8_t* smem, const Stencil& s, int TH, int TW, int Wimg, uint32_t npix_magic,
-                                            uint32_t tw_magic, int x0, int boff) {
-    constexpr int KS = SEP5 ? 5 : 3;
-    const int npix = TH * TW, C = s.nchunks * 8;
-    const int dil = SEP5 ? 1 : s.dil, pitch = s.in_pitch;
+// SEP5 = false: 3x3 with dilation; SEP5 = true: the composed (5,1)x(1,5) pair (25 taps).
+// A thread owns one channel pair of one column and a strip of ST_ROWS output rows DIL apart, so every
+// input row it loads feeds up to KS outputs from registers, and its KS*KS weight pairs live in registers.
+// The four lanes of a pixel read the four 4-byte quarters of its 16-byte chunk: a warp's load is eight
+// neighbouring columns = 128 contiguous bytes, one shared-memory wavefront.  Each output accumulates its
+// taps in (ty, tx) order from zero, whatever the strip it falls in.
+// Output rows [rb, TH) of the tile; ST_ROWS = rows per strip.
+template <int KS, int DIL, int ST_ROWS, int NT>
+__device__ __forceinline__ void stencil_strips(uint8_t* smem, const Stencil& s, int rb, int TH, int TW, int Wimg, int x0, int boff) {
+    constexpr int NW = NT / 32, R = KS / 2;
+    const int C = s.nchunks * 8, pitch16 = s.in_pitch * 16;
     const float* wt = reinterpret_cast<const float*>(smem + s.w_off);
     const float* vec = reinterpret_cast<const float*>(smem + s.vec_off);
-    {
-        for (int item = threadIdx.x; item < npix * s.nchunks; item += NT) {
-            const int k = fastdiv(item, npix_magic), pix = item - k * npix;
-            const uint8_t* plane = smem + s.in_off + boff + (size_t)k * s.in_plane_bytes;
-            const float* wk = wt + k * 8;
-            const int r = fastdiv(pix, tw_magic), c = pix - r * TW;
-            // top-left tap of this pixel
-            const uint8_t* in = plane + (size_t)((r + s.halo - (KS / 2) * dil) * pitch + c + s.halo - (KS / 2) * dil) * 16;
-            float2 acc[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) acc[e] = make_float2(0.f, 0.f);
-#pragma unroll
-            for (int ty = 0; ty < KS; ++ty) {
-                uint4 q[KS];
-#pragma unroll
-                for (int tx = 0; tx < KS; ++tx)
-                    q[tx] = *reinterpret_cast<const uint4*>(in + (size_t)(ty * dil * pitch + tx * dil) * 16);
-#pragma unroll
-                for (int tx = 0; tx < KS; ++tx) {
-                    const float4 w0 = *reinterpret_cast<const float4*>(wk + (ty * KS + tx) * C);
-                    const float4 w1 = *reinterpret_cast<const float4*>(wk + (ty * KS + tx) * C + 4);
-                    acc[0] = ffma2(bf2_to_f2(q[tx].x), make_float2(w0.x, w0.y), acc[0]);
-                    acc[1] = ffma2(bf2_to_f2(q[tx].y), make_float2(w0.z, w0.w), acc[1]);
-                    acc[2] = ffma2(bf2_to_f2(q[tx].z), make_float2(w1.x, w1.y), acc[2]);
-                    acc[3] = ffma2(bf2_to_f2(q[tx].w), make_float2(w1.z, w1.w), acc[3]);
-                }
-            }
-            float4 sh0 = *reinterpret_cast<const float4*>(vec + k * 8), sh1 = *reinterpret_cast<const float4*>(vec + k * 8 + 4);
-            const float4 sl0 = *reinterpret_cast<const float4*>(vec + C + k * 8);
-            const float4 sl1 = *reinterpret_cast<const float4*>(vec + C + k * 8 + 4);
-            if (SEP5) {
-                // bias of the bare (5,1) conv seen through the (1,5) conv: only taps inside the image
-                const int xa = x0 + c;
-#pragma unroll
-                for (int kx = 0; kx < 5; ++kx) {
-                    const int xx = xa + kx - 2;
-                    if (xx >= 0 && xx < Wimg) {
-                        const float4 b0 = *reinterpret_cast<const float4*>(vec + (2 + kx) * C + k * 8);
-                        const float4 b1 = *reinterpret_cast<const float4*>(vec + (2 + kx) * C + k * 8 + 4);
-                        sh0.x += b0.x; sh0.y += b0.y; sh0.z += b0.z; sh0.w += b0.w;
-                        sh1.x += b1.x; sh1.y += b1.y; sh1.z += b1.z; sh1.w += b1.w;
-                    }
-                }
-            }
-            float a0 = acc[0].x + sh0.x, a1 = acc[0].y + sh0.y, a2 = acc[1].x + sh0.z, a3 = acc[1].y + sh0.w;
-            float a4 = acc[2].x + sh1.x, a5 = acc[2].y + sh1.y, a6 = acc[3].x + sh1.z, a7 = acc[3].y + sh1.w;
-            a0 = a0 >= 0.f ? a0 : a0 * sl0.x; a1 = a1 >= 0.f ? a1 : a1 * sl0.y;
-            a2 = a2 >= 0.f ? a2 : a2 * sl0.z; a3 = a3 >= 0.f ? a3 : a3 * sl0.w;
-            a4 = a4 >= 0.f ? a4 : a4 * sl1.x; a5 = a5 >= 0.f ? a5 : a5 * sl1.y;
-            a6 = a6 >= 0.f ? a6 : a6 * sl1.z; a7 = a7 >= 0.f ? a7 : a7 * sl1.w;
-            *reinterpret_cast<uint4*>(smem + s.out_off + (size_t)k * s.out_plane_bytes + (size_t)pix * 16) =
-                make_uint4(pack_bf16(a0, a1), pack_bf16(a2, a3), pack_bf16(a4, a5), pack_bf16(a6, a7));
+    const int lane = threadIdx.x & 31, sub = lane & 3, cl = lane >> 2;
+    const int ncg = (TW + 7) >> 3;                         // groups of 8 columns
+    const int ngroups = (TH - rb + ST_ROWS * DIL - 1) / (ST_ROWS * DIL);   // row groups; each holds DIL interleaved strips
+    const int last_row = TH + 2 * s.halo - 1;
+    // warp item = (chunk k, row group g, strip sd within the group, column group cg), cg fastest
+    int cg = threadIdx.x >> 5, sd = 0, g = 0, k = 0;
+    for (;;) {
+        while (cg >= ncg) {
+            cg -= ncg;
+            if (++sd == DIL) { sd = 0; if (++g == ngroups) { g = 0; ++k; } }
         }
+        if (k >= s.nchunks) break;
+        const int c = cg * 8 + cl, cld = c < TW ? c : TW - 1;
+        const int r0 = rb + g * (ST_ROWS * DIL) + sd;
+        const int ch = k * 8 + sub * 2;
+        float2 w[KS * KS];
+#pragma unroll
+        for (int t = 0; t < KS * KS; ++t) w[t] = *reinterpret_cast<const float2*>(wt + t * C + ch);
+        const int row0 = r0 + s.halo - R * DIL;            // plane row of the first input row
+        const uint8_t* in = smem + s.in_off + boff + (size_t)k * s.in_plane_bytes + sub * 4 + (cld + s.halo - R * DIL) * 16;
+        const int rmax = last_row - row0;                  // rows past the planes only feed outputs past the tile: clamp
+        float2 acc[ST_ROWS];
+#pragma unroll
+        for (int j = 0; j < ST_ROWS; ++j) acc[j] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int iy = 0; iy < ST_ROWS + KS - 1; ++iy) {
+            const uint8_t* row = in + (row0 + min(iy * DIL, rmax)) * pitch16;
+            float2 v[KS];
+#pragma unroll
+            for (int tx = 0; tx < KS; ++tx) v[tx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(row + tx * DIL * 16));
+#pragma unroll
+            for (int j = 0; j < ST_ROWS; ++j) {
+                const int ty = iy - j;
+                if (ty >= 0 && ty < KS) {
+#pragma unroll
+                    for (int tx = 0; tx < KS; ++tx) acc[j] = ffma2(v[tx], w[ty * KS + tx], acc[j]);
+                }
+            }
+        }
+        float2 sh = *reinterpret_cast<const float2*>(vec + ch);
+        const float2 sl = *reinterpret_cast<const float2*>(vec + C + ch);
+        if (KS == 5) {
+            // bias of the bare (5,1) conv seen through the (1,5) conv: only taps inside the image
+            const int xa = x0 + c;
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx) {
+                const int xx = xa + kx - 2;
+                if (xx >= 0 && xx < Wimg) {
+                    const float2 b = *reinterpret_cast<const float2*>(vec + (2 + kx) * C + ch);
+                    sh.x += b.x; sh.y += b.y;
+                }
+            }
+        }
+        uint8_t* out = smem + s.out_off + (size_t)k * s.out_plane_bytes + sub * 4 + (r0 * TW + c) * 16;
+        const int nrows = c < TW ? TH - r0 : 0;            // outputs j with j * DIL < nrows exist
+#pragma unroll
+        for (int j = 0; j < ST_ROWS; ++j) {
+            float a0 = acc[j].x + sh.x, a1 = acc[j].y + sh.y;
+            a0 = a0 >= 0.f ? a0 : a0 * sl.x; a1 = a1 >= 0.f ? a1 : a1 * sl.y;
+            const uint32_t o = pack_bf16(a0, a1);
+            if (j * DIL < nrows) *reinterpret_cast<uint32_t*>(out + j * DIL * TW * 16) = o;
+        }
+        cg += NW;
     }
+}
+
+// SEP5 = false: 3x3 with dilation 1 / 2 / 4 (segment.py:399-418); SEP5 = true: the composed 5x5
+template <bool SEP5, int NT>
+__device__ __forceinline__ void run_stencil(uint8_t* smem, const Stencil& s, int TH, int TW, int Wimg, int x0, int boff) {
+    if (SEP5) stencil_strips<5, 1, 4, NT>(smem, s, 0, TH, TW, Wimg, x0, boff);
+    else if (s.dil == 1) stencil_strips<3, 1, 4, NT>(smem, s, 0, TH, TW, Wimg, x0, boff);
+    else if (s.dil == 2) stencil_strips<3, 2, 4, NT>(smem, s, 0, TH, TW, Wimg, x0, boff);
+    else stencil_strips<3, 4, 4, NT>(smem, s, 0, TH, TW, Wimg, x0, boff);
 }
 
 __device__ __forceinline__ uint32_t bf2max(uint32_t a, uint32_t b) {
@@ -491,8 +514,8 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         if (it == 0) FK_STAMP(2);
 
         if (p.st.on) {
-            if (p.st.sep5) run_stencil<true, NT>(smem, p.st, p.TH, p.TW, p.W, p.npix_magic, p.tw_magic, x0, boff);
-            else run_stencil<false, NT>(smem, p.st, p.TH, p.TW, p.W, p.npix_magic, p.tw_magic, x0, boff);
+            if (p.st.sep5) run_stencil<true, NT>(smem, p.st, p.TH, p.TW, p.W, x0, boff);
+            else run_stencil<false, NT>(smem, p.st, p.TH, p.TW, p.W, x0, boff);
             tc::fence_proxy_async();
             __syncthreads();
         }

@@ -22,7 +22,7 @@ constexpr int CLUSTER = 4;
 constexpr int HALO = 4;           // rows / columns of zero (or neighbour) halo around m1: max dilation
 constexpr int MAX_BLOCKS = 5;
 
-struct Block { int dil, sep5; };
+struct Block { int dil, sep5, sr; };   // sr: output rows per stencil strip (4 / 2): 4 unless sr * dil would exceed the CTA's rows
 
 struct Params {
     int H, W, R;                  // image rows / columns at this resolution, rows per CTA (H = 4 R)
@@ -48,6 +48,7 @@ __device__ __forceinline__ uint32_t cluster_rank() {
     return r;
 }
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 // 16-byte store into the shared memory of CTA `rank` of the cluster at the same offset as local address `laddr`
 __device__ __forceinline__ void st_remote_16(uint32_t laddr, uint32_t rank, uint4 v) {
@@ -71,15 +72,16 @@ __device__ __forceinline__ void issue_gemm(uint32_t a_addr, int a_plane_bytes, u
 }
 
 // ---- epilogue of the first GEMM: m1 = PReLU(acc + shift) -> zero-haloed m1 planes (+ neighbours' halo rows) ----
+// (M tiles mt0 .. mt0 + nmt - 1)
 __device__ __forceinline__ void epi_m1(uint8_t* smem, const Params& p, const uint8_t* wb, uint32_t tmem_base, int reach,
-                                       uint32_t rank) {
+                                       uint32_t rank, int mt0, int nmt) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, quad = warp & 3, grp = warp >> 2;
-    const int ncc = p.Cm >> 4, nitems = p.n_mt * ncc;
+    const int ncc = p.Cm >> 4, nitems = nmt * ncc;
     const float* vec = reinterpret_cast<const float*>(wb + p.v0_off);
-    const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16) + mt0 * p.Cm;
     const int plane_bytes = p.rows_p * p.pitch * 16;
     for (int item = grp; item < nitems; item += NGROUPS) {
-        int mt = 0, cc = item;
+        int mt = mt0, cc = item;
         while (cc >= ncc) { cc -= ncc; ++mt; }
         uint32_t ra[16];
         __syncwarp();
@@ -123,15 +125,16 @@ __device__ __forceinline__ void epi_m1(uint8_t* smem, const Params& p, const uin
 }
 
 // ---- epilogue of the second GEMM: x = PReLU(acc + shift + x), in place in the resident x planes ----
-__device__ __forceinline__ void epi_x(uint8_t* smem, const Params& p, const uint8_t* wb, uint32_t tmem_base) {
+// (M tiles mt0 .. mt0 + nmt - 1)
+__device__ __forceinline__ void epi_x(uint8_t* smem, const Params& p, const uint8_t* wb, uint32_t tmem_base, int mt0, int nmt) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, quad = warp & 3, grp = warp >> 2;
-    const int ncc = p.Cs >> 4, nitems = p.n_mt * ncc;
+    const int ncc = p.Cs >> 4, nitems = nmt * ncc;
     const float* vec = reinterpret_cast<const float*>(wb + p.v2_off);
-    const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16) + mt0 * p.Cs;
     const int plane_bytes = p.npx * 16;
     int item = grp;
     if (item >= nitems) return;
-    int mt = 0, cc = item;
+    int mt = mt0, cc = item;
     while (cc >= ncc) { cc -= ncc; ++mt; }
     uint32_t ra[16];
     __syncwarp();
@@ -170,6 +173,23 @@ __device__ __forceinline__ void epi_x(uint8_t* smem, const Params& p, const uint
         item = nxt;
         cc += NGROUPS;
         while (cc >= ncc) { cc -= ncc; ++mt; }
+    }
+}
+
+// depthwise stencil of output rows [rb, re) with the strip height the host chose for this block
+__device__ __forceinline__ void stencil(uint8_t* smem, const fk::Stencil& st, const Block& blk, int rb, int re, int W) {
+    if (blk.sep5) {
+        if (blk.sr == 4) fk::stencil_strips<5, 1, 4, THREADS>(smem, st, rb, re, W, W, 0, 0);
+        else fk::stencil_strips<5, 1, 2, THREADS>(smem, st, rb, re, W, W, 0, 0);
+    } else if (blk.dil == 1) {
+        if (blk.sr == 4) fk::stencil_strips<3, 1, 4, THREADS>(smem, st, rb, re, W, W, 0, 0);
+        else fk::stencil_strips<3, 1, 2, THREADS>(smem, st, rb, re, W, W, 0, 0);
+    } else if (blk.dil == 2) {
+        if (blk.sr == 4) fk::stencil_strips<3, 2, 4, THREADS>(smem, st, rb, re, W, W, 0, 0);
+        else fk::stencil_strips<3, 2, 2, THREADS>(smem, st, rb, re, W, W, 0, 0);
+    } else {
+        if (blk.sr == 4) fk::stencil_strips<3, 4, 4, THREADS>(smem, st, rb, re, W, W, 0, 0);
+        else fk::stencil_strips<3, 4, 2, THREADS>(smem, st, rb, re, W, W, 0, 0);
     }
 }
 
@@ -251,7 +271,7 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
             tc::tc_fence_after();
             MEGA_ACC(1);   // weights wait + first GEMM
             if (pending2) { cluster_wait(); pending2 = false; }   // neighbours have read their halo of the previous block
-            epi_m1(smem, p, wb, tmem_base, blk.sep5 ? 2 : blk.dil, rank);
+            epi_m1(smem, p, wb, tmem_base, blk.sep5 ? 2 : blk.dil, rank, 0, p.n_mt);
             tc::tc_fence_before();
             MEGA_ACC(2);   // m1 epilogue (+ wait for the neighbours' previous reads)
             cluster_arrive();       // release: my rows (local and pushed) are written ...
@@ -264,13 +284,15 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
                 st.halo = HALO; st.nchunks = p.Cm >> 3; st.dil = blk.dil;
                 st.w_off = p.wbuf_off[wbi] + p.dw_off; st.vec_off = p.wbuf_off[wbi] + p.dv_off; st.sep5 = blk.sep5;
                 st.out_off = p.d_off; st.out_plane_bytes = p.npx * 16;
-                if (blk.sep5) fk::run_stencil<true, THREADS>(smem, st, p.R, p.W, p.W, p.npx_magic, p.w_magic, 0, 0);
-                else fk::run_stencil<false, THREADS>(smem, st, p.R, p.W, p.W, p.npx_magic, p.w_magic, 0, 0);
+                stencil(smem, st, blk, 0, p.R, p.W);
             }
             tc::fence_proxy_async();
             __syncthreads();
-            MEGA_ACC(4);   // depthwise stencil
-            cluster_arrive();       // my reads of the m1 planes are done (waited for before the next push)
+            MEGA_ACC(blk.sep5 ? 7 : 4);   // depthwise stencil (slot 7: the 25-tap kind)
+            // my reads of the m1 planes are done (their values are consumed): no memory ordering to publish, so
+            // the arrival is relaxed -- a releasing one drains every outstanding store first.  Waited for before
+            // the next block's pushes.
+            cluster_arrive_relaxed();
             pending2 = true;
             // ---- x = PReLU(W2 . d + x) ----
             if ((tid & 31) == 0 && warp < n_issuers) {
@@ -283,7 +305,7 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
             tc::mbar_wait(&bars[3], mma_n & 1); ++mma_n;
             tc::tc_fence_after();
             MEGA_ACC(5);   // second GEMM
-            epi_x(smem, p, wb, tmem_base);
+            epi_x(smem, p, wb, tmem_base, 0, p.n_mt);
             tc::fence_proxy_async();   // x planes: next read by tcgen05.mma / the TMA store
             tc::tc_fence_before();
             __syncthreads();
