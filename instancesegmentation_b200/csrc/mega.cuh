@@ -95,11 +95,10 @@ __device__ __forceinline__ void epi_m1(uint8_t* smem, const Params& p, const uin
         for (int j = 0; j < 4; ++j) {
             const float4 sh = *reinterpret_cast<const float4*>(vec + col0 + 4 * j);
             const float4 sl = *reinterpret_cast<const float4*>(vec + p.Cm + col0 + 4 * j);
-            float a;
-            a = __uint_as_float(ra[4 * j + 0]) + sh.x; v[4 * j + 0] = a >= 0.f ? a : a * sl.x;
-            a = __uint_as_float(ra[4 * j + 1]) + sh.y; v[4 * j + 1] = a >= 0.f ? a : a * sl.y;
-            a = __uint_as_float(ra[4 * j + 2]) + sh.z; v[4 * j + 2] = a >= 0.f ? a : a * sl.z;
-            a = __uint_as_float(ra[4 * j + 3]) + sh.w; v[4 * j + 3] = a >= 0.f ? a : a * sl.w;
+            const float2 a = fk::fadd2(make_float2(__uint_as_float(ra[4 * j]), __uint_as_float(ra[4 * j + 1])), make_float2(sh.x, sh.y));
+            const float2 b = fk::fadd2(make_float2(__uint_as_float(ra[4 * j + 2]), __uint_as_float(ra[4 * j + 3])), make_float2(sh.z, sh.w));
+            v[4 * j + 0] = a.x >= 0.f ? a.x : a.x * sl.x; v[4 * j + 1] = a.y >= 0.f ? a.y : a.y * sl.y;
+            v[4 * j + 2] = b.x >= 0.f ? b.x : b.x * sl.z; v[4 * j + 3] = b.y >= 0.f ? b.y : b.y * sl.w;
         }
         const uint4 q0 = make_uint4(fk::pack_bf16(v[0], v[1]), fk::pack_bf16(v[2], v[3]), fk::pack_bf16(v[4], v[5]),
                                     fk::pack_bf16(v[6], v[7]));
@@ -125,7 +124,31 @@ __device__ __forceinline__ void epi_m1(uint8_t* smem, const Params& p, const uin
 }
 
 // ---- epilogue of the second GEMM: x = PReLU(acc + shift + x), in place in the resident x planes ----
-// (M tiles mt0 .. mt0 + nmt - 1)
+// one item = 16 accumulator columns of one pixel per lane
+__device__ __forceinline__ void epi_x_item(uint8_t* xp, int plane_bytes, const float* vec, int Cs, int col0,
+                                           const uint32_t (&ra)[16]) {
+    const uint4 q0 = *reinterpret_cast<const uint4*>(xp), q1 = *reinterpret_cast<const uint4*>(xp + plane_bytes);
+    const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float4 sh = *reinterpret_cast<const float4*>(vec + col0 + 4 * j);
+        const float4 sl = *reinterpret_cast<const float4*>(vec + Cs + col0 + 4 * j);
+        // (acc + x) + shift, two columns per instruction
+        float2 a = fk::fadd2(fk::fadd2(make_float2(__uint_as_float(ra[4 * j]), __uint_as_float(ra[4 * j + 1])),
+                                       fk::bf2_to_f2(w[2 * j])), make_float2(sh.x, sh.y));
+        float2 b = fk::fadd2(fk::fadd2(make_float2(__uint_as_float(ra[4 * j + 2]), __uint_as_float(ra[4 * j + 3])),
+                                       fk::bf2_to_f2(w[2 * j + 1])), make_float2(sh.z, sh.w));
+        a.x = a.x >= 0.f ? a.x : a.x * sl.x; a.y = a.y >= 0.f ? a.y : a.y * sl.y;
+        b.x = b.x >= 0.f ? b.x : b.x * sl.z; b.y = b.y >= 0.f ? b.y : b.y * sl.w;
+        o[2 * j] = fk::pack_bf16(a.x, a.y); o[2 * j + 1] = fk::pack_bf16(b.x, b.y);
+    }
+    *reinterpret_cast<uint4*>(xp) = make_uint4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<uint4*>(xp + plane_bytes) = make_uint4(o[4], o[5], o[6], o[7]);
+}
+
+// (M tiles mt0 .. mt0 + nmt - 1)  Two register sets alternate so that the TMEM load of the next item is in
+// flight during the arithmetic of the current one without copying the accumulators.
 __device__ __forceinline__ void epi_x(uint8_t* smem, const Params& p, const uint8_t* wb, uint32_t tmem_base, int mt0, int nmt) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, quad = warp & 3, grp = warp >> 2;
     const int ncc = p.Cs >> 4, nitems = nmt * ncc;
@@ -136,43 +159,27 @@ __device__ __forceinline__ void epi_x(uint8_t* smem, const Params& p, const uint
     if (item >= nitems) return;
     int mt = mt0, cc = item;
     while (cc >= ncc) { cc -= ncc; ++mt; }
-    uint32_t ra[16];
+    uint8_t* xbase = smem + p.x_off + (size_t)(quad * 32 + lane) * 16;
+    auto xptr = [&]() { return xbase + (size_t)(cc * 2) * plane_bytes + (size_t)mt * (128 * 16); };
+    auto advance = [&]() { cc += NGROUPS; while (cc >= ncc) { cc -= ncc; ++mt; } };
+    uint32_t ra[16], rb[16];
     __syncwarp();
     fk::tmem_ld16_nowait(lane_base + item * 16, ra);
     while (true) {
         fk::tmem_ld_wait_dep(ra);
-        const int px = mt * 128 + quad * 32 + lane;
-        const int col0 = cc * 16;
-        float v[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(ra[i]);
-        const int nxt = item + NGROUPS;
+        int nxt = item + NGROUPS;
         __syncwarp();
-        if (nxt < nitems) fk::tmem_ld16_nowait(lane_base + nxt * 16, ra);
-        uint8_t* xp = smem + p.x_off + (size_t)(col0 >> 3) * plane_bytes + (size_t)px * 16;
-        if (px < p.npx) {
-            float f[16];
-            fk::unpack8(*reinterpret_cast<const uint4*>(xp), f);
-            fk::unpack8(*reinterpret_cast<const uint4*>(xp + plane_bytes), f + 8);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float4 sh = *reinterpret_cast<const float4*>(vec + col0 + 4 * j);
-                const float4 sl = *reinterpret_cast<const float4*>(vec + p.Cs + col0 + 4 * j);
-                float a;
-                a = v[4 * j + 0] + f[4 * j + 0] + sh.x; v[4 * j + 0] = a >= 0.f ? a : a * sl.x;
-                a = v[4 * j + 1] + f[4 * j + 1] + sh.y; v[4 * j + 1] = a >= 0.f ? a : a * sl.y;
-                a = v[4 * j + 2] + f[4 * j + 2] + sh.z; v[4 * j + 2] = a >= 0.f ? a : a * sl.z;
-                a = v[4 * j + 3] + f[4 * j + 3] + sh.w; v[4 * j + 3] = a >= 0.f ? a : a * sl.w;
-            }
-            *reinterpret_cast<uint4*>(xp) = make_uint4(fk::pack_bf16(v[0], v[1]), fk::pack_bf16(v[2], v[3]),
-                                                       fk::pack_bf16(v[4], v[5]), fk::pack_bf16(v[6], v[7]));
-            *reinterpret_cast<uint4*>(xp + plane_bytes) = make_uint4(fk::pack_bf16(v[8], v[9]), fk::pack_bf16(v[10], v[11]),
-                                                                     fk::pack_bf16(v[12], v[13]), fk::pack_bf16(v[14], v[15]));
-        }
+        if (nxt < nitems) fk::tmem_ld16_nowait(lane_base + nxt * 16, rb);
+        epi_x_item(xptr(), plane_bytes, vec, p.Cs, cc * 16, ra);
         if (nxt >= nitems) break;
-        item = nxt;
-        cc += NGROUPS;
-        while (cc >= ncc) { cc -= ncc; ++mt; }
+        advance();
+        fk::tmem_ld_wait_dep(rb);
+        item = nxt + NGROUPS;
+        __syncwarp();
+        if (item < nitems) fk::tmem_ld16_nowait(lane_base + item * 16, ra);
+        epi_x_item(xptr(), plane_bytes, vec, p.Cs, cc * 16, rb);
+        if (item >= nitems) break;
+        advance();
     }
 }
 
