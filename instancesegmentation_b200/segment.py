@@ -264,7 +264,7 @@ class Segment(nn.Module):
         t = self.bottle5_2(self.bottle5_1up(t, keep1))
         return self.bottle6_2(self.bottle6_1(t))
 
-    def forward_u8(self, x, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5)):
+    def forward_u8(self, x, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5), out=None):
         """Eval-mode forward from uint8 NHWC images [B,H,W,C] on the device: the reference's
         ``ToTensor`` + ``Normalize(mean, std)`` (train_instance.py:80-85) run inside the engine's first
         kernel.  Equals ``forward(((x / 255 - mean) / std).permute(0, 3, 1, 2))``."""
@@ -274,7 +274,7 @@ class Segment(nn.Module):
         if not x.is_cuda:
             raise RuntimeError("Segment.forward_u8 runs only in the sm_100a CUDA engine (libisg.so)")
         eng = self._engine_for(x.device, x.shape[0], x.shape[1], x.shape[2])
-        return eng.forward_u8(x, mean, std)
+        return eng.forward_u8(x, mean, std, out=out)
 
     def _forward_engine(self, x):
         if not x.is_cuda:
