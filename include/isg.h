@@ -107,6 +107,23 @@ ISG_API int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int 
                float threshold, uint8_t* masks_dev, uint8_t* soft_dev, int32_t* area_dev,
                int32_t* bbox_dev, void* stream);
 
+/* Tiled decode for ragged box sizes (0/1 masks only), optionally fused with the id map.
+ * Same inputs/outputs as isg_decode; the work is cut into tiles of isg_decode_tile_rows()
+ * consecutive mask rows of one instance, handed out dynamically so that boxes of very
+ * different sizes keep every SM busy.  tile_first_dev [n_inst+1] int32 = exclusive prefix of
+ * ceil(hk / rows) over the instances (0 tiles for an empty box), n_tiles = its last entry.
+ * idmap_dev (nullable) [n_img,canvas_h,canvas_w] int32 with the rule of isg_idmap; needs
+ * inst_img_dev [n_inst] (image of each instance), img_first_dev [n_img+1] and at most 32
+ * instances per image (set pixels OR their instance bit into the canvas word; contested
+ * pixels are resolved by comparing probabilities, exact ones when they are close). */
+ISG_API int isg_decode_tile_rows(void);
+ISG_API int isg_decode_tiled(const void* logits_dev, int logits_bf16, int n_inst, int h, int w,
+                     const int32_t* boxes_dev, const int64_t* mask_off_dev,
+                     const int32_t* tile_first_dev, int n_tiles, float threshold,
+                     uint8_t* masks_dev, int32_t* area_dev, int32_t* bbox_dev,
+                     const int32_t* inst_img_dev, const int32_t* img_first_dev, int n_img,
+                     int canvas_h, int canvas_w, int32_t* idmap_dev, void* stream);
+
 /* id map [n_img,canvas_h,canvas_w] int32: per pixel the 1-based index of the covering
  * instance with set mask and largest probability (ties -> lowest index), 0 = background.
  * img_first_dev [n_img+1] int32: instances of image i are img_first[i]..img_first[i+1]-1. */

@@ -32,6 +32,8 @@ SIGNATURES = {
     "isg_plan_tap_shape": (_i, [_vp, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)]),
     "isg_plan_tap_read": (_i, [_vp, _i, _i, _vp]),
     "isg_decode": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _f, _vp, _vp, _vp, _vp, _vp]),
+    "isg_decode_tile_rows": (_i, []),
+    "isg_decode_tiled": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "isg_idmap": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _f, _vp, _vp]),
     "isg_mask_iou_counts": (_i, [_vp, _vp, _i64, _vp, _vp]),
     "isg_adam_step": (_i, [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp]),

@@ -31,6 +31,12 @@ __device__ __noinline__ float exact_prob_nl(const TL* L, int w, int y0, int y1, 
     return exact_prob(L, w, ty, tx);
 }
 
+// same, from output coordinates (id-map tie-breaks)
+template <typename TL>
+__device__ __noinline__ float exact_prob_at_nl(const TL* L, int h, int w, int oy, float sy, int ox, float sx) {
+    return exact_prob(L, w, make_tap(oy, h, sy), make_tap(ox, w, sx));
+}
+
 struct DecAcc { int cnt, xmin, ymin, xmax, ymax; };
 
 // pixels [idx, idx+nv) of one instance; IDENT: the mask has the size of the logit map
@@ -325,6 +331,227 @@ idmap_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restr
     idmap[((size_t)img * Hs + y) * Ws + x] = best;
 }
 
+// ---- tiled resize decode (any box size, 0/1 masks only) with fused id-map claims ------------------
+// Work unit = one output ROW per warp: the vertical tap, the two source-row pointers and the row's
+// statistics are warp-uniform, lanes take consecutive output pixels (the four bilinear taps of a warp
+// fall into ~scale*128 bytes per source row), no per-pixel division.  A tile = DT_ROWS consecutive
+// rows of one instance (two adjacent rows per warp); `tile_first` is the exclusive prefix of the
+// instances' tile counts.  Tiles are handed out by an atomic counter (boxes of U(96,640) pixels make
+// tiles of very different cost; the next tile's index and instance are fetched while the current one
+// is computed), so the resident wave stays busy until the list is empty.
+// Decision ladder per pixel: (1) all four logits on one side of logit(thr) by more than `margin`
+// -> decided without any sigmoid (a convex mix of probabilities stays on that side); (2) MUFU
+// probability further than DECIDE_MARGIN from thr; (3) the exact sequence, out of line.
+// Statistics: counts / x-extent come from the ballots, y-extent from the row index; one set of
+// atomics per warp and tile, the warp that completes the instance's last row publishes.
+// With `claims` (the id-map buffer, zeroed by the caller) every set pixel ORs the instance's bit
+// (index within its image, < 32) into the canvas word; idmap_finalize_kernel turns the bit sets into
+// ids and compares probabilities only where two or more instances claim the same pixel.
+constexpr int DT_THREADS = 256, DT_WARPS = DT_THREADS / 32, DT_RPW = 2, DT_ROWS = DT_WARPS * DT_RPW;
+__device__ unsigned g_dt_next, g_dt_done;
+
+// source indices of the align_corners=False rule (make_tap without the weights)
+__device__ __forceinline__ void tap_index(int dst, int in, float scale, int& i0, int& i1) {
+    float s = __fsub_rn(__fmul_rn(scale, __fadd_rn((float)dst, 0.5f)), 0.5f);
+    if (s < 0.0f) s = 0.0f;
+    i0 = min((int)s, in - 1);
+    i1 = i0 + (i0 < in - 1 ? 1 : 0);
+}
+
+template <typename TL>
+__global__ void __launch_bounds__(DT_THREADS, 4)
+decode_tiled_kernel(const TL* __restrict__ logits, int n_inst, int h, int w, const int32_t* __restrict__ boxes,
+                    const int64_t* __restrict__ mask_off, const int32_t* __restrict__ tile_first, int n_tiles,
+                    float thr, float thr_logit, float margin, uint8_t* __restrict__ masks,
+                    int32_t* __restrict__ area, int32_t* __restrict__ bbox,
+                    const int32_t* __restrict__ inst_img, const int32_t* __restrict__ img_first,
+                    int Hs, int Ws, unsigned* __restrict__ claims) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __shared__ int s_tile[2][2];   // {tile, instance} of the current and the next tile
+    auto fetch = [&](int slot) {   // thread 0: next tile index and the instance it belongs to
+        const int t = (int)atomicAdd(&g_dt_next, 1u);
+        int lo = 0;
+        if (t < n_tiles) {
+            int hi = n_inst - 1;
+            while (lo < hi) {   // last n with tile_first[n] <= t (instances without tiles are skipped: <=)
+                const int mid = (lo + hi + 1) >> 1;
+                if (__ldg(tile_first + mid) <= t) lo = mid; else hi = mid - 1;
+            }
+        }
+        s_tile[slot][0] = t; s_tile[slot][1] = lo;
+    };
+    if (blockIdx.x == 0) {   // boxes without pixels publish an empty result (nobody owns a tile of them)
+        for (int n = threadIdx.x; n < n_inst; n += DT_THREADS)
+            if (tile_first[n + 1] == tile_first[n]) {
+                area[n] = 0;
+                bbox[4 * n] = bbox[4 * n + 1] = bbox[4 * n + 2] = bbox[4 * n + 3] = 0;
+            }
+    }
+    if (threadIdx.x == 0) fetch(0);
+    __syncthreads();
+    for (int it = 0;; ++it) {
+        const int t = s_tile[it & 1][0], n = s_tile[it & 1][1];
+        if (threadIdx.x == 0) fetch((it + 1) & 1);
+        if (t >= n_tiles) break;
+        const int4 bx = __ldg(reinterpret_cast<const int4*>(boxes) + n);
+        const int wk = bx.z, hk = bx.w;
+        const TL* L = logits + (size_t)n * h * w;
+        uint8_t* dst = masks + mask_off[n];
+        const float sy = __fdiv_rn((float)h, (float)hk), sx = __fdiv_rn((float)w, (float)wk);
+        unsigned* cl = nullptr;
+        unsigned bit = 0;
+        if (claims) {
+            const int img = __ldg(inst_img + n);
+            cl = claims + (size_t)img * Hs * Ws;
+            bit = 1u << (n - __ldg(img_first + img));
+        }
+        const int row0 = (t - __ldg(tile_first + n)) * DT_ROWS + warp * DT_RPW;
+        int cnt = 0, xmin = INT_MAX, xmax = -1, ymin = INT_MAX, ymax = -1, rows = 0;
+#pragma unroll 1
+        for (int oy = row0; oy < min(row0 + DT_RPW, hk); ++oy) {
+            ++rows;
+            int y0, y1;
+            tap_index(oy, h, sy, y0, y1);
+            const TL* r0 = L + (size_t)y0 * w;
+            const TL* r1 = L + (size_t)y1 * w;
+            uint8_t* drow = dst + (size_t)oy * wk;
+            const bool word_out = (reinterpret_cast<uintptr_t>(drow) & 3) == 0;
+            const int cy = bx.y + oy;
+            unsigned* crow = (cl && cy >= 0 && cy < Hs) ? cl + (size_t)cy * Ws : nullptr;
+            int rcnt = 0;
+            for (int x0 = 0; x0 < wk; x0 += 128) {
+                float a[4], b[4], c[4], d[4];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const int ox = x0 + 32 * r + lane;
+                    a[r] = b[r] = c[r] = d[r] = 0.f;
+                    if (ox < wk) {
+                        int i0, i1;
+                        tap_index(ox, w, sx, i0, i1);
+                        a[r] = ldl(r0 + i0); b[r] = ldl(r0 + i1); c[r] = ldl(r1 + i0); d[r] = ldl(r1 + i1);
+                    }
+                }
+                unsigned bal[4];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const int ox = x0 + 32 * r + lane;
+                    bool m = false;
+                    if (ox < wk) {
+                        const float lo4 = fminf(fminf(a[r], b[r]), fminf(c[r], d[r]));
+                        const float hi4 = fmaxf(fmaxf(a[r], b[r]), fmaxf(c[r], d[r]));
+                        // fminf/fmaxf drop NaN operands: a NaN tap (or inf - inf) shows in the sum and goes down the ladder
+                        const float s4 = (a[r] + b[r]) + (c[r] + d[r]);
+                        if (s4 == s4 && lo4 - thr_logit > margin) m = true;
+                        else if (s4 == s4 && thr_logit - hi4 > margin) m = false;
+                        else {
+                            const Tap ty = make_tap(oy, h, sy), tx = make_tap(ox, w, sx);
+                            const float p = ty.l0 * (tx.l0 * fast_sigmoid(a[r]) + tx.l1 * fast_sigmoid(b[r])) +
+                                            ty.l1 * (tx.l0 * fast_sigmoid(c[r]) + tx.l1 * fast_sigmoid(d[r]));
+                            if (fabsf(p - thr) > DECIDE_MARGIN) m = p > thr;
+                            else m = exact_prob_at_nl(L, h, w, oy, sy, ox, sx) > thr;
+                        }
+                        if (m && crow) {
+                            const int cx = bx.x + ox;
+                            if (cx >= 0 && cx < Ws) atomicOr(crow + cx, bit);
+                        }
+                    }
+                    bal[r] = __ballot_sync(0xffffffffu, m);
+                    if (bal[r]) {
+                        rcnt += __popc(bal[r]);
+                        xmin = min(xmin, x0 + 32 * r + __ffs(bal[r]) - 1);
+                        xmax = max(xmax, x0 + 32 * r + 31 - __clz(bal[r]));
+                    }
+                }
+                if (word_out && x0 + 128 <= wk) {
+                    // lane i owns pixels x0 + 4i .. x0 + 4i + 3: nibble (i & 7) of ballot (i >> 3)
+                    const unsigned bsel = lane < 16 ? (lane < 8 ? bal[0] : bal[1]) : (lane < 24 ? bal[2] : bal[3]);
+                    const unsigned nib = (bsel >> (4 * (lane & 7))) & 0xfu;
+                    __stcs(reinterpret_cast<unsigned*>(drow + x0) + lane, (nib * 0x00204081u) & 0x01010101u);
+                } else {
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const int ox = x0 + 32 * r + lane;
+                        if (ox < wk) drow[ox] = (uint8_t)((bal[r] >> lane) & 1u);
+                    }
+                }
+            }
+            if (rcnt) { cnt += rcnt; ymin = min(ymin, oy); ymax = max(ymax, oy); }
+        }
+        if (lane == 0 && rows) {
+            int* acc = g_dec_acc[n];
+            if (cnt) {
+                atomicAdd(acc, cnt);
+                atomicMax(acc + 1, INT_MAX - xmin); atomicMax(acc + 2, INT_MAX - ymin);
+                atomicMax(acc + 3, xmax + 1); atomicMax(acc + 4, ymax + 1);
+            }
+            __threadfence();
+            if (atomicAdd(&g_dec_ticket[n], (unsigned)rows) + (unsigned)rows == (unsigned)hk) {   // all rows are in
+                __threadfence();
+                const int ar = atomicExch(acc, 0);
+                const int e1 = atomicExch(acc + 1, 0), e2 = atomicExch(acc + 2, 0);
+                const int e3 = atomicExch(acc + 3, 0), e4 = atomicExch(acc + 4, 0);
+                g_dec_ticket[n] = 0;
+                area[n] = ar;
+                if (ar == 0) { bbox[4 * n] = bbox[4 * n + 1] = bbox[4 * n + 2] = bbox[4 * n + 3] = 0; }
+                else {
+                    bbox[4 * n] = INT_MAX - e1 + bx.x; bbox[4 * n + 1] = INT_MAX - e2 + bx.y;
+                    bbox[4 * n + 2] = e3 + bx.x; bbox[4 * n + 3] = e4 + bx.y;
+                }
+            }
+        }
+        __syncthreads();   // the next tile's {index, instance} is in place; this one's slot may be refilled
+    }
+    if (threadIdx.x == 0) {   // the last CTA to run dry re-arms the tile counter for the next launch
+        __threadfence();
+        if (atomicAdd(&g_dt_done, 1u) == gridDim.x - 1) { g_dt_next = 0; g_dt_done = 0; __threadfence(); }
+    }
+}
+
+// claims word -> id: one claimant needs no arithmetic; contested pixels compare exact probabilities
+// (largest wins, ties -> lowest index), exactly the rule idmap_kernel applies to every pixel
+template <typename TL>
+__global__ void __launch_bounds__(256)
+idmap_finalize_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restrict__ boxes,
+                      const int32_t* __restrict__ img_first, int Hs, int Ws, int64_t total, int32_t* __restrict__ idmap) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    unsigned bits = (unsigned)idmap[i];
+    if (!bits) return;
+    const int64_t per = (int64_t)Hs * Ws;
+    const int img = (int)(i / per);
+    const int rem = (int)(i - img * per);
+    const int y = rem / Ws, x = rem - y * Ws;
+    const int first = __ldg(img_first + img);
+    int best = first + __ffs(bits);
+    if (bits & (bits - 1)) {
+        // MUFU probabilities (abs error < 2e-6) name the winner unless the two best are closer than 1e-5;
+        // only then the exact sequence is evaluated for every claimant
+        float p1 = -1.f, p2 = -1.f;
+        for (unsigned bb = bits; bb; bb &= bb - 1) {
+            const int n = first + __ffs(bb) - 1;
+            const int4 bx = __ldg(reinterpret_cast<const int4*>(boxes) + n);
+            const TL* L = logits + (size_t)n * h * w;
+            const Tap ty = make_tap(y - bx.y, h, __fdiv_rn((float)h, (float)bx.w));
+            const Tap tx = make_tap(x - bx.x, w, __fdiv_rn((float)w, (float)bx.z));
+            const float p = fast_prob(L, w, ty, tx);
+            if (p > p1) { p2 = p1; p1 = p; best = n + 1; }
+            else if (p > p2) p2 = p;
+        }
+        if (!(p1 - p2 > 1e-5f)) {
+            float bp = 0.f;
+            best = 0;
+            for (unsigned bb = bits; bb; bb &= bb - 1) {
+                const int n = first + __ffs(bb) - 1;
+                const int4 bx = __ldg(reinterpret_cast<const int4*>(boxes) + n);
+                const float p = exact_prob_at_nl(logits + (size_t)n * h * w, h, w, y - bx.y, __fdiv_rn((float)h, (float)bx.w),
+                                                 x - bx.x, __fdiv_rn((float)w, (float)bx.z));
+                if (best == 0 || p > bp) { best = n + 1; bp = p; }
+            }
+        }
+    }
+    idmap[i] = best;
+}
+
 __global__ void iou_counts_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, int64_t n,
                                   unsigned long long* out) {
     unsigned inter = 0, uni = 0;
@@ -409,6 +636,63 @@ int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int h, int w
     else { if (soft_dev) ISG_DEC(float, true); else ISG_DEC(float, false); }
 #undef ISG_DEC
     ISG_CUDA(cudaGetLastError());
+    return ISG_OK;
+}
+
+int isg_decode_tile_rows(void) { return DT_ROWS; }
+
+int isg_decode_tiled(const void* logits_dev, int logits_bf16, int n_inst, int h, int w, const int32_t* boxes_dev,
+                     const int64_t* mask_off_dev, const int32_t* tile_first_dev, int n_tiles, float threshold,
+                     uint8_t* masks_dev, int32_t* area_dev, int32_t* bbox_dev, const int32_t* inst_img_dev,
+                     const int32_t* img_first_dev, int n_img, int canvas_h, int canvas_w, int32_t* idmap_dev,
+                     void* stream) {
+    if (n_inst == 0) return ISG_OK;
+    if (!logits_dev || !boxes_dev || !mask_off_dev || !tile_first_dev || !masks_dev || !area_dev || !bbox_dev)
+        return fail(ISG_ERR_ARG, "isg_decode_tiled: null argument");
+    if (n_inst < 0 || n_inst > 65535 || h < 1 || w < 1 || n_tiles < 0)
+        return fail(ISG_ERR_ARG, "isg_decode_tiled: bad sizes (n_inst=%d h=%d w=%d n_tiles=%d)", n_inst, h, w, n_tiles);
+    if (idmap_dev && (!inst_img_dev || !img_first_dev || n_img < 1 || canvas_h < 1 || canvas_w < 1))
+        return fail(ISG_ERR_ARG, "isg_decode_tiled: id map requested without image table / canvas size");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const double t = threshold;
+    const bool logit_cmp = t > 1e-3 && t < 1.0 - 1e-3;
+    const float thr_logit = logit_cmp ? (float)log(t / (1.0 - t)) : 0.f;
+    // step 1 of the ladder decides |logit - logit(thr)| > margin for all four taps: 2e-5 in probability,
+    // against < 1e-6 of rounding in the exact bilinear sequence; thresholds next to 0/1 skip the step
+    const float margin = logit_cmp ? (float)(2e-5 / (t * (1.0 - t)) + 4e-6 * (1.0 + fabs((double)thr_logit))) : INFINITY;
+    const int64_t total = idmap_dev ? (int64_t)n_img * canvas_h * canvas_w : 0;
+    if (idmap_dev) ISG_CUDA(cudaMemsetAsync(idmap_dev, 0, (size_t)total * 4, st));
+    static int slots_tab[2] = {0, 0};
+    int& slots = slots_tab[logits_bf16 ? 1 : 0];
+    if (!slots) {
+        int dev = 0, sms = 148, occ = 2;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (logits_bf16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_tiled_kernel<bf16>, DT_THREADS, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, decode_tiled_kernel<float>, DT_THREADS, 0);
+        slots = getenv("ISG_DEC_SLOTS") ? atoi(getenv("ISG_DEC_SLOTS")) : sms * std::max(occ, 1);
+    }
+    const int grid = std::max(1, std::min(n_tiles, slots));
+    unsigned* claims = reinterpret_cast<unsigned*>(idmap_dev);
+    if (logits_bf16)
+        decode_tiled_kernel<bf16><<<grid, DT_THREADS, 0, st>>>(static_cast<const bf16*>(logits_dev), n_inst, h, w, boxes_dev,
+            mask_off_dev, tile_first_dev, n_tiles, threshold, thr_logit, margin, masks_dev, area_dev, bbox_dev,
+            inst_img_dev, img_first_dev, canvas_h, canvas_w, claims);
+    else
+        decode_tiled_kernel<float><<<grid, DT_THREADS, 0, st>>>(static_cast<const float*>(logits_dev), n_inst, h, w, boxes_dev,
+            mask_off_dev, tile_first_dev, n_tiles, threshold, thr_logit, margin, masks_dev, area_dev, bbox_dev,
+            inst_img_dev, img_first_dev, canvas_h, canvas_w, claims);
+    ISG_CUDA(cudaGetLastError());
+    if (idmap_dev) {
+        const unsigned blocks = (unsigned)((total + 255) / 256);
+        if (logits_bf16)
+            idmap_finalize_kernel<bf16><<<blocks, 256, 0, st>>>(static_cast<const bf16*>(logits_dev), h, w, boxes_dev,
+                                                                 img_first_dev, canvas_h, canvas_w, total, idmap_dev);
+        else
+            idmap_finalize_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(logits_dev), h, w, boxes_dev,
+                                                                  img_first_dev, canvas_h, canvas_w, total, idmap_dev);
+        ISG_CUDA(cudaGetLastError());
+    }
     return ISG_OK;
 }
 

@@ -63,6 +63,36 @@ class DecodePlan:
         self.max_w = int(self.boxes[:, 2].max()) if n else 1
         self.max_h = int(self.boxes[:, 3].max()) if n else 1
         self.total = max(int(self.offsets[-1]), 1)
+        # tiled kernel (isg_decode_tiled): exclusive prefix of the instances' tile counts
+        rows = _lib.lib().isg_decode_tile_rows()
+        hk = np.where(self.boxes[:, 2] > 0, self.boxes[:, 3], 0).astype(np.int64) if n else np.zeros(0, np.int64)
+        tf = np.zeros(n + 1, np.int64)
+        np.cumsum((np.maximum(hk, 0) + rows - 1) // rows, out=tf[1:])
+        if tf[-1] >= 2 ** 31:
+            raise ValueError("too many mask pixels for one decode call")
+        self.n_tiles = int(tf[-1])
+        self.tile_first_d = torch.from_numpy(tf.astype(np.int32)).to(self.device)
+        self._idmap_tables, self._identity = {}, {}
+
+    def is_identity(self, h, w):
+        if (h, w) not in self._identity:
+            b = self.boxes
+            self._identity[(h, w)] = bool(len(b)) and bool((b[:, 2] == w).all() and (b[:, 3] == h).all())
+        return self._identity[(h, w)]
+
+    def idmap_tables(self, img_first):
+        """(img_first on the device, image of every instance on the device, max instances per image)"""
+        first = np.ascontiguousarray(np.asarray(img_first, np.int32))
+        key = first.tobytes()
+        if key not in self._idmap_tables:
+            if first[0] != 0 or first[-1] != len(self.boxes) or (np.diff(first) < 0).any():
+                raise ValueError("img_first must rise from 0 to the number of instances")
+            counts = np.diff(first)
+            inst_img = np.repeat(np.arange(len(counts), dtype=np.int32), counts)
+            self._idmap_tables[key] = (torch.from_numpy(first).to(self.device),
+                                       torch.from_numpy(inst_img).to(self.device),
+                                       int(counts.max()) if len(counts) else 0)
+        return self._idmap_tables[key]
 
 
 def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=None, canvas=None,
@@ -99,21 +129,35 @@ def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=N
             masks = torch.empty(total, dtype=torch.uint8, device=dev)
         soft = torch.empty(total, dtype=torch.uint8, device=dev) if want_soft else None
         area, bbox, boxes_d, off_d = plan.area, plan.bbox, plan.boxes_d, plan.off_d
-        if N:
-            _lib.check(l.isg_decode(logits.data_ptr(), int(logits.dtype == torch.bfloat16), N, h, w,
+        bf = int(logits.dtype == torch.bfloat16)
+        idmap = first_d = inst_img_d = None
+        per_img = 0
+        if img_first is not None:
+            if canvas is None:
+                raise ValueError("canvas=(Hs, Ws) is required with img_first")
+            first_d, inst_img_d, per_img = plan.idmap_tables(img_first)
+            n_img = first_d.numel() - 1
+            idmap = torch.empty((n_img, canvas[0], canvas[1]), dtype=torch.int32, device=dev)
+        identity = plan.is_identity(h, w)
+        fuse_ids = bool(idmap is not None and N and per_img <= 32 and not want_soft)
+        if N and not want_soft and (fuse_ids or not identity):
+            # ragged sizes: balanced tile list; the id map rides along as bit claims when it fits a word
+            _lib.check(l.isg_decode_tiled(logits.data_ptr(), bf, N, h, w, boxes_d.data_ptr(), off_d.data_ptr(),
+                                          plan.tile_first_d.data_ptr(), plan.n_tiles, float(threshold),
+                                          masks.data_ptr(), area.data_ptr(), bbox.data_ptr(),
+                                          inst_img_d.data_ptr() if fuse_ids else None,
+                                          first_d.data_ptr() if fuse_ids else None,
+                                          n_img if fuse_ids else 0, canvas[0] if fuse_ids else 0,
+                                          canvas[1] if fuse_ids else 0,
+                                          idmap.data_ptr() if fuse_ids else None, st))
+        elif N:
+            _lib.check(l.isg_decode(logits.data_ptr(), bf, N, h, w,
                                     boxes_d.data_ptr(), off_d.data_ptr(), plan.max_w,
                                     plan.max_h, float(threshold), masks.data_ptr(),
                                     soft.data_ptr() if want_soft else None, area.data_ptr(),
                                     bbox.data_ptr(), st))
-        idmap = None
-        if img_first is not None:
-            if canvas is None:
-                raise ValueError("canvas=(Hs, Ws) is required with img_first")
-            first = np.ascontiguousarray(np.asarray(img_first, np.int32))
-            n_img = len(first) - 1
-            idmap = torch.empty((n_img, canvas[0], canvas[1]), dtype=torch.int32, device=dev)
-            first_d = torch.from_numpy(first).to(dev)
-            _lib.check(l.isg_idmap(logits.data_ptr(), int(logits.dtype == torch.bfloat16), h, w,
+        if idmap is not None and not fuse_ids:
+            _lib.check(l.isg_idmap(logits.data_ptr(), bf, h, w,
                                    boxes_d.data_ptr(), first_d.data_ptr(), n_img, canvas[0], canvas[1],
                                    float(threshold), idmap.data_ptr(), st))
     return DecodeResult(masks, soft, off, boxes, area, bbox, idmap)

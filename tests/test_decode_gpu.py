@@ -73,6 +73,68 @@ def test_many_overlapping_instances_and_idmap():
     assert got.max() > per  # ids are 1-based global instance indices
 
 
+def test_idmap_more_than_32_instances_per_image_uses_gather_kernel():
+    n_img, per = 1, 40
+    boxes, first = synth.boxes(n_img, per, 64, 80, seed=11, lo=8, hi=60)
+    L = synth.logits(n_img * per, 32, 32, seed=12)
+    r = decode_masks(torch.from_numpy(L).cuda(), boxes, img_first=first, canvas=(64, 80))
+    assert np.array_equal(r.idmap.cpu().numpy(), D.idmap(L, boxes, first, 64, 80))
+    o = D.decode(L, boxes)
+    assert np.array_equal(r.area.cpu().numpy(), o["area"]) and np.array_equal(r.bbox.cpu().numpy(), o["bbox"])
+
+
+def test_tiled_decode_boxes_off_canvas_nan_and_thresholds():
+    """ragged sizes through isg_decode_tiled: boxes hanging over the canvas edge, NaN/inf taps, thresholds
+    next to 0/1 (the logit shortcut is off there), tight packing (byte stores)"""
+    n_img, per = 3, 7
+    boxes, first = synth.boxes(n_img, per, 72, 88, seed=21, lo=5, hi=70)
+    boxes[0, :2] = [-9, -4]            # hangs over the top-left corner
+    boxes[5, :2] = [70, 60]            # and over the bottom-right one
+    L = synth.logits(n_img * per, 40, 56, seed=22)
+    L[2, 3:6, 4:9] = np.nan
+    L[3, 10, :] = np.inf
+    L[4, :, 7] = -np.inf
+    L[6, 0:8, 0:8] = [[0.0, 1e-9, 1e-7, 6e-8, -1e-9, 5.9e-8, 6.1e-8, 3e-8]] * 8
+    for thr in (0.5, 0.3, 0.9995, 2e-4):
+        for align in (16, 1):
+            _compare(L, boxes, thr=thr, align=align)
+        r = decode_masks(torch.from_numpy(L).cuda(), boxes, threshold=thr, img_first=first, canvas=(72, 88))
+        want = D.idmap(L, boxes, first, 72, 88, thr=thr)
+        got = r.idmap.cpu().numpy()
+        assert np.array_equal(got, want), (thr, int((got != want).sum()))
+
+
+def test_tiled_decode_full_size_balanced_and_deterministic():
+    """cfg4-like mix of box sizes at 1024x1024: statistics agree with the masks, two runs agree, and the
+    id map only names instances whose mask is set at that pixel"""
+    n_img, per, S = 2, 20, 1024
+    boxes, first = synth.boxes(n_img, per, S, S, seed=7, lo=96, hi=640)
+    L = torch.from_numpy(synth.logits(n_img * per, S, S, seed=5)).cuda()
+    r = decode_masks(L, boxes, img_first=first, canvas=(S, S))
+    r2 = decode_masks(L, boxes, img_first=first, canvas=(S, S))
+    assert torch.equal(r.masks, r2.masks) and torch.equal(r.idmap, r2.idmap) and torch.equal(r.bbox, r2.bbox)
+    ids = r.idmap.cpu().numpy()
+    cover = np.zeros_like(ids)
+    for n in range(n_img * per):
+        m = r.mask(n)
+        x0, y0, wk, hk = (int(v) for v in boxes[n])
+        assert int(r.area[n]) == int(m.sum())
+        if int(r.area[n]):
+            ys, xs = torch.nonzero(m, as_tuple=True)
+            assert r.bbox[n].tolist() == [x0 + int(xs.min()), y0 + int(ys.min()), x0 + int(xs.max()) + 1, y0 + int(ys.max()) + 1]
+        img = int(np.searchsorted(first, n, side="right") - 1)
+        mm = m.cpu().numpy()
+        ya, yb, xa, xb = max(y0, 0), min(y0 + hk, S), max(x0, 0), min(x0 + wk, S)
+        sub = mm[ya - y0:yb - y0, xa - x0:xb - x0]
+        cover[img, ya:yb, xa:xb] |= sub
+        named = ids[img, ya:yb, xa:xb] == n + 1
+        assert not (named & (sub == 0)).any()
+    assert np.array_equal(ids != 0, cover != 0)
+    # a 96-row slice of the first instance against the scalar oracle
+    o = D.decode(L[:1].cpu().numpy(), boxes[:1])
+    assert np.array_equal(r.mask(0).cpu().numpy().ravel(), o["masks"][:o["off"][1]])
+
+
 def test_bf16_logits():
     L = torch.from_numpy(synth.logits(2, 48, 64, seed=9)).to(torch.bfloat16)
     boxes = np.array([[0, 0, 64, 48], [2, 2, 100, 70]], np.int32)
