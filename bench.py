@@ -273,9 +273,10 @@ def run_ours(args, rank, world, local_rank):
 def run_cfg4(args, rank, world, local_rank):
     """BASELINE configs[3] / SURVEY 8(d) cfg4: ``n_img`` source images of 1024x1024 with 20 instances each.
     One network sample = one object crop (train_instance.py:141-196), so a step is the forward of
-    n_img*20 crops at the network size (uint8 NHWC, groups of 32) followed by ONE decode launch that
-    resizes every logit map to its instance box (U(96,640) px, seed 7), thresholds it, reduces area
-    and bbox, and one id-map launch that pastes the instances of each image into its canvas."""
+    n_img*20 crops at the network size (uint8 NHWC, groups of 32) followed by ONE tiled decode launch
+    (isg_decode_tiled) that resizes every logit map to its instance box (U(96,640) px, seed 7),
+    thresholds it, reduces area and bbox and ORs every set pixel's instance bit into its image's
+    canvas, and one finalize launch that turns the bit sets into the id map."""
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -350,6 +351,10 @@ def run_cfg4(args, rank, world, local_rank):
         out_px = int((boxes[:, 2].astype(np.int64) * boxes[:, 3]).sum())
         dec_bytes = N * (S * S * 4 + 20) + out_px                      # full logit map in + mask out
         dec_gbs = dec_bytes * K / (dk_ms * 1e-3) / 1e9
+        # dram__bytes_read.sum + dram__bytes_write.sum of one tiled decode launch at exactly this geometry (boxes
+        # seed 7): profiles/r1h_decode_cfg4_launches.txt -- below the algorithmic bytes because a downsampling
+        # box never touches the source rows between its taps
+        dec_traffic = 1981.2e6 if (rank == 0 and world == 1) else None
         emit({
             "metric": "images/sec", "value": world * n_img * K / (total_ms * 1e-3), "unit": "images/s",
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True,
@@ -369,7 +374,7 @@ def run_cfg4(args, rank, world, local_rank):
                                  f"{flop_img / 1e9:.4f} GFLOP/crop, peak = sustained bf16 of {pk['src']}",
                          "ms_per_forward_group": fwd_ms / K / (N / group)},
             "roofline_decode": {"bound": "hbm", "achieved": dec_gbs, "peak": pk["hbm"], "unit": "GB/s",
-                                "frac": dec_gbs / pk["hbm"], "traffic": None, "bytes_per_launch": dec_bytes,
+                                "frac": dec_gbs / pk["hbm"], "traffic": dec_traffic, "bytes_per_launch": dec_bytes,
                                 "ms_per_decode": dk_ms / K, "ms_decode_plus_idmap": dec_ms / K,
                                 "what": f"{N} instance maps of {S}x{S} fp32 resized to their boxes ({out_px / N:.0f} px mean)"},
             "gpu_launches": K * (eng.launches_per_forward * (N // group) + 2),

@@ -136,6 +136,18 @@ ISG_API int isg_idmap(const void* logits_dev, int logits_bf16, int h, int w, con
 ISG_API int isg_mask_iou_counts(const uint8_t* a_dev, const uint8_t* b_dev, int64_t n,
                         unsigned long long* inter_union_dev, void* stream);
 
+/* ---- input side ------------------------------------------------------------
+ * Keypoint heat maps of the Segment(20) variant (train_instance.py:33-68 keypoint2heatmaps,
+ * called at :202): kp_dev [batch,n_parts,3] fp32 rows (x, y, flag), flag 1 = present and
+ * visible (drawn), anything else = zero map.  Writes fp32 [batch,n_parts,height,width] with
+ * the given batch stride (elements), e.g. channels 3.. of the [B,20,H,W] network input, so
+ * the torch.cat of model/segment.py:531-533 is never materialised separately.  The value is
+ * the reference's float64 exp(-((x-kx)^2+(y-ky)^2)/sigma^2) where > threshold, inside the
+ * reference's clipped box (last row/column excluded as np.arange does), rounded to fp32. */
+ISG_API int isg_keypoint_heatmaps(const float* kp_dev, int batch, int n_parts, int height, int width,
+                          float sigma, float threshold, float* out_dev, int64_t out_batch_stride,
+                          void* stream);
+
 /* ---- training step exchange (train_instance.py:379-380) ---------------------
  * fused "unscale + Adam" over the flat fp32 gradient bucket after the NCCL all-reduce:
  * g = grad * grad_scale; standard Adam (lr, beta1, beta2, eps), bias-corrected by `step`. */

@@ -112,7 +112,8 @@ def test_tiled_decode_full_size_balanced_and_deterministic():
     L = torch.from_numpy(synth.logits(n_img * per, S, S, seed=5)).cuda()
     r = decode_masks(L, boxes, img_first=first, canvas=(S, S))
     r2 = decode_masks(L, boxes, img_first=first, canvas=(S, S))
-    assert torch.equal(r.masks, r2.masks) and torch.equal(r.idmap, r2.idmap) and torch.equal(r.bbox, r2.bbox)
+    assert torch.equal(r.idmap, r2.idmap) and torch.equal(r.bbox, r2.bbox) and torch.equal(r.area, r2.area)
+    assert all(torch.equal(r.mask(n), r2.mask(n)) for n in range(n_img * per))   # (alignment gaps are never written)
     ids = r.idmap.cpu().numpy()
     cover = np.zeros_like(ids)
     for n in range(n_img * per):

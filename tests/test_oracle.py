@@ -111,3 +111,19 @@ def test_idmap_oracle_rules():
     assert ids[5, 5] == 2                          # tie between 2 and 3 -> lowest index
     assert ids[9, 9] == 3 and ids[11, 0] == 0      # box clipped by the canvas; unset mask -> 0
     assert D.mask_iou([1, 1, 0, 0], [1, 0, 1, 0]) == 1 / 3
+
+
+def test_heatmap_oracle_matches_reference_function_golden():
+    """oracle/heatmap_oracle.py against the vectors tests/golden/make_golden_heatmaps.py produced by
+    executing the reference's own keypoint2heatmaps (train_instance.py:33-68): bit-exact."""
+    from oracle.heatmap_oracle import keypoint_heatmaps
+    z = np.load(os.path.join(GOLDEN, "heatmaps_golden.npz"))
+    assert int(z["n"]) >= 4
+    for i in range(int(z["n"])):
+        h, w, sigma, thr = z[f"meta{i}"]
+        got = keypoint_heatmaps(z[f"kp{i}"], (int(h), int(w)), sigma=int(sigma), threshold=float(thr))
+        want = z[f"maps{i}"]
+        assert got.dtype == np.float32 and got.shape == want.shape
+        assert np.array_equal(got, want), i
+        assert want[z[f"kp{i}"][:, 2] != 1].max(initial=0) == 0      # hidden / missing parts stay empty
+        assert want[:, -1, :].max() == 0 and want[:, :, -1].max() == 0   # the reference never writes the last row/column

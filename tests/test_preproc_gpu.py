@@ -1,0 +1,74 @@
+"""GPU parity tests of the input side: keypoint heat maps against the golden vectors the
+reference's own keypoint2heatmaps produced, and the Segment(20) path fed by them."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from instancesegmentation_b200 import Segment, synth
+from instancesegmentation_b200.heatmaps import keypoint_heatmaps, stack_input
+from oracle.heatmap_oracle import keypoint_heatmaps as oracle_heatmaps
+from oracle.segment_oracle import segment_forward
+
+from conftest import randomized_state
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _ulp_diff(a, b):
+    ai, bi = a.view(np.int32).astype(np.int64), b.view(np.int32).astype(np.int64)
+    return np.abs(ai - bi)
+
+
+def test_heatmaps_match_reference_golden():
+    """float64 exp on the device may differ from numpy's by one ulp of the double, i.e. virtually never after
+    rounding to fp32: at most 1 fp32 ulp on at most 2 values per case, support identical elsewhere"""
+    z = np.load(os.path.join(GOLDEN, "heatmaps_golden.npz"))
+    for i in range(int(z["n"])):
+        h, w, sigma, thr = z[f"meta{i}"]
+        kp = torch.from_numpy(z[f"kp{i}"]).cuda()[None]
+        got = keypoint_heatmaps(kp, (int(h), int(w)), sigma=float(sigma), threshold=float(thr))[0].cpu().numpy()
+        want = z[f"maps{i}"]
+        d = _ulp_diff(got, want)
+        assert d.max() <= 1 and int((d != 0).sum()) <= 2, (i, int(d.max()), int((d != 0).sum()))
+        assert int(((got != 0) != (want != 0)).sum()) <= 1, i
+
+
+def test_heatmaps_batch_and_in_place_channel_slice():
+    rng = np.random.default_rng(5)
+    B, H, W = 5, 96, 128
+    kp = np.zeros((B, 17, 3), np.float32)
+    kp[..., 0] = rng.uniform(-20, W + 20, (B, 17))
+    kp[..., 1] = rng.uniform(-20, H + 20, (B, 17))
+    kp[..., 2] = rng.choice([0, 1, 1, 2], (B, 17))
+    img = torch.from_numpy(synth.batch(B, H, W, seed=3)).cuda()
+    x = stack_input(img, torch.from_numpy(kp).cuda())
+    assert x.shape == (B, 20, H, W)
+    assert torch.equal(x[:, :3], img)
+    want = np.stack([oracle_heatmaps(kp[b], (H, W)) for b in range(B)])
+    d = _ulp_diff(x[:, 3:].cpu().numpy(), want)
+    assert d.max() <= 1 and int((d != 0).sum()) <= 4
+    with pytest.raises(ValueError):
+        keypoint_heatmaps(torch.zeros((1, 17, 2), device="cuda"), (H, W))
+
+
+def test_segment20_train_batch_with_device_heatmaps():
+    """Segment(20).train_batch(image, heatmaps) (segment.py:531-534) with the maps produced on the device"""
+    ref = randomized_state(20, seed=5)
+    sd = ref.state_dict()
+    m = Segment(20)
+    m.load_state_dict(sd, strict=True)
+    m.precision, m.max_batch = "fp32", 2
+    m = m.cuda().eval()
+    B, H, W = 2, 64, 96
+    rng = np.random.default_rng(8)
+    kp = np.concatenate([rng.uniform(0, W, (B, 17, 1)), rng.uniform(0, H, (B, 17, 1)), np.ones((B, 17, 1))], 2).astype(np.float32)
+    img = torch.from_numpy(synth.batch(B, H, W, seed=1))
+    maps = keypoint_heatmaps(torch.from_numpy(kp).cuda(), (H, W))
+    with torch.no_grad():
+        got = m.train_batch(img.cuda(), maps).cpu()
+    x = torch.cat([img, torch.from_numpy(np.stack([oracle_heatmaps(kp[b], (H, W)) for b in range(B)]))], 1)
+    want = torch.sigmoid(segment_forward(sd, x))
+    assert float((got - want).abs().max()) <= 1e-4
