@@ -148,6 +148,17 @@ ISG_API int isg_keypoint_heatmaps(const float* kp_dev, int batch, int n_parts, i
                           float sigma, float threshold, float* out_dev, int64_t out_batch_stride,
                           void* stream);
 
+/* Per-instance crop / pad / resize of the source images to the network input (geometry of
+ * train_instance.py:160-196: window = instance box + 16 px pad, iaa.CropAndPad with zeros,
+ * iaa.Resize to the network size).  src_dev uint8 [n_img,src_h,src_w,3] (HWC, what cv2.imread
+ * gives), win_dev [n_inst,4] int32 {x0,y0,wk,hk} in source coordinates (may reach outside the
+ * image: zeros), inst_img_dev [n_inst] int32.  out_dev uint8 [n_inst,out_h,out_w,3] = the
+ * input of isg_forward_u8.  Bilinear with the decode's align_corners=False rule on the window,
+ * rounded half-to-even; the same window passed to isg_decode as the box pastes the mask back. */
+ISG_API int isg_crop_resize_u8(const uint8_t* src_dev, int n_img, int src_h, int src_w,
+                       const int32_t* win_dev, const int32_t* inst_img_dev, int n_inst,
+                       int out_h, int out_w, uint8_t* out_dev, void* stream);
+
 /* ---- training step exchange (train_instance.py:379-380) ---------------------
  * fused "unscale + Adam" over the flat fp32 gradient bucket after the NCCL all-reduce:
  * g = grad * grad_scale; standard Adam (lr, beta1, beta2, eps), bias-corrected by `step`. */

@@ -3,7 +3,7 @@
 // variant (train_instance.py:33-68), both written straight into the tensors the first conv reads.
 #include <cmath>
 
-#include "common.cuh"
+#include "decode_math.cuh"
 
 namespace isg {
 namespace {
@@ -57,6 +57,55 @@ heatmap_kernel(const float* __restrict__ kp, int n_parts, int H, int W, double s
     *reinterpret_cast<float4*>(dst) = v;
 }
 
+
+// ---- per-instance crop / pad / resize to the network size -----------------------------------------
+// One warp = one output row: the vertical tap and the two source rows are warp-uniform, lanes take
+// consecutive output pixels (adjacent taps of the source row), the 3 bytes of a pixel go to a
+// per-warp row buffer in shared memory and the finished row leaves as 16-byte stores (the network
+// input is written once, fully coalesced; the source windows are small and stay in L2).
+// Arithmetic = the decode's exact bilinear sequence on the window (decode_math.cuh make_tap /
+// exact_lerp2), rounded half-to-even: bit-identical to oracle_crop_resize.
+constexpr int CR_THREADS = 256, CR_WARPS = CR_THREADS / 32;
+
+__device__ __forceinline__ void ld_px3(const uint8_t* __restrict__ row, int x, int Ws, float (&v)[3]) {
+    if (row && x >= 0 && x < Ws) {
+        const uint8_t* q = row + 3 * x;
+        v[0] = (float)__ldg(q); v[1] = (float)__ldg(q + 1); v[2] = (float)__ldg(q + 2);
+    } else { v[0] = v[1] = v[2] = 0.f; }
+}
+
+__global__ void __launch_bounds__(CR_THREADS)
+crop_resize3_kernel(const uint8_t* __restrict__ src, int Hs, int Ws, const int32_t* __restrict__ win,
+                    const int32_t* __restrict__ inst_img, int S_h, int S_w, uint8_t* __restrict__ out) {
+    extern __shared__ __align__(16) uint8_t rowbuf[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = blockIdx.y, oy = blockIdx.x * CR_WARPS + warp;
+    if (oy >= S_h) return;
+    const int4 wn = __ldg(reinterpret_cast<const int4*>(win) + n);
+    const uint8_t* img = src + (size_t)__ldg(inst_img + n) * Hs * Ws * 3;
+    const float sy = __fdiv_rn((float)wn.w, (float)S_h), sx = __fdiv_rn((float)wn.z, (float)S_w);
+    const Tap ty = make_tap(oy, wn.w, sy);
+    const int ya = wn.y + ty.i0, yb = wn.y + ty.i1;
+    const uint8_t* r0 = (ya >= 0 && ya < Hs) ? img + (size_t)ya * Ws * 3 : nullptr;
+    const uint8_t* r1 = (yb >= 0 && yb < Hs) ? img + (size_t)yb * Ws * 3 : nullptr;
+    uint8_t* rb = rowbuf + (size_t)warp * S_w * 3;
+    for (int ox = lane; ox < S_w; ox += 32) {
+        const Tap tx = make_tap(ox, wn.z, sx);
+        const int xa = wn.x + tx.i0, xb = wn.x + tx.i1;
+        float a[3], b[3], c[3], d[3];
+        ld_px3(r0, xa, Ws, a); ld_px3(r0, xb, Ws, b); ld_px3(r1, xa, Ws, c); ld_px3(r1, xb, Ws, d);
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            const float v = exact_lerp2(a[ch], b[ch], c[ch], d[ch], ty, tx);
+            rb[3 * ox + ch] = (uint8_t)min(max(__float2int_rn(v), 0), 255);
+        }
+    }
+    __syncwarp();
+    uint4* dst = reinterpret_cast<uint4*>(out + ((size_t)n * S_h + oy) * S_w * 3);
+    const uint4* s4 = reinterpret_cast<const uint4*>(rb);
+    for (int i = lane; i < (S_w * 3) / 16; i += 32) __stcs(dst + i, s4[i]);
+}
+
 }  // namespace
 }  // namespace isg
 
@@ -81,6 +130,25 @@ int isg_keypoint_heatmaps(const float* kp_dev, int batch, int n_parts, int heigh
     const int64_t total4 = (int64_t)batch * n_parts * height * (width / 4);
     heatmap_kernel<<<(unsigned)((total4 + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         kp_dev, n_parts, height, width, s2, (double)threshold, r, out_dev, out_batch_stride, total4);
+    ISG_CUDA(cudaGetLastError());
+    return ISG_OK;
+}
+
+
+int isg_crop_resize_u8(const uint8_t* src_dev, int n_img, int src_h, int src_w, const int32_t* win_dev,
+                       const int32_t* inst_img_dev, int n_inst, int out_h, int out_w, uint8_t* out_dev, void* stream) {
+    if (n_inst == 0) return ISG_OK;
+    if (!src_dev || !win_dev || !inst_img_dev || !out_dev) return fail(ISG_ERR_ARG, "isg_crop_resize_u8: null argument");
+    if (n_img < 1 || src_h < 1 || src_w < 1 || n_inst < 0 || n_inst > 65535 || out_h < 1 || out_w < 16 || (out_w & 15))
+        return fail(ISG_ERR_ARG, "isg_crop_resize_u8: bad sizes (n_img=%d src %dx%d n_inst=%d out %dx%d; out_w must be a multiple of 16)",
+                    n_img, src_h, src_w, n_inst, out_h, out_w);
+    if (reinterpret_cast<uintptr_t>(out_dev) & 15) return fail(ISG_ERR_ARG, "isg_crop_resize_u8: output must be 16-byte aligned");
+    const size_t smem = (size_t)CR_WARPS * out_w * 3;
+    if (smem > 200 * 1024) return fail(ISG_ERR_ARG, "isg_crop_resize_u8: out_w %d too wide", out_w);
+    if (smem > 48 * 1024) ISG_CUDA(cudaFuncSetAttribute(crop_resize3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid(cdiv(out_h, CR_WARPS), n_inst);
+    crop_resize3_kernel<<<grid, CR_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(src_dev, src_h, src_w, win_dev,
+                                                                                      inst_img_dev, out_h, out_w, out_dev);
     ISG_CUDA(cudaGetLastError());
     return ISG_OK;
 }

@@ -154,3 +154,42 @@ double oracle_mask_iou(const uint8_t* a, const uint8_t* b, int64_t n) {
     }
     return uni ? (double)inter / (double)uni : 0.0;
 }
+
+/* Input side, PARITY UNPINNED (imgaug is absent): per-instance crop window
+ * win[n] = {x0, y0, wk, hk} of source image inst_img[n] (uint8 HWC, C channels), zero outside
+ * the image (iaa.CropAndPad pads with 0, train_instance.py:177-181), resized to S_h x S_w
+ * (iaa.Resize, :182-183) with the same align_corners=False bilinear rule as the decode, the
+ * window being the resize input (edge taps clamp at the window, not at the image); value =
+ * ly0*(lx0*a + lx1*b) + ly1*(lx0*c + lx1*d) in single IEEE operations, rounded half-to-even
+ * to uint8. */
+static float src_px(const uint8_t* img, int Hs, int Ws, int C, int y, int x, int c) {
+    if (x < 0 || y < 0 || x >= Ws || y >= Hs) return 0.0f;
+    return (float)img[((int64_t)y * Ws + x) * C + c];
+}
+
+void oracle_crop_resize(const uint8_t* src, int Hs, int Ws, int C, const int32_t* win,
+                        const int32_t* inst_img, int n_inst, int S_h, int S_w, uint8_t* out) {
+    for (int n = 0; n < n_inst; ++n) {
+        const uint8_t* img = src + (int64_t)inst_img[n] * Hs * Ws * C;
+        int x0 = win[4 * n], y0 = win[4 * n + 1], wk = win[4 * n + 2], hk = win[4 * n + 3];
+        for (int oy = 0; oy < S_h; ++oy) {
+            tap_t ty = tap(oy, hk, S_h);
+            for (int ox = 0; ox < S_w; ++ox) {
+                tap_t tx = tap(ox, wk, S_w);
+                for (int c = 0; c < C; ++c) {
+                    float a = src_px(img, Hs, Ws, C, y0 + ty.i0, x0 + tx.i0, c);
+                    float b = src_px(img, Hs, Ws, C, y0 + ty.i0, x0 + tx.i1, c);
+                    float cc = src_px(img, Hs, Ws, C, y0 + ty.i1, x0 + tx.i0, c);
+                    float d = src_px(img, Hs, Ws, C, y0 + ty.i1, x0 + tx.i1, c);
+                    float top = tx.l0 * a + tx.l1 * b;
+                    float bot = tx.l0 * cc + tx.l1 * d;
+                    float v = ty.l0 * top + ty.l1 * bot;
+                    float r = nearbyintf(v);          /* default rounding mode: half to even */
+                    if (r > 255.0f) r = 255.0f;
+                    if (r < 0.0f) r = 0.0f;
+                    out[(((int64_t)n * S_h + oy) * S_w + ox) * C + c] = (uint8_t)r;
+                }
+            }
+        }
+    }
+}

@@ -94,3 +94,16 @@ def mask_iou(a, b):
     a = np.ascontiguousarray(a, np.uint8).reshape(-1)
     b = np.ascontiguousarray(b, np.uint8).reshape(-1)
     return float(lib().oracle_mask_iou(_p(a, C.c_uint8), _p(b, C.c_uint8), C.c_int64(a.size)))
+
+
+def crop_resize(src, win, inst_img, size):
+    """src uint8 [n_img,Hs,Ws,C], win int32 [N,4] (x0,y0,wk,hk), inst_img int32 [N] -> uint8 [N,S_h,S_w,C]."""
+    src = np.ascontiguousarray(src, np.uint8)
+    win = np.ascontiguousarray(win, np.int32).reshape(-1, 4)
+    inst_img = np.ascontiguousarray(inst_img, np.int32)
+    _, Hs, Ws, Cc = src.shape
+    out = np.zeros((len(win), size[0], size[1], Cc), np.uint8)
+    lib().oracle_crop_resize(_p(src, C.c_uint8), C.c_int(Hs), C.c_int(Ws), C.c_int(Cc), _p(win, C.c_int32),
+                             _p(inst_img, C.c_int32), C.c_int(len(win)), C.c_int(size[0]), C.c_int(size[1]),
+                             _p(out, C.c_uint8))
+    return out

@@ -127,3 +127,38 @@ def test_heatmap_oracle_matches_reference_function_golden():
         assert np.array_equal(got, want), i
         assert want[z[f"kp{i}"][:, 2] != 1].max(initial=0) == 0      # hidden / missing parts stay empty
         assert want[:, -1, :].max() == 0 and want[:, :, -1].max() == 0   # the reference never writes the last row/column
+
+
+def test_bf16_tolerance_of_the_north_star_is_below_the_reference_graphs_own_bf16_sensitivity(golden_state):
+    """north_star asks max-abs 2e-2 / mean-abs 2e-3 for bf16.  Evidence that no bf16-storage execution of
+    this graph can meet it: the reference's fp32 arithmetic itself moves further than
+    that when ONLY the input image, or ONLY the conv weights, are rounded to bf16 once.  The GPU test therefore
+    asserts 'no worse than torch's own bf16 execution' and reports the numbers."""
+    x = torch.from_numpy(synth.batch(1, 256, 256, seed=77))
+    want = segment_forward(golden_state, x)
+    d_in = (segment_forward(golden_state, x.to(torch.bfloat16).float()) - want).abs()
+    sd_w = {k: (v.to(torch.bfloat16).float() if k.endswith("conv.weight") else v) for k, v in golden_state.items()}
+    d_w = (segment_forward(sd_w, x) - want).abs()
+    print(f"input->bf16: max {float(d_in.max()):.3f} mean {float(d_in.mean()):.4f} | "
+          f"weights->bf16: max {float(d_w.max()):.3f} mean {float(d_w.mean()):.4f}")
+    assert float(d_in.max()) > 2e-2 and float(d_in.mean()) > 2e-3
+    assert float(d_w.max()) > 2e-2 and float(d_w.mean()) > 2e-3
+
+
+def test_crop_resize_oracle_rules():
+    """oracle_crop_resize (parity unpinned -- imgaug is absent): identity windows copy, everything outside the
+    image is zero (CropAndPad), and the interpolation agrees with F.interpolate(bilinear, align_corners=False)
+    on the zero-padded window to within the final rounding"""
+    rng = np.random.default_rng(3)
+    src = rng.integers(0, 256, (2, 40, 56, 3), dtype=np.uint8)
+    same = D.crop_resize(src, np.array([[0, 0, 56, 40]], np.int32), np.array([1], np.int32), (40, 56))
+    assert np.array_equal(same[0], src[1])
+    out = D.crop_resize(src, np.array([[100, 100, 20, 20]], np.int32), np.array([0], np.int32), (16, 16))
+    assert out.max() == 0
+    win = np.array([[-7, -5, 50, 44]], np.int32)
+    got = D.crop_resize(src, win, np.array([0], np.int32), (64, 80))[0].astype(np.float32)
+    pad = np.zeros((44, 50, 3), np.float32)
+    pad[5:44, 7:50] = src[0, 0:39, 0:43]
+    want = F.interpolate(torch.from_numpy(pad).permute(2, 0, 1)[None], size=(64, 80), mode="bilinear",
+                         align_corners=False)[0].permute(1, 2, 0).numpy()
+    assert np.abs(got - want).max() <= 0.5 + 1e-3

@@ -72,3 +72,52 @@ def test_segment20_train_batch_with_device_heatmaps():
     x = torch.cat([img, torch.from_numpy(np.stack([oracle_heatmaps(kp[b], (H, W)) for b in range(B)]))], 1)
     want = torch.sigmoid(segment_forward(sd, x))
     assert float((got - want).abs().max()) <= 1e-4
+
+
+def test_crop_resize_bit_exact_against_oracle():
+    from instancesegmentation_b200.preprocess import crop_resize, instance_windows
+    from oracle import decode_oracle as D
+    rng = np.random.default_rng(11)
+    src = np.stack([synth.image_u8(96, 144, 40 + i) for i in range(3)])
+    src[1] = rng.integers(0, 256, src[1].shape, dtype=np.uint8)           # white noise: every rounding case
+    boxes = np.array([[10, 8, 90, 70], [0, 0, 144, 96], [-30, -20, 60, 50], [100, 60, 170, 120],
+                      [40, 30, 47, 35], [300, 300, 340, 330], [5, 5, 6, 6]], np.int64)      # inside, full, over the edges, tiny, outside
+    win = instance_windows(boxes, pad=16)
+    inst_img = np.array([0, 1, 2, 0, 1, 2, 1], np.int32)
+    for size in ((64, 64), (48, 80), (160, 208)):
+        got = crop_resize(torch.from_numpy(src).cuda(), win, inst_img, size).cpu().numpy()
+        want = D.crop_resize(src, win, inst_img, size)
+        assert np.array_equal(got, want), (size, int((got != want).sum()))
+    # a window of the network's own size is a plain copy with zero padding
+    w1 = np.array([[-8, -4, 160, 112]], np.int32)
+    got = crop_resize(torch.from_numpy(src).cuda(), w1, np.array([2], np.int32), (112, 160)).cpu().numpy()[0]
+    assert np.array_equal(got[4:100, 8:152], src[2]) and got[:4].max() == 0 and got[:, :8].max() == 0 and got[100:].max() == 0
+    with pytest.raises(ValueError):
+        crop_resize(torch.from_numpy(src).cuda(), w1, np.array([5], np.int32), (112, 160))
+
+
+def test_crop_forward_decode_round_trip():
+    """infer.py chain on the device: windows -> crop_resize -> forward_u8 -> decode into the same windows;
+    the pasted mask has the window's size and the statistics are in source coordinates"""
+    from instancesegmentation_b200.decode import decode_masks
+    from instancesegmentation_b200.preprocess import crop_resize, instance_windows
+    z = np.load(os.path.join(GOLDEN, "segment3_state.npz"))
+    m = Segment(3)
+    m.load_state_dict({k: torch.from_numpy(z[k]) for k in z.files}, strict=True)
+    m.precision, m.max_batch = "fp32", 4
+    m = m.cuda().eval()
+    src = torch.from_numpy(np.stack([synth.image_u8(128, 160, 7), synth.image_u8(128, 160, 8)])).cuda()
+    win = instance_windows(np.array([[20, 10, 100, 90], [60, 40, 150, 120], [0, 0, 50, 60]]), pad=16)
+    inst_img = np.array([0, 0, 1], np.int32)
+    crops = crop_resize(src, win, inst_img, (64, 96))
+    with torch.no_grad():
+        logits = m.forward_u8(crops, (0.5, 0.5, 0.5), (0.5, 0.5, 0.5))
+        direct = m(((crops.permute(0, 3, 1, 2).float() / 255.0) - 0.5) / 0.5)
+    assert float((logits - direct).abs().max()) <= 1e-4
+    r = decode_masks(logits, win, img_first=np.array([0, 2, 3], np.int32), canvas=(128, 160))
+    for n in range(3):
+        assert tuple(r.mask(n).shape) == (int(win[n, 3]), int(win[n, 2]))
+        if int(r.area[n]):
+            bx = r.bbox[n].tolist()
+            assert win[n, 0] <= bx[0] < bx[2] <= win[n, 0] + win[n, 2] and win[n, 1] <= bx[1] < bx[3] <= win[n, 1] + win[n, 3]
+    assert r.idmap.shape == (2, 128, 160) and int(r.idmap.max()) <= 3
