@@ -39,6 +39,18 @@ __device__ __noinline__ float exact_prob_at_nl(const TL* L, int h, int w, int oy
 
 struct DecAcc { int cnt, xmin, ymin, xmax, ymax; };
 
+// launch with programmatic stream serialization (the kernels start with griddepcontrol.wait)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, int block, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // pixels [idx, idx+nv) of one instance; IDENT: the mask has the size of the logit map
 template <typename TL, bool SOFT, bool IDENT>
 __device__ __forceinline__ void decode_run(const TL* __restrict__ L, int h, int w, int wk, int hk, int npix, int idx, int nv,
@@ -200,6 +212,9 @@ decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __rest
               const int64_t* __restrict__ mask_off, float thr, float thr_logit, float margin, int use_logit_cmp,
               uint8_t* __restrict__ masks, uint8_t* __restrict__ soft, int32_t* __restrict__ area,
               int32_t* __restrict__ bbox) {
+    // launched with programmatic stream serialization: the grid is staged while the previous kernel of the
+    // stream drains; nothing is read or written before that kernel has completed
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int n = blockIdx.y;
     const int4 bx = __ldg(reinterpret_cast<const int4*>(boxes) + n);
     const int wk = bx.z, hk = bx.w;
@@ -350,12 +365,14 @@ idmap_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restr
 constexpr int DT_THREADS = 256, DT_WARPS = DT_THREADS / 32, DT_RPW = 2, DT_ROWS = DT_WARPS * DT_RPW;
 __device__ unsigned g_dt_next, g_dt_done;
 
-// source indices of the align_corners=False rule (make_tap without the weights)
-__device__ __forceinline__ void tap_index(int dst, int in, float scale, int& i0, int& i1) {
+// source indices of the align_corners=False rule; returns the clamped source coordinate s, from which the
+// weights follow as make_tap derives them: l1 = s - i0, l0 = 1 - l1
+__device__ __forceinline__ float tap_index(int dst, int in, float scale, int& i0, int& i1) {
     float s = __fsub_rn(__fmul_rn(scale, __fadd_rn((float)dst, 0.5f)), 0.5f);
     if (s < 0.0f) s = 0.0f;
     i0 = min((int)s, in - 1);
     i1 = i0 + (i0 < in - 1 ? 1 : 0);
+    return s;
 }
 
 template <typename TL>
@@ -368,6 +385,7 @@ decode_tiled_kernel(const TL* __restrict__ logits, int n_inst, int h, int w, con
                     int Hs, int Ws, unsigned* __restrict__ claims) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     __shared__ int s_tile[2][2];   // {tile, instance} of the current and the next tile
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // see decode_kernel
     auto fetch = [&](int slot) {   // thread 0: next tile index and the instance it belongs to
         const int t = (int)atomicAdd(&g_dt_next, 1u);
         int lo = 0;
@@ -411,7 +429,8 @@ decode_tiled_kernel(const TL* __restrict__ logits, int n_inst, int h, int w, con
         for (int oy = row0; oy < min(row0 + DT_RPW, hk); ++oy) {
             ++rows;
             int y0, y1;
-            tap_index(oy, h, sy, y0, y1);
+            const float ys = tap_index(oy, h, sy, y0, y1);
+            const float ly1 = __fsub_rn(ys, (float)y0), ly0 = __fsub_rn(1.0f, ly1);
             const TL* r0 = L + (size_t)y0 * w;
             const TL* r1 = L + (size_t)y1 * w;
             uint8_t* drow = dst + (size_t)oy * wk;
@@ -420,14 +439,14 @@ decode_tiled_kernel(const TL* __restrict__ logits, int n_inst, int h, int w, con
             unsigned* crow = (cl && cy >= 0 && cy < Hs) ? cl + (size_t)cy * Ws : nullptr;
             int rcnt = 0;
             for (int x0 = 0; x0 < wk; x0 += 128) {
-                float a[4], b[4], c[4], d[4];
+                float a[4], b[4], c[4], d[4], fx[4];
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
                     const int ox = x0 + 32 * r + lane;
-                    a[r] = b[r] = c[r] = d[r] = 0.f;
+                    a[r] = b[r] = c[r] = d[r] = fx[r] = 0.f;
                     if (ox < wk) {
                         int i0, i1;
-                        tap_index(ox, w, sx, i0, i1);
+                        fx[r] = __fsub_rn(tap_index(ox, w, sx, i0, i1), (float)i0);   // lx1
                         a[r] = ldl(r0 + i0); b[r] = ldl(r0 + i1); c[r] = ldl(r1 + i0); d[r] = ldl(r1 + i1);
                     }
                 }
@@ -444,9 +463,9 @@ decode_tiled_kernel(const TL* __restrict__ logits, int n_inst, int h, int w, con
                         if (s4 == s4 && lo4 - thr_logit > margin) m = true;
                         else if (s4 == s4 && thr_logit - hi4 > margin) m = false;
                         else {
-                            const Tap ty = make_tap(oy, h, sy), tx = make_tap(ox, w, sx);
-                            const float p = ty.l0 * (tx.l0 * fast_sigmoid(a[r]) + tx.l1 * fast_sigmoid(b[r])) +
-                                            ty.l1 * (tx.l0 * fast_sigmoid(c[r]) + tx.l1 * fast_sigmoid(d[r]));
+                            const float lx1 = fx[r], lx0 = 1.0f - lx1;
+                            const float p = ly0 * (lx0 * fast_sigmoid(a[r]) + lx1 * fast_sigmoid(b[r])) +
+                                            ly1 * (lx0 * fast_sigmoid(c[r]) + lx1 * fast_sigmoid(d[r]));
                             if (fabsf(p - thr) > DECIDE_MARGIN) m = p > thr;
                             else m = exact_prob_at_nl(L, h, w, oy, sy, ox, sx) > thr;
                         }
@@ -627,11 +646,10 @@ int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int h, int w
     }
     const int groups = cdiv(max_wk * max_hk, DEC_PPB);
     dim3 grid(std::max(1, std::min(groups, slots / n_inst)), n_inst);
-#define ISG_DEC(TL, SOFT)                                                                                     \
-    decode_kernel<TL, SOFT><<<grid, DEC_THREADS, 0, st>>>(static_cast<const TL*>(logits_dev), h, w, boxes_dev, \
-                                                           mask_off_dev, threshold, thr_logit, margin,         \
-                                                           use_logit_cmp,                                      \
-                                                           masks_dev, soft_dev, area_dev, bbox_dev)
+#define ISG_DEC(TL, SOFT)                                                                                        \
+    ISG_CUDA(launch_pdl(decode_kernel<TL, SOFT>, grid, DEC_THREADS, st, static_cast<const TL*>(logits_dev), h, w, \
+                        boxes_dev, mask_off_dev, threshold, thr_logit, margin, use_logit_cmp, masks_dev, soft_dev, \
+                        area_dev, bbox_dev))
     if (logits_bf16) { if (soft_dev) ISG_DEC(bf16, true); else ISG_DEC(bf16, false); }
     else { if (soft_dev) ISG_DEC(float, true); else ISG_DEC(float, false); }
 #undef ISG_DEC
@@ -675,13 +693,13 @@ int isg_decode_tiled(const void* logits_dev, int logits_bf16, int n_inst, int h,
     const int grid = std::max(1, std::min(n_tiles, slots));
     unsigned* claims = reinterpret_cast<unsigned*>(idmap_dev);
     if (logits_bf16)
-        decode_tiled_kernel<bf16><<<grid, DT_THREADS, 0, st>>>(static_cast<const bf16*>(logits_dev), n_inst, h, w, boxes_dev,
-            mask_off_dev, tile_first_dev, n_tiles, threshold, thr_logit, margin, masks_dev, area_dev, bbox_dev,
-            inst_img_dev, img_first_dev, canvas_h, canvas_w, claims);
+        ISG_CUDA(launch_pdl(decode_tiled_kernel<bf16>, dim3(grid), DT_THREADS, st, static_cast<const bf16*>(logits_dev), n_inst,
+                            h, w, boxes_dev, mask_off_dev, tile_first_dev, n_tiles, threshold, thr_logit, margin, masks_dev,
+                            area_dev, bbox_dev, inst_img_dev, img_first_dev, canvas_h, canvas_w, claims));
     else
-        decode_tiled_kernel<float><<<grid, DT_THREADS, 0, st>>>(static_cast<const float*>(logits_dev), n_inst, h, w, boxes_dev,
-            mask_off_dev, tile_first_dev, n_tiles, threshold, thr_logit, margin, masks_dev, area_dev, bbox_dev,
-            inst_img_dev, img_first_dev, canvas_h, canvas_w, claims);
+        ISG_CUDA(launch_pdl(decode_tiled_kernel<float>, dim3(grid), DT_THREADS, st, static_cast<const float*>(logits_dev), n_inst,
+                            h, w, boxes_dev, mask_off_dev, tile_first_dev, n_tiles, threshold, thr_logit, margin, masks_dev,
+                            area_dev, bbox_dev, inst_img_dev, img_first_dev, canvas_h, canvas_w, claims));
     ISG_CUDA(cudaGetLastError());
     if (idmap_dev) {
         const unsigned blocks = (unsigned)((total + 255) / 256);

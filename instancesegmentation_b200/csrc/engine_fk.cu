@@ -529,13 +529,22 @@ struct FkBuilder {
             const int keep = tune ? per_mode : 1;
             for (int i = 0; i < (int)found.size() && i < keep; ++i) out.push_back(found[i]);
         }
-        if (out.empty() && (env_ctas || env_lbuf)) {   // pinned mode infeasible for this launch: default mode
-            for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
-                Lay L;
-                if (!layout(s, TH, TW0, 1, 2, L)) continue;
-                L.score = (double)(TH * TW0) / (L.n_mt * 128) + 1e-4 * TH;
-                if (out.empty() || L.score > out[0].score) { out.clear(); out.push_back(L); }
-            }
+        if (out.empty()) {
+            // the requested mode (pinned by the environment, or the single default mode when tuning is off) has no
+            // feasible tile for this launch at this image size: search every generic mode and narrower tiles
+            for (int nb = 2; nb >= 1 && out.empty(); --nb)
+                for (int c = 1; c <= 2 && out.empty(); ++c)
+                    for (int split = 1; split <= 8; ++split) {
+                        const int TW = cdiv(s.qW, nx * split);
+                        if (split > 1 && TW < 16) break;
+                        for (int TH = 1; TH <= s.qH && TH + 2 * max_halo <= 256; ++TH) {
+                            Lay L;
+                            if (!layout(s, TH, TW, c, nb, L)) continue;
+                            L.score = (double)(TH * TW) / (L.n_mt * 128) + 1e-4 * TH;
+                            if (out.empty() || L.score > out[0].score) { out.clear(); out.push_back(L); }
+                        }
+                        if (!out.empty()) break;
+                    }
         }
         // the heuristic's favourite of the default mode stays first (it is what runs without tuning)
         return out;

@@ -1,6 +1,7 @@
 // Input side of the hot path: the per-instance crop / pad / resize to the network
 // size (geometry of reference train_instance.py:160-196) and the keypoint heat maps of the Segment(20)
 // variant (train_instance.py:33-68), both written straight into the tensors the first conv reads.
+#include <climits>
 #include <cmath>
 
 #include "decode_math.cuh"
@@ -59,13 +60,16 @@ heatmap_kernel(const float* __restrict__ kp, int n_parts, int H, int W, double s
 
 
 // ---- per-instance crop / pad / resize to the network size -----------------------------------------
-// One warp = one output row: the vertical tap and the two source rows are warp-uniform, lanes take
-// consecutive output pixels (adjacent taps of the source row), the 3 bytes of a pixel go to a
-// per-warp row buffer in shared memory and the finished row leaves as 16-byte stores (the network
-// input is written once, fully coalesced; the source windows are small and stay in L2).
-// Arithmetic = the decode's exact bilinear sequence on the window (decode_math.cuh make_tap /
-// exact_lerp2), rounded half-to-even: bit-identical to oracle_crop_resize.
-constexpr int CR_THREADS = 256, CR_WARPS = CR_THREADS / 32;
+// One warp = CR_ROWS consecutive output rows, lanes = consecutive output pixels.  Windows are usually
+// upsampled (instance boxes are smaller than the network input), so neighbouring output rows share
+// their pair of source rows: the horizontal part of the bilinear form (lx0*a + lx1*b per source row and
+// channel) is computed once per distinct source-row pair and only the vertical mix runs per output row.
+// The 3 bytes of a pixel go to a per-warp row buffer in shared memory and finished rows leave as
+// 16-byte streaming stores (the network input is written once, fully coalesced; the source windows are
+// small and stay in L2).  Arithmetic = the decode's exact bilinear sequence on the window
+// (decode_math.cuh make_tap / exact_lerp2 order), rounded half-to-even: bit-identical to
+// oracle_crop_resize.
+constexpr int CR_THREADS = 256, CR_WARPS = CR_THREADS / 32, CR_ROWS = 4;
 
 __device__ __forceinline__ void ld_px3(const uint8_t* __restrict__ row, int x, int Ws, float (&v)[3]) {
     if (row && x >= 0 && x < Ws) {
@@ -74,36 +78,60 @@ __device__ __forceinline__ void ld_px3(const uint8_t* __restrict__ row, int x, i
     } else { v[0] = v[1] = v[2] = 0.f; }
 }
 
+__device__ __forceinline__ unsigned sat_u8(float v) {   // round half to even, clamp to 0..255
+    unsigned r;
+    asm("cvt.rni.sat.u8.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return r;
+}
+
 __global__ void __launch_bounds__(CR_THREADS)
 crop_resize3_kernel(const uint8_t* __restrict__ src, int Hs, int Ws, const int32_t* __restrict__ win,
                     const int32_t* __restrict__ inst_img, int S_h, int S_w, uint8_t* __restrict__ out) {
     extern __shared__ __align__(16) uint8_t rowbuf[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n = blockIdx.y, oy = blockIdx.x * CR_WARPS + warp;
-    if (oy >= S_h) return;
+    const int n = blockIdx.y, oy0 = (blockIdx.x * CR_WARPS + warp) * CR_ROWS;
+    if (oy0 >= S_h) return;
     const int4 wn = __ldg(reinterpret_cast<const int4*>(win) + n);
     const uint8_t* img = src + (size_t)__ldg(inst_img + n) * Hs * Ws * 3;
     const float sy = __fdiv_rn((float)wn.w, (float)S_h), sx = __fdiv_rn((float)wn.z, (float)S_w);
-    const Tap ty = make_tap(oy, wn.w, sy);
-    const int ya = wn.y + ty.i0, yb = wn.y + ty.i1;
-    const uint8_t* r0 = (ya >= 0 && ya < Hs) ? img + (size_t)ya * Ws * 3 : nullptr;
-    const uint8_t* r1 = (yb >= 0 && yb < Hs) ? img + (size_t)yb * Ws * 3 : nullptr;
-    uint8_t* rb = rowbuf + (size_t)warp * S_w * 3;
+    const int nrows = min(CR_ROWS, S_h - oy0);
+    Tap ty[CR_ROWS];
+#pragma unroll
+    for (int j = 0; j < CR_ROWS; ++j) ty[j] = make_tap(min(oy0 + j, S_h - 1), wn.w, sy);
+    const int row_bytes = S_w * 3;
+    uint8_t* rb = rowbuf + (size_t)warp * CR_ROWS * row_bytes;
     for (int ox = lane; ox < S_w; ox += 32) {
         const Tap tx = make_tap(ox, wn.z, sx);
         const int xa = wn.x + tx.i0, xb = wn.x + tx.i1;
-        float a[3], b[3], c[3], d[3];
-        ld_px3(r0, xa, Ws, a); ld_px3(r0, xb, Ws, b); ld_px3(r1, xa, Ws, c); ld_px3(r1, xb, Ws, d);
+        float top[3] = {0.f, 0.f, 0.f}, bot[3] = {0.f, 0.f, 0.f};
+        int pa = INT_MIN, pb = INT_MIN;
 #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-            const float v = exact_lerp2(a[ch], b[ch], c[ch], d[ch], ty, tx);
-            rb[3 * ox + ch] = (uint8_t)min(max(__float2int_rn(v), 0), 255);
+        for (int j = 0; j < CR_ROWS; ++j) {
+            if (j < nrows) {
+                if (ty[j].i0 != pa || ty[j].i1 != pb) {      // warp-uniform: a new pair of source rows
+                    pa = ty[j].i0; pb = ty[j].i1;
+                    const int ya = wn.y + pa, yb = wn.y + pb;
+                    const uint8_t* r0 = (ya >= 0 && ya < Hs) ? img + (size_t)ya * Ws * 3 : nullptr;
+                    const uint8_t* r1 = (yb >= 0 && yb < Hs) ? img + (size_t)yb * Ws * 3 : nullptr;
+                    float a[3], b[3], c[3], d[3];
+                    ld_px3(r0, xa, Ws, a); ld_px3(r0, xb, Ws, b); ld_px3(r1, xa, Ws, c); ld_px3(r1, xb, Ws, d);
+#pragma unroll
+                    for (int ch = 0; ch < 3; ++ch) {
+                        top[ch] = __fadd_rn(__fmul_rn(tx.l0, a[ch]), __fmul_rn(tx.l1, b[ch]));
+                        bot[ch] = __fadd_rn(__fmul_rn(tx.l0, c[ch]), __fmul_rn(tx.l1, d[ch]));
+                    }
+                }
+                uint8_t* o = rb + j * row_bytes + 3 * ox;
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch)
+                    o[ch] = (uint8_t)sat_u8(__fadd_rn(__fmul_rn(ty[j].l0, top[ch]), __fmul_rn(ty[j].l1, bot[ch])));
+            }
         }
     }
     __syncwarp();
-    uint4* dst = reinterpret_cast<uint4*>(out + ((size_t)n * S_h + oy) * S_w * 3);
+    uint4* dst = reinterpret_cast<uint4*>(out + ((size_t)n * S_h + oy0) * row_bytes);   // the rows are contiguous
     const uint4* s4 = reinterpret_cast<const uint4*>(rb);
-    for (int i = lane; i < (S_w * 3) / 16; i += 32) __stcs(dst + i, s4[i]);
+    for (int i = lane; i < (nrows * row_bytes) / 16; i += 32) __stcs(dst + i, s4[i]);
 }
 
 }  // namespace
@@ -143,10 +171,10 @@ int isg_crop_resize_u8(const uint8_t* src_dev, int n_img, int src_h, int src_w, 
         return fail(ISG_ERR_ARG, "isg_crop_resize_u8: bad sizes (n_img=%d src %dx%d n_inst=%d out %dx%d; out_w must be a multiple of 16)",
                     n_img, src_h, src_w, n_inst, out_h, out_w);
     if (reinterpret_cast<uintptr_t>(out_dev) & 15) return fail(ISG_ERR_ARG, "isg_crop_resize_u8: output must be 16-byte aligned");
-    const size_t smem = (size_t)CR_WARPS * out_w * 3;
+    const size_t smem = (size_t)CR_WARPS * CR_ROWS * out_w * 3;
     if (smem > 200 * 1024) return fail(ISG_ERR_ARG, "isg_crop_resize_u8: out_w %d too wide", out_w);
     if (smem > 48 * 1024) ISG_CUDA(cudaFuncSetAttribute(crop_resize3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid(cdiv(out_h, CR_WARPS), n_inst);
+    dim3 grid(cdiv(out_h, CR_WARPS * CR_ROWS), n_inst);
     crop_resize3_kernel<<<grid, CR_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(src_dev, src_h, src_w, win_dev,
                                                                                       inst_img_dev, out_h, out_w, out_dev);
     ISG_CUDA(cudaGetLastError());

@@ -128,10 +128,11 @@ def test_weight_reload_and_batch_independence(golden_state):
     assert float((y2.cpu() - segment_forward(sd2, x.cpu())).abs().max()) <= FP32_TOL
 
 
-@pytest.mark.parametrize("H,W", [(96, 160), (512, 512), (208, 48)])
+@pytest.mark.parametrize("H,W", [(96, 160), (512, 512), (208, 48), (16, 16), (1024, 1024), (64, 2048), (1536, 32)])
 def test_bf16_layerwise_against_oracle(golden_state, H, W):
     """Every tapped activation of the tensor-core path stays within bf16 noise of the oracle
-    (a wrong descriptor, tap offset or weight slot shows up as an O(1) relative error)."""
+    (a wrong descriptor, tap offset or weight slot shows up as an O(1) relative error); sizes from the
+    smallest legal one to cfg4's 1024x1024 and very wide / very tall images."""
     m = _model(golden_state, precision="bf16", max_batch=2)
     x = torch.from_numpy(synth.batch(2, H, W, seed=4321))
     taps = {}
@@ -217,6 +218,8 @@ np.save(sys.argv[3], y.cpu().numpy())
                    {"ISG_FK_FORCE_PIPE": "1"}]),
     # 512x512: the residual-bottleneck runs go through the cluster-resident launch (csrc/mega.cuh)
     ("3x512x512", [{"ISG_FK_NO_MEGA": "1", "ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_NO_MEGA8": "1"}]),
+    # 1024x1024 (cfg4): the untuned default mode has no feasible tile for one launch -> fallback search
+    ("2x1024x1024", [{"ISG_FK_NO_TUNE": "1"}, {}]),
 ])
 def test_bf16_launch_variants_are_bitwise_identical(tmp_path, size, envs):
     """Every way a fused launch may run (tile, CTAs per SM, load buffering -- the autotuner's choices -- and
