@@ -294,7 +294,7 @@ inline cudaError_t launch_fk(int ctas, int grid, size_t smem, const FkMaps& m, c
     static const bool pdl = getenv("ISG_FK_NO_PDL") == nullptr;
     cudaLaunchConfig_t cfg;
     std::memset(&cfg, 0, sizeof cfg);
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(ctas == 2 ? 256 : 512);
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(ctas == 4 ? 128 : ctas == 2 ? 256 : 512);
     cfg.dynamicSmemBytes = smem; cfg.stream = stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -302,6 +302,8 @@ inline cudaError_t launch_fk(int ctas, int grid, size_t smem, const FkMaps& m, c
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
     if (p.pipe_slots)
         return cudaLaunchKernelEx(&cfg, fk::fk_pipe_kernel, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+    if (ctas == 4)
+        return cudaLaunchKernelEx(&cfg, fk::fk_kernel<128>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
     if (ctas == 2)
         return cudaLaunchKernelEx(&cfg, fk::fk_kernel<256>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
     return cudaLaunchKernelEx(&cfg, fk::fk_kernel<512>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
@@ -474,7 +476,7 @@ struct FkBuilder {
         off = r128(off + rel);
         L.bar_off = off;
         L.smem = (size_t)off + 128 + 2 * 3 * 40 * 8;   // barriers + A-descriptor tables
-        return L.smem <= (ctas == 2 ? 112 * 1024 : 224 * 1024);
+        return L.smem <= (ctas == 4 ? 55 * 1024 : ctas == 2 ? 112 * 1024 : 224 * 1024);
     }
 
     // candidate layouts, best heuristic score first.  The plan times them on the device
@@ -494,14 +496,16 @@ struct FkBuilder {
         const int env_lbuf = getenv("ISG_FK_LBUF") ? atoi(getenv("ISG_FK_LBUF")) : 0;
         const int per_mode = getenv("ISG_FK_TUNE_TOP") ? atoi(getenv("ISG_FK_TUNE_TOP")) : 3;
         std::vector<Lay> out;
-        for (int mode = 0; mode < 8; ++mode) {
+        for (int mode = 0; mode < 10; ++mode) {
             // modes 0-3: generic kernel (mode 0 = one double-buffered CTA per SM); 4-7: warp-specialised,
-            // 2 / 3 load slots x 3 / 2 epilogue warp groups
-            const int pipe = mode >= 4 ? 2 + (mode & 1) : 0;
+            // 2 / 3 load slots x 3 / 2 epilogue warp groups; 8-9: generic kernel, four 128-thread CTAs per SM
+            const bool quad = mode >= 8;
+            const int pipe = (mode >= 4 && !quad) ? 2 + (mode & 1) : 0;
             const int groups = mode >= 6 ? 2 : 3;
+            if (quad && getenv("ISG_FK_NO_QUAD")) continue;
             if (pipe && (!pipe_ok(s) || env_ctas || env_lbuf)) continue;
             if (!pipe && getenv("ISG_FK_FORCE_PIPE") && pipe_ok(s)) continue;   // tests: every eligible launch warp-specialised
-            const int c = pipe ? 1 : (mode & 1 ? 2 : 1), nb = pipe ? 2 : (mode & 2 ? 1 : 2);
+            const int c = quad ? 4 : pipe ? 1 : (mode & 1 ? 2 : 1), nb = quad ? (mode & 1 ? 1 : 2) : pipe ? 2 : (mode & 2 ? 1 : 2);
             if (!tune && mode && !(env_ctas || env_lbuf)) break;
             if (env_ctas && c != env_ctas) continue;
             if (env_lbuf && nb != env_lbuf) continue;
@@ -735,6 +739,7 @@ struct FkBuilder {
         });
         cudaFuncSetAttribute(fk::fk_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         cudaFuncSetAttribute(fk::fk_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024);
+        cudaFuncSetAttribute(fk::fk_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 56 * 1024);
         cudaFuncSetAttribute(fk::fk_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         int num_sms = 148;
         cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, P->device);

@@ -438,7 +438,7 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
 }
 
 template <int NT>
-__global__ void __launch_bounds__(NT, NT == 512 ? 1 : 2)
+__global__ void __launch_bounds__(NT, NT == 512 ? 1 : (NT == 256 ? 2 : 4))
 fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtensorMap m1,
           const __grid_constant__ CUtensorMap m2, const __grid_constant__ CUtensorMap m3,
           const __grid_constant__ CUtensorMap mo0, const __grid_constant__ CUtensorMap mo1,

@@ -64,9 +64,9 @@ heatmap_kernel(const float* __restrict__ kp, int n_parts, int H, int W, double s
 // upsampled (instance boxes are smaller than the network input), so neighbouring output rows share
 // their pair of source rows: the horizontal part of the bilinear form (lx0*a + lx1*b per source row and
 // channel) is computed once per distinct source-row pair and only the vertical mix runs per output row.
-// The 3 bytes of a pixel go to a per-warp row buffer in shared memory and finished rows leave as
-// 16-byte streaming stores (the network input is written once, fully coalesced; the source windows are
-// small and stay in L2).  Arithmetic = the decode's exact bilinear sequence on the window
+// The 3 bytes of a pixel go to a per-warp 32-pixel chunk in shared memory and every chunk leaves as
+// 16-byte streaming stores of whole 32-byte sectors (the network input is written once; the source
+// windows are small and stay in L2).  Arithmetic = the decode's exact bilinear sequence on the window
 // (decode_math.cuh make_tap / exact_lerp2 order), rounded half-to-even: bit-identical to
 // oracle_crop_resize.
 constexpr int CR_THREADS = 256, CR_WARPS = CR_THREADS / 32, CR_ROWS = 4;
@@ -74,20 +74,21 @@ constexpr int CR_THREADS = 256, CR_WARPS = CR_THREADS / 32, CR_ROWS = 4;
 __device__ __forceinline__ void ld_px3(const uint8_t* __restrict__ row, int x, int Ws, float (&v)[3]) {
     if (row && x >= 0 && x < Ws) {
         const uint8_t* q = row + 3 * x;
-        v[0] = (float)__ldg(q); v[1] = (float)__ldg(q + 1); v[2] = (float)__ldg(q + 2);
+        // byte -> float through the mantissa of 2^23 (exact; keeps the conversions off the quarter-rate pipe)
+        v[0] = __uint_as_float(0x4B000000u | __ldg(q)) - 8388608.0f;
+        v[1] = __uint_as_float(0x4B000000u | __ldg(q + 1)) - 8388608.0f;
+        v[2] = __uint_as_float(0x4B000000u | __ldg(q + 2)) - 8388608.0f;
     } else { v[0] = v[1] = v[2] = 0.f; }
 }
 
-__device__ __forceinline__ unsigned sat_u8(float v) {   // round half to even, clamp to 0..255
-    unsigned r;
-    asm("cvt.rni.sat.u8.f32 %0, %1;" : "=r"(r) : "f"(v));
-    return r;
-}
+// round half to even for v in [0, 255.5): adding 1.5 * 2^23 leaves the rounded integer in the low mantissa
+// bits (the fp32 add itself rounds to nearest-even at unit spacing); the byte store keeps the low 8 bits
+__device__ __forceinline__ unsigned sat_u8(float v) { return __float_as_uint(__fadd_rn(v, 12582912.0f)); }
 
 __global__ void __launch_bounds__(CR_THREADS)
 crop_resize3_kernel(const uint8_t* __restrict__ src, int Hs, int Ws, const int32_t* __restrict__ win,
                     const int32_t* __restrict__ inst_img, int S_h, int S_w, uint8_t* __restrict__ out) {
-    extern __shared__ __align__(16) uint8_t rowbuf[];
+    __shared__ __align__(16) uint8_t chunk[CR_WARPS][CR_ROWS][96];   // 32 pixels x 3 bytes of each of the warp's rows
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = blockIdx.y, oy0 = (blockIdx.x * CR_WARPS + warp) * CR_ROWS;
     if (oy0 >= S_h) return;
@@ -99,15 +100,18 @@ crop_resize3_kernel(const uint8_t* __restrict__ src, int Hs, int Ws, const int32
 #pragma unroll
     for (int j = 0; j < CR_ROWS; ++j) ty[j] = make_tap(min(oy0 + j, S_h - 1), wn.w, sy);
     const int row_bytes = S_w * 3;
-    uint8_t* rb = rowbuf + (size_t)warp * CR_ROWS * row_bytes;
-    for (int ox = lane; ox < S_w; ox += 32) {
-        const Tap tx = make_tap(ox, wn.z, sx);
-        const int xa = wn.x + tx.i0, xb = wn.x + tx.i1;
-        float top[3] = {0.f, 0.f, 0.f}, bot[3] = {0.f, 0.f, 0.f};
-        int pa = INT_MIN, pb = INT_MIN;
+    uint8_t* orow = out + ((size_t)n * S_h + oy0) * row_bytes;
+    // the 16-byte piece of the chunk this lane stores: row sj, bytes [16 sq, 16 sq + 16)
+    const int sj = lane / 6, sq = lane - sj * 6;
+    for (int x0 = 0; x0 < S_w; x0 += 32) {
+        const int ox = x0 + lane;
+        if (ox < S_w) {
+            const Tap tx = make_tap(ox, wn.z, sx);
+            const int xa = wn.x + tx.i0, xb = wn.x + tx.i1;
+            float top[3] = {0.f, 0.f, 0.f}, bot[3] = {0.f, 0.f, 0.f};
+            int pa = INT_MIN, pb = INT_MIN;
 #pragma unroll
-        for (int j = 0; j < CR_ROWS; ++j) {
-            if (j < nrows) {
+            for (int j = 0; j < CR_ROWS; ++j) {
                 if (ty[j].i0 != pa || ty[j].i1 != pb) {      // warp-uniform: a new pair of source rows
                     pa = ty[j].i0; pb = ty[j].i1;
                     const int ya = wn.y + pa, yb = wn.y + pb;
@@ -121,17 +125,19 @@ crop_resize3_kernel(const uint8_t* __restrict__ src, int Hs, int Ws, const int32
                         bot[ch] = __fadd_rn(__fmul_rn(tx.l0, c[ch]), __fmul_rn(tx.l1, d[ch]));
                     }
                 }
-                uint8_t* o = rb + j * row_bytes + 3 * ox;
+                uint8_t* o = &chunk[warp][j][3 * lane];
 #pragma unroll
                 for (int ch = 0; ch < 3; ++ch)
                     o[ch] = (uint8_t)sat_u8(__fadd_rn(__fmul_rn(ty[j].l0, top[ch]), __fmul_rn(ty[j].l1, bot[ch])));
             }
         }
+        __syncwarp();
+        // 32 pixels = 96 bytes = three full 32-byte sectors of every row (rows and chunks are 32-byte aligned)
+        if (sj < nrows && 3 * x0 + 16 * sq < row_bytes && lane < 6 * CR_ROWS)
+            __stcs(reinterpret_cast<uint4*>(orow + (size_t)sj * row_bytes + 3 * x0 + 16 * sq),
+                   *reinterpret_cast<const uint4*>(&chunk[warp][sj][16 * sq]));
+        __syncwarp();
     }
-    __syncwarp();
-    uint4* dst = reinterpret_cast<uint4*>(out + ((size_t)n * S_h + oy0) * row_bytes);   // the rows are contiguous
-    const uint4* s4 = reinterpret_cast<const uint4*>(rb);
-    for (int i = lane; i < (nrows * row_bytes) / 16; i += 32) __stcs(dst + i, s4[i]);
 }
 
 }  // namespace
@@ -171,11 +177,8 @@ int isg_crop_resize_u8(const uint8_t* src_dev, int n_img, int src_h, int src_w, 
         return fail(ISG_ERR_ARG, "isg_crop_resize_u8: bad sizes (n_img=%d src %dx%d n_inst=%d out %dx%d; out_w must be a multiple of 16)",
                     n_img, src_h, src_w, n_inst, out_h, out_w);
     if (reinterpret_cast<uintptr_t>(out_dev) & 15) return fail(ISG_ERR_ARG, "isg_crop_resize_u8: output must be 16-byte aligned");
-    const size_t smem = (size_t)CR_WARPS * CR_ROWS * out_w * 3;
-    if (smem > 200 * 1024) return fail(ISG_ERR_ARG, "isg_crop_resize_u8: out_w %d too wide", out_w);
-    if (smem > 48 * 1024) ISG_CUDA(cudaFuncSetAttribute(crop_resize3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(cdiv(out_h, CR_WARPS * CR_ROWS), n_inst);
-    crop_resize3_kernel<<<grid, CR_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(src_dev, src_h, src_w, win_dev,
+    crop_resize3_kernel<<<grid, CR_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(src_dev, src_h, src_w, win_dev,
                                                                                       inst_img_dev, out_h, out_w, out_dev);
     ISG_CUDA(cudaGetLastError());
     return ISG_OK;

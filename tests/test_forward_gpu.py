@@ -215,7 +215,8 @@ np.save(sys.argv[3], y.cpu().numpy())
 @pytest.mark.parametrize("size,envs", [
     ("4x128x192", [{"ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "1"},
                    {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "2"}, {"ISG_FK_CTAS": "1", "ISG_FK_LBUF": "1"},
-                   {"ISG_FK_FORCE_PIPE": "1"}]),
+                   {"ISG_FK_FORCE_PIPE": "1"}, {"ISG_FK_CTAS": "4", "ISG_FK_LBUF": "2"},
+                   {"ISG_FK_CTAS": "4", "ISG_FK_LBUF": "1"}]),
     # 512x512: the residual-bottleneck runs go through the cluster-resident launch (csrc/mega.cuh)
     ("3x512x512", [{"ISG_FK_NO_MEGA": "1", "ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_NO_MEGA8": "1"}]),
     # 1024x1024 (cfg4): the untuned default mode has no feasible tile for one launch -> fallback search
