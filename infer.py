@@ -1,7 +1,8 @@
 """Inference CLI with the reference's call surface (reference infer.py:12-36): flags
 ``-i/--test-image-dir``, ``-o/--output-dir``, ``--continue-test`` and ``path_decompose``.
-The reference's loop body stops after ``path_decompose``; here it is completed: load ->
-resize to the network size -> uint8 NHWC batch to the device -> ToTensor + Normalize(0.5, 0.5)
+The reference's loop body stops after ``path_decompose``; here it is completed: load -> uint8 image to
+the device -> resize to the network size (libisg, the crop/resize kernel of the training data path,
+train_instance.py:160-196, with the whole image as the window) -> ToTensor + Normalize(0.5, 0.5)
 (train_instance.py:80-85) inside the first kernel -> Segment forward (libisg) -> mask decode back to
 the source resolution (libisg) -> ``<name>.png``.
 """
@@ -42,6 +43,7 @@ def run(args):
     import torch
 
     from instancesegmentation_b200.decode import decode_masks
+    from instancesegmentation_b200.preprocess import crop_resize
     from model.segment import Segment
 
     dev = torch.device("cuda", torch.cuda.current_device())
@@ -60,14 +62,16 @@ def run(args):
             todo.append((path, dst))
     S = args.size
     for i in range(0, len(todo), args.batch):
-        chunk, imgs, boxes = todo[i:i + args.batch], [], []
-        for path, _ in chunk:
+        chunk, boxes = todo[i:i + args.batch], []
+        x = torch.empty((len(chunk), S, S, 3), dtype=torch.uint8, device=dev)     # network inputs, uint8 NHWC
+        for n, (path, _) in enumerate(chunk):
             bgr = cv2.imread(path, cv2.IMREAD_COLOR)
             if bgr is None:
                 raise IOError(f"cannot read {path}")
-            boxes.append((0, 0, bgr.shape[1], bgr.shape[0]))
-            imgs.append(cv2.cvtColor(cv2.resize(bgr, (S, S)), cv2.COLOR_BGR2RGB))
-        x = torch.from_numpy(np.stack(imgs)).pin_memory().to(dev, non_blocking=True)   # uint8 [B,S,S,3]
+            h, w = bgr.shape[:2]
+            boxes.append((0, 0, w, h))
+            rgb = torch.from_numpy(np.ascontiguousarray(bgr[:, :, ::-1])).pin_memory().to(dev, non_blocking=True)
+            crop_resize(rgb[None], np.array([[0, 0, w, h]], np.int32), np.zeros(1, np.int32), (S, S), out=x[n:n + 1])
         with torch.no_grad():
             res = decode_masks(model.forward_u8(x, (0.5, 0.5, 0.5), (0.5, 0.5, 0.5)), np.array(boxes, np.int32),
                                want_soft=args.soft)

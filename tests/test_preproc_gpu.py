@@ -121,3 +121,37 @@ def test_crop_forward_decode_round_trip():
             bx = r.bbox[n].tolist()
             assert win[n, 0] <= bx[0] < bx[2] <= win[n, 0] + win[n, 2] and win[n, 1] <= bx[1] < bx[3] <= win[n, 1] + win[n, 3]
     assert r.idmap.shape == (2, 128, 160) and int(r.idmap.max()) <= 3
+
+
+def test_infer_cli_end_to_end(tmp_path):
+    """infer.py (reference flags, infer.py:12-29) over a directory of images of different sizes: every output is a
+    0/255 PNG of its source's size and equals the library chain run by hand; --continue-test skips existing files"""
+    import cv2
+    import infer
+    from instancesegmentation_b200.decode import decode_masks
+    from instancesegmentation_b200.preprocess import crop_resize
+    src_dir, out_dir = tmp_path / "in", tmp_path / "out"
+    src_dir.mkdir()
+    sizes = {"a.png": (70, 90), "b.jpg": (128, 64), "c.png": (33, 200)}
+    for name, (h, w) in sizes.items():
+        cv2.imwrite(str(src_dir / name), synth.image_u8(h, w, seed=h + w)[:, :, ::-1])
+    ck = tmp_path / "ck.pth"
+    z = np.load(os.path.join(GOLDEN, "segment3_state.npz"))
+    sd = {k: torch.from_numpy(z[k]) for k in z.files}
+    torch.save({"state_dict": sd}, ck)
+    args = infer.parse_args(["-i", str(src_dir), "-o", str(out_dir), "--checkpoint", str(ck), "--size", "64", "--batch", "2"])
+    assert infer.run(args) == 3
+    m = Segment(3)
+    m.load_state_dict(sd, strict=True)
+    m.precision, m.max_batch = "fp32", 1
+    m = m.cuda().eval()
+    for name, (h, w) in sizes.items():
+        got = cv2.imread(str(out_dir / (name[:-4] + ".png")), cv2.IMREAD_GRAYSCALE)
+        assert got.shape == (h, w) and set(np.unique(got)) <= {0, 255}
+        rgb = torch.from_numpy(np.ascontiguousarray(cv2.imread(str(src_dir / name), cv2.IMREAD_COLOR)[:, :, ::-1])).cuda()
+        box = np.array([[0, 0, w, h]], np.int32)
+        with torch.no_grad():
+            r = decode_masks(m.forward_u8(crop_resize(rgb[None], box, np.zeros(1, np.int32), (64, 64)), (0.5,) * 3, (0.5,) * 3), box)
+        assert np.array_equal(got, r.mask(0).cpu().numpy() * 255)
+    args2 = infer.parse_args(["-i", str(src_dir), "-o", str(out_dir), "--checkpoint", str(ck), "--size", "64", "--continue-test"])
+    assert infer.run(args2) == 0
