@@ -30,7 +30,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", choices=("cfg2", "cfg4"), default="cfg2",
+    ap.add_argument("--workload", choices=("cfg2", "cfg4", "cfg5"), default="cfg2",
                     help="cfg2 = BASELINE configs[1] (the metric's configuration); cfg4 = configs[3]: 32 source "
                          "images at 1024x1024 with 20 instances each (640 network crops), resize decode + id map")
     return ap.parse_args()
@@ -419,6 +419,84 @@ def run_cfg4(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_cfg5(args, rank, world, local_rank):
+    """BASELINE configs[4] / SURVEY 8(e): the train_instance.py step (:372-380), 16 images per GPU at 512x512,
+    bf16 autocast.  Forward/backward run through torch autograd on the drop-in module's parameters (library
+    kernels -- native backward kernels are SURVEY 8f-1, "next"); what this repo owns in the step is the exchange:
+    gradients accumulate straight into ONE flat fp32 bucket (views), one NCCL all-reduce over NVLink, and the
+    1/world scale + Adam update in one libisg launch (isg_adam_step).  The line reports the whole step and the
+    exchange separately."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from instancesegmentation_b200 import Segment, synth
+    from instancesegmentation_b200.train_step import FlatBucket
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, S, K, W = 16, 512, args.steps, max(args.warmup, 3)
+    torch.manual_seed(0)
+    model = Segment(3).to(dev).train()
+    bucket = FlatBucket(model, grads_as_views=True)
+    xs = [torch.from_numpy(synth.batch(B, S, S, seed=1234 + 16 * rank + j)).to(dev) for j in range(2)]
+    ys = [(torch.from_numpy(synth.logits(B, S, S, seed=77 + rank + j)) > 0.8).float()[:, None].to(dev) for j in range(2)]
+    crit = torch.nn.BCELoss()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * K + 1)]
+    sampler = ClockSampler(local_rank)
+    loss = None
+    for i in range(W + K):
+        if i == W:
+            barrier()
+            sampler.start()
+            ev[0].record()
+        bucket.zero_grads()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            p = model.train_batch(xs[i % 2])
+        loss = crit(p.float(), ys[i % 2])
+        loss.backward()
+        if i >= W:
+            ev[2 * (i - W) + 1].record()
+        bucket.pack_grads()
+        bucket.adam_step(bucket.allreduce())
+        model.invalidate()
+        if i >= W:
+            ev[2 * (i - W) + 2].record()
+    barrier()
+    sampler.stop_flag = True
+    sampler.join()
+    total_ms = ev[0].elapsed_time(ev[2 * K])
+    ex_ms = sum(ev[2 * i + 1].elapsed_time(ev[2 * i + 2]) for i in range(K))
+    t = torch.tensor([total_ms, ex_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, ex_ms = t.tolist()
+    if rank == 0:
+        emit({
+            "metric": "images/sec", "value": world * B * K / (total_ms * 1e-3), "unit": "images/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"configs[4]: train_instance.py step, {B} images/GPU at 3x{S}x{S}, bf16 autocast forward/"
+                                   f"backward by torch autograd (library kernels), BCE, flat gradient bucket -> NCCL "
+                                   f"all-reduce -> fused scale + Adam in libisg",
+                       "global_batch": world * B, "parallelism": f"data-parallel x{world}, one all-reduce of "
+                                                                  f"{bucket.numel * 4} bytes per step"},
+            "exchange": {"ms": ex_ms / K, "bucket_bytes": bucket.numel * 4,
+                         "what": "all-reduce of the flat bucket + isg_adam_step (1/world scale fused)"},
+            "loss": float(loss.detach()), "gpu_launches": K, "clocks": sampler.summary(),
+        })
+    if world > 1:
+        dist.destroy_process_group()
+
+
 _RESULT_FD = None
 
 
@@ -451,6 +529,8 @@ def main():
         sys.exit(subprocess.call(cmd, stdout=_RESULT_FD))
     if args.workload == "cfg4":
         return run_cfg4(args, rank, world, local_rank)
+    if args.workload == "cfg5":
+        return run_cfg5(args, rank, world, local_rank)
     run_ours(args, rank, world, local_rank)
 
 

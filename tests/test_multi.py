@@ -93,6 +93,24 @@ def test_flat_views_keep_state_dict_keys():
     assert torch.allclose(next(iter(model.parameters())).reshape(-1)[:4], bucket.flat[:4])
 
 
+def test_grads_as_bucket_views_equal_packed_grads():
+    """gradient-as-bucket-view mode: autograd accumulates into the flat bucket; same numbers as packing"""
+    torch.manual_seed(3)
+    a, b = Segment(3), Segment(3)
+    b.load_state_dict(a.state_dict())
+    ba, bb = FlatBucket(a), FlatBucket(b, grads_as_views=True)
+    x = torch.from_numpy(synth.batch(2, 32, 32, seed=5))
+    y = (torch.from_numpy(synth.logits(2, 32, 32, seed=6)) > 0).float()[:, None]
+    for step in range(2):            # the second step checks that zero_grads really clears the views
+        for m, bk in ((a, ba), (b, bb)):
+            m.train()
+            bk.zero_grads()
+            torch.nn.BCELoss()(m.train_batch(x), y).backward()
+            bk.pack_grads()
+        assert torch.equal(ba.grad, bb.grad)
+        assert all(p.grad.data_ptr() >= bb.grad.data_ptr() for p in bb.params)
+
+
 @pytest.mark.gpu
 def test_adam_step_matches_torch_adam():
     torch.manual_seed(1)
