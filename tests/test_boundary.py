@@ -111,6 +111,19 @@ def test_library_rejects_bad_arguments_without_gpu():
     assert b"multiples of 16" in l.isg_last_error()
     assert l.isg_plan_create(0, 3, 64, 64, 1, 7, ctypes.byref(h)) == -1
     assert l.isg_forward(None, None, 1, None, None) == -1
+    # entry points added for the ragged decode and the input side: argument checks come before any CUDA call
+    assert l.isg_decode_tile_rows() == 16
+    assert l.isg_decode_tiled(None, 0, 1, 64, 64, None, None, None, 1, 0.5, None, None, None, None, None, 0, 0, 0, None, None) == -1
+    assert b"null argument" in l.isg_last_error()
+    assert l.isg_decode_tiled(None, 0, 0, 64, 64, None, None, None, 0, 0.5, None, None, None, None, None, 0, 0, 0, None, None) == 0
+    buf = (ctypes.c_uint8 * 64)()
+    pbuf = ctypes.cast(buf, ctypes.c_void_p)
+    assert l.isg_crop_resize_u8(pbuf, 1, 8, 8, pbuf, pbuf, 1, 16, 24, pbuf, None) == -1
+    assert b"multiple of 16" in l.isg_last_error()
+    assert l.isg_keypoint_heatmaps(pbuf, 1, 17, 16, 18, 10.0, 0.01, pbuf, 17 * 16 * 18, None) == -1
+    assert b"multiple of 4" in l.isg_last_error()
+    assert l.isg_keypoint_heatmaps(pbuf, 1, 17, 16, 16, 10.0, 1.5, pbuf, 17 * 16 * 16, None) == -1
+    assert b"threshold" in l.isg_last_error()
 
 
 def test_infer_call_surface():
