@@ -21,6 +21,14 @@ struct TensorD {
     //  perm: logical channel -> storage channel (empty = identity)
     int layout = 0;
     std::vector<int> perm;
+    // global memory order of the bf16 path: false = pixel-major [B][H][W][Cs]; true = planar [B][Cs/8][H][W][8]
+    // (TMA boxes of planar tensors have rows of tile-width x 16 contiguous bytes, see tc_common.cuh tma_load_act)
+    bool planar = false;
+    // element index of storage channel sc of pixel (y, x) of image b (Hs x Ws = stored spatial size)
+    size_t index(int b, int y, int x, int sc, int Hs, int Ws, int Ct) const {
+        if (planar) return (((size_t)b * (Ct / 8) + sc / 8) * Hs * Ws + (size_t)y * Ws + x) * 8 + sc % 8;
+        return (((size_t)b * Hs + y) * Ws + x) * Ct + sc;
+    }
     int storage_of(int c) const { return perm.empty() ? c : perm[c]; }
     int logical_of(int s) const {
         if (perm.empty()) return s < C ? s : -1;

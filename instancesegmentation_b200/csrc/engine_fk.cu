@@ -25,10 +25,18 @@ namespace {
 // network input NCHW fp32 -> X2 [B,H/2,W/2,Cs2] bf16, channel (ry*2+rx)*Cin + c (space-to-depth
 // of the stride-2 stem conv, segment.py:23-24), plus max_pool2d(x,4,4) (segment.py:29) into
 // channels [16,16+Cin) of init_down.  One thread = one 4x4 input patch.
+// channels [0,8) of pixel (y, x) of image b in the space-to-depth input x2 ([B][H2][W2][Cs2] or planar
+// [B][Cs2/8][H2][W2][8]); `half` = element distance to channels [8,16)
+__device__ __forceinline__ bf16* x2_pixel(bf16* x2, int b, int y, int x, int H2, int W2, int Cs2, int planar, int& half) {
+    if (planar) { half = H2 * W2 * 8; return x2 + ((size_t)b * (Cs2 >> 3) * H2 * W2 + (size_t)y * W2 + x) * 8; }
+    half = 8;
+    return x2 + (((size_t)b * H2 + y) * W2 + x) * Cs2;
+}
+
 template <int CIN>
 __global__ void __launch_bounds__(128)
-prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, bf16* __restrict__ init,
-            int Cs_init, int total) {
+prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, int planar2,
+            bf16* __restrict__ init, int Cs_init, int total) {
     // launched with programmatic stream serialization: x2 / init_down may still be read by the
     // previous forward's kernels until the wait returns
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -59,10 +67,11 @@ prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, in
                 for (int rx = 0; rx < 2; ++rx)
 #pragma unroll
                     for (int c = 0; c < CIN; ++c) f[(ry * 2 + rx) * CIN + c] = v[c][2 * a + ry][2 * bb + rx];
-            bf16* d = x2 + (((size_t)b * (H >> 1) + 2 * y4 + a) * (W >> 1) + 2 * x4 + bb) * Cs2;
+            int half;
+            bf16* d = x2_pixel(x2, b, 2 * y4 + a, 2 * x4 + bb, H >> 1, W >> 1, Cs2, planar2, half);
             fk::st_global_16(d, make_uint4(fk::pack_bf16(f[0], f[1]), fk::pack_bf16(f[2], f[3]),
                                            fk::pack_bf16(f[4], f[5]), fk::pack_bf16(f[6], f[7])));
-            fk::st_global_16(d + 8, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
+            fk::st_global_16(d + half, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
                                                fk::pack_bf16(f[12], f[13]), fk::pack_bf16(f[14], f[15])));
         }
     float m[8];
@@ -88,8 +97,8 @@ prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, in
 // One thread = one 4x4 patch = four 12-byte rows.
 struct NormU8 { float mean[3], std[3]; };
 __global__ void __launch_bounds__(128)
-prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, bf16* __restrict__ init,
-               int Cs_init, int total, NormU8 nm) {
+prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, int planar2,
+               bf16* __restrict__ init, int Cs_init, int total, NormU8 nm) {
     // a byte has 256 values: the IEEE sequence is evaluated once per (channel, value) and CTA
     __shared__ float lut[3][256];
     for (int e = threadIdx.x; e < 768; e += blockDim.x) {
@@ -123,10 +132,11 @@ prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x
                 for (int rx = 0; rx < 2; ++rx)
 #pragma unroll
                     for (int c = 0; c < 3; ++c) f[(ry * 2 + rx) * 3 + c] = v[c][2 * a + ry][2 * bb + rx];
-            bf16* d = x2 + (((size_t)b * (H >> 1) + 2 * y4 + a) * (W >> 1) + 2 * x4 + bb) * Cs2;
+            int half;
+            bf16* d = x2_pixel(x2, b, 2 * y4 + a, 2 * x4 + bb, H >> 1, W >> 1, Cs2, planar2, half);
             fk::st_global_16(d, make_uint4(fk::pack_bf16(f[0], f[1]), fk::pack_bf16(f[2], f[3]),
                                            fk::pack_bf16(f[4], f[5]), fk::pack_bf16(f[6], f[7])));
-            fk::st_global_16(d + 8, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
+            fk::st_global_16(d + half, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
                                                fk::pack_bf16(f[12], f[13]), fk::pack_bf16(f[14], f[15])));
         }
     float m[3];
@@ -146,7 +156,7 @@ prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x
 
 // generic (any Cin) variant: one thread = one (patch, channel)
 __global__ void __launch_bounds__(128)
-prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __restrict__ x2, int Cs2,
+prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __restrict__ x2, int Cs2, int planar2,
                     bf16* __restrict__ init, int Cs_init, int total) {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -160,8 +170,10 @@ prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __
         for (int k = 0; k < 4; ++k) {
             mx = fmaxf(mx, f[k]);
             const int sy = 2 * y4 + (r >> 1), sx = 2 * x4 + (k >> 1);
-            x2[(((size_t)b * (H >> 1) + sy) * (W >> 1) + sx) * Cs2 + ((r & 1) * 2 + (k & 1)) * Cin + c] =
-                __float2bfloat16_rn(f[k]);
+            const int sc = ((r & 1) * 2 + (k & 1)) * Cin + c, H2 = H >> 1, W2 = W >> 1;
+            const size_t e = planar2 ? (((size_t)b * (Cs2 >> 3) + (sc >> 3)) * H2 * W2 + (size_t)sy * W2 + sx) * 8 + (sc & 7)
+                                     : (((size_t)b * H2 + sy) * W2 + sx) * Cs2 + sc;
+            x2[e] = __float2bfloat16_rn(f[k]);
         }
     }
     init[(((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16 + c] = __float2bfloat16_rn(mx);
@@ -172,7 +184,7 @@ prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __
 // This kernel subtracts, for the border ring of the logits, the contributions of those
 // outside positions.  One thread = one border pixel.
 struct TailFixParams {
-    const bf16* in; int Hq, Wq, Cs;    // [B,Hq,Wq,16]
+    const bf16* in; int Hq, Wq, Cs, planar;    // [B,Hq,Wq,16] or planar [B,2,Hq,Wq,8]
     float* logits;                     // [B,4Hq,4Wq]
     const float* g;                    // [ky(8)][kx(8)][d(9)][ci(16)]: transposed-conv tap (ky,kx) seen through 3x3 tap d
     const float* gb;                   // [d(9)]: the transposed conv's bias seen through 3x3 tap d
@@ -205,11 +217,14 @@ __global__ void __launch_bounds__(128) tail_fix_kernel(TailFixParams p) {
             for (int e = 0; e < 2; ++e) {
                 const int ix = ix1 - 1 + e, kx = tx + 2 - 4 * ix;
                 if (ix < 0 || ix >= p.Wq) continue;
-                const uint4* src = reinterpret_cast<const uint4*>(p.in + (((size_t)b * p.Hq + iy) * p.Wq + ix) * p.Cs);
+                const uint4* src = reinterpret_cast<const uint4*>(
+                    p.planar ? p.in + ((size_t)b * (p.Cs >> 3) * p.Hq * p.Wq + (size_t)iy * p.Wq + ix) * 8
+                             : p.in + (((size_t)b * p.Hq + iy) * p.Wq + ix) * p.Cs);
+                const int half = p.planar ? p.Hq * p.Wq : 1;   // uint4 units between channels [0,8) and [8,16)
                 const float4* g = reinterpret_cast<const float4*>(p.g + ((size_t)(ky * 8 + kx) * 9 + d) * 16);
                 float f[16];
                 fk::unpack8(__ldg(src), f);
-                fk::unpack8(__ldg(src + 1), f + 8);
+                fk::unpack8(__ldg(src + half), f + 8);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const float4 w = __ldg(g + q);
@@ -353,8 +368,16 @@ struct FkBuilder {
     isg_plan* P;
     explicit FkBuilder(isg_plan* p) : P(p) {}
 
+    // Global layout: planar [B][Cs/8][H][W][8] unless the tensor is read through a 2x2 stride-2 (space-to-depth)
+    // map, whose pixel-pair chunks only exist pixel-major: the stem output and the output of the bottle1 run.
+    // ISG_FK_NO_PLANAR=1 keeps every tensor pixel-major (A/B runs).
+    static bool planar_for(const std::string& name) {
+        static const bool off = getenv("ISG_FK_NO_PLANAR") != nullptr;
+        return !off && name != "init_down" && name != "bottle1_5";
+    }
     int tensor(const std::string& name, int C, int H, int W, bool tap = false) {
         TensorD t{name, C, round_up(C, 16), H, W, P->ws_bytes, tap};
+        t.planar = planar_for(name);
         size_t bytes = (size_t)P->max_batch * H * W * t.Cs * 2;
         P->ws_bytes += (bytes + 255) / 256 * 256;
         P->tensors.push_back(t);
@@ -364,6 +387,7 @@ struct FkBuilder {
     int view(const std::string& name, int of, int C, int Cs, int H, int W, bool tap, int layout) {
         TensorD t{name, C, Cs, H, W, P->tensors[of].off, tap};
         t.layout = layout;
+        t.planar = P->tensors[of].planar;
         P->tensors.push_back(t);
         if (tap) P->taps.push_back((int)P->tensors.size() - 1);
         return (int)P->tensors.size() - 1;
@@ -487,7 +511,7 @@ struct FkBuilder {
         for (auto& l : s.loads) max_halo = std::max(max_halo, l.halo);
         // tile width: the image width split evenly so that every TMA box fits 256 columns
         int nx = 1;
-        while (cdiv(s.qW, nx) + 2 * max_halo > 256) ++nx;
+        while (cdiv(s.qW, nx) + 2 * max_halo > 128) ++nx;   // a planar box row holds at most 256 8-byte elements = 128 pixels
         const int TW0 = cdiv(s.qW, nx);
         const char* cap_env = getenv("ISG_FK_MAX_MT");
         const int mt_cap = cap_env ? atoi(cap_env) : 16;
@@ -572,6 +596,8 @@ struct FkBuilder {
             fk::Load& d = q.loads[i];
             d.map = i; d.smem_off = L.load_off[i]; d.dx = -l.halo; d.dy = -l.halo; d.chunk0 = l.chunk0;
             d.folded = l.s2d ? 1 : 0; d.rows_per_img = s.qH; d.step = 1;
+            d.planar = td(l.tensor).planar ? 1 : 0;
+            if (l.s2d && d.planar) { fprintf(stderr, "libisg: %s: space-to-depth load of a planar tensor\n", s.name.c_str()); abort(); }
         }
         q.lbuf_stride = L.lbuf_stride;
         q.tx_bytes = L.tx; q.blob_off = L.blob_off; q.blob_bytes = L.blob_bytes; q.bar_off = L.bar_off;
@@ -629,11 +655,12 @@ struct FkBuilder {
                 if (st.shuf != 2 || st.Cp % 16) { fprintf(stderr, "libisg: pixel shuffle needs shuf 2, Cp %% 16 == 0\n"); abort(); }
                 d.cp_magic = magic(st.Cp / 16);
             }
-            if (st.out_tensor >= 0) d.Cs_out = td(st.out_tensor).Cs;
+            if (st.out_tensor >= 0) { d.Cs_out = td(st.out_tensor).Cs; d.out_planar = td(st.out_tensor).planar ? 1 : 0; }
         }
         if (s.pool_tensor >= 0) {
             q.pool_on = 1; q.pool_in_off = L.load_off[0]; q.pool_in_plane_bytes = L.load_plane[0];
             q.pool_nchunks = td(s.pool_tensor).Cs / 8; q.pool_off = L.pool_off; q.pool_plane_bytes = L.pool_plane;
+            q.pool_planar = td(s.pool_tensor).planar ? 1 : 0;
         }
         // single load buffer: may the next tile's boxes be issued as soon as the stage-0 MMAs completed?
         q.early_load = s.pool_tensor >= 0 ? 0 : 1;
@@ -716,7 +743,7 @@ struct FkBuilder {
                     int rc;
                     if (l.s2d) rc = tc::make_s2d_map(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH, sp.name.c_str());
                     else rc = tc::make_act_map_chunks(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW + 2 * l.halo,
-                                                      L.TH + 2 * l.halo, L.load_planes[i], sp.name.c_str());
+                                                      L.TH + 2 * l.halo, L.load_planes[i], sp.name.c_str(), t.planar);
                     if (rc) return rc;
                 }
                 for (size_t i = sp.loads.size(); i < 4; ++i) maps->in[i] = maps->in[0];
@@ -724,14 +751,14 @@ struct FkBuilder {
                     if (k < sp.stages.size() && sp.stages[k].out_mode == fk::OUT_STAGE && sp.stages[k].store) {
                         const TensorD& t = P->tensors[sp.stages[k].out_tensor];
                         int rc = tc::make_act_map_chunks(&maps->out[k], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH,
-                                                         sp.stages[k].N / 8, sp.name.c_str());
+                                                         sp.stages[k].N / 8, sp.name.c_str(), t.planar);
                         if (rc) return rc;
                     } else maps->out[k] = maps->in[0];
                 }
                 if (sp.pool_tensor >= 0) {
                     const TensorD& t = P->tensors[sp.pool_tensor];
                     int rc = tc::make_act_map_chunks(&maps->out[1], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH, t.Cs / 8,
-                                                     sp.name.c_str());
+                                                     sp.name.c_str(), t.planar);
                     if (rc) return rc;
                 }
             }
@@ -817,14 +844,14 @@ struct FkBuilder {
                 NormU8 nm;
                 for (int c = 0; c < 3; ++c) { nm.mean[c] = P->u8_mean[c]; nm.std[c] = P->u8_std[c]; }
                 const int total = n * (H / 4) * (W / 4);
-                return launch_pdl(prep_u8_kernel, cdiv(total, 128), 128, st, P->u8_src, H, W, px2, x2.Cs, pin, init.Cs, total, nm);
+                return launch_pdl(prep_u8_kernel, cdiv(total, 128), 128, st, P->u8_src, H, W, px2, x2.Cs, (int)x2.planar, pin, init.Cs, total, nm);
             }
             if (cin == 3) {
                 const int total = n * (H / 4) * (W / 4);
-                return launch_pdl(prep_kernel<3>, cdiv(total, 128), 128, st, x, H, W, px2, x2.Cs, pin, init.Cs, total);
+                return launch_pdl(prep_kernel<3>, cdiv(total, 128), 128, st, x, H, W, px2, x2.Cs, (int)x2.planar, pin, init.Cs, total);
             }
             const int total = n * cin * (H / 4) * (W / 4);
-            return launch_pdl(prep_generic_kernel, cdiv(total, 128), 128, st, x, cin, H, W, px2, x2.Cs, pin, init.Cs, total);
+            return launch_pdl(prep_generic_kernel, cdiv(total, 128), 128, st, x, cin, H, W, px2, x2.Cs, (int)x2.planar, pin, init.Cs, total);
         };
         P->ops.push_back(op);
     }
@@ -1016,7 +1043,7 @@ struct FkBuilder {
         q.H = H; q.W = W; q.R = H / mega::CLUSTER;
         q.Cs = round_up(C, 16); q.Cm = round_up(mid, 16);
         q.npx = q.R * W;
-        if (q.npx % 128 || q.R < mega::HALO || W + 2 * mega::HALO > 256 || q.R > 256) return L;
+        if (q.npx % 128 || q.R < mega::HALO || W > 128 || q.R > 256) return L;   // W <= 128: one planar box row
         q.n_mt = q.npx / 128;
         q.pitch = W + 2 * mega::HALO; q.rows_p = q.R + 2 * mega::HALO;
         auto magic = [](int d) -> uint32_t { return d > 1 ? (uint32_t)(((1ull << 32) + d - 1) / d) : 0u; };
@@ -1112,9 +1139,11 @@ struct FkBuilder {
         const int maxB = P->max_batch;
         const TensorD to = td(out);
         P->finalizers.push_back([=]() -> int {
-            int rc = tc::make_act_map_chunks(&maps->in[0], P->ws + tx.off, maxB, tx.H, tx.W, tx.Cs, tx.W, q.R, tx.Cs / 8, name.c_str());
+            int rc = tc::make_act_map_chunks(&maps->in[0], P->ws + tx.off, maxB, tx.H, tx.W, tx.Cs, tx.W, q.R, tx.Cs / 8, name.c_str(),
+                                             tx.planar);
             if (rc) return rc;
-            return tc::make_act_map_chunks(&maps->out[0], P->ws + to.off, maxB, to.H, to.W, to.Cs, to.W, q.R, to.Cs / 8, name.c_str());
+            return tc::make_act_map_chunks(&maps->out[0], P->ws + to.off, maxB, to.H, to.W, to.Cs, to.W, q.R, to.Cs / 8, name.c_str(),
+                                           to.planar);
         });
         cudaFuncSetAttribute(mega::mega_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         cudaFuncSetAttribute(mega::mega_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
@@ -1122,6 +1151,7 @@ struct FkBuilder {
         auto nclusters = std::make_shared<int>(0);
         op.launch = [=](int n, const float*, float*, cudaStream_t stream) -> cudaError_t {
             mega::Params p = q;
+            p.in_planar = tx.planar ? 1 : 0; p.out_planar = to.planar ? 1 : 0;
             p.blob = reinterpret_cast<const uint8_t*>(P->arena + blob);
             p.nimg = n;
             cudaLaunchConfig_t cfg;
@@ -1571,7 +1601,7 @@ struct FkBuilder {
         };
         op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
             TailFixParams p;
-            p.in = reinterpret_cast<const bf16*>(P->ws + ty.off); p.Hq = ty.H; p.Wq = ty.W; p.Cs = ty.Cs;
+            p.in = reinterpret_cast<const bf16*>(P->ws + ty.off); p.Hq = ty.H; p.Wq = ty.W; p.Cs = ty.Cs; p.planar = ty.planar ? 1 : 0;
             p.logits = logits; p.g = P->arena + og; p.gb = P->arena + ogb;
             const int H = 4 * ty.H, W = 4 * ty.W;
             p.total = n * (2 * W + 2 * (H - 2));

@@ -42,6 +42,7 @@ struct Load {
     int folded;               // 1: map folds the batch into y (2x2 stride-2 patches), 5th coordinate 0
     int rows_per_img;         // folded maps: rows of one image
     int step;                 // tile origin multiplier (1; loads of a x2-upsampled consumer would use 1/2)
+    int planar;               // 1: the tensor is stored planar [B][Cs/8][H][W][8] (4-D map), see tc::tma_load_act
 };
 
 struct Stage {
@@ -62,6 +63,7 @@ struct Stage {
     int stage_off, stage_plane_bytes, stage_compact;
     int store;                     // 1: TMA-store the staging planes through the stage's out map
     int store_chunk0;
+    int out_planar;                // the output tensor (TMA store or direct stores) is stored planar
     void* gptr; int Cs_out, shuf, Cp;   // direct-store modes
     // 16-column chunk cc -> (cc / (res_mod/16), cc / (Cp/16)) by magic multiplication (0: divisor 1 or unused)
     uint32_t res_magic, cp_magic;
@@ -95,7 +97,7 @@ struct Params {
     Stencil st;
     // optional 2x2 max-pool of a folded space-to-depth load (BottleneckDown2's residual, segment.py:145):
     // max over the four sub-pixel plane groups -> pool planes -> TMA store through the second out map
-    int pool_on, pool_in_off, pool_in_plane_bytes, pool_nchunks, pool_off, pool_plane_bytes;
+    int pool_on, pool_in_off, pool_in_plane_bytes, pool_nchunks, pool_off, pool_plane_bytes, pool_planar;
     int nstages; Stage stage[2];
     int bar_off;                   // 3 mbarriers + tmem slot
     long long* prof;               // debug (ISG_FK_PROF=1): per-CTA phase time stamps, else null
@@ -418,16 +420,20 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
                 }
             } else if (g.inimg) {
                 bf16* o;
+                int plane = 8;   // elements between the two 8-channel halves: adjacent (pixel-major) or one plane apart
                 if (out_mode == OUT_S2D) {
-                    o = reinterpret_cast<bf16*>(gimg) + ((g.y >> 1) * (p.W >> 1) + (g.x >> 1)) * (4 * N) +
-                        ((g.y & 1) * 2 + (g.x & 1)) * N + col0;
+                    const int sc = ((g.y & 1) * 2 + (g.x & 1)) * N + col0, pix = (g.y >> 1) * (p.W >> 1) + (g.x >> 1);
+                    if (s.out_planar) { plane = (p.H >> 1) * (p.W >> 1) * 8; o = reinterpret_cast<bf16*>(gimg) + (sc >> 3) * plane + pix * 8; }
+                    else o = reinterpret_cast<bf16*>(gimg) + pix * (4 * N) + sc;
                 } else {  // OUT_SHUF_BF16: column = phase * Cp + channel, phase = (py, px) of the x`shuf` upsampling
                     const int phase = fastdiv(cc, s.cp_magic), ch = col0 - phase * s.Cp;
                     const int py = phase >> 1, px = phase & 1;   // shuf == 2 (ConvT k4 s2)
-                    o = reinterpret_cast<bf16*>(gimg) + ((g.y * s.shuf + py) * (p.W * s.shuf) + g.x * s.shuf + px) * s.Cs_out + ch;
+                    const int pix = (g.y * s.shuf + py) * (p.W * s.shuf) + g.x * s.shuf + px;
+                    if (s.out_planar) { plane = p.H * p.W * s.shuf * s.shuf * 8; o = reinterpret_cast<bf16*>(gimg) + (ch >> 3) * plane + pix * 8; }
+                    else o = reinterpret_cast<bf16*>(gimg) + pix * s.Cs_out + ch;
                 }
                 st_global_16(o, q0);
-                st_global_16(o + 8, q1);
+                st_global_16(o + plane, q1);
             }
         }
         if (nxt >= nitems) break;
@@ -484,8 +490,8 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             const Load& l = p.loads[i];
             const int cx = txi * p.TW * l.step + l.dx;
             const int cy = tyi * p.TH * l.step + l.dy + (l.folded ? bi * l.rows_per_img : 0);
-            tc::tma_load_5d(smem + l.smem_off + buf * p.lbuf_stride, maps[l.map], &bars[buf], 0, cx, cy, l.chunk0,
-                            l.folded ? 0 : bi);
+            tc::tma_load_act(smem + l.smem_off + buf * p.lbuf_stride, maps[l.map], &bars[buf], l.planar, cx, cy, l.chunk0,
+                             l.folded ? 0 : bi);
         }
     };
     // programmatic dependent launch: this grid may have been scheduled while its predecessor in the
@@ -548,11 +554,12 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             if (it == 0) FK_STAMP(5 + 2 * k);
             FK_ACC(11 + 2 * k);
             if (tid == 0 && s.out_mode == OUT_STAGE && s.store) {
-                tc::tma_store_5d(k ? &mo1 : &mo0, smem + s.stage_off + (s.stage_in_load ? boff : 0), 0, x0, y0, s.store_chunk0, b);
+                tc::tma_store_act(k ? &mo1 : &mo0, smem + s.stage_off + (s.stage_in_load ? boff : 0), s.out_planar, x0, y0,
+                                  s.store_chunk0, b);
                 tc::tma_store_commit();
             }
             if (k == 0 && tid == 0 && p.pool_on) {
-                tc::tma_store_5d(&mo1, smem + p.pool_off, 0, x0, y0, 0, b);
+                tc::tma_store_act(&mo1, smem + p.pool_off, p.pool_planar, x0, y0, 0, b);
                 tc::tma_store_commit();
             }
         }
@@ -634,7 +641,7 @@ fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ C
                     const Load& l = p.loads[i];
                     const int cx = txi * p.TW * l.step + l.dx;
                     const int cy = tyi * p.TH * l.step + l.dy + (l.folded ? bi * l.rows_per_img : 0);
-                    tc::tma_load_5d(smem + l.smem_off + slot * p.lbuf_stride, maps[l.map], &bars[slot], 0, cx, cy, l.chunk0,
+                    tc::tma_load_act(smem + l.smem_off + slot * p.lbuf_stride, maps[l.map], &bars[slot], l.planar, cx, cy, l.chunk0,
                                     l.folded ? 0 : bi);
                 }
             }
@@ -680,7 +687,7 @@ fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ C
                 tc::fence_proxy_async();
                 epi_bar_sync(PIPE_EPI_WARPS * 32);
                 if (leader) {
-                    tc::tma_store_5d(&mo0, smem + s.stage_off, 0, x0, y0, s.store_chunk0, b);
+                    tc::tma_store_act(&mo0, smem + s.stage_off, s.out_planar, x0, y0, s.store_chunk0, b);
                     tc::tma_store_commit();
                 }
             }

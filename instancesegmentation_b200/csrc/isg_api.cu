@@ -264,12 +264,12 @@ int isg_plan_tap_read(isg_plan* plan, int index, int n, float* out_host) {
             const int sc = t.storage_of(c);
             for (int y = 0; y < t.H; ++y)
                 for (int x = 0; x < t.W; ++x) {
-                    size_t i;
+                    size_t i;   // element index in the workspace tensor (image b included)
                     if (t.layout == 1)
-                        i = (((size_t)(y >> 1) * (t.W >> 1)) + (x >> 1)) * (4 * (size_t)t.Cs) + ((y & 1) * 2 + (x & 1)) * t.Cs + sc;
+                        i = t.index(b, y >> 1, x >> 1, ((y & 1) * 2 + (x & 1)) * t.Cs + sc, t.H >> 1, t.W >> 1, 4 * t.Cs);
                     else
-                        i = ((size_t)y * t.W + x) * t.Cs + sc;
-                    out_host[(((size_t)b * t.C + c) * t.H + y) * t.W + x] = raw_to_float(raw.data(), b * per_img + i, is_bf16);
+                        i = t.index(b, y, x, sc, t.H, t.W, t.Cs);
+                    out_host[(((size_t)b * t.C + c) * t.H + y) * t.W + x] = raw_to_float(raw.data(), i, is_bf16);
                 }
         }
     return ISG_OK;

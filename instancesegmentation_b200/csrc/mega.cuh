@@ -31,6 +31,7 @@ struct Params {
     int pitch, rows_p;            // m1 plane: W + 2 HALO columns, R + 2 HALO rows
     uint32_t w_magic, npx_magic;  // fastdiv by W, by npx
     int nimg, nblocks;
+    int in_planar, out_planar;    // global layout of the run's input / output tensor (tc::tma_load_act)
     Block blk[MAX_BLOCKS];
     const uint8_t* blob;          // per block: [W0 | shift0,slope0 | dw taps | dw shift,slope(,bw) | W2 | shift2,slope2]
     int blob_stride, blob_bytes;
@@ -257,7 +258,7 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
         if (tid == 0) {
             tc::tma_store_wait_read();       // the previous image's store has read the x planes
             tc::mbar_expect_tx(&bars[0], x_bytes);
-            tc::tma_load_5d(smem + p.x_off, &min, &bars[0], 0, 0, (int)rank * p.R, 0, img);
+            tc::tma_load_act(smem + p.x_off, &min, &bars[0], p.in_planar, 0, (int)rank * p.R, 0, img);
         }
         tc::mbar_wait(&bars[0], it & 1);
         MEGA_ACC(0);   // x load
@@ -321,7 +322,7 @@ mega_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CUt
             if (tid == 0 && seq + 2 < total_seq) load_weights(seq + 2);
         }
         if (tid == 0) {
-            tc::tma_store_5d(&mout, smem + p.x_off, 0, 0, (int)rank * p.R, 0, img);
+            tc::tma_store_act(&mout, smem + p.x_off, p.out_planar, 0, (int)rank * p.R, 0, img);
             tc::tma_store_commit();
         }
     }

@@ -92,6 +92,26 @@ __device__ __forceinline__ void tma_store_5d(const CUtensorMap* m, const void* s
                  ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
                  : "memory");
 }
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+// activation box (x, y, first chunk, image) of a tensor in either global layout:
+//   pixel-major [B][H][W][Cs]      -> 5-D map (8 ch, x, y, chunk, b): every box element is 16 bytes
+//   planar      [B][Cs/8][H][W][8] -> 4-D map of 8-byte elements (2 per pixel): the box's inner extent is the tile
+//                                     width x 16 bytes (a TMA unit retires ~1 element per clock whatever its size)
+// Both land in shared memory as the same [chunk][row][col][8 ch] planes.
+__device__ __forceinline__ void tma_load_act(void* dst, const CUtensorMap* m, uint64_t* bar, int planar, int x, int y,
+                                             int chunk, int b) {
+    if (planar) tma_load_4d(dst, m, bar, 2 * x, y, chunk, b);
+    else tma_load_5d(dst, m, bar, 0, x, y, chunk, b);
+}
+__device__ __forceinline__ void tma_store_act(const CUtensorMap* m, const void* src, int planar, int x, int y, int chunk,
+                                              int b) {
+    if (planar) tma_store_4d(m, src, 2 * x, y, chunk, b);
+    else tma_store_5d(m, src, 0, x, y, chunk, b);
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // only until the shared-memory source has been read (enough before the CTA exits)

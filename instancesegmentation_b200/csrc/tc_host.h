@@ -58,10 +58,29 @@ inline int make_act_map(CUtensorMap* out, void* base, int B, int H, int W, int C
     return make_map5(out, base, dims, st, box, what);
 }
 
+// planar activation [B][Cs/8][H][W][8 ch] as (8-byte elements: 2 per pixel along x, y, chunk, b); box (2 bw, bh, nchunks, 1).
+// Same shared-memory image as the 5-D pixel-major box, with rows of bw * 16 contiguous bytes instead of 16-byte elements.
+inline int make_act_map_planar(CUtensorMap* out, void* base, int B, int H, int W, int Cs, int bw, int bh, int nchunks,
+                               const char* what) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(ISG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    if (2 * bw > 256) return fail(ISG_ERR_ARG, "%s: planar box of %d pixels exceeds 256 elements", what, bw);
+    cuuint64_t d[4] = {(cuuint64_t)2 * W, (cuuint64_t)H, (cuuint64_t)Cs / 8, (cuuint64_t)B};
+    cuuint64_t st[3] = {(cuuint64_t)W * 16, (cuuint64_t)H * W * 16, (cuuint64_t)(Cs / 8) * H * W * 16};
+    cuuint32_t bx[4] = {(cuuint32_t)(2 * bw), (cuuint32_t)bh, (cuuint32_t)nchunks, 1}, es[4] = {1, 1, 1, 1};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT64, 4, base, d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(ISG_ERR_CUDA, "cuTensorMapEncodeTiled(%s, planar) failed with %d: %dx%dx%d box %dx%dx%d", what, (int)r, W, H,
+                    Cs, bw, bh, nchunks);
+    return 0;
+}
+
 // same view, but the box covers only `nchunks` 8-channel chunks (channel subsets, e.g. the conv half
 // of init_down or the two halves of an up block's low-resolution tensor)
 inline int make_act_map_chunks(CUtensorMap* out, void* base, int B, int H, int W, int Cs, int bw, int bh, int nchunks,
-                               const char* what) {
+                               const char* what, bool planar = false) {
+    if (planar) return make_act_map_planar(out, base, B, H, W, Cs, bw, bh, nchunks, what);
     const uint64_t dims[5] = {8, (uint64_t)W, (uint64_t)H, (uint64_t)Cs / 8, (uint64_t)B};
     const uint64_t st[4] = {(uint64_t)Cs * 2, (uint64_t)W * Cs * 2, 16, (uint64_t)H * W * Cs * 2};
     const uint32_t box[5] = {8, (uint32_t)bw, (uint32_t)bh, (uint32_t)nchunks, 1};
