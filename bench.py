@@ -244,10 +244,10 @@ def run_ours(args, rank, world, local_rank):
         dec_bytes = B * (S * S * DECODE_BYTES_PER_PIXEL + 20)
         dec_gbs = dec_bytes * K / (dk_ms * 1e-3) / 1e9
         # dram__bytes_read.sum + dram__bytes_write.sum from ncu at exactly this workload (bytes per forward of 64
-        # images summed over its 23 launches / per decode launch): profiles/r1f_dram_traffic_per_launch.txt,
+        # images summed over its 23 launches / per decode launch): profiles/r1i_forward_inst_per_launch.txt,
         # profiles/r1f_ncu_decode_kernel.txt.  Any other workload has no capture -> null.
         cfg2 = (B == 64 and S == 512 and args.precision == "bf16")
-        conv_traffic = 1355.4e6 if cfg2 else None
+        conv_traffic = 1373.8e6 if cfg2 else None
         dec_traffic = 69.74e6 if cfg2 else None
         line = {
             "metric": "images/sec", "value": imgs / (total_ms * 1e-3), "unit": "images/s", "n_gpus": world,

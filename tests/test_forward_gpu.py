@@ -216,9 +216,10 @@ np.save(sys.argv[3], y.cpu().numpy())
     ("4x128x192", [{"ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "1"},
                    {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "2"}, {"ISG_FK_CTAS": "1", "ISG_FK_LBUF": "1"},
                    {"ISG_FK_FORCE_PIPE": "1"}, {"ISG_FK_CTAS": "4", "ISG_FK_LBUF": "2"},
-                   {"ISG_FK_CTAS": "4", "ISG_FK_LBUF": "1"}]),
+                   {"ISG_FK_CTAS": "4", "ISG_FK_LBUF": "1"}, {"ISG_FK_NO_PLANAR": "1"}]),
     # 512x512: the residual-bottleneck runs go through the cluster-resident launch (csrc/mega.cuh)
-    ("3x512x512", [{"ISG_FK_NO_MEGA": "1", "ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_NO_MEGA8": "1"}]),
+    # ISG_FK_NO_PLANAR: pixel-major instead of planar global tensors (only the TMA box shape differs)
+    ("3x512x512", [{"ISG_FK_NO_MEGA": "1", "ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_NO_MEGA8": "1"}, {"ISG_FK_NO_PLANAR": "1"}]),
     # 1024x1024 (cfg4): the untuned default mode has no feasible tile for one launch -> fallback search
     ("2x1024x1024", [{"ISG_FK_NO_TUNE": "1"}, {}]),
 ])
