@@ -80,6 +80,16 @@ struct isg_plan {
     // run once after the finalizers: each fused launch times its candidate tilings on the device
     // (scratch logits buffer of max_batch images, stream) and keeps the fastest
     std::vector<std::function<int(float*, cudaStream_t)>> tuners;
+    // second pass (isg_plan_create): the choice of every launch with several close candidates is re-made on the time
+    // of the WHOLE forward, because a launch timed alone (hot caches, nothing before or after it) ranks its variants
+    // differently than the chain does
+    struct TuneSite {
+        std::string name;
+        std::vector<float> iso_ms;          // time of every variant alone (first pass)
+        std::function<void(int)> set;       // select a variant
+        std::function<int()> get;
+    };
+    std::vector<TuneSite> tune_sites;
 
     size_t esize() const { return mode == ISG_MODE_BF16 ? 2 : 4; }
     void* tptr(int id) const { return ws + tensors[id].off; }

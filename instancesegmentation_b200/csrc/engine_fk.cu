@@ -790,6 +790,15 @@ struct FkBuilder {
             return run(*chosen, n, logits, stream, prof_on);
         };
         // autotune: time every variant at the plan's batch size on the device, keep the fastest
+        const size_t site = P->tune_sites.size();
+        {
+            isg_plan::TuneSite ts;
+            ts.name = sp.name;
+            ts.iso_ms.assign(vars->size(), 0.f);
+            ts.set = [=](int i) { *chosen = i; };
+            ts.get = [=]() { return *chosen; };
+            P->tune_sites.push_back(ts);
+        }
         P->tuners.push_back([=](float* logits, cudaStream_t stream) -> int {
             const bool verbose = getenv("ISG_FK_VERBOSE") != nullptr;
             float best = 1e30f;
@@ -809,6 +818,7 @@ struct FkBuilder {
                 if (verbose)
                     fprintf(stderr, "tune %-40s tile %3dx%-3d n_mt %2d ctas %d lbuf %d pipe %d smem %6zu: %7.1f us\n", sp.name.c_str(),
                             L.TH, L.TW, L.n_mt, L.ctas, L.nlbuf, L.pipe * 10 + (L.pipe ? L.groups : 0), L.smem, ms * 1e3);
+                P->tune_sites[site].iso_ms[i] = ms;
                 if (ms < best) { best = ms; *chosen = i; }
             }
             cudaEventDestroy(e0); cudaEventDestroy(e1);

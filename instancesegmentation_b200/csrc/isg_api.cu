@@ -1,4 +1,5 @@
 // C ABI of libisg (include/isg.h): network description, plan lifetime, forward, test taps.
+#include <algorithm>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -26,6 +27,10 @@ inline float raw_to_float(const void* raw, size_t i, bool is_bf16) {
     memcpy(&f, &u, 4);
     return f;
 }
+}  // namespace
+
+namespace {
+int tune_in_chain(isg_plan* p, float* logits);   // defined at the end of the file
 }  // namespace
 
 extern "C" {
@@ -85,6 +90,7 @@ int isg_plan_create(int device, int in_channel, int height, int width, int max_b
         for (auto& tune : p->tuners)
             if ((rc = tune(scratch, nullptr))) break;
         cudaDeviceSynchronize();
+        if (!rc && !getenv("ISG_FK_NO_CHAIN_TUNE")) rc = tune_in_chain(p.get(), scratch);
         cudaFree(scratch);
         if (rc) { cudaFree(p->ws); cudaFree(p->arena); return fail(rc, "autotune launch failed: %s", cudaGetErrorString(cudaGetLastError())); }
     }
@@ -276,3 +282,61 @@ int isg_plan_tap_read(isg_plan* plan, int index, int n, float* out_host) {
 }
 
 }  // extern "C"
+
+namespace {
+
+// Second tuning pass: for every launch whose first-pass (stand-alone) timings left several candidates within 25 % of
+// the best, time the whole forward of max_batch images with each of them (all other launches at their current
+// choice) and keep the one that makes the FORWARD fastest.  All-zero input and weights: timing is data independent.
+int tune_in_chain(isg_plan* p, float* logits) {
+    const bool verbose = getenv("ISG_FK_VERBOSE") != nullptr;
+    float* x = nullptr;
+    const size_t in_floats = (size_t)p->max_batch * p->cin * p->H * p->W;
+    if (cudaMalloc(&x, in_floats * sizeof(float)) != cudaSuccess) { cudaGetLastError(); return ISG_OK; }   // no room: keep pass 1
+    cudaMemset(x, 0, in_floats * sizeof(float));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    int rc = ISG_OK;
+    auto forward_ms = [&]() -> float {   // best of 3 measurements of 3 forwards each
+        float best = 1e30f;
+        for (int m = 0; m < 3 && rc == ISG_OK; ++m) {
+            cudaEventRecord(e0, nullptr);
+            for (int r = 0; r < 3 && rc == ISG_OK; ++r) rc = run_group(p, x, nullptr, p->max_batch, logits, nullptr);
+            cudaEventRecord(e1, nullptr);
+            if (cudaEventSynchronize(e1) != cudaSuccess) rc = ISG_ERR_CUDA;
+            float ms = 0;
+            cudaEventElapsedTime(&ms, e0, e1);
+            best = ms / 3 < best ? ms / 3 : best;
+        }
+        return best;
+    };
+    forward_ms();   // warm up
+    for (int pass = 0; pass < 2 && rc == ISG_OK; ++pass)
+        for (auto& site : p->tune_sites) {
+            float iso_best = 1e30f;
+            for (float v : site.iso_ms) if (v > 0.f && v < iso_best) iso_best = v;
+            std::vector<int> cand;
+            for (size_t i = 0; i < site.iso_ms.size(); ++i)
+                if (site.iso_ms[i] > 0.f && site.iso_ms[i] <= 1.25f * iso_best) cand.push_back((int)i);
+            if (cand.size() < 2) continue;
+            std::sort(cand.begin(), cand.end(), [&](int a, int b) { return site.iso_ms[a] < site.iso_ms[b]; });
+            if (cand.size() > 6) cand.resize(6);
+            const int before = site.get();
+            int best_i = before;
+            float best_ms = 1e30f;
+            for (int i : cand) {
+                site.set(i);
+                const float ms = forward_ms();
+                if (rc != ISG_OK) break;
+                if (ms < best_ms) { best_ms = ms; best_i = i; }
+            }
+            site.set(best_i);
+            if (verbose)
+                fprintf(stderr, "chain-tune pass %d %-44s %zu candidates: variant %d -> %d, forward %.1f us\n", pass,
+                        site.name.c_str(), cand.size(), before, best_i, best_ms * 1e3);
+        }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(x);
+    return rc;
+}
+}  // namespace
