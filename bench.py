@@ -431,7 +431,7 @@ def run_cfg5(args, rank, world, local_rank):
     import torch.distributed as dist
 
     from instancesegmentation_b200 import Segment, synth
-    from instancesegmentation_b200.train_step import FlatBucket
+    from instancesegmentation_b200.train_step import FlatBucket, GraphedTrainStep
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -450,6 +450,29 @@ def run_cfg5(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def eager_step(i):
+        bucket.zero_grads()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            p = model.train_batch(xs[i % 2])
+        l = crit(p.float(), ys[i % 2])
+        l.backward()
+        return l.detach()
+
+    # the reference's eager sequence (sigmoid -> BCELoss -> backward), timed first for the comparison field
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for i in range(W + K):
+        if i == W:
+            barrier()
+            e0.record()
+        eager_step(i)
+        bucket.adam_step(bucket.allreduce())
+        model.invalidate()
+    e1.record()
+    barrier()
+    eager_ms = e0.elapsed_time(e1) / K
+
+    # the measured step: forward + isg_bce_sigmoid + backward replayed from one CUDA graph
+    step = GraphedTrainStep(model, bucket, xs[0], ys[0])
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * K + 1)]
     sampler = ClockSampler(local_rank)
     loss = None
@@ -458,14 +481,12 @@ def run_cfg5(args, rank, world, local_rank):
             barrier()
             sampler.start()
             ev[0].record()
-        bucket.zero_grads()
-        with torch.autocast("cuda", dtype=torch.bfloat16):
-            p = model.train_batch(xs[i % 2])
-        loss = crit(p.float(), ys[i % 2])
-        loss.backward()
+        step.x.copy_(xs[i % 2], non_blocking=True)
+        step.y.copy_(ys[i % 2], non_blocking=True)
+        step.graph.replay()
+        loss = step.loss
         if i >= W:
             ev[2 * (i - W) + 1].record()
-        bucket.pack_grads()
         bucket.adam_step(bucket.allreduce())
         model.invalidate()
         if i >= W:
@@ -485,13 +506,15 @@ def run_cfg5(args, rank, world, local_rank):
             "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"configs[4]: train_instance.py step, {B} images/GPU at 3x{S}x{S}, bf16 autocast forward/"
-                                   f"backward by torch autograd (library kernels), BCE, flat gradient bucket -> NCCL "
+                                   f"backward by torch autograd (library kernels) + fused sigmoid/BCE loss and gradient "
+                                   f"(isg_bce_sigmoid) replayed from one CUDA graph, flat gradient bucket -> NCCL "
                                    f"all-reduce -> fused scale + Adam in libisg",
                        "global_batch": world * B, "parallelism": f"data-parallel x{world}, one all-reduce of "
                                                                   f"{bucket.numel * 4} bytes per step"},
             "exchange": {"ms": ex_ms / K, "bucket_bytes": bucket.numel * 4,
                          "what": "all-reduce of the flat bucket + isg_adam_step (1/world scale fused)"},
-            "loss": float(loss.detach()), "gpu_launches": K, "clocks": sampler.summary(),
+            "eager_ms_per_step": eager_ms,
+            "loss": float(loss.detach()), "gpu_launches": 2 * K, "clocks": sampler.summary(),
         })
     if world > 1:
         dist.destroy_process_group()

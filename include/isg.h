@@ -166,6 +166,16 @@ ISG_API int isg_adam_step(float* param_dev, const float* grad_dev, float* exp_av
                   float* exp_avg_sq_dev, int64_t n, float grad_scale, float lr, float beta1,
                   float beta2, float eps, int step, void* stream);
 
+/* ---- training step loss (train_instance.py:299 BCELoss(), :377-378 sigmoid -> loss -> backward) ----
+ * One launch: loss = mean(BCE(sigmoid(logit), target)) with torch's rules (log clamped at -100) and, when
+ * dlogits_dev is not NULL, d(loss)/d(logit) in the logits' type (the product of BCELoss's and sigmoid's
+ * backward, 1e-12 clamp included).  logits fp32 or bf16 [n], target fp32 [n]; loss_dev: one float.
+ * workspace_dev: isg_bce_workspace_bytes() bytes, 8-byte aligned, zeroed once by the caller before its first
+ * use (the kernel leaves it ready for the next launch).  The sum order is fixed: results are deterministic. */
+ISG_API int64_t isg_bce_workspace_bytes(void);
+ISG_API int isg_bce_sigmoid(const void* logits_dev, int logits_bf16, const float* target_dev, int64_t n,
+                    void* dlogits_dev, void* workspace_dev, float* loss_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libisg.so")
-SOURCES = ["isg_api.cu", "engine_build.cu", "engine_fk.cu", "decode.cu", "preproc.cu"]
+SOURCES = ["isg_api.cu", "engine_build.cu", "engine_fk.cu", "decode.cu", "preproc.cu", "train.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr",

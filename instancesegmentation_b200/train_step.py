@@ -86,6 +86,109 @@ class FlatBucket:
                 self.step_count, torch.cuda.current_stream().cuda_stream))
 
 
+_BCE_WS = {}
+
+
+def _bce_workspace(dev):
+    """per-device scratch of isg_bce_sigmoid (per-block partial sums + ticket), zeroed once"""
+    key = (dev.type, dev.index)
+    if key not in _BCE_WS:
+        _BCE_WS[key] = torch.zeros(_lib.lib().isg_bce_workspace_bytes() // 8, dtype=torch.float64, device=dev)
+    return _BCE_WS[key]
+
+
+class _BceSigmoid(torch.autograd.Function):
+    """loss = BCELoss()(sigmoid(logits), target) and its gradient w.r.t. the logits in one libisg launch."""
+
+    @staticmethod
+    def forward(ctx, logits, target):
+        if not logits.is_cuda:
+            raise _lib.IsgError("bce_sigmoid_loss runs in libisg on CUDA only; there is no CPU path")
+        if logits.dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError(f"logits must be float32 or bfloat16, got {logits.dtype}")
+        if target.shape != logits.shape:
+            raise ValueError(f"target shape {tuple(target.shape)} differs from logits {tuple(logits.shape)}")
+        if logits.numel() == 0:
+            raise ValueError("bce_sigmoid_loss of an empty batch")
+        logits = logits.contiguous()
+        target = target.to(torch.float32).contiguous()
+        need_grad = ctx.needs_input_grad[0]
+        dlogits = torch.empty_like(logits) if need_grad else None
+        loss = torch.empty((), dtype=torch.float32, device=logits.device)
+        with torch.cuda.device(logits.device):
+            _lib.check(_lib.lib().isg_bce_sigmoid(
+                logits.data_ptr(), int(logits.dtype == torch.bfloat16), target.data_ptr(), logits.numel(),
+                dlogits.data_ptr() if need_grad else None, _bce_workspace(logits.device).data_ptr(),
+                loss.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        ctx.dlogits = dlogits
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        d = ctx.dlogits
+        ctx.dlogits = None
+        return (d * g.to(d.dtype) if d is not None else None), None
+
+
+def bce_sigmoid_loss(logits, target):
+    """``torch.nn.BCELoss()(torch.sigmoid(logits), target)`` (train_instance.py:299, :377-378, segment.py:534)
+    computed from the raw logits of ``Segment.forward`` -- same value, same gradient, one kernel."""
+    return _BceSigmoid.apply(logits, target)
+
+
+class GraphedTrainStep:
+    """The step of train_instance.py:372-380 with forward, loss and backward replayed from ONE CUDA graph.
+
+    The step is ~1.5 k small library launches for 16 images; captured once, a step is: copy the batch into
+    the static input buffers, replay, all-reduce the flat bucket, ``isg_adam_step``.  BatchNorm running
+    statistics touched by the capture warm-up are restored, so step k of this class equals step k of
+    ``train_step`` on the same data."""
+
+    def __init__(self, model, bucket, images, masks, autocast_dtype=torch.bfloat16, warmup=3):
+        if not bucket.grads_as_views:
+            raise ValueError("GraphedTrainStep needs FlatBucket(model, grads_as_views=True): the graph writes "
+                             "the gradients at fixed addresses")
+        if not images.is_cuda:
+            raise _lib.IsgError("GraphedTrainStep runs on CUDA only")
+        self.model, self.bucket, self.autocast_dtype = model, bucket, autocast_dtype
+        self.x, self.y = torch.empty_like(images), torch.empty_like(masks, dtype=torch.float32)
+        self.x.copy_(images)
+        self.y.copy_(masks)
+        model.train()
+        saved = {k: v.clone() for k, v in model.named_buffers()}
+        side = torch.cuda.Stream(device=images.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._body()
+        torch.cuda.current_stream().wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = self._body()
+        with torch.no_grad():
+            for k, v in model.named_buffers():
+                v.copy_(saved[k])
+
+    def _body(self):
+        self.bucket.zero_grads()
+        if self.autocast_dtype is None:
+            logits = self.model(self.x)
+        else:
+            with torch.autocast("cuda", dtype=self.autocast_dtype):
+                logits = self.model(self.x)
+        loss = bce_sigmoid_loss(logits, self.y)
+        loss.backward()
+        return loss.detach()
+
+    def __call__(self, images, masks):
+        self.x.copy_(images, non_blocking=True)
+        self.y.copy_(masks, non_blocking=True)
+        self.graph.replay()
+        self.bucket.adam_step(self.bucket.allreduce())
+        self.model.invalidate()
+        return self.loss
+
+
 def train_step(model, bucket, images, masks, criterion=None):
     """forward -> BCE -> backward -> one all-reduce -> fused Adam (train_instance.py:372-380)."""
     criterion = criterion or torch.nn.BCELoss()

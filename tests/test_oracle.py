@@ -162,3 +162,22 @@ def test_crop_resize_oracle_rules():
     want = F.interpolate(torch.from_numpy(pad).permute(2, 0, 1)[None], size=(64, 80), mode="bilinear",
                          align_corners=False)[0].permute(1, 2, 0).numpy()
     assert np.abs(got - want).max() <= 0.5 + 1e-3
+
+
+def test_bce_oracle_matches_torch_bceloss_of_sigmoid():
+    """pins oracle/bce_oracle.py on the reference's own calls (train_instance.py:299, :377-378): value and
+    autograd gradient of BCELoss()(sigmoid(x), y) on CPU, including logits far enough out that the -100
+    log clamp and the 1e-12 gradient clamp are in play"""
+    from oracle.bce_oracle import bce_sigmoid
+    rng = np.random.default_rng(5)
+    x = (rng.standard_normal((2, 1, 37, 53)) * 4).astype(np.float32)
+    x.reshape(-1)[:6] = [-200.0, 200.0, -90.0, 90.0, -20.0, 20.0]
+    y = (rng.random(x.shape) > 0.7).astype(np.float32)
+    y.reshape(-1)[:6] = [1, 0, 1, 0, 0, 1]
+    for target in (y, rng.random(x.shape).astype(np.float32)):   # 0/1 masks, then soft targets
+        xt = torch.from_numpy(x).requires_grad_(True)
+        loss = torch.nn.BCELoss()(torch.sigmoid(xt), torch.from_numpy(target))
+        loss.backward()
+        o_loss, o_grad = bce_sigmoid(x, target)
+        assert abs(float(o_loss) - loss.item()) <= 1e-6 * abs(loss.item())
+        np.testing.assert_allclose(o_grad, xt.grad.numpy(), rtol=2e-5, atol=1e-10)

@@ -1,0 +1,108 @@
+"""Training-step pieces that run in libisg (first slice): the fused sigmoid + BCE loss with its
+gradient (isg_bce_sigmoid) against oracle/bce_oracle.py, and the graph-replayed step against the eager one."""
+import numpy as np
+import pytest
+import torch
+
+from instancesegmentation_b200 import Segment, _lib, synth
+from instancesegmentation_b200.train_step import FlatBucket, GraphedTrainStep, bce_sigmoid_loss
+from oracle.bce_oracle import bce_sigmoid
+
+pytestmark = pytest.mark.gpu
+
+
+def _case(shape, seed, scale=4.0):
+    rng = np.random.default_rng(seed)
+    x = (rng.standard_normal(shape) * scale).astype(np.float32)
+    y = (rng.random(shape) > 0.7).astype(np.float32)
+    return x, y
+
+
+@pytest.mark.parametrize("shape", [(1,), (3, 1, 17, 29), (16, 1, 512, 512)])
+def test_bce_sigmoid_fp32_matches_oracle(shape):
+    x, y = _case(shape, 11)
+    if x.size >= 6:
+        x.reshape(-1)[:6] = [-200.0, 200.0, -90.0, 90.0, -20.0, 20.0]   # log clamp (-100) and gradient clamp (1e-12)
+        y.reshape(-1)[:6] = [1, 0, 1, 0, 0, 1]
+    o_loss, o_grad = bce_sigmoid(x, y)
+    xt = torch.from_numpy(x).cuda().requires_grad_(True)
+    loss = bce_sigmoid_loss(xt, torch.from_numpy(y).cuda())
+    loss.backward()
+    # fp32: device expf/logf differ from the host's by a few ulp per element; tolerance 2e-6 relative on the mean
+    assert abs(loss.item() - float(o_loss)) <= 2e-6 * abs(float(o_loss))
+    np.testing.assert_allclose(xt.grad.cpu().numpy(), o_grad, rtol=2e-5, atol=1e-10 / x.size)
+
+
+def test_bce_sigmoid_bf16_logits_and_upstream_gradient():
+    x, y = _case((4, 1, 64, 96), 12)
+    xb = torch.from_numpy(x).cuda().to(torch.bfloat16)
+    o_loss, o_grad = bce_sigmoid(xb.float().cpu().numpy(), y)     # the oracle sees the same rounded logits
+    xt = xb.clone().requires_grad_(True)
+    loss = bce_sigmoid_loss(xt, torch.from_numpy(y).cuda())
+    (loss * 3.0).backward()
+    assert loss.dtype == torch.float32 and xt.grad.dtype == torch.bfloat16
+    assert abs(loss.item() - float(o_loss)) <= 2e-6 * abs(float(o_loss))
+    # gradient is stored in bf16 (8 mantissa bits), then scaled by the upstream 3.0 in bf16
+    np.testing.assert_allclose(xt.grad.float().cpu().numpy(), 3.0 * o_grad, rtol=2 ** -7, atol=1e-12)
+
+
+def test_bce_sigmoid_is_deterministic_and_reusable():
+    x, y = _case((8, 1, 256, 256), 13)
+    xt, yt = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    vals = [bce_sigmoid_loss(xt, yt).item() for _ in range(5)]     # same workspace, ticket reset by the kernel
+    assert len(set(vals)) == 1
+    ref = torch.nn.BCELoss()(torch.sigmoid(xt), yt).item()
+    assert abs(vals[0] - ref) <= 2e-6 * abs(ref)
+
+
+def test_bce_sigmoid_argument_errors():
+    xt = torch.zeros(4, device="cuda")
+    with pytest.raises(ValueError):
+        bce_sigmoid_loss(xt, torch.zeros(5, device="cuda"))
+    with pytest.raises(ValueError):
+        bce_sigmoid_loss(xt[:0], xt[:0])
+    with pytest.raises(TypeError):
+        bce_sigmoid_loss(xt.half(), xt)
+    with pytest.raises(_lib.IsgError):
+        bce_sigmoid_loss(xt.cpu(), xt.cpu())
+    l = _lib.lib()
+    assert l.isg_bce_sigmoid(None, 0, None, 4, None, None, None, None) != 0
+    assert b"null" in l.isg_last_error()
+
+
+def test_graphed_step_equals_eager_step():
+    """one step of GraphedTrainStep (graph replay of forward + isg_bce_sigmoid + backward) leaves the same
+    loss, gradients and BatchNorm statistics as the reference's eager sequence (train_instance.py:372-378)"""
+    B, S = 2, 128
+    x = torch.from_numpy(synth.batch(B, S, S, seed=21)).cuda()
+    y = (torch.from_numpy(synth.logits(B, S, S, seed=22)) > 0.8).float()[:, None].cuda()
+    torch.manual_seed(3)
+    a = Segment(3).cuda().train()
+    torch.manual_seed(3)
+    b = Segment(3).cuda().train()
+    ba, bb = FlatBucket(a, grads_as_views=True), FlatBucket(b, grads_as_views=True)
+    ba.zero_grads()
+    loss_a = torch.nn.BCELoss()(a.train_batch(x), y)
+    loss_a.backward()
+    step = GraphedTrainStep(b, bb, x, y, autocast_dtype=None)
+    loss_b = step(x, y)
+    torch.cuda.synchronize()
+    assert abs(loss_a.item() - loss_b.item()) <= 1e-5 * abs(loss_a.item())
+    ga, gb = ba.grad, bb.grad
+    assert float((ga - gb).abs().max()) <= 2e-3 * float(ga.abs().max())
+    for (ka, va), (kb, vb) in zip(a.named_buffers(), b.named_buffers()):
+        assert ka == kb
+        if va.dtype.is_floating_point:
+            assert torch.allclose(va, vb, rtol=1e-4, atol=1e-6), ka      # warm-up passes did not leak into the stats
+        else:
+            assert torch.equal(va, vb), ka                               # num_batches_tracked == 1 on both
+    assert bb.step_count == 1
+    # second replay with another batch follows the eager model too
+    x2 = torch.from_numpy(synth.batch(B, S, S, seed=23)).cuda()
+    ba.adam_step(ba.allreduce())
+    a.invalidate()
+    ba.zero_grads()
+    loss_a2 = torch.nn.BCELoss()(a.train_batch(x2), y)
+    loss_b2 = step(x2, y)
+    torch.cuda.synchronize()
+    assert abs(loss_a2.item() - loss_b2.item()) <= 5e-3 * abs(loss_a2.item())
