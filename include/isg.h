@@ -176,6 +176,23 @@ ISG_API int64_t isg_bce_workspace_bytes(void);
 ISG_API int isg_bce_sigmoid(const void* logits_dev, int logits_bf16, const float* target_dev, int64_t n,
                     void* dlogits_dev, void* workspace_dev, float* loss_dev, void* stream);
 
+/* ---- train-mode BatchNorm2d (segment.py:41, one per Conv; train_instance.py:372 model.train()) -------------
+ * NCHW activations [batch, channels, hw] contiguous, bf16 or fp32 (bf16 != 0); gamma/beta/statistics fp32 [channels]
+ * (gamma, beta, running_* may be NULL).  forward: batch statistics (biased variance for y, unbiased into
+ * running_var, running = (1-momentum)*running + momentum*batch), y = (x-mean)*invstd*gamma+beta, and the
+ * mean / invstd the backward needs.  backward: dx (may be NULL), dgamma, dbeta (may be NULL) of that op.
+ * workspace_dev: channels * isg_bn_max_split() * 16 bytes, 8-byte aligned, contents irrelevant.  Sums are
+ * combined in a fixed order: deterministic. */
+ISG_API int isg_bn_max_split(void);
+ISG_API int isg_bn_train_forward(const void* x_dev, int bf16, int batch, int channels, int64_t hw,
+                         const float* gamma_dev, const float* beta_dev, float* running_mean_dev,
+                         float* running_var_dev, float momentum, float eps, void* y_dev,
+                         float* save_mean_dev, float* save_invstd_dev, void* workspace_dev, void* stream);
+ISG_API int isg_bn_train_backward(const void* dy_dev, const void* x_dev, int bf16, int batch, int channels,
+                          int64_t hw, const float* gamma_dev, const float* save_mean_dev,
+                          const float* save_invstd_dev, void* dx_dev, float* dgamma_dev, float* dbeta_dev,
+                          void* workspace_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

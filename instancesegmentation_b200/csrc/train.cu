@@ -65,6 +65,219 @@ bce_sigmoid_kernel(const T* __restrict__ logits, const float* __restrict__ targe
     }
 }
 
+
+// ---- train-mode BatchNorm2d (reference segment.py:41 nn.BatchNorm2d inside every Conv, train_instance.py:372) ----
+// NCHW, bf16 or fp32 activations, fp32 statistics.  The library kernels behind the same op take 44 % of the
+// reference's training step on this GPU (scripts/train_profile.py); these are plain streaming passes:
+//   forward : bn_stats (sum, sum of squares about a per-channel shift)  ->  bn_apply (y = x*scale + shift', running stats)
+//   backward: bn_bwd_reduce (sum dy, sum dy*(x-mean))                   ->  bn_bwd_apply (dx, dgamma, dbeta)
+// grid = (splits, channels): every block owns a contiguous range of 16-byte vectors of one channel; partial sums are
+// combined in double in a fixed order, so results are deterministic.
+constexpr int BN_THREADS = 256;
+constexpr int BN_MAX_SPLIT = 64;
+
+template <typename T, int V> struct VecIO;
+template <> struct VecIO<float, 4> {
+    static __device__ __forceinline__ void load(const float* p, float (&v)[4]) {
+        const float4 a = *reinterpret_cast<const float4*>(p);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+    }
+    static __device__ __forceinline__ void store(float* p, const float (&v)[4]) {
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+};
+template <> struct VecIO<float, 1> {
+    static __device__ __forceinline__ void load(const float* p, float (&v)[1]) { v[0] = *p; }
+    static __device__ __forceinline__ void store(float* p, const float (&v)[1]) { *p = v[0]; }
+};
+template <> struct VecIO<__nv_bfloat16, 8> {
+    static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&v)[8]) {
+        const uint4 a = *reinterpret_cast<const uint4*>(p);
+        const unsigned w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            v[2 * i] = __uint_as_float(w[i] << 16);
+            v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        }
+    }
+    static __device__ __forceinline__ void store(__nv_bfloat16* p, const float (&v)[8]) {
+        unsigned w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+            w[i] = *reinterpret_cast<const unsigned*>(&h);
+        }
+        *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+};
+template <> struct VecIO<__nv_bfloat16, 1> {
+    static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&v)[1]) { v[0] = __bfloat162float(*p); }
+    static __device__ __forceinline__ void store(__nv_bfloat16* p, const float (&v)[1]) { *p = __float2bfloat16_rn(v[0]); }
+};
+
+__device__ __forceinline__ float to_float(float v) { return v; }
+__device__ __forceinline__ float to_float(__nv_bfloat16 v) { return __bfloat162float(v); }
+
+// this block's [lo, hi) range of V-element vectors of one channel (n_vec = B*HW/V of them)
+__device__ __forceinline__ void bn_range(unsigned n_vec, unsigned& lo, unsigned& hi) {
+    const unsigned per = (n_vec + gridDim.x - 1) / gridDim.x;
+    lo = min(n_vec, blockIdx.x * per);
+    hi = min(n_vec, lo + per);
+}
+
+// block-wide sum of two doubles in a fixed order; valid in thread 0
+__device__ __forceinline__ void block_sum2(double& a, double& b) {
+    __shared__ double sh[2][BN_THREADS / 32];
+    for (int o = 16; o; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = a; sh[1][threadIdx.x >> 5] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        a = 0.0; b = 0.0;
+        for (int w = 0; w < BN_THREADS / 32; ++w) { a += sh[0][w]; b += sh[1][w]; }
+    }
+}
+
+// sum of the gridDim.x partial pairs of channel c (every thread gets the result)
+__device__ __forceinline__ void partial_total(const double* __restrict__ part, int c, double& a, double& b) {
+    a = 0.0; b = 0.0;
+    for (unsigned s = 0; s < gridDim.x; ++s) {
+        a += part[((size_t)c * gridDim.x + s) * 2];
+        b += part[((size_t)c * gridDim.x + s) * 2 + 1];
+    }
+}
+
+template <typename T, int V>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_stats_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, double* __restrict__ part) {
+    const int c = blockIdx.y;
+    const float shift = to_float(x[(size_t)c * HW]);   // sums about the channel's first element: no cancellation in E[d^2]-E[d]^2
+    unsigned lo, hi;
+    bn_range(n_vec, lo, hi);
+    float s1 = 0.f, s2 = 0.f;
+    for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
+        const unsigned e = i * V, b = e / HW, off = e - b * HW;
+        float v[V];
+        VecIO<T, V>::load(x + ((size_t)b * C + c) * HW + off, v);
+#pragma unroll
+        for (int k = 0; k < V; ++k) { const float d = v[k] - shift; s1 += d; s2 = fmaf(d, d, s2); }
+    }
+    double a = s1, b2 = s2;
+    block_sum2(a, b2);
+    if (threadIdx.x == 0) {
+        part[((size_t)c * gridDim.x + blockIdx.x) * 2] = a;
+        part[((size_t)c * gridDim.x + blockIdx.x) * 2 + 1] = b2;
+    }
+}
+
+template <typename T, int V>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_apply_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, const double* __restrict__ part,
+                const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ running_mean,
+                float* __restrict__ running_var, float momentum, float eps, T* __restrict__ y,
+                float* __restrict__ save_mean, float* __restrict__ save_invstd) {
+    const int c = blockIdx.y;
+    const double n = (double)n_vec * V;
+    double s1, s2;
+    partial_total(part, c, s1, s2);
+    const double dm = s1 / n;
+    const double var = fmax(s2 / n - dm * dm, 0.0);
+    const float mean = (float)((double)to_float(x[(size_t)c * HW]) + dm);
+    const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        save_mean[c] = mean;
+        save_invstd[c] = invstd;
+        if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        if (running_var) {
+            const float unbiased = (float)(n > 1.0 ? var * n / (n - 1.0) : var);
+            running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+        }
+    }
+    const float g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+    const float scale = g * invstd;
+    unsigned lo, hi;
+    bn_range(n_vec, lo, hi);
+    for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
+        const unsigned e = i * V, b = e / HW, off = e - b * HW;
+        const size_t at = ((size_t)b * C + c) * HW + off;
+        float v[V];
+        VecIO<T, V>::load(x + at, v);
+#pragma unroll
+        for (int k = 0; k < V; ++k) v[k] = fmaf(v[k] - mean, scale, bt);
+        VecIO<T, V>::store(y + at, v);
+    }
+}
+
+template <typename T, int V>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec,
+                     const float* __restrict__ save_mean, double* __restrict__ part) {
+    const int c = blockIdx.y;
+    const float mean = save_mean[c];
+    unsigned lo, hi;
+    bn_range(n_vec, lo, hi);
+    float s1 = 0.f, s2 = 0.f;
+    for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
+        const unsigned e = i * V, b = e / HW, off = e - b * HW;
+        const size_t at = ((size_t)b * C + c) * HW + off;
+        float g[V], v[V];
+        VecIO<T, V>::load(dy + at, g);
+        VecIO<T, V>::load(x + at, v);
+#pragma unroll
+        for (int k = 0; k < V; ++k) { s1 += g[k]; s2 = fmaf(g[k], v[k] - mean, s2); }
+    }
+    double a = s1, b2 = s2;
+    block_sum2(a, b2);
+    if (threadIdx.x == 0) {
+        part[((size_t)c * gridDim.x + blockIdx.x) * 2] = a;
+        part[((size_t)c * gridDim.x + blockIdx.x) * 2 + 1] = b2;
+    }
+}
+
+template <typename T, int V>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec,
+                    const double* __restrict__ part, const float* __restrict__ gamma, const float* __restrict__ save_mean,
+                    const float* __restrict__ save_invstd, T* __restrict__ dx, float* __restrict__ dgamma,
+                    float* __restrict__ dbeta) {
+    const int c = blockIdx.y;
+    const double n = (double)n_vec * V;
+    double sdy, sdyxmu;
+    partial_total(part, c, sdy, sdyxmu);
+    const float mean = save_mean[c], invstd = save_invstd[c];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (dgamma) dgamma[c] = (float)(sdyxmu * (double)invstd);
+        if (dbeta) dbeta[c] = (float)sdy;
+    }
+    if (!dx) return;
+    const float g = gamma ? gamma[c] : 1.f;
+    const float k1 = (float)(sdy / n);
+    const float k2 = (float)(sdyxmu * (double)invstd * (double)invstd / n);
+    const float gs = g * invstd;
+    unsigned lo, hi;
+    bn_range(n_vec, lo, hi);
+    for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
+        const unsigned e = i * V, b = e / HW, off = e - b * HW;
+        const size_t at = ((size_t)b * C + c) * HW + off;
+        float gy[V], v[V];
+        VecIO<T, V>::load(dy + at, gy);
+        VecIO<T, V>::load(x + at, v);
+#pragma unroll
+        for (int k = 0; k < V; ++k) v[k] = (gy[k] - k1 - (v[k] - mean) * k2) * gs;
+        VecIO<T, V>::store(dx + at, v);
+    }
+}
+
+inline int bn_split(int channels, unsigned n_vec) {
+    int s = (148 * 8 + channels - 1) / channels;                     // ~8 blocks per SM over all channels
+    const unsigned by_work = (n_vec + BN_THREADS * 2 - 1) / (BN_THREADS * 2);   // at least two vectors per thread
+    if ((unsigned)s > by_work) s = (int)by_work;
+    if (s > BN_MAX_SPLIT) s = BN_MAX_SPLIT;
+    return s < 1 ? 1 : s;
+}
+
 }  // namespace
 }  // namespace isg
 
@@ -93,6 +306,81 @@ int isg_bce_sigmoid(const void* logits_dev, int logits_bf16, const float* target
         bce_sigmoid_kernel<float><<<(unsigned)blocks, BCE_THREADS, 0, st>>>(
             static_cast<const float*>(logits_dev), target_dev, n, inv_n, static_cast<float*>(dlogits_dev), partial, ticket,
             loss_dev);
+    ISG_CUDA(cudaGetLastError());
+    return ISG_OK;
+}
+
+int isg_bn_max_split(void) { return BN_MAX_SPLIT; }
+
+static int bn_check(const char* who, int bf16, int batch, int channels, int64_t hw, const void* a, const void* b,
+                    const void* ws) {
+    if (!a || !b || !ws) return fail(ISG_ERR_ARG, "%s: null argument", who);
+    if (batch < 1 || channels < 1 || channels > 65535 || hw < 1 || (int64_t)batch * hw >= (1ll << 31))
+        return fail(ISG_ERR_ARG, "%s: bad sizes (batch=%d channels=%d hw=%lld; batch*hw must be below 2^31)", who, batch,
+                    channels, (long long)hw);
+    (void)bf16;
+    return ISG_OK;
+}
+
+// 16-byte vectors when every channel plane starts 16-byte aligned and holds a whole number of them
+static bool bn_wide(int bf16, int64_t hw, const void* p0, const void* p1, const void* p2) {
+    const int v = bf16 ? 8 : 4;
+    auto al = [](const void* p) { return !p || (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    return hw % v == 0 && al(p0) && al(p1) && al(p2);
+}
+
+int isg_bn_train_forward(const void* x_dev, int bf16, int batch, int channels, int64_t hw, const float* gamma_dev,
+                         const float* beta_dev, float* running_mean_dev, float* running_var_dev, float momentum, float eps,
+                         void* y_dev, float* save_mean_dev, float* save_invstd_dev, void* workspace_dev, void* stream) {
+    if (int rc = bn_check("isg_bn_train_forward", bf16, batch, channels, hw, x_dev, y_dev, workspace_dev)) return rc;
+    if (!save_mean_dev || !save_invstd_dev) return fail(ISG_ERR_ARG, "isg_bn_train_forward: null argument");
+    if (!(eps >= 0.f) || !(momentum >= 0.f && momentum <= 1.f))
+        return fail(ISG_ERR_ARG, "isg_bn_train_forward: eps must be >= 0 and momentum in [0,1]");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    double* part = static_cast<double*>(workspace_dev);
+    const bool wide = bn_wide(bf16, hw, x_dev, y_dev, nullptr);
+    const unsigned HW = (unsigned)hw;
+#define ISG_BN_FWD(T, V)                                                                                              \
+    do {                                                                                                              \
+        const unsigned n_vec = (unsigned)((int64_t)batch * hw / V);                                                   \
+        dim3 grid(bn_split(channels, n_vec), channels);                                                               \
+        bn_stats_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, part);  \
+        bn_apply_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, part,   \
+                                                           gamma_dev, beta_dev, running_mean_dev, running_var_dev,    \
+                                                           momentum, eps, static_cast<T*>(y_dev), save_mean_dev,      \
+                                                           save_invstd_dev);                                          \
+    } while (0)
+    if (bf16) { if (wide) ISG_BN_FWD(__nv_bfloat16, 8); else ISG_BN_FWD(__nv_bfloat16, 1); }
+    else      { if (wide) ISG_BN_FWD(float, 4); else ISG_BN_FWD(float, 1); }
+#undef ISG_BN_FWD
+    ISG_CUDA(cudaGetLastError());
+    return ISG_OK;
+}
+
+int isg_bn_train_backward(const void* dy_dev, const void* x_dev, int bf16, int batch, int channels, int64_t hw,
+                          const float* gamma_dev, const float* save_mean_dev, const float* save_invstd_dev, void* dx_dev,
+                          float* dgamma_dev, float* dbeta_dev, void* workspace_dev, void* stream) {
+    if (int rc = bn_check("isg_bn_train_backward", bf16, batch, channels, hw, dy_dev, x_dev, workspace_dev)) return rc;
+    if (!save_mean_dev || !save_invstd_dev) return fail(ISG_ERR_ARG, "isg_bn_train_backward: null argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    double* part = static_cast<double*>(workspace_dev);
+    const bool wide = bn_wide(bf16, hw, dy_dev, x_dev, dx_dev);
+    const unsigned HW = (unsigned)hw;
+#define ISG_BN_BWD(T, V)                                                                                              \
+    do {                                                                                                              \
+        const unsigned n_vec = (unsigned)((int64_t)batch * hw / V);                                                   \
+        dim3 grid(bn_split(channels, n_vec), channels);                                                               \
+        bn_bwd_reduce_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(dy_dev),                        \
+                                                                static_cast<const T*>(x_dev), channels, HW, n_vec,    \
+                                                                save_mean_dev, part);                                 \
+        bn_bwd_apply_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(dy_dev),                         \
+                                                               static_cast<const T*>(x_dev), channels, HW, n_vec,     \
+                                                               part, gamma_dev, save_mean_dev, save_invstd_dev,       \
+                                                               static_cast<T*>(dx_dev), dgamma_dev, dbeta_dev);       \
+    } while (0)
+    if (bf16) { if (wide) ISG_BN_BWD(__nv_bfloat16, 8); else ISG_BN_BWD(__nv_bfloat16, 1); }
+    else      { if (wide) ISG_BN_BWD(float, 4); else ISG_BN_BWD(float, 1); }
+#undef ISG_BN_BWD
     ISG_CUDA(cudaGetLastError());
     return ISG_OK;
 }

@@ -21,6 +21,8 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from .bn import BatchNorm2d
+
 __all__ = ["Segment", "topology"]
 
 
@@ -68,7 +70,7 @@ class _Unit(nn.Module):
             p = k // 2 if isinstance(k, int) else tuple(v // 2 for v in k)
         a = _act(act, cout)  # constructed first, like the reference's call sites
         self.conv = nn.Conv2d(cin, cout, k, s, p, groups=g, dilation=d, bias=True)
-        self.bn = nn.BatchNorm2d(cout)
+        self.bn = BatchNorm2d(cout)
         self.act = a
 
     def forward(self, x):
@@ -128,7 +130,7 @@ class _Block(nn.Module):
             ci, m, co, sk = a["cin"], a["mid"], a["cout"], a["skip"]
             self.convs = _seq(_Unit(ci, m, 1, act="relu"),
                               nn.ConvTranspose2d(m, m, 4, stride=2, padding=1),
-                              nn.BatchNorm2d(m),
+                              BatchNorm2d(m),
                               nn.ReLU(inplace=True),
                               _Unit(m, co, 1))
             self.conv2 = _seq(_Unit(ci, co, 1))
