@@ -124,6 +124,16 @@ def test_library_rejects_bad_arguments_without_gpu():
     assert b"multiple of 4" in l.isg_last_error()
     assert l.isg_keypoint_heatmaps(pbuf, 1, 17, 16, 16, 10.0, 1.5, pbuf, 17 * 16 * 16, None) == -1
     assert b"threshold" in l.isg_last_error()
+    # training-step entry points (SURVEY 8f-1 slice)
+    assert l.isg_bce_workspace_bytes() >= 8 * 1024 and l.isg_bn_max_split() >= 1
+    assert l.isg_bce_sigmoid(pbuf, 0, pbuf, 0, None, pbuf, pbuf, None) == -1
+    assert b"empty batch" in l.isg_last_error()
+    assert l.isg_bce_sigmoid(pbuf, 0, None, 4, None, pbuf, pbuf, None) == -1
+    assert l.isg_bn_train_forward(pbuf, 0, 0, 4, 16, None, None, None, None, 0.1, 1e-5, pbuf, pbuf, pbuf, pbuf, None) == -1
+    assert b"bad sizes" in l.isg_last_error()
+    assert l.isg_bn_train_forward(pbuf, 0, 1, 4, 4, None, None, None, None, 1.5, 1e-5, pbuf, pbuf, pbuf, pbuf, None) == -1
+    assert b"momentum" in l.isg_last_error()
+    assert l.isg_bn_train_backward(pbuf, None, 0, 1, 4, 4, None, pbuf, pbuf, pbuf, None, None, pbuf, None) == -1
 
 
 def test_infer_call_surface():
