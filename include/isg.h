@@ -176,22 +176,29 @@ ISG_API int64_t isg_bce_workspace_bytes(void);
 ISG_API int isg_bce_sigmoid(const void* logits_dev, int logits_bf16, const float* target_dev, int64_t n,
                     void* dlogits_dev, void* workspace_dev, float* loss_dev, void* stream);
 
-/* ---- train-mode BatchNorm2d (segment.py:41, one per Conv; train_instance.py:372 model.train()) -------------
+/* ---- train-mode BatchNorm2d (+ the activation of the Conv block) (segment.py:41-45, one per Conv;
+ * train_instance.py:372 model.train()) -------------------------------------------------------------------
  * NCHW activations [batch, channels, hw] contiguous, bf16 or fp32 (bf16 != 0); gamma/beta/statistics fp32 [channels]
  * (gamma, beta, running_* may be NULL).  forward: batch statistics (biased variance for y, unbiased into
- * running_var, running = (1-momentum)*running + momentum*batch), y = (x-mean)*invstd*gamma+beta, and the
- * mean / invstd the backward needs.  backward: dx (may be NULL), dgamma, dbeta (may be NULL) of that op.
- * workspace_dev: channels * isg_bn_max_split() * 16 bytes, 8-byte aligned, contents irrelevant.  Sums are
+ * running_var, running = (1-momentum)*running + momentum*batch), z = (x-mean)*invstd*gamma+beta, y = act(z)
+ * with act 0 none / 1 ReLU / 2 PReLU (slope_dev: 1 or `channels` slopes), and the mean / invstd the backward
+ * needs.  mean_offset_dev (may be NULL): a per-channel constant the caller left out of x -- the conv bias, which
+ * the mean subtraction cancels exactly -- added to the batch mean that goes into running_mean.
+ * backward: given dy = d loss / d y and the same x: dx (may be NULL), dgamma, dbeta, dslope [channels] (may be NULL;
+ * a 1-slope PReLU sums dslope over channels itself); z is recomputed, no activation input is kept.
+ * workspace_dev: channels * isg_bn_max_split() * 24 bytes, 8-byte aligned, contents irrelevant.  Sums are
  * combined in a fixed order: deterministic. */
 ISG_API int isg_bn_max_split(void);
 ISG_API int isg_bn_train_forward(const void* x_dev, int bf16, int batch, int channels, int64_t hw,
-                         const float* gamma_dev, const float* beta_dev, float* running_mean_dev,
-                         float* running_var_dev, float momentum, float eps, void* y_dev,
+                         const float* gamma_dev, const float* beta_dev, const float* mean_offset_dev,
+                         float* running_mean_dev, float* running_var_dev, float momentum, float eps,
+                         int act, const float* slope_dev, int slope_count, void* y_dev,
                          float* save_mean_dev, float* save_invstd_dev, void* workspace_dev, void* stream);
 ISG_API int isg_bn_train_backward(const void* dy_dev, const void* x_dev, int bf16, int batch, int channels,
-                          int64_t hw, const float* gamma_dev, const float* save_mean_dev,
-                          const float* save_invstd_dev, void* dx_dev, float* dgamma_dev, float* dbeta_dev,
-                          void* workspace_dev, void* stream);
+                          int64_t hw, const float* gamma_dev, const float* beta_dev,
+                          const float* save_mean_dev, const float* save_invstd_dev, int act,
+                          const float* slope_dev, int slope_count, void* dx_dev, float* dgamma_dev,
+                          float* dbeta_dev, float* dslope_dev, void* workspace_dev, void* stream);
 
 #ifdef __cplusplus
 }

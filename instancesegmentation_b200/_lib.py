@@ -40,8 +40,8 @@ SIGNATURES = {
     "isg_crop_resize_u8": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "isg_adam_step": (_i, [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp]),
     "isg_bn_max_split": (_i, []),
-    "isg_bn_train_forward": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
-    "isg_bn_train_backward": (_i, [_vp, _vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "isg_bn_train_forward": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    "isg_bn_train_backward": (_i, [_vp, _vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "isg_bce_workspace_bytes": (_i64, []),
     "isg_bce_sigmoid": (_i, [_vp, _i, _vp, _i64, _vp, _vp, _vp, _vp]),
 }

@@ -1,20 +1,28 @@
 """Train-mode BatchNorm2d of the reference's ``Conv`` block (model/segment.py:41; ``model.train()`` at
-train_instance.py:372) in libisg: batch statistics, normalisation, running-stat update and the backward as
-four streaming kernels (``isg_bn_train_forward`` / ``isg_bn_train_backward``).  Same module class, same
-``state_dict`` keys; eval mode is folded into the conv weights by the engine and never comes here."""
+train_instance.py:372) in libisg: batch statistics, normalisation, running-stat update, the activation that
+follows it in the block (segment.py:42-45) and the backward of both, as four streaming kernels
+(``isg_bn_train_forward`` / ``isg_bn_train_backward``).  Same module class, same ``state_dict`` keys; eval mode
+is folded into the conv weights by the engine and never comes here."""
 import torch
+import torch.nn.functional as F
 from torch import nn
 
 from . import _lib
 
+ACT_NONE, ACT_RELU, ACT_PRELU = 0, 1, 2
+
 
 def _workspace(x, channels):
-    return torch.empty(channels * _lib.lib().isg_bn_max_split() * 2, dtype=torch.float64, device=x.device)
+    return torch.empty(channels * _lib.lib().isg_bn_max_split() * 3, dtype=torch.float64, device=x.device)
+
+
+def _ptr(t):
+    return t.data_ptr() if t is not None else None
 
 
 class _BnTrain(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps):
+    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, mean_offset, act, slope):
         B, C = x.shape[0], x.shape[1]
         hw = x.numel() // (B * C)
         x = x.contiguous()
@@ -23,36 +31,37 @@ class _BnTrain(torch.autograd.Function):
         invstd = torch.empty(C, dtype=torch.float32, device=x.device)
         with torch.cuda.device(x.device):
             _lib.check(_lib.lib().isg_bn_train_forward(
-                x.data_ptr(), int(x.dtype == torch.bfloat16), B, C, hw,
-                weight.data_ptr() if weight is not None else None, bias.data_ptr() if bias is not None else None,
-                running_mean.data_ptr() if running_mean is not None else None,
-                running_var.data_ptr() if running_var is not None else None,
-                float(momentum), float(eps), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                x.data_ptr(), int(x.dtype == torch.bfloat16), B, C, hw, _ptr(weight), _ptr(bias), _ptr(mean_offset),
+                _ptr(running_mean), _ptr(running_var), float(momentum), float(eps), int(act), _ptr(slope),
+                slope.numel() if slope is not None else 0, y.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
                 _workspace(x, C).data_ptr(), torch.cuda.current_stream().cuda_stream))
-        ctx.save_for_backward(x, weight, mean, invstd)
-        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, weight, bias, mean, invstd, slope)
+        ctx.act = int(act)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, weight, mean, invstd = ctx.saved_tensors
+        x, weight, bias, mean, invstd, slope = ctx.saved_tensors
         B, C = x.shape[0], x.shape[1]
         hw = x.numel() // (B * C)
         dy = dy.contiguous()
         if dy.dtype != x.dtype:
             dy = dy.to(x.dtype)
-        need_x, need_w, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
-        dx = torch.empty_like(x) if need_x else None
-        dgamma = torch.empty(C, dtype=torch.float32, device=x.device) if (need_w and weight is not None) else None
-        dbeta = torch.empty(C, dtype=torch.float32, device=x.device) if (need_b and ctx.has_bias) else None
-        with torch.cuda.device(x.device):
+        need = ctx.needs_input_grad
+        dev = x.device
+        dx = torch.empty_like(x) if need[0] else None
+        dgamma = torch.empty(C, dtype=torch.float32, device=dev) if (need[1] and weight is not None) else None
+        dbeta = torch.empty(C, dtype=torch.float32, device=dev) if (need[2] and bias is not None) else None
+        dslope = torch.empty(C, dtype=torch.float32, device=dev) if (need[9] and slope is not None) else None
+        with torch.cuda.device(dev):
             _lib.check(_lib.lib().isg_bn_train_backward(
-                dy.data_ptr(), x.data_ptr(), int(x.dtype == torch.bfloat16), B, C, hw,
-                weight.data_ptr() if weight is not None else None, mean.data_ptr(), invstd.data_ptr(),
-                dx.data_ptr() if dx is not None else None, dgamma.data_ptr() if dgamma is not None else None,
-                dbeta.data_ptr() if dbeta is not None else None, _workspace(x, C).data_ptr(),
+                dy.data_ptr(), x.data_ptr(), int(x.dtype == torch.bfloat16), B, C, hw, _ptr(weight), _ptr(bias),
+                mean.data_ptr(), invstd.data_ptr(), ctx.act, _ptr(slope), slope.numel() if slope is not None else 0,
+                _ptr(dx), _ptr(dgamma), _ptr(dbeta), _ptr(dslope), _workspace(x, C).data_ptr(),
                 torch.cuda.current_stream().cuda_stream))
-        return dx, dgamma, dbeta, None, None, None, None
+        if dslope is not None and slope.numel() == 1:
+            dslope = dslope.sum().reshape(slope.shape)
+        return dx, dgamma, dbeta, None, None, None, None, None, None, dslope
 
 
 class BatchNorm2d(nn.BatchNorm2d):
@@ -60,9 +69,43 @@ class BatchNorm2d(nn.BatchNorm2d):
     -- eval mode, CPU tensors (the boundary tests compare train mode against the reference on CPU), cumulative
     averaging (``momentum=None``), other dtypes -- is the parent class unchanged."""
 
+    def native(self, x):
+        return bool(self.training and x.is_cuda and x.dim() == 4 and self.momentum is not None
+                    and self.track_running_stats and x.dtype in (torch.float32, torch.bfloat16) and x.numel() > 0)
+
     def forward(self, x):
-        if (self.training and x.is_cuda and x.dim() == 4 and self.momentum is not None and self.track_running_stats
-                and x.dtype in (torch.float32, torch.bfloat16) and x.numel() > 0):
-            self.num_batches_tracked.add_(1)
-            return _BnTrain.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.momentum, self.eps)
+        if self.native(x):
+            return self.fused(x)
         return super().forward(x)
+
+    def fused(self, x, mean_offset=None, act=None):
+        """``act(bn(x + mean_offset))`` for a native ``x``: ``mean_offset`` is a per-channel constant left out of ``x``
+        (the conv bias: train-mode normalisation cancels it, only ``running_mean`` sees it; its gradient is exactly
+        zero) and ``act`` the block's ``nn.PReLU`` / ``nn.ReLU`` / ``nn.Identity`` module, fused into the same kernels."""
+        kind, slope = ACT_NONE, None
+        if isinstance(act, nn.PReLU):
+            kind, slope = ACT_PRELU, act.weight
+        elif isinstance(act, nn.ReLU):
+            kind = ACT_RELU
+        elif act is not None and not isinstance(act, nn.Identity):
+            raise TypeError(f"cannot fuse activation {type(act).__name__}")
+        self.num_batches_tracked.add_(1)
+        off = mean_offset.detach() if mean_offset is not None else None
+        return _BnTrain.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.momentum, self.eps,
+                              off, kind, slope)
+
+
+def conv_bn_act(conv, bn, act, x):
+    """The reference's ``Conv.forward`` (segment.py:47-48): ``act(bn(conv(x)))``.  On the native train path the conv
+    runs without its bias (it cancels in the normalisation; ``ISG_TRAIN_KEEP_CONV_BIAS=1`` keeps the literal
+    sequence) and BatchNorm + activation are one forward and one backward kernel pair."""
+    import os
+    if (isinstance(bn, BatchNorm2d) and bn.training and x.is_cuda and bn.momentum is not None and bn.track_running_stats
+            and conv.padding_mode == "zeros" and not os.environ.get("ISG_TRAIN_KEEP_CONV_BIAS")):
+        z = F.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
+        if bn.native(z):
+            return bn.fused(z, conv.bias, act)
+        if conv.bias is not None:
+            z = z + conv.bias.view(1, -1, 1, 1).to(z.dtype)
+        return act(bn(z))
+    return act(bn(conv(x)))

@@ -125,28 +125,54 @@ __device__ __forceinline__ void bn_range(unsigned n_vec, unsigned& lo, unsigned&
     hi = min(n_vec, lo + per);
 }
 
-// block-wide sum of two doubles in a fixed order; valid in thread 0
-__device__ __forceinline__ void block_sum2(double& a, double& b) {
-    __shared__ double sh[2][BN_THREADS / 32];
-    for (int o = 16; o; o >>= 1) {
-        a += __shfl_xor_sync(0xffffffffu, a, o);
-        b += __shfl_xor_sync(0xffffffffu, b, o);
+// block-wide sums of N doubles in a fixed order; valid in thread 0
+template <int N>
+__device__ __forceinline__ void block_sum(double (&a)[N]) {
+    __shared__ double sh[N][BN_THREADS / 32];
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+        for (int o = 16; o; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) sh[k][threadIdx.x >> 5] = a[k];
     }
-    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = a; sh[1][threadIdx.x >> 5] = b; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        a = 0.0; b = 0.0;
-        for (int w = 0; w < BN_THREADS / 32; ++w) { a += sh[0][w]; b += sh[1][w]; }
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+            a[k] = 0.0;
+            for (int w = 0; w < BN_THREADS / 32; ++w) a[k] += sh[k][w];
+        }
     }
 }
 
-// sum of the gridDim.x partial pairs of channel c (every thread gets the result)
-__device__ __forceinline__ void partial_total(const double* __restrict__ part, int c, double& a, double& b) {
-    a = 0.0; b = 0.0;
+// partials are stored [channel][split][N]; total over the gridDim.x splits of channel c (every thread gets it)
+template <int N>
+__device__ __forceinline__ void partial_total(const double* __restrict__ part, int c, double (&a)[N]) {
+#pragma unroll
+    for (int k = 0; k < N; ++k) a[k] = 0.0;
     for (unsigned s = 0; s < gridDim.x; ++s) {
-        a += part[((size_t)c * gridDim.x + s) * 2];
-        b += part[((size_t)c * gridDim.x + s) * 2 + 1];
+#pragma unroll
+        for (int k = 0; k < N; ++k) a[k] += part[((size_t)c * gridDim.x + s) * N + k];
     }
+}
+template <int N>
+__device__ __forceinline__ void partial_store(double* __restrict__ part, int c, const double (&a)[N]) {
+#pragma unroll
+    for (int k = 0; k < N; ++k) part[((size_t)c * gridDim.x + blockIdx.x) * N + k] = a[k];
+}
+
+// activation that follows the BatchNorm inside the reference's Conv block (segment.py:42-45): ISG_ACT_* of isg.h
+__device__ __forceinline__ float act_fwd(float z, int act, float slope) {
+    if (act == 1) return z > 0.f ? z : 0.f;
+    if (act == 2) return z > 0.f ? z : z * slope;
+    return z;
+}
+// d act / d z times the incoming gradient (torch's conventions at z == 0: ReLU 0, PReLU slope)
+__device__ __forceinline__ float act_bwd(float z, float g, int act, float slope) {
+    if (act == 1) return z > 0.f ? g : 0.f;
+    if (act == 2) return z > 0.f ? g : g * slope;
+    return g;
 }
 
 template <typename T, int V>
@@ -164,32 +190,32 @@ bn_stats_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, dou
 #pragma unroll
         for (int k = 0; k < V; ++k) { const float d = v[k] - shift; s1 += d; s2 = fmaf(d, d, s2); }
     }
-    double a = s1, b2 = s2;
-    block_sum2(a, b2);
-    if (threadIdx.x == 0) {
-        part[((size_t)c * gridDim.x + blockIdx.x) * 2] = a;
-        part[((size_t)c * gridDim.x + blockIdx.x) * 2 + 1] = b2;
-    }
+    double a[2] = {s1, s2};
+    block_sum<2>(a);
+    if (threadIdx.x == 0) partial_store<2>(part, c, a);
 }
 
 template <typename T, int V>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_apply_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, const double* __restrict__ part,
-                const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ running_mean,
-                float* __restrict__ running_var, float momentum, float eps, T* __restrict__ y,
-                float* __restrict__ save_mean, float* __restrict__ save_invstd) {
+                const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean_offset,
+                float* __restrict__ running_mean, float* __restrict__ running_var, float momentum, float eps, int act,
+                const float* __restrict__ slope, int slope_stride, T* __restrict__ y, float* __restrict__ save_mean,
+                float* __restrict__ save_invstd) {
     const int c = blockIdx.y;
     const double n = (double)n_vec * V;
-    double s1, s2;
-    partial_total(part, c, s1, s2);
-    const double dm = s1 / n;
-    const double var = fmax(s2 / n - dm * dm, 0.0);
+    double s[2];
+    partial_total<2>(part, c, s);
+    const double dm = s[0] / n;
+    const double var = fmax(s[1] / n - dm * dm, 0.0);
     const float mean = (float)((double)to_float(x[(size_t)c * HW]) + dm);
     const float invstd = (float)(1.0 / sqrt(var + (double)eps));
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         save_mean[c] = mean;
         save_invstd[c] = invstd;
-        if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        // mean_offset: a per-channel constant the caller left out of x (the conv bias, which the mean subtraction cancels)
+        const float m_full = mean + (mean_offset ? mean_offset[c] : 0.f);
+        if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m_full;
         if (running_var) {
             const float unbiased = (float)(n > 1.0 ? var * n / (n - 1.0) : var);
             running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
@@ -197,6 +223,7 @@ bn_apply_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, con
     }
     const float g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
     const float scale = g * invstd;
+    const float sl = (act == 2) ? slope[c * slope_stride] : 0.f;
     unsigned lo, hi;
     bn_range(n_vec, lo, hi);
     for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
@@ -205,20 +232,25 @@ bn_apply_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, con
         float v[V];
         VecIO<T, V>::load(x + at, v);
 #pragma unroll
-        for (int k = 0; k < V; ++k) v[k] = fmaf(v[k] - mean, scale, bt);
+        for (int k = 0; k < V; ++k) v[k] = act_fwd(fmaf(v[k] - mean, scale, bt), act, sl);
         VecIO<T, V>::store(y + at, v);
     }
 }
 
+// sums over one channel of: gz, gz * (x - mean), and (PReLU) dy * z where z <= 0;  gz = dy * act'(z), z = bn(x)
 template <typename T, int V>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec,
-                     const float* __restrict__ save_mean, double* __restrict__ part) {
+                     const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ save_mean,
+                     const float* __restrict__ save_invstd, int act, const float* __restrict__ slope, int slope_stride,
+                     double* __restrict__ part) {
     const int c = blockIdx.y;
     const float mean = save_mean[c];
+    const float scale = (gamma ? gamma[c] : 1.f) * save_invstd[c], bt = beta ? beta[c] : 0.f;
+    const float sl = (act == 2) ? slope[c * slope_stride] : 0.f;
     unsigned lo, hi;
     bn_range(n_vec, lo, hi);
-    float s1 = 0.f, s2 = 0.f;
+    float s1 = 0.f, s2 = 0.f, s3 = 0.f;
     for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
         const unsigned e = i * V, b = e / HW, off = e - b * HW;
         const size_t at = ((size_t)b * C + c) * HW + off;
@@ -226,36 +258,46 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, u
         VecIO<T, V>::load(dy + at, g);
         VecIO<T, V>::load(x + at, v);
 #pragma unroll
-        for (int k = 0; k < V; ++k) { s1 += g[k]; s2 = fmaf(g[k], v[k] - mean, s2); }
+        for (int k = 0; k < V; ++k) {
+            const float xm = v[k] - mean;
+            float gz = g[k];
+            if (act) {
+                const float z = fmaf(xm, scale, bt);
+                gz = act_bwd(z, g[k], act, sl);
+                if (act == 2 && !(z > 0.f)) s3 = fmaf(g[k], z, s3);
+            }
+            s1 += gz;
+            s2 = fmaf(gz, xm, s2);
+        }
     }
-    double a = s1, b2 = s2;
-    block_sum2(a, b2);
-    if (threadIdx.x == 0) {
-        part[((size_t)c * gridDim.x + blockIdx.x) * 2] = a;
-        part[((size_t)c * gridDim.x + blockIdx.x) * 2 + 1] = b2;
-    }
+    double a[3] = {s1, s2, s3};
+    block_sum<3>(a);
+    if (threadIdx.x == 0) partial_store<3>(part, c, a);
 }
 
 template <typename T, int V>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec,
-                    const double* __restrict__ part, const float* __restrict__ gamma, const float* __restrict__ save_mean,
-                    const float* __restrict__ save_invstd, T* __restrict__ dx, float* __restrict__ dgamma,
-                    float* __restrict__ dbeta) {
+                    const double* __restrict__ part, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ save_mean, const float* __restrict__ save_invstd, int act,
+                    const float* __restrict__ slope, int slope_stride, T* __restrict__ dx, float* __restrict__ dgamma,
+                    float* __restrict__ dbeta, float* __restrict__ dslope) {
     const int c = blockIdx.y;
     const double n = (double)n_vec * V;
-    double sdy, sdyxmu;
-    partial_total(part, c, sdy, sdyxmu);
+    double s[3];
+    partial_total<3>(part, c, s);
     const float mean = save_mean[c], invstd = save_invstd[c];
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        if (dgamma) dgamma[c] = (float)(sdyxmu * (double)invstd);
-        if (dbeta) dbeta[c] = (float)sdy;
+        if (dgamma) dgamma[c] = (float)(s[1] * (double)invstd);
+        if (dbeta) dbeta[c] = (float)s[0];
+        if (dslope) dslope[c] = (float)s[2];
     }
     if (!dx) return;
-    const float g = gamma ? gamma[c] : 1.f;
-    const float k1 = (float)(sdy / n);
-    const float k2 = (float)(sdyxmu * (double)invstd * (double)invstd / n);
+    const float g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+    const float k1 = (float)(s[0] / n);
+    const float k2 = (float)(s[1] * (double)invstd * (double)invstd / n);
     const float gs = g * invstd;
+    const float sl = (act == 2) ? slope[c * slope_stride] : 0.f;
     unsigned lo, hi;
     bn_range(n_vec, lo, hi);
     for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
@@ -265,7 +307,11 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, un
         VecIO<T, V>::load(dy + at, gy);
         VecIO<T, V>::load(x + at, v);
 #pragma unroll
-        for (int k = 0; k < V; ++k) v[k] = (gy[k] - k1 - (v[k] - mean) * k2) * gs;
+        for (int k = 0; k < V; ++k) {
+            const float xm = v[k] - mean;
+            const float gz = act ? act_bwd(fmaf(xm, gs, bt), gy[k], act, sl) : gy[k];
+            v[k] = (gz - k1 - xm * k2) * gs;
+        }
         VecIO<T, V>::store(dx + at, v);
     }
 }
@@ -322,6 +368,13 @@ static int bn_check(const char* who, int bf16, int batch, int channels, int64_t 
     return ISG_OK;
 }
 
+static int bn_act_check(const char* who, int act, const float* slope, int slope_count, int channels) {
+    if (act < 0 || act > 2) return fail(ISG_ERR_ARG, "%s: act must be 0 (none), 1 (ReLU) or 2 (PReLU)", who);
+    if (act == 2 && (!slope || (slope_count != 1 && slope_count != channels)))
+        return fail(ISG_ERR_ARG, "%s: PReLU needs 1 or %d slopes, got %d", who, channels, slope_count);
+    return ISG_OK;
+}
+
 // 16-byte vectors when every channel plane starts 16-byte aligned and holds a whole number of them
 static bool bn_wide(int bf16, int64_t hw, const void* p0, const void* p1, const void* p2) {
     const int v = bf16 ? 8 : 4;
@@ -330,25 +383,29 @@ static bool bn_wide(int bf16, int64_t hw, const void* p0, const void* p1, const 
 }
 
 int isg_bn_train_forward(const void* x_dev, int bf16, int batch, int channels, int64_t hw, const float* gamma_dev,
-                         const float* beta_dev, float* running_mean_dev, float* running_var_dev, float momentum, float eps,
-                         void* y_dev, float* save_mean_dev, float* save_invstd_dev, void* workspace_dev, void* stream) {
+                         const float* beta_dev, const float* mean_offset_dev, float* running_mean_dev,
+                         float* running_var_dev, float momentum, float eps, int act, const float* slope_dev,
+                         int slope_count, void* y_dev, float* save_mean_dev, float* save_invstd_dev, void* workspace_dev,
+                         void* stream) {
     if (int rc = bn_check("isg_bn_train_forward", bf16, batch, channels, hw, x_dev, y_dev, workspace_dev)) return rc;
     if (!save_mean_dev || !save_invstd_dev) return fail(ISG_ERR_ARG, "isg_bn_train_forward: null argument");
     if (!(eps >= 0.f) || !(momentum >= 0.f && momentum <= 1.f))
         return fail(ISG_ERR_ARG, "isg_bn_train_forward: eps must be >= 0 and momentum in [0,1]");
+    if (int rc = bn_act_check("isg_bn_train_forward", act, slope_dev, slope_count, channels)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     double* part = static_cast<double*>(workspace_dev);
     const bool wide = bn_wide(bf16, hw, x_dev, y_dev, nullptr);
     const unsigned HW = (unsigned)hw;
+    const int sstride = slope_count == 1 ? 0 : 1;
 #define ISG_BN_FWD(T, V)                                                                                              \
     do {                                                                                                              \
         const unsigned n_vec = (unsigned)((int64_t)batch * hw / V);                                                   \
         dim3 grid(bn_split(channels, n_vec), channels);                                                               \
         bn_stats_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, part);  \
         bn_apply_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, part,   \
-                                                           gamma_dev, beta_dev, running_mean_dev, running_var_dev,    \
-                                                           momentum, eps, static_cast<T*>(y_dev), save_mean_dev,      \
-                                                           save_invstd_dev);                                          \
+                                                           gamma_dev, beta_dev, mean_offset_dev, running_mean_dev,    \
+                                                           running_var_dev, momentum, eps, act, slope_dev, sstride,   \
+                                                           static_cast<T*>(y_dev), save_mean_dev, save_invstd_dev);   \
     } while (0)
     if (bf16) { if (wide) ISG_BN_FWD(__nv_bfloat16, 8); else ISG_BN_FWD(__nv_bfloat16, 1); }
     else      { if (wide) ISG_BN_FWD(float, 4); else ISG_BN_FWD(float, 1); }
@@ -358,25 +415,31 @@ int isg_bn_train_forward(const void* x_dev, int bf16, int batch, int channels, i
 }
 
 int isg_bn_train_backward(const void* dy_dev, const void* x_dev, int bf16, int batch, int channels, int64_t hw,
-                          const float* gamma_dev, const float* save_mean_dev, const float* save_invstd_dev, void* dx_dev,
-                          float* dgamma_dev, float* dbeta_dev, void* workspace_dev, void* stream) {
+                          const float* gamma_dev, const float* beta_dev, const float* save_mean_dev,
+                          const float* save_invstd_dev, int act, const float* slope_dev, int slope_count, void* dx_dev,
+                          float* dgamma_dev, float* dbeta_dev, float* dslope_dev, void* workspace_dev, void* stream) {
     if (int rc = bn_check("isg_bn_train_backward", bf16, batch, channels, hw, dy_dev, x_dev, workspace_dev)) return rc;
     if (!save_mean_dev || !save_invstd_dev) return fail(ISG_ERR_ARG, "isg_bn_train_backward: null argument");
+    if (int rc = bn_act_check("isg_bn_train_backward", act, slope_dev, slope_count, channels)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     double* part = static_cast<double*>(workspace_dev);
     const bool wide = bn_wide(bf16, hw, dy_dev, x_dev, dx_dev);
     const unsigned HW = (unsigned)hw;
+    const int sstride = slope_count == 1 ? 0 : 1;
 #define ISG_BN_BWD(T, V)                                                                                              \
     do {                                                                                                              \
         const unsigned n_vec = (unsigned)((int64_t)batch * hw / V);                                                   \
         dim3 grid(bn_split(channels, n_vec), channels);                                                               \
         bn_bwd_reduce_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(dy_dev),                        \
                                                                 static_cast<const T*>(x_dev), channels, HW, n_vec,    \
-                                                                save_mean_dev, part);                                 \
+                                                                gamma_dev, beta_dev, save_mean_dev, save_invstd_dev,  \
+                                                                act, slope_dev, sstride, part);                       \
         bn_bwd_apply_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(dy_dev),                         \
                                                                static_cast<const T*>(x_dev), channels, HW, n_vec,     \
-                                                               part, gamma_dev, save_mean_dev, save_invstd_dev,       \
-                                                               static_cast<T*>(dx_dev), dgamma_dev, dbeta_dev);       \
+                                                               part, gamma_dev, beta_dev, save_mean_dev,              \
+                                                               save_invstd_dev, act, slope_dev, sstride,              \
+                                                               static_cast<T*>(dx_dev), dgamma_dev, dbeta_dev,        \
+                                                               dslope_dev);                                           \
     } while (0)
     if (bf16) { if (wide) ISG_BN_BWD(__nv_bfloat16, 8); else ISG_BN_BWD(__nv_bfloat16, 1); }
     else      { if (wide) ISG_BN_BWD(float, 4); else ISG_BN_BWD(float, 1); }

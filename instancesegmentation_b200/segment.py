@@ -21,7 +21,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .bn import BatchNorm2d
+from .bn import BatchNorm2d, conv_bn_act
 
 __all__ = ["Segment", "topology"]
 
@@ -74,7 +74,7 @@ class _Unit(nn.Module):
         self.act = a
 
     def forward(self, x):
-        return self.act(self.bn(self.conv(x)))
+        return conv_bn_act(self.conv, self.bn, self.act, x)
 
 
 def _seq(*mods):

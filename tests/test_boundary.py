@@ -129,11 +129,18 @@ def test_library_rejects_bad_arguments_without_gpu():
     assert l.isg_bce_sigmoid(pbuf, 0, pbuf, 0, None, pbuf, pbuf, None) == -1
     assert b"empty batch" in l.isg_last_error()
     assert l.isg_bce_sigmoid(pbuf, 0, None, 4, None, pbuf, pbuf, None) == -1
-    assert l.isg_bn_train_forward(pbuf, 0, 0, 4, 16, None, None, None, None, 0.1, 1e-5, pbuf, pbuf, pbuf, pbuf, None) == -1
+    bn_fwd = lambda batch, mom, act, slope, ns: l.isg_bn_train_forward(
+        pbuf, 0, batch, 4, 4, None, None, None, None, None, mom, 1e-5, act, slope, ns, pbuf, pbuf, pbuf, pbuf, None)
+    assert bn_fwd(0, 0.1, 0, None, 0) == -1
     assert b"bad sizes" in l.isg_last_error()
-    assert l.isg_bn_train_forward(pbuf, 0, 1, 4, 4, None, None, None, None, 1.5, 1e-5, pbuf, pbuf, pbuf, pbuf, None) == -1
+    assert bn_fwd(1, 1.5, 0, None, 0) == -1
     assert b"momentum" in l.isg_last_error()
-    assert l.isg_bn_train_backward(pbuf, None, 0, 1, 4, 4, None, pbuf, pbuf, pbuf, None, None, pbuf, None) == -1
+    assert bn_fwd(1, 0.1, 3, None, 0) == -1
+    assert b"act must be" in l.isg_last_error()
+    assert bn_fwd(1, 0.1, 2, pbuf, 3) == -1
+    assert b"slopes" in l.isg_last_error()
+    assert l.isg_bn_train_backward(pbuf, None, 0, 1, 4, 4, None, None, pbuf, pbuf, 0, None, 0, pbuf, None, None, None,
+                                   pbuf, None) == -1
 
 
 def test_infer_call_surface():

@@ -169,5 +169,56 @@ def test_bn_train_is_deterministic_and_falls_back_outside_its_domain():
     cpu = BatchNorm2d(3).train()
     assert cpu(torch.randn(2, 3, 4, 4)).shape == (2, 3, 4, 4)      # CPU tensors: parent class (boundary tests use it)
     l = _lib.lib()
-    assert l.isg_bn_train_forward(None, 0, 1, 1, 1, None, None, None, None, 0.1, 1e-5, None, None, None, None, None) != 0
+    assert l.isg_bn_train_forward(None, 0, 1, 1, 1, None, None, None, None, None, 0.1, 1e-5, 0, None, 0, None, None,
+                                  None, None, None) != 0
     assert b"null" in l.isg_last_error()
+
+
+@pytest.mark.parametrize("act", ["prelu", "relu", "none"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_conv_bn_act_block_matches_the_literal_sequence(act, dtype):
+    """the reference's Conv block act(bn(conv(x))) (segment.py:34-48) in train mode: the native path (conv without
+    its bias, BatchNorm + activation fused, forward and backward) against the same modules evaluated literally in
+    float64 on CPU -- output, input gradient, every parameter gradient, running statistics"""
+    import copy
+    from instancesegmentation_b200.segment import _Unit
+    torch.manual_seed(7)
+    u = _Unit(12, 24, 3, act=act if act != "none" else None)
+    with torch.no_grad():
+        u.conv.bias.normal_(0, 2.0)          # a bias the normalisation has to cancel
+        u.bn.weight.uniform_(0.5, 1.5)
+        u.bn.bias.normal_()
+        if act == "prelu":
+            u.act.weight.uniform_(0.05, 0.5)
+    ref = copy.deepcopy(u).double().train()
+    x = torch.randn(4, 12, 24, 40)
+    dy = torch.randn(4, 24, 24, 40)
+    xr = x.double().requires_grad_(True)
+    yr = ref(xr)
+    yr.backward(dy.double())
+    g = u.cuda().train()
+    xg = x.cuda().requires_grad_(True)
+    if dtype == torch.bfloat16:
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            yg = g(xg)
+    else:
+        yg = g(xg)
+    assert yg.dtype == dtype
+    yg.backward(dy.cuda().to(dtype))
+    tol = 2e-5 if dtype == torch.float32 else 3e-2     # bf16: conv inputs, weights and activations rounded to 8 bits
+
+    def close(a, r, t=tol):
+        a, r = a.double().cpu(), r.double()
+        assert float((a - r).abs().max()) <= t * max(float(r.abs().max()), 1e-3), float((a - r).abs().max())
+
+    close(yg, yr.detach())
+    close(xg.grad, xr.grad)
+    close(g.conv.weight.grad, ref.conv.weight.grad, tol * 5)
+    close(g.bn.weight.grad, ref.bn.weight.grad, tol * 5)
+    close(g.bn.bias.grad, ref.bn.bias.grad, tol * 5)
+    if act == "prelu":
+        close(g.act.weight.grad, ref.act.weight.grad, tol * 5)
+    # the conv bias: analytically zero gradient (the literal sequence produces rounding noise there), not computed
+    assert g.conv.bias.grad is None and float(ref.conv.bias.grad.abs().max()) < 1e-9
+    close(g.bn.running_mean, ref.bn.running_mean, 1e-5 if dtype == torch.float32 else 1e-2)
+    close(g.bn.running_var, ref.bn.running_var, 1e-5 if dtype == torch.float32 else 2e-2)
