@@ -10,6 +10,8 @@ from instancesegmentation_b200 import Segment, synth  # noqa: E402
 from instancesegmentation_b200.train_step import FlatBucket, bce_sigmoid_loss  # noqa: E402
 
 cl = len(sys.argv) > 1 and sys.argv[1] == "channels_last"
+if len(sys.argv) > 1 and sys.argv[1] == "benchmark":
+    torch.backends.cudnn.benchmark = True
 dev = torch.device("cuda")
 torch.manual_seed(0)
 model = Segment(3).to(dev).train()
@@ -28,7 +30,7 @@ def step():
     loss.backward()
 
 
-for _ in range(3):
+for _ in range(6):
     step()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
