@@ -200,9 +200,6 @@ def test_conv_bn_act_block_matches_the_literal_sequence(act, dtype):
     ref = copy.deepcopy(u).double().train()
     x = torch.randn(4, 12, 24, 40)
     dy = torch.randn(4, 24, 24, 40)
-    xr = x.double().requires_grad_(True)
-    yr = ref(xr)
-    yr.backward(dy.double())
     g = u.cuda().train()
     xg = x.cuda().requires_grad_(True)
     tf32 = torch.backends.cudnn.allow_tf32
@@ -215,6 +212,16 @@ def test_conv_bn_act_block_matches_the_literal_sequence(act, dtype):
     assert yg.dtype == dtype
     yg.backward(dy.cuda().to(dtype))
     torch.backends.cudnn.allow_tf32 = tf32
+    # literal sequence in float64.  The activation's branch (z > 0) is taken from the device result: rounding moves a few
+    # z across 0 (|z| tiny there, so y still agrees) and the gradient of those elements follows the branch actually taken
+    xr = x.double().requires_grad_(True)
+    z = ref.bn(ref.conv(xr))
+    if act == "none":
+        yr = z
+    else:
+        slope = ref.act.weight.view(1, -1, 1, 1) if act == "prelu" else 0.0
+        yr = torch.where(yg.detach().cpu() > 0, z, z * slope)
+    yr.backward(dy.double())
     tol = 2e-5 if dtype == torch.float32 else 3e-2     # bf16: conv inputs, weights and activations rounded to 8 bits
 
     def close(a, r, t=tol):
@@ -222,14 +229,7 @@ def test_conv_bn_act_block_matches_the_literal_sequence(act, dtype):
         assert float((a - r).abs().max()) <= t * max(float(r.abs().max()), 1e-3), float((a - r).abs().max())
 
     close(yg, yr.detach())
-    if dtype == torch.bfloat16 and act != "none":
-        # 8-bit rounding moves z = bn(conv(x)) across 0 for a few elements, whose activation gradient then flips
-        # (any bf16 execution of the literal sequence does the same): bound the bulk, not the maximum
-        d = (xg.grad.double().cpu() - xr.grad).abs().flatten()
-        scale = float(xr.grad.abs().max())
-        assert float(d.mean()) <= 4e-3 * scale and float(torch.quantile(d, 0.99)) <= tol * scale
-    else:
-        close(xg.grad, xr.grad)
+    close(xg.grad, xr.grad)
     close(g.conv.weight.grad, ref.conv.weight.grad, tol * 5)
     close(g.bn.weight.grad, ref.bn.weight.grad, tol * 5)
     close(g.bn.bias.grad, ref.bn.bias.grad, tol * 5)
