@@ -78,21 +78,23 @@ constexpr int BN_MAX_SPLIT = 64;
 
 template <typename T, int V> struct VecIO;
 template <> struct VecIO<float, 4> {
-    static __device__ __forceinline__ void load(const float* p, float (&v)[4]) {
-        const float4 a = *reinterpret_cast<const float4*>(p);
-        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-    }
+    typedef float4 Raw;
+    static __device__ __forceinline__ Raw ldraw(const float* p) { return *reinterpret_cast<const float4*>(p); }
+    static __device__ __forceinline__ void unpack(const Raw& a, float (&v)[4]) { v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; }
     static __device__ __forceinline__ void store(float* p, const float (&v)[4]) {
         *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
     }
 };
 template <> struct VecIO<float, 1> {
-    static __device__ __forceinline__ void load(const float* p, float (&v)[1]) { v[0] = *p; }
+    typedef float Raw;
+    static __device__ __forceinline__ Raw ldraw(const float* p) { return *p; }
+    static __device__ __forceinline__ void unpack(const Raw& a, float (&v)[1]) { v[0] = a; }
     static __device__ __forceinline__ void store(float* p, const float (&v)[1]) { *p = v[0]; }
 };
 template <> struct VecIO<__nv_bfloat16, 8> {
-    static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&v)[8]) {
-        const uint4 a = *reinterpret_cast<const uint4*>(p);
+    typedef uint4 Raw;
+    static __device__ __forceinline__ Raw ldraw(const __nv_bfloat16* p) { return *reinterpret_cast<const uint4*>(p); }
+    static __device__ __forceinline__ void unpack(const Raw& a, float (&v)[8]) {
         const unsigned w[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -111,7 +113,9 @@ template <> struct VecIO<__nv_bfloat16, 8> {
     }
 };
 template <> struct VecIO<__nv_bfloat16, 1> {
-    static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&v)[1]) { v[0] = __bfloat162float(*p); }
+    typedef __nv_bfloat16 Raw;
+    static __device__ __forceinline__ Raw ldraw(const __nv_bfloat16* p) { return *p; }
+    static __device__ __forceinline__ void unpack(const Raw& a, float (&v)[1]) { v[0] = __bfloat162float(a); }
     static __device__ __forceinline__ void store(__nv_bfloat16* p, const float (&v)[1]) { *p = __float2bfloat16_rn(v[0]); }
 };
 
@@ -124,6 +128,16 @@ __device__ __forceinline__ void bn_range(unsigned n_vec, unsigned& lo, unsigned&
     lo = min(n_vec, blockIdx.x * per);
     hi = min(n_vec, lo + per);
 }
+
+// element offset of vector i of channel c: planes of HW elements, batch stride C*HW (hw_shift >= 0: HW is a power of two)
+template <int V>
+__device__ __forceinline__ size_t bn_at(unsigned i, int c, int C, unsigned HW, int hw_shift) {
+    const unsigned e = i * V;
+    const unsigned b = hw_shift >= 0 ? e >> hw_shift : e / HW;
+    return ((size_t)b * C + c) * HW + (e - b * HW);
+}
+constexpr int BN_U1 = 4;   // independent 16-byte loads in flight per thread, one-tensor kernels
+constexpr int BN_U2 = 2;   // two-tensor kernels (dy and x)
 
 // block-wide sums of N doubles in a fixed order; valid in thread 0
 template <int N>
@@ -177,18 +191,25 @@ __device__ __forceinline__ float act_bwd(float z, float g, int act, float slope)
 
 template <typename T, int V>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_stats_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, double* __restrict__ part) {
+bn_stats_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, int hw_shift, double* __restrict__ part) {
     const int c = blockIdx.y;
     const float shift = to_float(x[(size_t)c * HW]);   // sums about the channel's first element: no cancellation in E[d^2]-E[d]^2
     unsigned lo, hi;
     bn_range(n_vec, lo, hi);
     float s1 = 0.f, s2 = 0.f;
-    for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
-        const unsigned e = i * V, b = e / HW, off = e - b * HW;
-        float v[V];
-        VecIO<T, V>::load(x + ((size_t)b * C + c) * HW + off, v);
+    for (unsigned i0 = lo + threadIdx.x; i0 < hi; i0 += BN_THREADS * BN_U1) {
+        typename VecIO<T, V>::Raw r[BN_U1];
 #pragma unroll
-        for (int k = 0; k < V; ++k) { const float d = v[k] - shift; s1 += d; s2 = fmaf(d, d, s2); }
+        for (int u = 0; u < BN_U1; ++u)
+            if (i0 + u * BN_THREADS < hi) r[u] = VecIO<T, V>::ldraw(x + bn_at<V>(i0 + u * BN_THREADS, c, C, HW, hw_shift));
+#pragma unroll
+        for (int u = 0; u < BN_U1; ++u) {
+            if (i0 + u * BN_THREADS >= hi) break;
+            float v[V];
+            VecIO<T, V>::unpack(r[u], v);
+#pragma unroll
+            for (int k = 0; k < V; ++k) { const float d = v[k] - shift; s1 += d; s2 = fmaf(d, d, s2); }
+        }
     }
     double a[2] = {s1, s2};
     block_sum<2>(a);
@@ -197,7 +218,7 @@ bn_stats_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, dou
 
 template <typename T, int V>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_apply_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, const double* __restrict__ part,
+bn_apply_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, int hw_shift, const double* __restrict__ part,
                 const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean_offset,
                 float* __restrict__ running_mean, float* __restrict__ running_var, float momentum, float eps, int act,
                 const float* __restrict__ slope, int slope_stride, T* __restrict__ y, float* __restrict__ save_mean,
@@ -226,21 +247,31 @@ bn_apply_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, con
     const float sl = (act == 2) ? slope[c * slope_stride] : 0.f;
     unsigned lo, hi;
     bn_range(n_vec, lo, hi);
-    for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
-        const unsigned e = i * V, b = e / HW, off = e - b * HW;
-        const size_t at = ((size_t)b * C + c) * HW + off;
-        float v[V];
-        VecIO<T, V>::load(x + at, v);
+    for (unsigned i0 = lo + threadIdx.x; i0 < hi; i0 += BN_THREADS * BN_U1) {
+        typename VecIO<T, V>::Raw r[BN_U1];
+        size_t at[BN_U1];
 #pragma unroll
-        for (int k = 0; k < V; ++k) v[k] = act_fwd(fmaf(v[k] - mean, scale, bt), act, sl);
-        VecIO<T, V>::store(y + at, v);
+        for (int u = 0; u < BN_U1; ++u)
+            if (i0 + u * BN_THREADS < hi) {
+                at[u] = bn_at<V>(i0 + u * BN_THREADS, c, C, HW, hw_shift);
+                r[u] = VecIO<T, V>::ldraw(x + at[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < BN_U1; ++u) {
+            if (i0 + u * BN_THREADS >= hi) break;
+            float v[V];
+            VecIO<T, V>::unpack(r[u], v);
+#pragma unroll
+            for (int k = 0; k < V; ++k) v[k] = act_fwd(fmaf(v[k] - mean, scale, bt), act, sl);
+            VecIO<T, V>::store(y + at[u], v);
+        }
     }
 }
 
 // sums over one channel of: gz, gz * (x - mean), and (PReLU) dy * z where z <= 0;  gz = dy * act'(z), z = bn(x)
 template <typename T, int V>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec,
+bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, int hw_shift,
                      const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ save_mean,
                      const float* __restrict__ save_invstd, int act, const float* __restrict__ slope, int slope_stride,
                      double* __restrict__ part) {
@@ -251,23 +282,33 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, u
     unsigned lo, hi;
     bn_range(n_vec, lo, hi);
     float s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
-        const unsigned e = i * V, b = e / HW, off = e - b * HW;
-        const size_t at = ((size_t)b * C + c) * HW + off;
-        float g[V], v[V];
-        VecIO<T, V>::load(dy + at, g);
-        VecIO<T, V>::load(x + at, v);
+    for (unsigned i0 = lo + threadIdx.x; i0 < hi; i0 += BN_THREADS * BN_U2) {
+        typename VecIO<T, V>::Raw rg[BN_U2], rx[BN_U2];
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-            const float xm = v[k] - mean;
-            float gz = g[k];
-            if (act) {
-                const float z = fmaf(xm, scale, bt);
-                gz = act_bwd(z, g[k], act, sl);
-                if (act == 2 && !(z > 0.f)) s3 = fmaf(g[k], z, s3);
+        for (int u = 0; u < BN_U2; ++u)
+            if (i0 + u * BN_THREADS < hi) {
+                const size_t at = bn_at<V>(i0 + u * BN_THREADS, c, C, HW, hw_shift);
+                rg[u] = VecIO<T, V>::ldraw(dy + at);
+                rx[u] = VecIO<T, V>::ldraw(x + at);
             }
-            s1 += gz;
-            s2 = fmaf(gz, xm, s2);
+#pragma unroll
+        for (int u = 0; u < BN_U2; ++u) {
+            if (i0 + u * BN_THREADS >= hi) break;
+            float g[V], v[V];
+            VecIO<T, V>::unpack(rg[u], g);
+            VecIO<T, V>::unpack(rx[u], v);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                const float xm = v[k] - mean;
+                float gz = g[k];
+                if (act) {
+                    const float z = fmaf(xm, scale, bt);
+                    gz = act_bwd(z, g[k], act, sl);
+                    if (act == 2 && !(z > 0.f)) s3 = fmaf(g[k], z, s3);
+                }
+                s1 += gz;
+                s2 = fmaf(gz, xm, s2);
+            }
         }
     }
     double a[3] = {s1, s2, s3};
@@ -277,7 +318,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, u
 
 template <typename T, int V>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec,
+bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, int hw_shift,
                     const double* __restrict__ part, const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ save_mean, const float* __restrict__ save_invstd, int act,
                     const float* __restrict__ slope, int slope_stride, T* __restrict__ dx, float* __restrict__ dgamma,
@@ -300,19 +341,30 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, un
     const float sl = (act == 2) ? slope[c * slope_stride] : 0.f;
     unsigned lo, hi;
     bn_range(n_vec, lo, hi);
-    for (unsigned i = lo + threadIdx.x; i < hi; i += BN_THREADS) {
-        const unsigned e = i * V, b = e / HW, off = e - b * HW;
-        const size_t at = ((size_t)b * C + c) * HW + off;
-        float gy[V], v[V];
-        VecIO<T, V>::load(dy + at, gy);
-        VecIO<T, V>::load(x + at, v);
+    for (unsigned i0 = lo + threadIdx.x; i0 < hi; i0 += BN_THREADS * BN_U2) {
+        typename VecIO<T, V>::Raw rg[BN_U2], rx[BN_U2];
+        size_t at[BN_U2];
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-            const float xm = v[k] - mean;
-            const float gz = act ? act_bwd(fmaf(xm, gs, bt), gy[k], act, sl) : gy[k];
-            v[k] = (gz - k1 - xm * k2) * gs;
+        for (int u = 0; u < BN_U2; ++u)
+            if (i0 + u * BN_THREADS < hi) {
+                at[u] = bn_at<V>(i0 + u * BN_THREADS, c, C, HW, hw_shift);
+                rg[u] = VecIO<T, V>::ldraw(dy + at[u]);
+                rx[u] = VecIO<T, V>::ldraw(x + at[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < BN_U2; ++u) {
+            if (i0 + u * BN_THREADS >= hi) break;
+            float gy[V], v[V];
+            VecIO<T, V>::unpack(rg[u], gy);
+            VecIO<T, V>::unpack(rx[u], v);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                const float xm = v[k] - mean;
+                const float gz = act ? act_bwd(fmaf(xm, gs, bt), gy[k], act, sl) : gy[k];
+                v[k] = (gz - k1 - xm * k2) * gs;
+            }
+            VecIO<T, V>::store(dx + at[u], v);
         }
-        VecIO<T, V>::store(dx + at, v);
     }
 }
 
@@ -396,13 +448,15 @@ int isg_bn_train_forward(const void* x_dev, int bf16, int batch, int channels, i
     double* part = static_cast<double*>(workspace_dev);
     const bool wide = bn_wide(bf16, hw, x_dev, y_dev, nullptr);
     const unsigned HW = (unsigned)hw;
+    int hs = -1;
+    if ((hw & (hw - 1)) == 0) { hs = 0; while ((1ll << hs) < hw) ++hs; }
     const int sstride = slope_count == 1 ? 0 : 1;
 #define ISG_BN_FWD(T, V)                                                                                              \
     do {                                                                                                              \
         const unsigned n_vec = (unsigned)((int64_t)batch * hw / V);                                                   \
         dim3 grid(bn_split(channels, n_vec), channels);                                                               \
-        bn_stats_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, part);  \
-        bn_apply_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, part,   \
+        bn_stats_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, hs, part);   \
+        bn_apply_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, hs, part,   \
                                                            gamma_dev, beta_dev, mean_offset_dev, running_mean_dev,    \
                                                            running_var_dev, momentum, eps, act, slope_dev, sstride,   \
                                                            static_cast<T*>(y_dev), save_mean_dev, save_invstd_dev);   \
@@ -425,17 +479,19 @@ int isg_bn_train_backward(const void* dy_dev, const void* x_dev, int bf16, int b
     double* part = static_cast<double*>(workspace_dev);
     const bool wide = bn_wide(bf16, hw, dy_dev, x_dev, dx_dev);
     const unsigned HW = (unsigned)hw;
+    int hs = -1;
+    if ((hw & (hw - 1)) == 0) { hs = 0; while ((1ll << hs) < hw) ++hs; }
     const int sstride = slope_count == 1 ? 0 : 1;
 #define ISG_BN_BWD(T, V)                                                                                              \
     do {                                                                                                              \
         const unsigned n_vec = (unsigned)((int64_t)batch * hw / V);                                                   \
         dim3 grid(bn_split(channels, n_vec), channels);                                                               \
         bn_bwd_reduce_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(dy_dev),                        \
-                                                                static_cast<const T*>(x_dev), channels, HW, n_vec,    \
+                                                                static_cast<const T*>(x_dev), channels, HW, n_vec, hs,\
                                                                 gamma_dev, beta_dev, save_mean_dev, save_invstd_dev,  \
                                                                 act, slope_dev, sstride, part);                       \
         bn_bwd_apply_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(dy_dev),                         \
-                                                               static_cast<const T*>(x_dev), channels, HW, n_vec,     \
+                                                               static_cast<const T*>(x_dev), channels, HW, n_vec, hs, \
                                                                part, gamma_dev, beta_dev, save_mean_dev,              \
                                                                save_invstd_dev, act, slope_dev, sstride,              \
                                                                static_cast<T*>(dx_dev), dgamma_dev, dbeta_dev,        \
