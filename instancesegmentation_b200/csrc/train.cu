@@ -7,6 +7,8 @@
 // The sum is deterministic: a fixed grid, every block adds its elements in a fixed order in double, the last
 // block to finish (ticket) adds the per-block partials in index order and resets the ticket.
 #include <cmath>
+#include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 
@@ -368,6 +370,229 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, un
     }
 }
 
+// ---- one launch per op: a thread-block cluster per channel --------------------------------------------------------
+// grid (CL, channels), cluster (CL,1,1): the CL CTAs of a cluster split one channel, leave their partial sums in their own
+// shared memory, meet at a cluster barrier, read each other's partials through distributed shared memory (fixed rank
+// order -> deterministic, every CTA gets bit-identical totals) and go straight on to the normalisation pass, whose
+// re-read of x (and dy) is served by L2 for the layer sizes of this network.  No global partials, no second launch.
+constexpr int BN_CL_MAX = 8;
+constexpr int BN_CL_MAX_THREADS = 1024;
+
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ double ld_dsmem_f64(const double* local, unsigned rank) {
+    unsigned a = (unsigned)__cvta_generic_to_shared(local), ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(rank));
+    double v;
+    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(ra) : "memory");
+    return v;
+}
+
+// sums of N per-thread values over the whole cluster (all CTAs, all threads get the same totals)
+template <int N>
+__device__ __forceinline__ void cluster_sum(double (&a)[N]) {
+    __shared__ double warp_part[N][BN_CL_MAX_THREADS / 32];
+    __shared__ double cta_part[N];
+    const int nwarp = blockDim.x >> 5;
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+        for (int o = 16; o; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) warp_part[k][threadIdx.x >> 5] = a[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < N) {
+        double t = 0.0;
+        for (int w = 0; w < nwarp; ++w) t += warp_part[threadIdx.x][w];
+        cta_part[threadIdx.x] = t;
+    }
+    cluster_sync_all();                       // every CTA's cta_part is written and visible cluster-wide
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        double t = 0.0;
+        for (unsigned r = 0; r < gridDim.x; ++r) t += ld_dsmem_f64(&cta_part[k], r);
+        a[k] = t;
+    }
+    cluster_sync_all();                       // nobody leaves (or reuses cta_part) while a peer still reads it
+}
+
+template <typename T, int V>
+__global__ void __launch_bounds__(BN_CL_MAX_THREADS)
+bn_fwd_cluster_kernel(const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, int hw_shift,
+                      const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean_offset,
+                      float* __restrict__ running_mean, float* __restrict__ running_var, float momentum, float eps, int act,
+                      const float* __restrict__ slope, int slope_stride, T* __restrict__ y, float* __restrict__ save_mean,
+                      float* __restrict__ save_invstd) {
+    const int c = blockIdx.y;
+    const unsigned nthr = blockDim.x;
+    const float shift = to_float(x[(size_t)c * HW]);
+    unsigned lo, hi;
+    bn_range(n_vec, lo, hi);
+    float s1 = 0.f, s2 = 0.f;
+    for (unsigned i0 = lo + threadIdx.x; i0 < hi; i0 += nthr * BN_U1) {
+        typename VecIO<T, V>::Raw r[BN_U1];
+#pragma unroll
+        for (int u = 0; u < BN_U1; ++u)
+            if (i0 + u * nthr < hi) r[u] = VecIO<T, V>::ldraw(x + bn_at<V>(i0 + u * nthr, c, C, HW, hw_shift));
+#pragma unroll
+        for (int u = 0; u < BN_U1; ++u) {
+            if (i0 + u * nthr >= hi) break;
+            float v[V];
+            VecIO<T, V>::unpack(r[u], v);
+#pragma unroll
+            for (int k = 0; k < V; ++k) { const float d = v[k] - shift; s1 += d; s2 = fmaf(d, d, s2); }
+        }
+    }
+    double s[2] = {s1, s2};
+    cluster_sum<2>(s);
+    const double n = (double)n_vec * V;
+    const double dm = s[0] / n;
+    const double var = fmax(s[1] / n - dm * dm, 0.0);
+    const float mean = (float)((double)shift + dm);
+    const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        save_mean[c] = mean;
+        save_invstd[c] = invstd;
+        const float m_full = mean + (mean_offset ? mean_offset[c] : 0.f);
+        if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m_full;
+        if (running_var) {
+            const float unbiased = (float)(n > 1.0 ? var * n / (n - 1.0) : var);
+            running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+        }
+    }
+    const float g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+    const float scale = g * invstd;
+    const float sl = (act == 2) ? slope[c * slope_stride] : 0.f;
+    for (unsigned i0 = lo + threadIdx.x; i0 < hi; i0 += nthr * BN_U1) {
+        typename VecIO<T, V>::Raw r[BN_U1];
+        size_t at[BN_U1];
+#pragma unroll
+        for (int u = 0; u < BN_U1; ++u)
+            if (i0 + u * nthr < hi) {
+                at[u] = bn_at<V>(i0 + u * nthr, c, C, HW, hw_shift);
+                r[u] = VecIO<T, V>::ldraw(x + at[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < BN_U1; ++u) {
+            if (i0 + u * nthr >= hi) break;
+            float v[V];
+            VecIO<T, V>::unpack(r[u], v);
+#pragma unroll
+            for (int k = 0; k < V; ++k) v[k] = act_fwd(fmaf(v[k] - mean, scale, bt), act, sl);
+            VecIO<T, V>::store(y + at[u], v);
+        }
+    }
+}
+
+template <typename T, int V>
+__global__ void __launch_bounds__(BN_CL_MAX_THREADS)
+bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, int C, unsigned HW, unsigned n_vec, int hw_shift,
+                      const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ save_mean,
+                      const float* __restrict__ save_invstd, int act, const float* __restrict__ slope, int slope_stride,
+                      T* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dslope) {
+    const int c = blockIdx.y;
+    const unsigned nthr = blockDim.x;
+    const float mean = save_mean[c], invstd = save_invstd[c];
+    const float g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+    const float gs = g * invstd;
+    const float sl = (act == 2) ? slope[c * slope_stride] : 0.f;
+    unsigned lo, hi;
+    bn_range(n_vec, lo, hi);
+    float s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    for (unsigned i0 = lo + threadIdx.x; i0 < hi; i0 += nthr * BN_U2) {
+        typename VecIO<T, V>::Raw rg[BN_U2], rx[BN_U2];
+#pragma unroll
+        for (int u = 0; u < BN_U2; ++u)
+            if (i0 + u * nthr < hi) {
+                const size_t at = bn_at<V>(i0 + u * nthr, c, C, HW, hw_shift);
+                rg[u] = VecIO<T, V>::ldraw(dy + at);
+                rx[u] = VecIO<T, V>::ldraw(x + at);
+            }
+#pragma unroll
+        for (int u = 0; u < BN_U2; ++u) {
+            if (i0 + u * nthr >= hi) break;
+            float gy[V], v[V];
+            VecIO<T, V>::unpack(rg[u], gy);
+            VecIO<T, V>::unpack(rx[u], v);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                const float xm = v[k] - mean;
+                float gz = gy[k];
+                if (act) {
+                    const float z = fmaf(xm, gs, bt);
+                    gz = act_bwd(z, gy[k], act, sl);
+                    if (act == 2 && !(z > 0.f)) s3 = fmaf(gy[k], z, s3);
+                }
+                s1 += gz;
+                s2 = fmaf(gz, xm, s2);
+            }
+        }
+    }
+    double s[3] = {s1, s2, s3};
+    cluster_sum<3>(s);
+    const double n = (double)n_vec * V;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (dgamma) dgamma[c] = (float)(s[1] * (double)invstd);
+        if (dbeta) dbeta[c] = (float)s[0];
+        if (dslope) dslope[c] = (float)s[2];
+    }
+    if (!dx) return;
+    const float k1 = (float)(s[0] / n);
+    const float k2 = (float)(s[1] * (double)invstd * (double)invstd / n);
+    for (unsigned i0 = lo + threadIdx.x; i0 < hi; i0 += nthr * BN_U2) {
+        typename VecIO<T, V>::Raw rg[BN_U2], rx[BN_U2];
+        size_t at[BN_U2];
+#pragma unroll
+        for (int u = 0; u < BN_U2; ++u)
+            if (i0 + u * nthr < hi) {
+                at[u] = bn_at<V>(i0 + u * nthr, c, C, HW, hw_shift);
+                rg[u] = VecIO<T, V>::ldraw(dy + at[u]);
+                rx[u] = VecIO<T, V>::ldraw(x + at[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < BN_U2; ++u) {
+            if (i0 + u * nthr >= hi) break;
+            float gy[V], v[V];
+            VecIO<T, V>::unpack(rg[u], gy);
+            VecIO<T, V>::unpack(rx[u], v);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                const float xm = v[k] - mean;
+                const float gz = act ? act_bwd(fmaf(xm, gs, bt), gy[k], act, sl) : gy[k];
+                v[k] = (gz - k1 - xm * k2) * gs;
+            }
+            VecIO<T, V>::store(dx + at[u], v);
+        }
+    }
+}
+
+// cluster size and CTA size for n_vec vectors per channel: aim at >= 4 vectors per thread, then as wide as allowed
+inline void bn_cluster_shape(unsigned n_vec, int channels, int* cl, int* threads) {
+    int t = 256;
+    int c = 1;
+    while (c < BN_CL_MAX && (unsigned)(c * t * 4) < n_vec) c *= 2;
+    while (t < BN_CL_MAX_THREADS && (unsigned)(c * t * 8) < n_vec) t *= 2;
+    // few channels: keep the machine busy with more, smaller CTAs rather than one fat CTA per SM
+    (void)channels;
+    *cl = c; *threads = t;
+}
+
+template <typename K, typename... Args>
+inline cudaError_t launch_cluster(K kernel, int cl, int channels, int threads, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(cl, channels);
+    cfg.blockDim = dim3(threads);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
 inline int bn_split(int channels, unsigned n_vec) {
     int s = (148 * 8 + channels - 1) / channels;                     // ~8 blocks per SM over all channels
     const unsigned by_work = (n_vec + BN_THREADS * 2 - 1) / (BN_THREADS * 2);   // at least two vectors per thread
@@ -448,12 +673,24 @@ int isg_bn_train_forward(const void* x_dev, int bf16, int batch, int channels, i
     double* part = static_cast<double*>(workspace_dev);
     const bool wide = bn_wide(bf16, hw, x_dev, y_dev, nullptr);
     const unsigned HW = (unsigned)hw;
+    // one cluster launch, except for planes so large that 8 CTAs per channel cannot stream them as fast as the
+    // many-block two-launch kernels do (measured: 33.6 MB / 16 channels 36 vs 27 us); ISG_BN_TWO_PASS / ISG_BN_CLUSTER force
+    const bool two_pass = getenv("ISG_BN_TWO_PASS") || (!getenv("ISG_BN_CLUSTER") && (int64_t)batch * hw > (bf16 ? 65536 * 8 : 65536 * 4));
     int hs = -1;
     if ((hw & (hw - 1)) == 0) { hs = 0; while ((1ll << hs) < hw) ++hs; }
     const int sstride = slope_count == 1 ? 0 : 1;
 #define ISG_BN_FWD(T, V)                                                                                              \
     do {                                                                                                              \
         const unsigned n_vec = (unsigned)((int64_t)batch * hw / V);                                                   \
+        if (!two_pass) {                                                                                              \
+            int cl, threads;                                                                                          \
+            bn_cluster_shape(n_vec, channels, &cl, &threads);                                                         \
+            ISG_CUDA(launch_cluster(bn_fwd_cluster_kernel<T, V>, cl, channels, threads, st,                           \
+                                    static_cast<const T*>(x_dev), channels, HW, n_vec, hs, gamma_dev, beta_dev,       \
+                                    mean_offset_dev, running_mean_dev, running_var_dev, momentum, eps, act, slope_dev,\
+                                    sstride, static_cast<T*>(y_dev), save_mean_dev, save_invstd_dev));                \
+            break;                                                                                                    \
+        }                                                                                                             \
         dim3 grid(bn_split(channels, n_vec), channels);                                                               \
         bn_stats_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, hs, part);   \
         bn_apply_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(x_dev), channels, HW, n_vec, hs, part,   \
@@ -479,12 +716,24 @@ int isg_bn_train_backward(const void* dy_dev, const void* x_dev, int bf16, int b
     double* part = static_cast<double*>(workspace_dev);
     const bool wide = bn_wide(bf16, hw, dy_dev, x_dev, dx_dev);
     const unsigned HW = (unsigned)hw;
+    // one cluster launch, except for planes so large that 8 CTAs per channel cannot stream them as fast as the
+    // many-block two-launch kernels do (measured: 33.6 MB / 16 channels 36 vs 27 us); ISG_BN_TWO_PASS / ISG_BN_CLUSTER force
+    const bool two_pass = getenv("ISG_BN_TWO_PASS") || (!getenv("ISG_BN_CLUSTER") && (int64_t)batch * hw > (bf16 ? 65536 * 8 : 65536 * 4));
     int hs = -1;
     if ((hw & (hw - 1)) == 0) { hs = 0; while ((1ll << hs) < hw) ++hs; }
     const int sstride = slope_count == 1 ? 0 : 1;
 #define ISG_BN_BWD(T, V)                                                                                              \
     do {                                                                                                              \
         const unsigned n_vec = (unsigned)((int64_t)batch * hw / V);                                                   \
+        if (!two_pass) {                                                                                              \
+            int cl, threads;                                                                                          \
+            bn_cluster_shape(n_vec, channels, &cl, &threads);                                                         \
+            ISG_CUDA(launch_cluster(bn_bwd_cluster_kernel<T, V>, cl, channels, threads, st,                           \
+                                    static_cast<const T*>(dy_dev), static_cast<const T*>(x_dev), channels, HW, n_vec, \
+                                    hs, gamma_dev, beta_dev, save_mean_dev, save_invstd_dev, act, slope_dev, sstride, \
+                                    static_cast<T*>(dx_dev), dgamma_dev, dbeta_dev, dslope_dev));                     \
+            break;                                                                                                    \
+        }                                                                                                             \
         dim3 grid(bn_split(channels, n_vec), channels);                                                               \
         bn_bwd_reduce_kernel<T, V><<<grid, BN_THREADS, 0, st>>>(static_cast<const T*>(dy_dev),                        \
                                                                 static_cast<const T*>(x_dev), channels, HW, n_vec, hs,\

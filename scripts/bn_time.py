@@ -12,7 +12,8 @@ sys.path.insert(0, ".")
 from instancesegmentation_b200 import _lib  # noqa: E402
 
 once = len(sys.argv) > 1 and sys.argv[1] == "once"
-shapes = [(16, 16, 256, 256)] if once else [(16, 16, 256, 256), (16, 16, 128, 128), (16, 48, 64, 64), (16, 128, 32, 32)]
+shapes = [(16, 16, 256, 256)] if once else [(16, 16, 256, 256), (16, 16, 128, 128), (16, 48, 64, 64), (16, 128, 32, 32),
+                                             (16, 4, 128, 128), (16, 48, 128, 128)]
 try:
     peak = json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"]
 except Exception:

@@ -123,8 +123,15 @@ def _bn_reference(x, gamma, beta, dy, eps=1e-5, momentum=0.1):
 
 @pytest.mark.parametrize("shape", [(16, 16, 64, 64), (2, 48, 16, 16), (3, 19, 7, 9), (1, 4, 1, 2), (4, 128, 32, 32)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_bn_train_matches_torch_float64(shape, dtype):
+@pytest.mark.parametrize("two_pass", [False, True])
+def test_bn_train_matches_torch_float64(shape, dtype, two_pass, monkeypatch):
+    """two_pass=False: one launch per op, a thread-block cluster per channel (partials through DSMEM);
+    True: the two-launch kernels with global partials (ISG_BN_TWO_PASS=1)"""
     from instancesegmentation_b200.bn import BatchNorm2d
+    if two_pass:
+        monkeypatch.setenv("ISG_BN_TWO_PASS", "1")
+    else:
+        monkeypatch.delenv("ISG_BN_TWO_PASS", raising=False)
     torch.manual_seed(sum(shape))
     C = shape[1]
     # per-channel means up to 12 sigma away from zero (the shifted sums must not cancel); the 2-element case keeps small
