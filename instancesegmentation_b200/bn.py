@@ -3,6 +3,8 @@ train_instance.py:372) in libisg: batch statistics, normalisation, running-stat 
 follows it in the block (segment.py:42-45) and the backward of both, as four streaming kernels
 (``isg_bn_train_forward`` / ``isg_bn_train_backward``).  Same module class, same ``state_dict`` keys; eval mode
 is folded into the conv weights by the engine and never comes here."""
+import os
+
 import torch
 import torch.nn.functional as F
 from torch import nn
@@ -70,6 +72,8 @@ class BatchNorm2d(nn.BatchNorm2d):
     averaging (``momentum=None``), other dtypes -- is the parent class unchanged."""
 
     def native(self, x):
+        if os.environ.get("ISG_BN_LIBRARY"):      # A/B switch: the parent class's library kernels
+            return False
         return bool(self.training and x.is_cuda and x.dim() == 4 and self.momentum is not None
                     and self.track_running_stats and x.dtype in (torch.float32, torch.bfloat16) and x.numel() > 0)
 
@@ -99,10 +103,12 @@ def conv_bn_act(conv, bn, act, x):
     """The reference's ``Conv.forward`` (segment.py:47-48): ``act(bn(conv(x)))``.  On the native train path the conv
     runs without its bias (it cancels in the normalisation; ``ISG_TRAIN_KEEP_CONV_BIAS=1`` keeps the literal
     sequence) and BatchNorm + activation are one forward and one backward kernel pair."""
-    import os
     if (isinstance(bn, BatchNorm2d) and bn.training and x.is_cuda and bn.momentum is not None and bn.track_running_stats
             and conv.padding_mode == "zeros" and not os.environ.get("ISG_TRAIN_KEEP_CONV_BIAS")):
-        z = F.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
+        if hasattr(conv, "conv"):            # dwconv.DepthwiseConv2d: native stencil kernels
+            z = conv.conv(x, with_bias=False)
+        else:
+            z = F.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
         if bn.native(z):
             return bn.fused(z, conv.bias, act)
         if conv.bias is not None:

@@ -22,6 +22,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .bn import BatchNorm2d, conv_bn_act
+from .dwconv import DepthwiseConv2d
 
 __all__ = ["Segment", "topology"]
 
@@ -69,7 +70,8 @@ class _Unit(nn.Module):
         if p is None:
             p = k // 2 if isinstance(k, int) else tuple(v // 2 for v in k)
         a = _act(act, cout)  # constructed first, like the reference's call sites
-        self.conv = nn.Conv2d(cin, cout, k, s, p, groups=g, dilation=d, bias=True)
+        conv_cls = DepthwiseConv2d if (g > 1 and g == cin == cout) else nn.Conv2d
+        self.conv = conv_cls(cin, cout, k, s, p, groups=g, dilation=d, bias=True)
         self.bn = BatchNorm2d(cout)
         self.act = a
 
@@ -99,7 +101,7 @@ class _Block(nn.Module):
         elif kind == "res5":  # Bottleneck5x5, segment.py:82-111
             c, m = a["c"], a["mid"]
             self.convs = _seq(_Unit(c, m, 1, act="prelu"),
-                              nn.Conv2d(m, m, (5, 1), padding=(2, 0), groups=m),
+                              DepthwiseConv2d(m, m, (5, 1), padding=(2, 0), groups=m),
                               _Unit(m, m, (1, 5), p=(0, 2), g=m, act="prelu"),
                               _Unit(m, c, 1))
             self.prelu = nn.PReLU(c)

@@ -20,10 +20,17 @@ x = torch.from_numpy(synth.batch(16, 512, 512, seed=1)).to(dev)
 y = (torch.from_numpy(synth.logits(16, 512, 512, seed=2)) > 0.8).float()[:, None].to(dev)
 if cl:
     x = x.contiguous(memory_format=torch.channels_last)
+    for prm in model.parameters():
+        if prm.dim() == 4:
+            prm.data = prm.data.contiguous(memory_format=torch.channels_last)
+    bucket = None
 
 
 def step():
-    bucket.zero_grads()
+    if bucket is not None:
+        bucket.zero_grads()
+    else:
+        model.zero_grad(set_to_none=True)
     with torch.autocast("cuda", dtype=torch.bfloat16):
         out = model(x)
     loss = bce_sigmoid_loss(out, y)

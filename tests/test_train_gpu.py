@@ -246,3 +246,45 @@ def test_conv_bn_act_block_matches_the_literal_sequence(act, dtype):
     assert g.conv.bias.grad is None and float(ref.conv.bias.grad.abs().max()) < 1e-9
     close(g.bn.running_mean, ref.bn.running_mean, 1e-5 if dtype == torch.float32 else 1e-2)
     close(g.bn.running_var, ref.bn.running_var, 1e-5 if dtype == torch.float32 else 2e-2)
+
+
+@pytest.mark.parametrize("k,d", [((3, 3), 1), ((3, 3), 2), ((3, 3), 4), ((5, 1), 1), ((1, 5), 1), ((5, 5), 1)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_depthwise_conv_matches_torch_float64(k, d, dtype):
+    """the reference's depthwise convs (segment.py:58, :93-96: groups == channels; 3x3 dil 1/2/4, (5,1), (1,5)) in train
+    mode: forward, input gradient, weight and bias gradient against F.conv2d in float64 on CPU; plane sizes that are
+    not multiples of the 16x64 tile, several tiles per plane"""
+    from instancesegmentation_b200.dwconv import DepthwiseConv2d
+    torch.manual_seed(k[0] * 10 + k[1] + d)
+    C, B, H, W = 12, 3, 37, 70
+    pad = (d * (k[0] - 1) // 2, d * (k[1] - 1) // 2)
+    m = DepthwiseConv2d(C, C, k, padding=pad, dilation=d, groups=C).cuda().train()
+    x = torch.randn(B, C, H, W)
+    dy = torch.randn(B, C, H, W)
+    if dtype == torch.bfloat16:
+        x, dy = x.to(dtype).float(), dy.to(dtype).float()     # the reference sees the same rounded inputs
+    xr = x.double().requires_grad_(True)
+    wr = m.weight.detach().double().cpu().requires_grad_(True)
+    br = m.bias.detach().double().cpu().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xr, wr, br, 1, pad, d, C)
+    yr.backward(dy.double())
+    xg = x.cuda().to(dtype).requires_grad_(True)
+    assert m.native(xg)
+    yg = m(xg)
+    yg.backward(dy.cuda().to(dtype))
+    assert yg.dtype == dtype and m.weight.grad.dtype == torch.float32
+    tol = 1e-5 if dtype == torch.float32 else 2 ** -7       # bf16: outputs rounded to 8 bits; sums accumulate in fp32
+
+    def close(a, r, t):
+        a, r = a.double().cpu(), r.double()
+        assert float((a - r).abs().max()) <= t * max(float(r.abs().max()), 1e-3), float((a - r).abs().max())
+
+    close(yg.detach(), yr.detach(), tol)
+    close(xg.grad, xr.grad, tol)
+    close(m.weight.grad, wr.grad, 1e-5)      # fp32 accumulation of exactly representable products
+    close(m.bias.grad, br.grad, 1e-5)
+    # outside its domain the parent class runs: eval mode, stride 2
+    m.eval()
+    assert not m.native(xg)
+    assert torch.allclose(m(xg.detach()).float(), yg.detach().float(), atol=5e-2 if dtype == torch.bfloat16 else 1e-4)
+    assert not DepthwiseConv2d(C, C, 3, stride=2, padding=1, groups=C).cuda().train().native(xg)
