@@ -286,5 +286,6 @@ def test_depthwise_conv_matches_torch_float64(k, d, dtype):
     # outside its domain the parent class runs: eval mode, stride 2
     m.eval()
     assert not m.native(xg)
-    assert torch.allclose(m(xg.detach()).float(), yg.detach().float(), atol=5e-2 if dtype == torch.bfloat16 else 1e-4)
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=dtype == torch.bfloat16):
+        assert torch.allclose(m(xg.detach()).float(), yg.detach().float(), atol=5e-2 if dtype == torch.bfloat16 else 1e-4)
     assert not DepthwiseConv2d(C, C, 3, stride=2, padding=1, groups=C).cuda().train().native(xg)
