@@ -212,6 +212,13 @@ ISG_API int isg_dwconv_wgrad(const void* dy_dev, const void* x_dev, int bf16, in
                      int width, int kh, int kw, int pad_h, int pad_w, int dil_h, int dil_w,
                      float* dweight_dev, float* dbias_dev, void* stream);
 
+/* ---- ConvTranspose2d forward with kernel == 2*stride, 0 <= pad < stride, cout <= 8 (segment.py:435 bottle6_1: 16 -> 4,
+ * k8 s4 p2) in train mode.  in [batch,cin,hin,win] bf16 or fp32, weight fp32 [cin,cout,k,k] (torch's layout), bias fp32
+ * [cout] or NULL, out [batch,cout,(hin-1)*s-2p+k,(win-1)*s-2p+k].  The backward of this layer stays with the library. */
+ISG_API int isg_convt_k2s_forward(const void* in_dev, int bf16, int batch, int cin, int cout, int hin, int win,
+                          int k, int s, int p, const float* weight_dev, const float* bias_dev,
+                          void* out_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

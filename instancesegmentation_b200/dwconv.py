@@ -79,3 +79,59 @@ class DepthwiseConv2d(nn.Conv2d):
 
     def forward(self, x):
         return self.conv(x, True)
+
+
+class _ConvTk2s(torch.autograd.Function):
+    """forward in libisg (``isg_convt_k2s_forward``); backward = the library's ``convolution_backward`` of the same op"""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, padding):
+        x = x.contiguous()
+        B, Cin, H, W = x.shape
+        Cout, k = weight.shape[1], weight.shape[2]
+        w32 = weight.detach().to(torch.float32).contiguous()
+        b32 = bias.detach().to(torch.float32).contiguous() if bias is not None else None
+        out = torch.empty((B, Cout, (H - 1) * stride - 2 * padding + k, (W - 1) * stride - 2 * padding + k),
+                          dtype=x.dtype, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().isg_convt_k2s_forward(
+                x.data_ptr(), int(x.dtype == torch.bfloat16), B, Cin, Cout, H, W, k, stride, padding, w32.data_ptr(),
+                _ptr(b32), out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        ctx.save_for_backward(x, weight)
+        ctx.geom = (stride, padding, bias is not None)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        stride, padding, has_bias = ctx.geom
+        w = weight.detach().to(x.dtype)
+        dy = dy.contiguous().to(x.dtype)
+        mask = [ctx.needs_input_grad[0], ctx.needs_input_grad[1], bool(has_bias and ctx.needs_input_grad[2])]
+        dx, dw, db = torch.ops.aten.convolution_backward(
+            dy, x, w, [weight.shape[1]] if has_bias else None, [stride, stride], [padding, padding], [1, 1], True, [0, 0], 1, mask)
+        if dw is not None:
+            dw = dw.to(weight.dtype)
+        if db is not None:
+            db = db.to(weight.dtype)
+        return dx, dw, db, None, None
+
+
+class ConvTranspose2dK2S(nn.ConvTranspose2d):
+    """``nn.ConvTranspose2d`` with ``kernel == 2 * stride`` (segment.py:435 ``bottle6_1``); train-mode CUDA forward in
+    libisg when it fits the kernel's domain, otherwise (and ``ISG_CT_LIBRARY=1``) the parent class."""
+
+    def native(self, x):
+        if os.environ.get("ISG_CT_LIBRARY"):
+            return False
+        k, s, p = self.kernel_size, self.stride, self.padding
+        return bool(self.training and x.is_cuda and x.dim() == 4 and x.dtype in (torch.float32, torch.bfloat16)
+                    and k[0] == k[1] and s[0] == s[1] and p[0] == p[1] and k[0] == 2 * s[0] and 0 <= p[0] < s[0]
+                    and self.groups == 1 and self.dilation == (1, 1) and self.output_padding == (0, 0)
+                    and self.out_channels <= 8 and self.in_channels * self.out_channels * k[0] * k[0] * 4 <= 40 * 1024
+                    and x.numel() > 0)
+
+    def forward(self, x, output_size=None):
+        if output_size is None and self.native(x):
+            return _ConvTk2s.apply(x, self.weight, self.bias, self.stride[0], self.padding[0])
+        return super().forward(x, output_size)

@@ -22,7 +22,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .bn import BatchNorm2d, conv_bn_act
-from .dwconv import DepthwiseConv2d
+from .dwconv import ConvTranspose2dK2S, DepthwiseConv2d
 
 __all__ = ["Segment", "topology"]
 
@@ -170,7 +170,7 @@ def _make(kind, p):
     if kind == "seq":
         return nn.Sequential(*[_Block(k, **a) for k, a in p])
     if kind == "head_up":
-        return nn.ConvTranspose2d(p["cin"], p["cout"], kernel_size=8, padding=2, stride=4)
+        return ConvTranspose2dK2S(p["cin"], p["cout"], kernel_size=8, padding=2, stride=4)
     if kind == "head_out":
         return nn.Conv2d(p["cin"], p["cout"], kernel_size=3, padding=1)
     return _Block(kind, **p)

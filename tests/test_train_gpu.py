@@ -289,3 +289,45 @@ def test_depthwise_conv_matches_torch_float64(k, d, dtype):
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=dtype == torch.bfloat16):
         assert torch.allclose(m(xg.detach()).float(), yg.detach().float(), atol=5e-2 if dtype == torch.bfloat16 else 1e-4)
     assert not DepthwiseConv2d(C, C, 3, stride=2, padding=1, groups=C).cuda().train().native(xg)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("geom", [(16, 4, 8, 4, 2), (6, 8, 4, 2, 1), (3, 2, 2, 1, 0)])
+def test_conv_transpose_k2s_matches_torch_float64(geom, dtype):
+    """bottle6_1 (segment.py:435: ConvTranspose2d(16, 4, 8, stride 4, padding 2)) and two other kernel == 2*stride shapes:
+    native forward against F.conv_transpose2d in float64; gradients (library backward of the same op) as well"""
+    from instancesegmentation_b200.dwconv import ConvTranspose2dK2S
+    cin, cout, k, s, p = geom
+    torch.manual_seed(cin + k)
+    m = ConvTranspose2dK2S(cin, cout, k, stride=s, padding=p).cuda().train()
+    x = torch.randn(2, cin, 9, 13)
+    if dtype == torch.bfloat16:
+        x = x.to(dtype).float()
+    xr = x.double().requires_grad_(True)
+    wr = m.weight.detach().double().cpu().requires_grad_(True)
+    br = m.bias.detach().double().cpu().requires_grad_(True)
+    yr = torch.nn.functional.conv_transpose2d(xr, wr, br, s, p)
+    dy = torch.randn_like(yr).float()
+    if dtype == torch.bfloat16:
+        dy = dy.to(dtype).float()
+    yr.backward(dy.double())
+    xg = x.cuda().to(dtype).requires_grad_(True)
+    assert m.native(xg)
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    yg = m(xg)
+    yg.backward(dy.cuda().to(dtype))
+    torch.backends.cudnn.allow_tf32 = tf32
+    assert yg.shape == yr.shape and yg.dtype == dtype and m.weight.grad.dtype == torch.float32
+
+    def close(a, r, t):
+        a, r = a.double().cpu(), r.double()
+        assert float((a - r).abs().max()) <= t * max(float(r.abs().max()), 1e-3), float((a - r).abs().max())
+
+    close(yg.detach(), yr.detach(), 1e-5 if dtype == torch.float32 else 2 ** -7)
+    lib_tol = 1e-4 if dtype == torch.float32 else 3e-2       # library backward; bf16: weights rounded to 8 bits there
+    close(xg.grad, xr.grad, lib_tol)
+    close(m.weight.grad, wr.grad, lib_tol)
+    close(m.bias.grad, br.grad, lib_tol)
+    m.eval()
+    assert not m.native(xg)
