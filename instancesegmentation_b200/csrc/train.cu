@@ -944,7 +944,10 @@ int isg_dwconv_wgrad(const void* dy_dev, const void* x_dev, int bf16, int batch,
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof cfg);
-    cfg.gridDim = dim3(cl, channels); cfg.blockDim = dim3(DW_THREADS);   // wider CTAs measured slower (81 vs 35 us per call at 1024 threads) cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cfg.gridDim = dim3(cl, channels);
+    cfg.blockDim = dim3(DW_THREADS);   // wider CTAs measured slower (81 vs 35 us per call at 1024 threads)
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
