@@ -66,6 +66,26 @@ class _BnTrain(torch.autograd.Function):
         return dx, dgamma, dbeta, None, None, None, None, None, None, dslope
 
 
+_DEFERRED_COUNTERS = None      # list while a deferred_counters() block is active
+
+
+class deferred_counters:
+    """Inside the block every native BatchNorm2d records its ``num_batches_tracked`` instead of launching its own
+    ``add_(1)``; leaving the block adds 1 to all of them with one multi-tensor launch (74 launches -> 1 per step)."""
+
+    def __enter__(self):
+        global _DEFERRED_COUNTERS
+        self.prev, _DEFERRED_COUNTERS = _DEFERRED_COUNTERS, []
+        return self
+
+    def __exit__(self, *exc):
+        global _DEFERRED_COUNTERS
+        todo, _DEFERRED_COUNTERS = _DEFERRED_COUNTERS, self.prev
+        if todo and exc[0] is None:
+            torch._foreach_add_(todo, 1)
+        return False
+
+
 class BatchNorm2d(nn.BatchNorm2d):
     """``nn.BatchNorm2d`` whose train-mode CUDA path (bf16 / fp32, fixed momentum) runs in libisg.  Everything else
     -- eval mode, CPU tensors (the boundary tests compare train mode against the reference on CPU), cumulative
@@ -93,7 +113,10 @@ class BatchNorm2d(nn.BatchNorm2d):
             kind = ACT_RELU
         elif act is not None and not isinstance(act, nn.Identity):
             raise TypeError(f"cannot fuse activation {type(act).__name__}")
-        self.num_batches_tracked.add_(1)
+        if _DEFERRED_COUNTERS is not None:
+            _DEFERRED_COUNTERS.append(self.num_batches_tracked)
+        else:
+            self.num_batches_tracked.add_(1)
         off = mean_offset.detach() if mean_offset is not None else None
         return _BnTrain.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.momentum, self.eps,
                               off, kind, slope)

@@ -175,14 +175,31 @@ class GraphedTrainStep:
                 v.copy_(saved[k])
 
     def _body(self):
-        self.bucket.zero_grads()
-        if self.autocast_dtype is None:
-            logits = self.model(self.x)
-        else:
-            with torch.autocast("cuda", dtype=self.autocast_dtype):
+        """One forward + loss + backward.  Gradients are produced as fresh tensors (``p.grad = None`` first, so autograd
+        assigns instead of launching one accumulate kernel per parameter) and copied into the zeroed flat bucket with a
+        single multi-tensor copy; afterwards every ``p.grad`` is a view of the bucket again."""
+        from .bn import deferred_counters
+        b = self.bucket
+        b.grad.zero_()
+        for p in b.params:
+            p.grad = None
+        with deferred_counters():
+            if self.autocast_dtype is None:
                 logits = self.model(self.x)
+            else:
+                with torch.autocast("cuda", dtype=self.autocast_dtype):
+                    logits = self.model(self.x)
         loss = bce_sigmoid_loss(logits, self.y)
         loss.backward()
+        dst, src, o = [], [], 0
+        for p, n in zip(b.params, b.sizes):
+            if p.grad is not None:
+                dst.append(b.grad[o:o + n].view_as(p))
+                src.append(p.grad)
+            o += n
+        if dst:
+            torch._foreach_copy_(dst, src)
+        b.bind_grads()
         return loss.detach()
 
     def __call__(self, images, masks):
