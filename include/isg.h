@@ -204,13 +204,15 @@ ISG_API int isg_bn_train_backward(const void* dy_dev, const void* x_dev, int bf1
  * NCHW activations [batch, channels, height, width] bf16 or fp32; weight fp32 [channels, kh, kw], bias fp32 [channels]
  * or NULL.  Stride 1 and output size == input size only (2*pad == dil*(k-1)), kh*kw <= 25.
  * isg_dwconv_forward: out = conv(in) (+ bias); flip != 0: taps reversed = the gradient w.r.t. the conv's input when
- * `in` is d loss / d out.  isg_dwconv_wgrad: dweight [channels, kh, kw] and dbias [channels] (may be NULL). */
+ * `in` is d loss / d out.  isg_dwconv_wgrad: dweight [channels, kh, kw] and dbias [channels] (may be NULL);
+ * workspace_dev: isg_dwconv_wgrad_workspace_bytes(channels) bytes or NULL (then one cluster per channel only). */
 ISG_API int isg_dwconv_forward(const void* in_dev, int bf16, int batch, int channels, int height, int width,
                        const float* weight_dev, const float* bias_dev, int kh, int kw, int pad_h, int pad_w,
                        int dil_h, int dil_w, int flip, void* out_dev, void* stream);
 ISG_API int isg_dwconv_wgrad(const void* dy_dev, const void* x_dev, int bf16, int batch, int channels, int height,
                      int width, int kh, int kw, int pad_h, int pad_w, int dil_h, int dil_w,
-                     float* dweight_dev, float* dbias_dev, void* stream);
+                     float* dweight_dev, float* dbias_dev, void* workspace_dev, void* stream);
+ISG_API int64_t isg_dwconv_wgrad_workspace_bytes(int channels);
 
 /* ---- ConvTranspose2d forward with kernel == 2*stride, 0 <= pad < stride, cout <= 8 (segment.py:435 bottle6_1: 16 -> 4,
  * k8 s4 p2) in train mode.  in [batch,cin,hin,win] bf16 or fp32, weight fp32 [cin,cout,k,k] (torch's layout), bias fp32

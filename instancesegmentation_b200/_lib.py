@@ -43,7 +43,8 @@ SIGNATURES = {
     "isg_bn_train_forward": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
     "isg_bn_train_backward": (_i, [_vp, _vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "isg_dwconv_forward": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
-    "isg_dwconv_wgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "isg_dwconv_wgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "isg_dwconv_wgrad_workspace_bytes": (_i64, [_i]),
     "isg_convt_k2s_forward": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "isg_bce_workspace_bytes": (_i64, []),
     "isg_bce_sigmoid": (_i, [_vp, _i, _vp, _i64, _vp, _vp, _vp, _vp]),

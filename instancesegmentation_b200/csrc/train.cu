@@ -659,7 +659,7 @@ dw_stencil_kernel(const T* __restrict__ in, const float* __restrict__ weight, co
 template <typename T, int K>
 __global__ void __launch_bounds__(DW_THREADS)
 dw_wgrad_kernel(const T* __restrict__ dy, const T* __restrict__ x, DwGeom g, int batch, float* __restrict__ dweight,
-                float* __restrict__ dbias) {
+                float* __restrict__ dbias, float* __restrict__ partial) {
     extern __shared__ float dw_sm[];
     __shared__ int toff[K];
     const int c = blockIdx.y;
@@ -672,7 +672,8 @@ dw_wgrad_kernel(const T* __restrict__ dy, const T* __restrict__ x, DwGeom g, int
 #pragma unroll
     for (int t = 0; t <= K; ++t) acc[t] = 0.f;
     const int tiles = g.tiles_h * g.tiles_w, total = batch * tiles;
-    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+    // gridDim.z > 1: several clusters share a channel, each leaves its sums in partial[z][c][K+1] for dw_wgrad_final_kernel
+    for (int it = blockIdx.z * gridDim.x + blockIdx.x; it < total; it += gridDim.x * gridDim.z) {
         const int b = it / tiles, tt = it - b * tiles;
         const int th = tt / g.tiles_w, tw = tt - th * g.tiles_w;
         const int h0 = th * DW_TH, w0 = tw * DW_TW;
@@ -696,9 +697,27 @@ dw_wgrad_kernel(const T* __restrict__ dy, const T* __restrict__ x, DwGeom g, int
     for (int t = 0; t <= K; ++t) a[t] = acc[t];
     cluster_sum<K + 1>(a);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        for (int t = 0; t < ntaps; ++t) dweight[(size_t)c * ntaps + t] = (float)a[t];
-        if (dbias) dbias[c] = (float)a[K];
+        if (gridDim.z > 1) {
+            float* dst = partial + ((size_t)blockIdx.z * g.C + c) * (DW_MAX_TAPS + 1);
+            for (int t = 0; t < ntaps; ++t) dst[t] = (float)a[t];
+            dst[DW_MAX_TAPS] = (float)a[K];
+        } else {
+            for (int t = 0; t < ntaps; ++t) dweight[(size_t)c * ntaps + t] = (float)a[t];
+            if (dbias) dbias[c] = (float)a[K];
+        }
     }
+}
+
+// grid (C), 32 threads: sums the Z partial rows of a channel in z order
+__global__ void dw_wgrad_final_kernel(const float* __restrict__ partial, int C, int Z, int ntaps, float* __restrict__ dweight,
+                                      float* __restrict__ dbias) {
+    const int c = blockIdx.x, t = threadIdx.x;
+    if (t > ntaps) return;
+    const int col = t < ntaps ? t : DW_MAX_TAPS;
+    float s = 0.f;
+    for (int z = 0; z < Z; ++z) s += partial[((size_t)z * C + c) * (DW_MAX_TAPS + 1) + col];
+    if (t < ntaps) dweight[(size_t)c * ntaps + t] = s;
+    else if (dbias) dbias[c] = s;
 }
 
 
@@ -933,8 +952,13 @@ int isg_dwconv_forward(const void* in_dev, int bf16, int batch, int channels, in
     return ISG_OK;
 }
 
+int64_t isg_dwconv_wgrad_workspace_bytes(int channels) {
+    return (int64_t)BN_CL_MAX * (channels > 0 ? channels : 0) * (DW_MAX_TAPS + 1) * (int64_t)sizeof(float);
+}
+
 int isg_dwconv_wgrad(const void* dy_dev, const void* x_dev, int bf16, int batch, int channels, int height, int width, int kh,
-                     int kw, int pad_h, int pad_w, int dil_h, int dil_w, float* dweight_dev, float* dbias_dev, void* stream) {
+                     int kw, int pad_h, int pad_w, int dil_h, int dil_w, float* dweight_dev, float* dbias_dev,
+                     void* workspace_dev, void* stream) {
     if (!dy_dev || !x_dev || !dweight_dev) return fail(ISG_ERR_ARG, "isg_dwconv_wgrad: null argument");
     DwGeom g; size_t smem;
     if (int rc = dw_geom("isg_dwconv_wgrad", batch, channels, height, width, kh, kw, pad_h, pad_w, dil_h, dil_w, &g, &smem)) return rc;
@@ -944,7 +968,12 @@ int isg_dwconv_wgrad(const void* dy_dev, const void* x_dev, int bf16, int batch,
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof cfg);
-    cfg.gridDim = dim3(cl, channels);
+    // few channels: several clusters per channel (z) so that ~2 CTAs per SM are in flight; needs the workspace
+    int zs = 1;
+    if (workspace_dev)
+        while (zs < BN_CL_MAX && cl * channels * zs < 148 * 2 && cl * zs * 2 <= total) zs *= 2;
+    float* partial = static_cast<float*>(workspace_dev);
+    cfg.gridDim = dim3(cl, channels, zs);
     cfg.blockDim = dim3(DW_THREADS);   // wider CTAs measured slower (81 vs 35 us per call at 1024 threads)
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
@@ -955,10 +984,14 @@ int isg_dwconv_wgrad(const void* dy_dev, const void* x_dev, int bf16, int batch,
     const bool small = kh * kw <= 9;
 #define ISG_DW_WGRAD(T, K)                                                                                        \
     ISG_CUDA(cudaLaunchKernelEx(&cfg, dw_wgrad_kernel<T, K>, static_cast<const T*>(dy_dev), static_cast<const T*>(x_dev), \
-                                g, batch, dweight_dev, dbias_dev))
+                                g, batch, dweight_dev, dbias_dev, partial))
     if (bf16) { if (small) ISG_DW_WGRAD(__nv_bfloat16, 9); else ISG_DW_WGRAD(__nv_bfloat16, 25); }
     else      { if (small) ISG_DW_WGRAD(float, 9); else ISG_DW_WGRAD(float, 25); }
 #undef ISG_DW_WGRAD
+    if (zs > 1) {
+        dw_wgrad_final_kernel<<<channels, 32, 0, st>>>(partial, channels, zs, kh * kw, dweight_dev, dbias_dev);
+        ISG_CUDA(cudaGetLastError());
+    }
     return ISG_OK;
 }
 

@@ -50,8 +50,9 @@ class _DwConv(torch.autograd.Function):
             if ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2]):
                 dw = torch.empty(wshape, dtype=torch.float32, device=x.device)
                 db = torch.empty(C, dtype=torch.float32, device=x.device) if has_bias else None
+                ws = torch.empty(l.isg_dwconv_wgrad_workspace_bytes(C) // 4, dtype=torch.float32, device=x.device)
                 _lib.check(l.isg_dwconv_wgrad(dy.data_ptr(), x.data_ptr(), bf, B, C, H, W, kh, kw, padding[0], padding[1],
-                                              dilation[0], dilation[1], dw.data_ptr(), _ptr(db), st))
+                                              dilation[0], dilation[1], dw.data_ptr(), _ptr(db), ws.data_ptr(), st))
                 if wdtype != torch.float32:
                     dw = dw.to(wdtype)
         return dx, dw, db, None, None

@@ -143,7 +143,8 @@ def test_library_rejects_bad_arguments_without_gpu():
                                    pbuf, None) == -1
     assert l.isg_dwconv_forward(pbuf, 0, 1, 4, 4, 4, pbuf, None, 3, 3, 0, 1, 1, 1, 0, pbuf, None) == -1
     assert b"2*pad == dil*(k-1)" in l.isg_last_error()
-    assert l.isg_dwconv_wgrad(pbuf, None, 0, 1, 4, 4, 4, 3, 3, 1, 1, 1, 1, pbuf, None, None) == -1
+    assert l.isg_dwconv_wgrad(pbuf, None, 0, 1, 4, 4, 4, 3, 3, 1, 1, 1, 1, pbuf, None, None, None) == -1
+    assert l.isg_dwconv_wgrad_workspace_bytes(16) == 8 * 16 * 26 * 4
     assert l.isg_convt_k2s_forward(pbuf, 0, 1, 16, 4, 8, 8, 8, 3, 2, pbuf, None, pbuf, None) == -1
     assert b"kernel == 2*stride" in l.isg_last_error()
 
