@@ -176,6 +176,20 @@ ISG_API int64_t isg_bce_workspace_bytes(void);
 ISG_API int isg_bce_sigmoid(const void* logits_dev, int logits_bf16, const float* target_dev, int64_t n,
                     void* dlogits_dev, void* workspace_dev, float* loss_dev, void* stream);
 
+/* ---- isg_bce_sigmoid for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * Same inputs, outputs and arithmetic as isg_bce_sigmoid (same grid, same fixed sum order: the loss and the gradient
+ * are bitwise equal), but the per-block partial sums and the ticket live in a file-scope `static __device__` array of
+ * the library (8.3 KB, held by every GPU that loads libisg until exit) instead of a caller workspace.  The call
+ * allocates nothing (no cudaMalloc / cudaFree, no allocating library routine): the array's device address is looked
+ * up once per device (cudaGetSymbolAddress with the caller's current device) and the ticket is cleared on `stream`
+ * before every launch.  Limit: n <= isg_bce_sigmoid_static_max_n() = 2^26 elements per call; larger n is rejected
+ * with ISG_ERR_ARG (use isg_bce_sigmoid).  All calls on one device share the array: calls that overlap on the GPU
+ * (different streams, no ordering) race on it -- order them, or use isg_bce_sigmoid with separate workspaces. */
+ISG_API int64_t isg_bce_sigmoid_static_max_n(void);
+ISG_API int isg_bce_sigmoid_static(const void* logits_dev, int logits_bf16, const float* target_dev, int64_t n,
+                           void* dlogits_dev, float* loss_dev, void* stream);
+
 /* ---- train-mode BatchNorm2d (+ the activation of the Conv block) (segment.py:41-45, one per Conv;
  * train_instance.py:372 model.train()) -------------------------------------------------------------------
  * NCHW activations [batch, channels, hw] contiguous, bf16 or fp32 (bf16 != 0); gamma/beta/statistics fp32 [channels]

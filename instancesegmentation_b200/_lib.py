@@ -48,6 +48,8 @@ SIGNATURES = {
     "isg_convt_k2s_forward": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "isg_bce_workspace_bytes": (_i64, []),
     "isg_bce_sigmoid": (_i, [_vp, _i, _vp, _i64, _vp, _vp, _vp, _vp]),
+    "isg_bce_sigmoid_static_max_n": (_i64, []),
+    "isg_bce_sigmoid_static": (_i, [_vp, _i, _vp, _i64, _vp, _vp, _vp]),
 }
 
 

@@ -798,6 +798,58 @@ int isg_bce_sigmoid(const void* logits_dev, int logits_bf16, const float* target
     return ISG_OK;
 }
 
+// ---- isg_bce_sigmoid without a caller workspace and without any allocation ----
+// The per-block partial sums and the ticket live in a file-scope device array that every GPU loading the library
+// holds until exit (8.3 KB).  In host code `g_bce_static` is only a stand-in for the symbol: its device address is
+// looked up once per device with cudaGetSymbolAddress (that device current) and handed to the kernel.
+}  // extern "C"
+namespace {
+constexpr int64_t BCE_STATIC_MAX_N = (int64_t)1 << 26;   // elements per call (256 logit maps of 512 x 512)
+constexpr int BCE_STATIC_WORDS = BCE_MAX_BLOCKS + 8;     // doubles: partials, then the ticket
+static __device__ __align__(256) double g_bce_static[BCE_STATIC_WORDS];
+constexpr int BCE_STATIC_MAX_DEV = 64;
+double* g_bce_static_addr[BCE_STATIC_MAX_DEV] = {nullptr};   // device address of the array on each device, once known
+}  // namespace
+extern "C" {
+
+int64_t isg_bce_sigmoid_static_max_n(void) { return BCE_STATIC_MAX_N; }
+
+int isg_bce_sigmoid_static(const void* logits_dev, int logits_bf16, const float* target_dev, int64_t n, void* dlogits_dev,
+                           float* loss_dev, void* stream) {
+    if (n <= 0) return fail(ISG_ERR_ARG, "isg_bce_sigmoid_static: the mean of an empty batch is undefined (n=%lld)", (long long)n);
+    if (n > BCE_STATIC_MAX_N)
+        return fail(ISG_ERR_ARG, "isg_bce_sigmoid_static: n=%lld exceeds the static-scratch limit of %lld elements per call; "
+                    "use isg_bce_sigmoid with a caller workspace", (long long)n, (long long)BCE_STATIC_MAX_N);
+    if (!logits_dev || !target_dev || !loss_dev) return fail(ISG_ERR_ARG, "isg_bce_sigmoid_static: null argument");
+    int dev = -1;
+    ISG_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= BCE_STATIC_MAX_DEV) return fail(ISG_ERR_ARG, "isg_bce_sigmoid_static: device %d out of range", dev);
+    if (!g_bce_static_addr[dev]) {   // set-up, once per device, with that device current
+        double* p = nullptr;
+        ISG_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_bce_static));
+        if (!p) return fail(ISG_ERR_CUDA, "isg_bce_sigmoid_static: cudaGetSymbolAddress returned a null address");
+        g_bce_static_addr[dev] = p;
+    }
+    double* partial = g_bce_static_addr[dev];
+    unsigned* ticket = reinterpret_cast<unsigned*>(partial + BCE_MAX_BLOCKS);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // the array keeps the previous call's contents: the ticket must start at zero (the partials are overwritten)
+    ISG_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned), st));
+    int64_t blocks = (n + BCE_THREADS * 4 - 1) / (BCE_THREADS * 4);   // the grid of isg_bce_sigmoid: same sum order
+    if (blocks > BCE_MAX_BLOCKS) blocks = BCE_MAX_BLOCKS;
+    const float inv_n = (float)(1.0 / (double)n);
+    if (logits_bf16)
+        bce_sigmoid_kernel<__nv_bfloat16><<<(unsigned)blocks, BCE_THREADS, 0, st>>>(
+            static_cast<const __nv_bfloat16*>(logits_dev), target_dev, n, inv_n, static_cast<__nv_bfloat16*>(dlogits_dev),
+            partial, ticket, loss_dev);
+    else
+        bce_sigmoid_kernel<float><<<(unsigned)blocks, BCE_THREADS, 0, st>>>(
+            static_cast<const float*>(logits_dev), target_dev, n, inv_n, static_cast<float*>(dlogits_dev), partial, ticket,
+            loss_dev);
+    ISG_CUDA(cudaGetLastError());
+    return ISG_OK;
+}
+
 int isg_bn_max_split(void) { return BN_MAX_SPLIT; }
 
 static int bn_check(const char* who, int bf16, int batch, int channels, int64_t hw, const void* a, const void* b,
