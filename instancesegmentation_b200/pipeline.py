@@ -23,13 +23,16 @@ class _Slot:
         self.drained = torch.cuda.Event()
         self.res = None
         self.used = False
+        self.graph = None
 
 
 class Pipeline:
     """``submit(host_batch, masks_host, stats_host)`` enqueues one batch; ``finish()`` waits for all."""
 
-    def __init__(self, model, boxes, depth=2, threshold=0.5, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5)):
+    def __init__(self, model, boxes, depth=2, threshold=0.5, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5), graphs=False):
+        """``graphs=True``: forward + decode of every slot is captured once (GraphedStep) and replayed."""
         p = next(model.parameters())
+        self.graphs = graphs
         if not p.is_cuda:
             raise RuntimeError("Pipeline needs the model on a CUDA device; there is no CPU path")
         self.model, self.dev, self.threshold = model, p.device, threshold
@@ -61,13 +64,20 @@ class Pipeline:
             compute.wait_event(s.drained)                # the slot's masks left for the host
         if s.masks is None or s.masks.numel() < self.plan.total:
             s.masks = torch.empty(self.plan.total, dtype=torch.uint8, device=self.dev)
-        with torch.no_grad():
-            if s.x.dtype == torch.uint8:
-                logits = self.model.forward_u8(s.x, self.mean, self.std)
-            else:
-                logits = self.model(s.x)
+        if self.graphs:
+            if s.graph is None or s.graph.x is not s.x or s.graph.masks is not s.masks:
+                s.graph = GraphedStep(self.model, s.x, threshold=self.threshold, mean=self.mean, std=self.std,
+                                      plan=s.plan, masks=s.masks)
+            s.res = s.graph.replay()
             s.consumed.record(compute)
-            s.res = decode_masks(logits, threshold=self.threshold, out=s.masks, plan=s.plan)
+        else:
+            with torch.no_grad():
+                if s.x.dtype == torch.uint8:
+                    logits = self.model.forward_u8(s.x, self.mean, self.std)
+                else:
+                    logits = self.model(s.x)
+                s.consumed.record(compute)
+                s.res = decode_masks(logits, threshold=self.threshold, out=s.masks, plan=s.plan)
         s.computed.record(compute)
         with torch.cuda.stream(self.d2h):
             self.d2h.wait_event(s.computed)
@@ -90,3 +100,50 @@ class Pipeline:
 
 def identity_boxes(batch, height, width):
     return np.tile(np.array([0, 0, width, height], np.int32), (batch, 1))
+
+
+class GraphedStep:
+    """Forward + decode of one fixed batch buffer captured in a CUDA graph: one host call per step instead of the
+    plan's ~24 launches ("linear scaling limited only by host launch jitter -> CUDA graphs per GPU").
+
+    ``x``: the STATIC device input (fp32 [B,C,H,W] or uint8 [B,H,W,C]); refill it in place (``x.copy_``) and call
+    ``replay()``; ``result`` (DecodeResult: masks / area / bbox, and ``logits``) is rewritten by every replay.
+    The programmatic-dependent-launch edges of the kernels are kept by the capture."""
+
+    def __init__(self, model, x, boxes=None, threshold=0.5, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5),
+                 plan=None, masks=None, decode=True):
+        if not x.is_cuda:
+            raise RuntimeError("GraphedStep needs a CUDA input buffer; there is no CPU path")
+        self.model, self.x, self.threshold = model, x, threshold
+        self.mean, self.std = tuple(mean), tuple(std)
+        B = x.shape[0]
+        H, W = (x.shape[1], x.shape[2]) if x.dtype == torch.uint8 else (x.shape[2], x.shape[3])
+        self.plan = plan if plan is not None else (
+            DecodePlan(identity_boxes(B, H, W) if boxes is None else boxes, x.device) if decode else None)
+        self.masks = masks if masks is not None else (
+            torch.empty(self.plan.total, dtype=torch.uint8, device=x.device) if decode else None)
+        self.decode = decode
+        self.logits = self.result = None
+        side = torch.cuda.Stream(x.device)
+        side.wait_stream(torch.cuda.current_stream(x.device))
+        with torch.cuda.stream(side):
+            for _ in range(2):      # plan creation, autotune, weight upload and occupancy queries happen here, not in the capture
+                self._body()
+        torch.cuda.current_stream(x.device).wait_stream(side)
+        torch.cuda.synchronize(x.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._body()
+
+    def _body(self):
+        with torch.no_grad():
+            if self.x.dtype == torch.uint8:
+                self.logits = self.model.forward_u8(self.x, self.mean, self.std)
+            else:
+                self.logits = self.model(self.x)
+            if self.decode:
+                self.result = decode_masks(self.logits, threshold=self.threshold, out=self.masks, plan=self.plan)
+
+    def replay(self):
+        self.graph.replay()
+        return self.result
