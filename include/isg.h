@@ -43,7 +43,11 @@ enum isg_status {
 
 enum isg_mode {
     ISG_MODE_FP32 = 0,     /* fp32 storage + fp32 FMA, BatchNorm as fp32 epilogue affine (<=1e-4 vs reference) */
-    ISG_MODE_BF16 = 1      /* NHWC bf16 activations; GEMM-shaped convs on tcgen05 with fp32 TMEM accumulators */
+    ISG_MODE_BF16 = 1,     /* NHWC bf16 activations; GEMM-shaped convs on tcgen05 with fp32 TMEM accumulators
+                              (logits 0.3-0.8 max-abs from the reference: bf16 operand rounding) */
+    ISG_MODE_BF16X3 = 2    /* the same tcgen05 kernels with split-precision operands: every activation and weight is a bf16
+                              pair hi + lo, every GEMM accumulates A_hi.W_hi + A_lo.W_hi + A_hi.W_lo in fp32 TMEM
+                              (~16 significand bits per operand; logits within max-abs 2e-2 / mean-abs 2e-3) */
 };
 
 ISG_API const char* isg_last_error(void);
@@ -81,6 +85,11 @@ ISG_API int isg_forward(isg_plan* plan, const float* x_dev, int batch, float* lo
  * quarter of the PCIe bytes of the fp32 tensor.  mean_host / std_host: in_channel floats on the host. */
 ISG_API int isg_forward_u8(isg_plan* plan, const uint8_t* x_u8_dev, int batch, const float* mean_host,
                            const float* std_host, float* logits_dev, void* stream);
+
+/* test hook: lowers Segment(in_channel) at this size and mode to its launch list WITHOUT touching a device (tile
+ * feasibility of every fused launch: shared memory, TMEM columns, descriptor tables); returns the number of launches
+ * per forward or a negative isg_status.  Runs on a machine without a GPU. */
+ISG_API int isg_plan_dry_run(int in_channel, int height, int width, int max_batch, int mode);
 
 /* number of kernels isg_forward launches per group of <= max_batch images */
 ISG_API int isg_plan_launches_per_forward(const isg_plan* plan);

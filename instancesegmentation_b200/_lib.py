@@ -8,7 +8,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("ISG_LIB") or os.path.join(_HERE, "libisg.so")
 _lib = None
 
-MODE_FP32, MODE_BF16 = 0, 1
+MODE_FP32, MODE_BF16, MODE_BF16X3 = 0, 1, 2
 
 # every symbol include/isg.h declares: name -> (restype, argtypes)
 _vp, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
@@ -20,6 +20,7 @@ SIGNATURES = {
     "isg_state_numel": (_i64, [_i, _i]),
     "isg_state_is_int64": (_i, [_i, _i]),
     "isg_plan_create": (_i, [_i, _i, _i, _i, _i, _i, C.POINTER(_vp)]),
+    "isg_plan_dry_run": (_i, [_i, _i, _i, _i, _i]),
     "isg_plan_destroy": (_i, [_vp]),
     "isg_plan_workspace_bytes": (C.c_size_t, [_vp]),
     "isg_plan_load_weights": (_i, [_vp, C.POINTER(_vp), C.POINTER(_i64), _i]),

@@ -24,6 +24,10 @@ struct TensorD {
     // global memory order of the bf16 path: false = pixel-major [B][H][W][Cs]; true = planar [B][Cs/8][H][W][8]
     // (TMA boxes of planar tensors have rows of tile-width x 16 contiguous bytes, see tc_common.cuh tma_load_act)
     bool planar = false;
+    // split precision (ISG_MODE_BF16X3): channel c is stored twice, hi = bf16(v) at storage channel sc and
+    // lo = bf16(v - hi) at Cs + sc; the tensor holds Ct() = 2 Cs storage channels
+    bool split = false;
+    int Ct() const { return split ? 2 * Cs : Cs; }
     // element index of storage channel sc of pixel (y, x) of image b (Hs x Ws = stored spatial size)
     size_t index(int b, int y, int x, int sc, int Hs, int Ws, int Ct) const {
         if (planar) return (((size_t)b * (Ct / 8) + sc / 8) * Hs * Ws + (size_t)y * Ws + x) * 8 + sc % 8;
@@ -75,7 +79,8 @@ struct isg_plan {
     const uint8_t* u8_src = nullptr;
     float u8_mean[8] = {0}, u8_std[8] = {1, 1, 1, 1, 1, 1, 1, 1};
     float* u8_scratch = nullptr;
-    bool use_tc = false;       // bf16 mode: GEMM-shaped convs on tcgen05 (ISG_NO_TC=1 disables)
+    bool use_tc = false;       // bf16 modes: GEMM-shaped convs on tcgen05 (ISG_NO_TC=1 disables)
+    bool split = false;        // ISG_MODE_BF16X3: split-precision operands (hi + lo bf16 pairs, 3 MMA passes)
     std::vector<std::function<int()>> finalizers;  // run once after the workspace is allocated (tensor maps)
     // run once after the finalizers: each fused launch times its candidate tilings on the device
     // (scratch logits buffer of max_batch images, stream) and keeps the fastest
@@ -91,7 +96,7 @@ struct isg_plan {
     };
     std::vector<TuneSite> tune_sites;
 
-    size_t esize() const { return mode == ISG_MODE_BF16 ? 2 : 4; }
+    size_t esize() const { return mode != ISG_MODE_FP32 ? 2 : 4; }
     void* tptr(int id) const { return ws + tensors[id].off; }
 };
 

@@ -131,7 +131,8 @@ struct Builder {
 int build_plan(isg_plan* p) {
     // bf16 mode = fused tcgen05 block kernels (engine_fk.cu); ISG_NO_TC=1 keeps the CUDA-core
     // kernels with bf16 storage, which exist only as a debugging cross-check
-    p->use_tc = p->mode == ISG_MODE_BF16 && !getenv("ISG_NO_TC");
+    p->split = p->mode == ISG_MODE_BF16X3;
+    p->use_tc = p->split || (p->mode == ISG_MODE_BF16 && !getenv("ISG_NO_TC"));
     if (p->use_tc) build_fk_plan(p);
     else if (p->mode == ISG_MODE_BF16) Builder<bf16>(p).build();
     else Builder<float>(p).build();

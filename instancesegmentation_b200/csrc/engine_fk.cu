@@ -33,10 +33,44 @@ __device__ __forceinline__ bf16* x2_pixel(bf16* x2, int b, int y, int x, int H2,
     return x2 + (((size_t)b * H2 + y) * W2 + x) * Cs2;
 }
 
+// 16 channels of one pixel: two 8-channel groups `half` elements apart; split: the lo halves follow 2 groups later
+__device__ __forceinline__ void store16(bf16* d, int half, const float* f, int split) {
+    if (split) {
+        uint32_t h[8], l[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) fk::split_bf16(f[2 * i], f[2 * i + 1], h[i], l[i]);
+        fk::st_global_16(d, make_uint4(h[0], h[1], h[2], h[3]));
+        fk::st_global_16(d + half, make_uint4(h[4], h[5], h[6], h[7]));
+        fk::st_global_16(d + 2 * half, make_uint4(l[0], l[1], l[2], l[3]));
+        fk::st_global_16(d + 3 * half, make_uint4(l[4], l[5], l[6], l[7]));
+    } else {
+        fk::st_global_16(d, make_uint4(fk::pack_bf16(f[0], f[1]), fk::pack_bf16(f[2], f[3]),
+                                       fk::pack_bf16(f[4], f[5]), fk::pack_bf16(f[6], f[7])));
+        fk::st_global_16(d + half, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
+                                           fk::pack_bf16(f[12], f[13]), fk::pack_bf16(f[14], f[15])));
+    }
+}
+// max-pooled input channels (<= 8) of one init_down pixel at storage channel 16: 8 values + 8 zeros; split: lo at + lo_off
+__device__ __forceinline__ void store_pooled(bf16* d, const float* m, int split, int lo_off) {
+    if (split) {
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) fk::split_bf16(m[2 * i], m[2 * i + 1], h[i], l[i]);
+        fk::st_global_16(d, make_uint4(h[0], h[1], h[2], h[3]));
+        fk::st_global_16(d + 8, make_uint4(0, 0, 0, 0));
+        fk::st_global_16(d + lo_off, make_uint4(l[0], l[1], l[2], l[3]));
+        fk::st_global_16(d + lo_off + 8, make_uint4(0, 0, 0, 0));
+    } else {
+        fk::st_global_16(d, make_uint4(fk::pack_bf16(m[0], m[1]), fk::pack_bf16(m[2], m[3]), fk::pack_bf16(m[4], m[5]),
+                                       fk::pack_bf16(m[6], m[7])));
+        fk::st_global_16(d + 8, make_uint4(0, 0, 0, 0));
+    }
+}
+
 template <int CIN>
 __global__ void __launch_bounds__(128)
 prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, int planar2,
-            bf16* __restrict__ init, int Cs_init, int total) {
+            bf16* __restrict__ init, int Cs_init, int total, int split, int init_lo) {
     // launched with programmatic stream serialization: x2 / init_down may still be read by the
     // previous forward's kernels until the wait returns
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -69,10 +103,7 @@ prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, in
                     for (int c = 0; c < CIN; ++c) f[(ry * 2 + rx) * CIN + c] = v[c][2 * a + ry][2 * bb + rx];
             int half;
             bf16* d = x2_pixel(x2, b, 2 * y4 + a, 2 * x4 + bb, H >> 1, W >> 1, Cs2, planar2, half);
-            fk::st_global_16(d, make_uint4(fk::pack_bf16(f[0], f[1]), fk::pack_bf16(f[2], f[3]),
-                                           fk::pack_bf16(f[4], f[5]), fk::pack_bf16(f[6], f[7])));
-            fk::st_global_16(d + half, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
-                                               fk::pack_bf16(f[12], f[13]), fk::pack_bf16(f[14], f[15])));
+            store16(d, half, f, split);
         }
     float m[8];
 #pragma unroll
@@ -86,10 +117,7 @@ prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, in
             for (int q = 0; q < 4; ++q) mx = fmaxf(mx, v[c][r][q]);
         m[c] = mx;
     }
-    bf16* d = init + (((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16;
-    fk::st_global_16(d, make_uint4(fk::pack_bf16(m[0], m[1]), fk::pack_bf16(m[2], m[3]), fk::pack_bf16(m[4], m[5]),
-                                   fk::pack_bf16(m[6], m[7])));
-    fk::st_global_16(d + 8, make_uint4(0, 0, 0, 0));
+    store_pooled(init + (((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16, m, split, init_lo);
 }
 
 // the same from uint8 NHWC [B,H,W,3] (isg_forward_u8): ToTensor + Normalize of the reference's data
@@ -98,7 +126,7 @@ prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, in
 struct NormU8 { float mean[3], std[3]; };
 __global__ void __launch_bounds__(128)
 prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, int planar2,
-               bf16* __restrict__ init, int Cs_init, int total, NormU8 nm) {
+               bf16* __restrict__ init, int Cs_init, int total, NormU8 nm, int split, int init_lo) {
     // a byte has 256 values: the IEEE sequence is evaluated once per (channel, value) and CTA
     __shared__ float lut[3][256];
     for (int e = threadIdx.x; e < 768; e += blockDim.x) {
@@ -134,12 +162,9 @@ prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x
                     for (int c = 0; c < 3; ++c) f[(ry * 2 + rx) * 3 + c] = v[c][2 * a + ry][2 * bb + rx];
             int half;
             bf16* d = x2_pixel(x2, b, 2 * y4 + a, 2 * x4 + bb, H >> 1, W >> 1, Cs2, planar2, half);
-            fk::st_global_16(d, make_uint4(fk::pack_bf16(f[0], f[1]), fk::pack_bf16(f[2], f[3]),
-                                           fk::pack_bf16(f[4], f[5]), fk::pack_bf16(f[6], f[7])));
-            fk::st_global_16(d + half, make_uint4(fk::pack_bf16(f[8], f[9]), fk::pack_bf16(f[10], f[11]),
-                                               fk::pack_bf16(f[12], f[13]), fk::pack_bf16(f[14], f[15])));
+            store16(d, half, f, split);
         }
-    float m[3];
+    float m[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         float mx = v[c][0][0];
@@ -149,15 +174,14 @@ prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x
             for (int q = 0; q < 4; ++q) mx = fmaxf(mx, v[c][r][q]);
         m[c] = mx;
     }
-    bf16* d = init + (((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16;
-    fk::st_global_16(d, make_uint4(fk::pack_bf16(m[0], m[1]), fk::pack_bf16(m[2], 0.f), 0, 0));
-    fk::st_global_16(d + 8, make_uint4(0, 0, 0, 0));
+    store_pooled(init + (((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16, m, split, init_lo);
 }
 
 // generic (any Cin) variant: one thread = one (patch, channel)
 __global__ void __launch_bounds__(128)
 prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __restrict__ x2, int Cs2, int planar2,
-                    bf16* __restrict__ init, int Cs_init, int total) {
+                    bf16* __restrict__ init, int Cs_init, int total, int split, int x2_lo, int init_lo) {
+    // Cs2 / Cs_init: storage channels per pixel (hi + lo when split); x2_lo / init_lo: channels from hi to lo
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
@@ -173,10 +197,20 @@ prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __
             const int sc = ((r & 1) * 2 + (k & 1)) * Cin + c, H2 = H >> 1, W2 = W >> 1;
             const size_t e = planar2 ? (((size_t)b * (Cs2 >> 3) + (sc >> 3)) * H2 * W2 + (size_t)sy * W2 + sx) * 8 + (sc & 7)
                                      : (((size_t)b * H2 + sy) * W2 + sx) * Cs2 + sc;
-            x2[e] = __float2bfloat16_rn(f[k]);
+            const bf16 hi = __float2bfloat16_rn(f[k]);
+            x2[e] = hi;
+            if (split) {
+                const int sl = sc + x2_lo;
+                const size_t el = planar2 ? (((size_t)b * (Cs2 >> 3) + (sl >> 3)) * H2 * W2 + (size_t)sy * W2 + sx) * 8 + (sl & 7)
+                                          : (((size_t)b * H2 + sy) * W2 + sx) * Cs2 + sl;
+                x2[el] = __float2bfloat16_rn(f[k] - __bfloat162float(hi));
+            }
         }
     }
-    init[(((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16 + c] = __float2bfloat16_rn(mx);
+    bf16* dp = init + (((size_t)b * H4 + y4) * W4 + x4) * Cs_init + 16 + c;
+    const bf16 hi = __float2bfloat16_rn(mx);
+    *dp = hi;
+    if (split) dp[init_lo] = __float2bfloat16_rn(mx - __bfloat162float(hi));
 }
 
 // The composed tail GEMM treats the transposed conv's output as if it extended one pixel
@@ -184,7 +218,8 @@ prep_generic_kernel(const float* __restrict__ x, int Cin, int H, int W, bf16* __
 // This kernel subtracts, for the border ring of the logits, the contributions of those
 // outside positions.  One thread = one border pixel.
 struct TailFixParams {
-    const bf16* in; int Hq, Wq, Cs, planar;    // [B,Hq,Wq,16] or planar [B,2,Hq,Wq,8]
+    const bf16* in; int Hq, Wq, Cs, planar;    // [B,Hq,Wq,16] or planar [B,2,Hq,Wq,8]; Cs = storage channels per pixel
+    int lo;                            // split precision: 1 = add the lo half (16 channels after the hi half)
     float* logits;                     // [B,4Hq,4Wq]
     const float* g;                    // [ky(8)][kx(8)][d(9)][ci(16)]: transposed-conv tap (ky,kx) seen through 3x3 tap d
     const float* gb;                   // [d(9)]: the transposed conv's bias seen through 3x3 tap d
@@ -225,6 +260,13 @@ __global__ void __launch_bounds__(128) tail_fix_kernel(TailFixParams p) {
                 float f[16];
                 fk::unpack8(__ldg(src), f);
                 fk::unpack8(__ldg(src + half), f + 8);
+                if (p.lo) {
+                    float l[16];
+                    fk::unpack8(__ldg(src + 2 * half), l);
+                    fk::unpack8(__ldg(src + 3 * half), l + 8);
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) f[q] += l[q];
+                }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const float4 w = __ldg(g + q);
@@ -256,6 +298,8 @@ struct StageSpec {
     bool store = true;
     int shuf = 1, Cp = 0;
     bool to_logits = false;
+    // split precision: MMA passes of this stage (bit 0 A_hi.W_hi, bit 1 A_lo.W_hi, bit 2 A_hi.W_lo); -1 = all three
+    int passes = -1;
 };
 struct StencilSpec { int kind = 0; int load = -1; int dil = 1; StencilFill fill; };  // 1 dw3x3, 2 sep5
 struct Spec {
@@ -273,7 +317,9 @@ struct Lay {
     int pipe = 0;              // > 0: warp-specialised launch (fk_pipe_kernel) with this many load slots
     int groups = 3;            // ... and this many epilogue warp groups (the other warps issue MMAs)
     size_t smem = 0;
-    int load_off[fk::MAX_LOADS], load_plane[fk::MAX_LOADS], load_planes[fk::MAX_LOADS];
+    int load_off[fk::MAX_LOADS], load_plane[fk::MAX_LOADS], load_planes[fk::MAX_LOADS];   // planes = hi planes (logical chunks)
+    int load_lo[fk::MAX_LOADS];   // split precision: bytes from a hi plane of the load to its lo plane (0 = plain)
+    int st_out_lo = 0, stage_lo[2] = {0, 0}, pool_lo = 0, tab_n = 0;
     int st_out_off = 0, st_out_plane = 0, st_in_pitch = 0;
     int lbuf_stride = 0, stage_in_load[2] = {0, 0};
     int pool_off = 0, pool_plane = 0;
@@ -315,8 +361,17 @@ inline cudaError_t launch_fk(int ctas, int grid, size_t smem, const FkMaps& m, c
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    if (p.split) {   // split-precision instantiations (ISG_MODE_BF16X3)
+        if (p.pipe_slots)
+            return cudaLaunchKernelEx(&cfg, fk::fk_pipe_kernel<true>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+        if (ctas == 4)
+            return cudaLaunchKernelEx(&cfg, fk::fk_kernel<128, true>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+        if (ctas == 2)
+            return cudaLaunchKernelEx(&cfg, fk::fk_kernel<256, true>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+        return cudaLaunchKernelEx(&cfg, fk::fk_kernel<512, true>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+    }
     if (p.pipe_slots)
-        return cudaLaunchKernelEx(&cfg, fk::fk_pipe_kernel, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
+        return cudaLaunchKernelEx(&cfg, fk::fk_pipe_kernel<false>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
     if (ctas == 4)
         return cudaLaunchKernelEx(&cfg, fk::fk_kernel<128>, m.in[0], m.in[1], m.in[2], m.in[3], m.out[0], m.out[1], p);
     if (ctas == 2)
@@ -378,7 +433,8 @@ struct FkBuilder {
     int tensor(const std::string& name, int C, int H, int W, bool tap = false) {
         TensorD t{name, C, round_up(C, 16), H, W, P->ws_bytes, tap};
         t.planar = planar_for(name);
-        size_t bytes = (size_t)P->max_batch * H * W * t.Cs * 2;
+        t.split = P->split;
+        size_t bytes = (size_t)P->max_batch * H * W * t.Ct() * 2;
         P->ws_bytes += (bytes + 255) / 256 * 256;
         P->tensors.push_back(t);
         if (tap) P->taps.push_back((int)P->tensors.size() - 1);
@@ -388,6 +444,7 @@ struct FkBuilder {
         TensorD t{name, C, Cs, H, W, P->tensors[of].off, tap};
         t.layout = layout;
         t.planar = P->tensors[of].planar;
+        t.split = P->tensors[of].split;
         P->tensors.push_back(t);
         if (tap) P->taps.push_back((int)P->tensors.size() - 1);
         return (int)P->tensors.size() - 1;
@@ -408,8 +465,13 @@ struct FkBuilder {
     static bool pipe_ok(const Spec& s) {
         return s.stages.size() == 1 && !s.st.kind && s.pool_tensor < 0 && s.stages[0].res_load < 0 && !getenv("ISG_FK_NO_PIPE");
     }
+    // MMA passes of a stage: 0 = plain bf16 plan; split plans default to all three
+    int passes_of(const StageSpec& st) const { return !P->split ? 0 : (st.passes < 0 ? 7 : st.passes); }
+    static int npasses(int passes) { return passes ? (passes & 1) + ((passes >> 1) & 1) + ((passes >> 2) & 1) : 1; }
+
     bool layout(const Spec& s, int TH, int TW, int ctas, int nlbuf, Lay& L, int pipe = 0) const {
         const int hx = s.stages[0].taps9 ? 1 : 0;
+        const int mult = P->split ? 2 : 1;   // hi + lo plane groups
         L.TH = TH; L.TW = TW; L.pitch = TW + 2 * hx; L.ctas = ctas; L.nlbuf = nlbuf; L.pipe = pipe;
         if (pipe) nlbuf = pipe;
         const int mrows = TH * L.pitch;
@@ -430,8 +492,12 @@ struct FkBuilder {
             int bw, bh, planes;
             if (l.s2d) { bw = TW; bh = TH; planes = 4 * t.Cs / 8; }
             else { bw = TW + 2 * l.halo; bh = TH + 2 * l.halo; planes = l.nchunks < 0 ? t.Cs / 8 : l.nchunks; }
-            if (bw > 256 || bh > 256 || planes > 256) return false;
+            if (bw > 256 || bh > 256 || planes * (l.s2d ? mult : 1) > 256) return false;
             L.load_off[i] = off; L.load_plane[i] = bw * bh * 16; L.load_planes[i] = planes;
+            // split: [hi planes | lo planes]; a folded 2x2 load interleaves them per sub-pixel: [hi Cs/8 | lo Cs/8] x 4
+            // (the lo box is a TMA destination of its own: 128-byte aligned)
+            L.load_lo[i] = P->split ? (l.s2d ? (t.Cs / 8) * L.load_plane[i] : r128(planes * L.load_plane[i])) : 0;
+            const int load_bytes = (P->split && !l.s2d) ? L.load_lo[i] + planes * L.load_plane[i] : planes * mult * L.load_plane[i];
             bool is_a0 = false;
             for (auto& pt : s.stages[0].parts) is_a0 |= pt.kind == PART_LOAD && pt.load == (int)i;
             if (is_a0 && hx && l.halo != 1) return false;
@@ -439,8 +505,8 @@ struct FkBuilder {
             int slack = 0;
             if (is_a0) slack = std::max(0, a_rows * 16 - L.load_plane[i]);
             if ((int)i == s.stages[0].res_load && chained) slack = std::max(slack, L.n_mt * 128 * 16 - L.load_plane[i]);
-            L.tx += (uint32_t)planes * L.load_plane[i];
-            off = r128(off + planes * L.load_plane[i] + slack);
+            L.tx += (uint32_t)(planes * mult) * L.load_plane[i];
+            off = r128(off + load_bytes + slack);
         }
         // persistent CTAs double-buffer the whole load area: tile i+1 streams in while tile i computes
         L.lbuf_stride = off;
@@ -450,7 +516,8 @@ struct FkBuilder {
             const int nch = l.nchunks < 0 ? td(l.tensor).Cs / 8 : l.nchunks;
             L.st_in_pitch = TW + 2 * l.halo;
             L.st_out_off = off; L.st_out_plane = npix * 16;
-            off = r128(off + nch * L.st_out_plane + std::max(0, L.n_mt * 128 * 16 - L.st_out_plane));
+            L.st_out_lo = P->split ? r128(nch * L.st_out_plane) : 0;
+            off = r128(off + L.st_out_lo + nch * L.st_out_plane + std::max(0, L.n_mt * 128 * 16 - L.st_out_plane));
         }
         for (size_t k = 0; k < s.stages.size(); ++k) {
             const StageSpec& st = s.stages[k];
@@ -469,24 +536,27 @@ struct FkBuilder {
             if (!L.stage_compact[k] && st.store) return false;
             const int pix = L.stage_compact[k] ? npix : L.n_mt * 128;
             L.stage_plane[k] = pix * 16;
+            L.stage_lo[k] = P->split ? r128((st.N / 8) * L.stage_plane[k]) : 0;   // TMA store source of its own
             const bool alias = st.res_load >= 0 && st.res_mod == 0 && L.stage_compact[k] &&
                                L.load_planes[st.res_load] == st.N / 8 && s.loads[st.res_load].halo == 0;
             L.stage_in_load[k] = alias ? 1 : 0;
             if (alias) { L.stage_off[k] = L.load_off[st.res_load]; continue; }
             L.stage_off[k] = off;
             int slack = is_chain_src ? std::max(0, L.n_mt * 128 * 16 - L.stage_plane[k]) : 0;
-            off = r128(off + (st.N / 8) * L.stage_plane[k] + slack);
+            off = r128(off + L.stage_lo[k] + (st.N / 8) * L.stage_plane[k] + slack);
         }
         if (s.pool_tensor >= 0) {
             L.pool_off = off; L.pool_plane = npix * 16;
-            off = r128(off + (td(s.pool_tensor).Cs / 8) * L.pool_plane);
+            L.pool_lo = P->split ? r128((td(s.pool_tensor).Cs / 8) * L.pool_plane) : 0;
+            off = r128(off + L.pool_lo + (td(s.pool_tensor).Cs / 8) * L.pool_plane);
         }
         // constants blob
         L.blob_off = off;
         int rel = 0;
         for (size_t k = 0; k < s.stages.size(); ++k) {
             L.b_off[k] = rel;
-            rel = r128(rel + (s.stages[k].taps9 ? 9 : 1) * (L.K[k] / 16) * s.stages[k].N * 32);
+            // W_hi blocks, then W_lo blocks when the stage runs the A_hi.W_lo pass
+            rel = r128(rel + (s.stages[k].taps9 ? 9 : 1) * (L.K[k] / 16) * s.stages[k].N * 32 * ((passes_of(s.stages[k]) & 4) ? 2 : 1));
         }
         for (size_t k = 0; k < s.stages.size(); ++k) { L.vec_off[k] = rel; rel = r128(rel + 2 * s.stages[k].N * 4); }
         if (s.st.kind) {
@@ -499,6 +569,18 @@ struct FkBuilder {
         L.blob_bytes = rel;
         off = r128(off + rel);
         L.bar_off = off;
+        L.tab_n = 0;
+        if (P->split) {   // (A, B) descriptor pairs per table: MMAs per M tile over all passes
+            for (size_t k = 0; k < s.stages.size(); ++k) {
+                const StageSpec& st = s.stages[k];
+                int n = 0;
+                for (int t = 0; t < (st.taps9 ? 9 : 1); ++t)
+                    for (int ks = 0; ks < L.K[k] / 16; ++ks) n += (!st.used || st.used(t, ks)) ? 1 : 0;
+                L.tab_n = std::max(L.tab_n, n * npasses(passes_of(st)));
+            }
+            if (L.tab_n > fk::TAB_N_SPLIT) return false;
+            L.smem = (size_t)off + 128 + 2 * 3 * (size_t)L.tab_n * 16;
+        } else
         L.smem = (size_t)off + 128 + 2 * 3 * 40 * 8;   // barriers + A-descriptor tables
         return L.smem <= (ctas == 4 ? 55 * 1024 : ctas == 2 ? 112 * 1024 : 224 * 1024);
     }
@@ -590,14 +672,21 @@ struct FkBuilder {
         auto magic = [](int d) -> uint32_t { return d > 1 ? (uint32_t)(((1ull << 32) + d - 1) / d) : 0u; };
         q.tw_magic = magic(L.TW); q.npix_magic = magic(L.TH * L.TW);
         q.nlbuf = L.nlbuf;
-        q.nloads = (int)s.loads.size();
-        for (int i = 0; i < q.nloads; ++i) {
+        q.split = P->split ? 1 : 0; q.tab_n = L.tab_n;
+        q.nloads = 0;
+        for (int i = 0; i < (int)s.loads.size(); ++i) {
             const LoadSpec& l = s.loads[i];
-            fk::Load& d = q.loads[i];
-            d.map = i; d.smem_off = L.load_off[i]; d.dx = -l.halo; d.dy = -l.halo; d.chunk0 = l.chunk0;
-            d.folded = l.s2d ? 1 : 0; d.rows_per_img = s.qH; d.step = 1;
-            d.planar = td(l.tensor).planar ? 1 : 0;
-            if (l.s2d && d.planar) { fprintf(stderr, "libisg: %s: space-to-depth load of a planar tensor\n", s.name.c_str()); abort(); }
+            // split tensors arrive as two boxes through the same map: hi chunks, then the lo chunks Cs/8 later
+            // (a folded 2x2 load takes every chunk of its pixel pairs in one box)
+            for (int part = 0; part < (P->split && !l.s2d ? 2 : 1); ++part) {
+                if (q.nloads >= fk::MAX_LOADS) { fprintf(stderr, "libisg: %s: too many TMA loads\n", s.name.c_str()); abort(); }
+                fk::Load& d = q.loads[q.nloads++];
+                d.map = i; d.smem_off = L.load_off[i] + part * L.load_lo[i]; d.dx = -l.halo; d.dy = -l.halo;
+                d.chunk0 = l.chunk0 + part * td(l.tensor).Cs / 8;
+                d.folded = l.s2d ? 1 : 0; d.rows_per_img = s.qH; d.step = 1;
+                d.planar = td(l.tensor).planar ? 1 : 0;
+                if (l.s2d && d.planar) { fprintf(stderr, "libisg: %s: space-to-depth load of a planar tensor\n", s.name.c_str()); abort(); }
+            }
         }
         q.lbuf_stride = L.lbuf_stride;
         q.tx_bytes = L.tx; q.blob_off = L.blob_off; q.blob_bytes = L.blob_bytes; q.bar_off = L.bar_off;
@@ -612,6 +701,7 @@ struct FkBuilder {
             t.sep5 = s.st.kind == 2 ? 1 : 0;
             t.w_off = L.blob_off + L.stw_off; t.vec_off = L.blob_off + L.stvec_off;
             t.out_off = L.st_out_off; t.out_plane_bytes = L.st_out_plane;
+            t.in_lo = L.load_lo[s.st.load]; t.out_lo = L.st_out_lo;
         }
         q.nstages = (int)s.stages.size();
         for (int k = 0; k < q.nstages; ++k) {
@@ -621,14 +711,21 @@ struct FkBuilder {
             for (int t = 0; t < d.ntaps; ++t) d.tap_off[t] = st.taps9 ? (t / 3) * L.pitch + (t % 3) : 0;
             int nks = 0;
             for (auto& pt : st.parts) {
-                int base, plane, planes;
+                int base, plane, planes, lo = 0, sub_planes = 0;   // sub_planes > 0: folded split load, hi planes per sub-pixel
                 bool in_load = false;
-                if (pt.kind == PART_LOAD) { base = L.load_off[pt.load]; plane = L.load_plane[pt.load]; planes = L.load_planes[pt.load]; in_load = true; }
-                else if (pt.kind == PART_STENCIL) { base = L.st_out_off; plane = L.st_out_plane; planes = st_C / 8; }
-                else { base = L.stage_off[0]; plane = L.stage_plane[0]; planes = s.stages[0].N / 8; in_load = L.stage_in_load[0]; }
+                if (pt.kind == PART_LOAD) {
+                    base = L.load_off[pt.load]; plane = L.load_plane[pt.load]; planes = L.load_planes[pt.load]; in_load = true;
+                    lo = L.load_lo[pt.load];
+                    if (P->split && s.loads[pt.load].s2d) sub_planes = td(s.loads[pt.load].tensor).Cs / 8;
+                }
+                else if (pt.kind == PART_STENCIL) { base = L.st_out_off; plane = L.st_out_plane; planes = st_C / 8; lo = L.st_out_lo; }
+                else { base = L.stage_off[0]; plane = L.stage_plane[0]; planes = s.stages[0].N / 8; in_load = L.stage_in_load[0]; lo = L.stage_lo[0]; }
                 for (int j = 0; j < planes / 2; ++j) {
                     if (in_load) d.a_buf_mask |= 1u << nks;
-                    d.a_desc[nks++] = tc::umma_smem_desc(base + 2 * j * plane, plane, 128);
+                    int pl = 2 * j;   // first of the two hi planes of this K slice
+                    if (sub_planes) pl = (pl / sub_planes) * 2 * sub_planes + pl % sub_planes;   // [hi | lo] per sub-pixel
+                    d.a_lo[nks] = (uint32_t)lo >> 4;
+                    d.a_desc[nks++] = tc::umma_smem_desc(base + pl * plane, plane, 128);
                 }
             }
             d.stage_in_load = L.stage_in_load[k];
@@ -639,11 +736,15 @@ struct FkBuilder {
                 for (int ks = 0; ks < nks; ++ks)
                     if (!st.used || st.used(t, ks)) { d.tap_mask[t] |= 1u << ks; ++d.nent; }
             }
-            if (d.nent > fk::TAB_N) { fprintf(stderr, "libisg: %s: %d MMAs per M tile exceed the descriptor table\n", s.name.c_str(), d.nent); abort(); }
+            d.passes = passes_of(st);
+            d.nent_tab = d.nent * npasses(d.passes);
+            d.b_lo = (uint32_t)d.nent * st.N * 2;
+            if (P->split ? d.nent_tab > L.tab_n : d.nent > fk::TAB_N) { fprintf(stderr, "libisg: %s: %d MMAs per M tile exceed the descriptor table\n", s.name.c_str(), d.nent); abort(); }
             d.b_desc = tc::umma_smem_desc(L.blob_off + L.b_off[k], st.N * 16, 128);
             d.vec_off = L.blob_off + L.vec_off[k];
             if (st.res_load >= 0) {
                 d.res_on = 1; d.res_off = L.load_off[st.res_load]; d.res_plane_bytes = L.load_plane[st.res_load];
+                d.res_lo = L.load_lo[st.res_load];
                 d.res_mod = st.res_mod;
                 if (st.res_mod % 16) { fprintf(stderr, "libisg: res_mod must be a multiple of 16\n"); abort(); }
                 d.res_magic = magic(st.res_mod / 16);
@@ -656,11 +757,16 @@ struct FkBuilder {
                 d.cp_magic = magic(st.Cp / 16);
             }
             if (st.out_tensor >= 0) { d.Cs_out = td(st.out_tensor).Cs; d.out_planar = td(st.out_tensor).planar ? 1 : 0; }
+            d.split_out = (P->split && st.out_mode != fk::OUT_SHUF4_F32) ? 1 : 0;
+            d.stage_lo = L.stage_lo[k];
+            if (st.out_tensor >= 0) { d.out_lo_chunks = td(st.out_tensor).Cs / 8; d.Ct_out = td(st.out_tensor).Ct(); }
         }
         if (s.pool_tensor >= 0) {
             q.pool_on = 1; q.pool_in_off = L.load_off[0]; q.pool_in_plane_bytes = L.load_plane[0];
             q.pool_nchunks = td(s.pool_tensor).Cs / 8; q.pool_off = L.pool_off; q.pool_plane_bytes = L.pool_plane;
             q.pool_planar = td(s.pool_tensor).planar ? 1 : 0;
+            q.pool_grp_planes = q.pool_nchunks * (P->split ? 2 : 1);
+            q.pool_lo_in = L.load_lo[0]; q.pool_lo_out = L.pool_lo; q.pool_lo_chunks = q.pool_nchunks;
         }
         // single load buffer: may the next tile's boxes be issued as soon as the stage-0 MMAs completed?
         q.early_load = s.pool_tensor >= 0 ? 0 : 1;
@@ -688,6 +794,8 @@ struct FkBuilder {
         // constants blob in the arena
         const size_t blob = arena((size_t)L.blob_bytes / 4);
         const Spec sp = s;
+        std::vector<int> pass_bits;
+        for (auto& st : s.stages) pass_bits.push_back(passes_of(st));
         Op op;
         op.name = s.name + " [fk]";
         op.pack = [=](const HostWeights& w, float* A) {
@@ -705,6 +813,7 @@ struct FkBuilder {
                 for (int t = 0; t < ntaps; ++t)
                     for (int ks = 0; ks < nks; ++ks)
                         if (!st.used || st.used(t, ks)) slot[(size_t)t * nks + ks] = nslot++;
+                const bool lo_blocks = (pass_bits[k] & 4) != 0;
                 for (int t = 0; t < ntaps; ++t)
                     for (int kk = 0; kk < K; ++kk)
                         for (int n = 0; n < N; ++n) {
@@ -715,7 +824,10 @@ struct FkBuilder {
                                 continue;
                             }
                             const size_t idx = (size_t)blk * N * 16 + (size_t)((kk % 16) / 8) * N * 8 + (size_t)n * 8 + (kk % 8);
-                            wb[idx] = tc::f2bf(v);
+                            const uint16_t hi = tc::f2bf(v);
+                            wb[idx] = hi;
+                            // split precision: W_lo = bf16(w - W_hi) in a second run of blocks (pass A_hi.W_lo)
+                            if (lo_blocks) wb[(size_t)nslot * N * 16 + idx] = tc::f2bf(v - tc::bf2f(hi));
                         }
                 float* v = reinterpret_cast<float*>(base + L.vec_off[k]);
                 std::memcpy(v, shift.data(), sizeof(float) * N);
@@ -741,8 +853,8 @@ struct FkBuilder {
                     const LoadSpec& l = sp.loads[i];
                     const TensorD& t = P->tensors[l.tensor];
                     int rc;
-                    if (l.s2d) rc = tc::make_s2d_map(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH, sp.name.c_str());
-                    else rc = tc::make_act_map_chunks(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW + 2 * l.halo,
+                    if (l.s2d) rc = tc::make_s2d_map(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Ct(), L.TW, L.TH, sp.name.c_str());
+                    else rc = tc::make_act_map_chunks(&maps->in[i], P->ws + t.off, maxB, t.H, t.W, t.Ct(), L.TW + 2 * l.halo,
                                                       L.TH + 2 * l.halo, L.load_planes[i], sp.name.c_str(), t.planar);
                     if (rc) return rc;
                 }
@@ -750,14 +862,14 @@ struct FkBuilder {
                 for (size_t k = 0; k < 2; ++k) {
                     if (k < sp.stages.size() && sp.stages[k].out_mode == fk::OUT_STAGE && sp.stages[k].store) {
                         const TensorD& t = P->tensors[sp.stages[k].out_tensor];
-                        int rc = tc::make_act_map_chunks(&maps->out[k], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH,
+                        int rc = tc::make_act_map_chunks(&maps->out[k], P->ws + t.off, maxB, t.H, t.W, t.Ct(), L.TW, L.TH,
                                                          sp.stages[k].N / 8, sp.name.c_str(), t.planar);
                         if (rc) return rc;
                     } else maps->out[k] = maps->in[0];
                 }
                 if (sp.pool_tensor >= 0) {
                     const TensorD& t = P->tensors[sp.pool_tensor];
-                    int rc = tc::make_act_map_chunks(&maps->out[1], P->ws + t.off, maxB, t.H, t.W, t.Cs, L.TW, L.TH, t.Cs / 8,
+                    int rc = tc::make_act_map_chunks(&maps->out[1], P->ws + t.off, maxB, t.H, t.W, t.Ct(), L.TW, L.TH, t.Cs / 8,
                                                      sp.name.c_str(), t.planar);
                     if (rc) return rc;
                 }
@@ -767,7 +879,13 @@ struct FkBuilder {
         cudaFuncSetAttribute(fk::fk_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         cudaFuncSetAttribute(fk::fk_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024);
         cudaFuncSetAttribute(fk::fk_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 56 * 1024);
-        cudaFuncSetAttribute(fk::fk_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaFuncSetAttribute(fk::fk_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (P->split) {
+            cudaFuncSetAttribute(fk::fk_kernel<512, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+            cudaFuncSetAttribute(fk::fk_kernel<256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024);
+            cudaFuncSetAttribute(fk::fk_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 56 * 1024);
+            cudaFuncSetAttribute(fk::fk_pipe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        }
         int num_sms = 148;
         cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, P->device);
         auto run = [=](int which, int n, float* logits, cudaStream_t stream, bool prof) -> cudaError_t {
@@ -854,14 +972,17 @@ struct FkBuilder {
                 NormU8 nm;
                 for (int c = 0; c < 3; ++c) { nm.mean[c] = P->u8_mean[c]; nm.std[c] = P->u8_std[c]; }
                 const int total = n * (H / 4) * (W / 4);
-                return launch_pdl(prep_u8_kernel, cdiv(total, 128), 128, st, P->u8_src, H, W, px2, x2.Cs, (int)x2.planar, pin, init.Cs, total, nm);
+                return launch_pdl(prep_u8_kernel, cdiv(total, 128), 128, st, P->u8_src, H, W, px2, x2.Ct(), (int)x2.planar, pin, init.Ct(), total, nm,
+                                  (int)x2.split, init.Cs);
             }
             if (cin == 3) {
                 const int total = n * (H / 4) * (W / 4);
-                return launch_pdl(prep_kernel<3>, cdiv(total, 128), 128, st, x, H, W, px2, x2.Cs, (int)x2.planar, pin, init.Cs, total);
+                return launch_pdl(prep_kernel<3>, cdiv(total, 128), 128, st, x, H, W, px2, x2.Ct(), (int)x2.planar, pin, init.Ct(), total,
+                                  (int)x2.split, init.Cs);
             }
             const int total = n * cin * (H / 4) * (W / 4);
-            return launch_pdl(prep_generic_kernel, cdiv(total, 128), 128, st, x, cin, H, W, px2, x2.Cs, (int)x2.planar, pin, init.Cs, total);
+            return launch_pdl(prep_generic_kernel, cdiv(total, 128), 128, st, x, cin, H, W, px2, x2.Ct(), (int)x2.planar, pin, init.Ct(), total,
+                              (int)x2.split, x2.Cs, init.Cs);
         };
         P->ops.push_back(op);
     }
@@ -963,7 +1084,8 @@ struct FkBuilder {
     }
 
     // standalone 1x1 Conv wrapper over the concat of `srcs`
-    int pw_unit(const std::string& unit, const std::vector<int>& srcs, int cout, int act, const std::string& outname) {
+    int pw_unit(const std::string& unit, const std::vector<int>& srcs, int cout, int act, const std::string& outname,
+                int out_existing = -1) {
         const TensorD t0 = td(srcs[0]);
         Spec s;
         s.name = unit;
@@ -978,7 +1100,7 @@ struct FkBuilder {
             cin_total += td(srcs[i]).C;
         }
         st.N = round_up(cout, 16);
-        const int out = tensor(outname, cout, t0.H, t0.W);
+        const int out = out_existing >= 0 ? out_existing : tensor(outname, cout, t0.H, t0.W);
         st.out_tensor = out;
         macs(cout, cin_total, 1, 1, t0.H, t0.W);
         const int N = st.N;
@@ -994,6 +1116,50 @@ struct FkBuilder {
                 shift[o] = sh[o];
                 slope[o] = act == ACT_PRELU ? w.get(unit + ".act.weight")[o] : (act == ACT_RELU ? 0.f : 1.f);
             }
+        };
+        s.stages.push_back(st);
+        emit(s);
+        return out;
+    }
+
+    // Emit a block launch whose last stage may be followed by the next block's first 1x1 conv as a chained stage.
+    // Split-precision plans hold twice the planes and weights per tile: when the fused launch has no feasible tile the
+    // chained conv becomes a launch of its own (same arithmetic, one more round trip of `out`).
+    void emit_chained(Spec& s, const Next& nx, int Cprev, int Nprev, int out, int H, int W) {
+        if (nx.on) {
+            s.stages.push_back(chain_stage(nx, Cprev, Nprev));
+            if (P->split && candidates(s).empty()) {
+                s.stages.pop_back();
+                emit(s);
+                pw_unit(nx.unit, {out}, nx.mid, nx.act, "", nx.out);
+                return;
+            }
+            macs(nx.mid, Cprev, 1, 1, H, W);
+        }
+        emit(s);
+    }
+
+    // one K range of a 1x1 Conv wrapper as its own launch: out = W[:, cin_off : cin_off + C(src)] . src (+ res) (+ shift);
+    // no activation.  Used to split a convolution over a concatenation along K when the whole K does not fit a tile.
+    int pw_partial(const std::string& name, const std::string& unit, int src, int cin_total, int cin_off, int cout, int res,
+                   bool with_shift) {
+        const TensorD t0 = td(src);
+        Spec s;
+        s.name = name;
+        s.qH = t0.H; s.qW = t0.W;
+        s.loads.push_back(LoadSpec{src});
+        StageSpec st;
+        st.parts = {Part{PART_LOAD, 0}};
+        st.N = round_up(cout, 16);
+        if (res >= 0) { s.loads.push_back(LoadSpec{res}); st.res_load = 1; }
+        const int out = tensor(name, cout, t0.H, t0.W);
+        st.out_tensor = out;
+        const int N = st.N;
+        st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+            std::vector<float> sc(cout), sh(cout);
+            fold_unit(w, unit + ".conv", unit + ".bn", cout, sc.data(), sh.data());
+            put_pw(B, N, 0, t0, 0, t0.Cs / 8, w.get(unit + ".conv.weight"), cin_total, cin_off, sc.data(), cout, 0);
+            for (int o = 0; o < cout; ++o) { shift[o] = with_shift ? sh[o] : 0.f; slope[o] = 1.f; }
         };
         s.stages.push_back(st);
         emit(s);
@@ -1024,11 +1190,7 @@ struct FkBuilder {
         const int N = st.N;
         st.fill = res_out_fill(p, last, C, mid, N);
         s.stages.push_back(st);
-        if (nx.on) {
-            s.stages.push_back(chain_stage(nx, C, N));
-            macs(nx.mid, C, 1, 1, tx.H, tx.W);
-        }
-        emit(s);
+        emit_chained(s, nx, C, N, out, tx.H, tx.W);
         return out;
     }
     // last 1x1 conv + BN of a residual bottleneck and the block's PReLU: B[K = mid][N], shift, slope
@@ -1049,7 +1211,8 @@ struct FkBuilder {
         MegaLay L;
         mega::Params& q = L.q;
         std::memset(&q, 0, sizeof q);
-        if (getenv("ISG_FK_NO_MEGA") || nblocks > mega::MAX_BLOCKS || H % mega::CLUSTER) return L;
+        // split-precision plans keep hi + lo of x, m1 and d: twice the shared memory a 4-CTA cluster has -> per-block launches
+        if (P->split || getenv("ISG_FK_NO_MEGA") || nblocks > mega::MAX_BLOCKS || H % mega::CLUSTER) return L;
         q.H = H; q.W = W; q.R = H / mega::CLUSTER;
         q.Cs = round_up(C, 16); q.Cm = round_up(mid, 16);
         q.npx = q.R * W;
@@ -1285,11 +1448,7 @@ struct FkBuilder {
             for (int o = 0; o < cout; ++o) { shift[o] = sh[o] + shm[o]; slope[o] = wv.get(p + ".prelu.weight")[o]; }
         };
         s.stages.push_back(st);
-        if (nx.on) {
-            s.stages.push_back(chain_stage(nx, cout, N));
-            macs(nx.mid, cout, 1, 1, h, w);
-        }
-        emit(s);
+        emit_chained(s, nx, cout, N, out, h, w);
         return out;
     }
 
@@ -1329,11 +1488,36 @@ struct FkBuilder {
             }
         };
         s.stages.push_back(st);
-        if (nx.on) {
-            s.stages.push_back(chain_stage(nx, cout, N));
-            macs(nx.mid, cout, 1, 1, t0.H, t0.W);
+        if (P->split && candidates(s).empty()) {
+            // the whole K (mid + C0 + C1 channels, hi + lo) and its weights do not fit one tile (bottle3_1: 304 x 128):
+            // resconv runs split along K over the two concatenated inputs, r = W[:, :C0] . x0 + shift, r += W[:, C0:] . x1,
+            // and the block launch takes r as its residual
+            int r = pw_partial(p + ".resconv[x0]", p + ".resconv.0", x0, Cin, 0, cout, -1, true);
+            r = pw_partial(p + ".resconv[x1]+", p + ".resconv.0", x1, Cin, t0.C, cout, r, false);
+            Spec c;
+            c.name = p + ".dw+convs.2+res";
+            c.qH = t0.H; c.qW = t0.W;
+            c.loads.push_back(LoadSpec{m1, 0, -1, 1});
+            c.loads.push_back(LoadSpec{r});
+            c.st = s.st;
+            StageSpec st2;
+            st2.parts = {Part{PART_STENCIL, -1}};
+            st2.N = N;
+            st2.res_load = 1;
+            st2.out_tensor = out;
+            st2.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
+                std::vector<float> sc(cout), sh(cout);
+                fold_unit(w, p + ".convs.2.conv", p + ".convs.2.bn", cout, sc.data(), sh.data());
+                const float* W2 = w.get(p + ".convs.2.conv.weight");
+                for (int k = 0; k < mid; ++k)
+                    for (int o = 0; o < cout; ++o) B[(size_t)k * N + o] = W2[(size_t)o * mid + k] * sc[o];
+                for (int o = 0; o < cout; ++o) { shift[o] = sh[o]; slope[o] = last_prelu ? w.get(p + ".prelu.weight")[o] : 0.f; }
+            };
+            c.stages.push_back(st2);
+            emit_chained(c, nx, cout, N, out, t0.H, t0.W);
+            return out;
         }
-        emit(s);
+        emit_chained(s, nx, cout, N, out, t0.H, t0.W);
         return out;
     }
 
@@ -1554,6 +1738,8 @@ struct FkBuilder {
         st.N = 16;
         st.out_mode = fk::OUT_SHUF4_F32;
         st.to_logits = true;
+        if (getenv("ISG_X3_TAIL_PASSES")) st.passes = atoi(getenv("ISG_X3_TAIL_PASSES"));   // experiments: 1 / 3 / 5 / 7
+        const int tail_passes = passes_of(st);
         st.fill = [=](const HostWeights& w, float* B, float* shift, float* slope) {
             const float* W1 = w.get("bottle6_1.weight");  // [16][4][8][8]
             const float* b1 = w.get("bottle6_1.bias");
@@ -1611,7 +1797,8 @@ struct FkBuilder {
         };
         op.launch = [=](int n, const float*, float* logits, cudaStream_t stream) {
             TailFixParams p;
-            p.in = reinterpret_cast<const bf16*>(P->ws + ty.off); p.Hq = ty.H; p.Wq = ty.W; p.Cs = ty.Cs; p.planar = ty.planar ? 1 : 0;
+            p.in = reinterpret_cast<const bf16*>(P->ws + ty.off); p.Hq = ty.H; p.Wq = ty.W; p.Cs = ty.Ct(); p.planar = ty.planar ? 1 : 0;
+            p.lo = (ty.split && (tail_passes & 2)) ? 1 : 0;   // the same operand value the GEMM saw
             p.logits = logits; p.g = P->arena + og; p.gb = P->arena + ogb;
             const int H = 4 * ty.H, W = 4 * ty.W;
             p.total = n * (2 * W + 2 * (H - 2));

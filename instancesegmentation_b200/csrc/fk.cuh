@@ -27,7 +27,7 @@ namespace isg {
 namespace fk {
 
 constexpr int THREADS = 512;    // one CTA per SM; the 256-thread instantiation runs two CTAs per SM
-constexpr int MAX_LOADS = 5;
+constexpr int MAX_LOADS = 10;   // split precision: every tensor arrives as a hi and a lo box
 constexpr int MAX_KS = 20;      // K <= 320 per tap
 constexpr int MAX_MMA_TAPS = 9;
 constexpr int MAX_ST_TAPS = 25;
@@ -49,11 +49,22 @@ struct Stage {
     int N, ntaps, nks;
     int tap_off[MAX_MMA_TAPS];     // pixel offsets dy*pitch + dx
     uint32_t tap_mask[MAX_MMA_TAPS];   // bit ks set: K slice ks of this tap has weights (structural zeros are skipped)
-    int nent;                      // MMAs per M tile = set bits; the packed B blocks follow the same order
+    int nent;                      // MMAs per M tile and pass = set bits; the packed B blocks follow the same order
+    int nent_tab;                  // split precision: entries of the (A, B) table = nent * number of passes
     uint64_t a_desc[MAX_KS];       // UMMA descriptor of K slice ks (16 channels = 2 planes) relative to the
                                    // dynamic shared memory base: the kernel adds (base + row offset) >> 4
     uint64_t b_desc;               // descriptor of the first packed B block [tap][ks][2][N][8] bf16
     uint32_t a_buf_mask;           // bit ks set: that K slice lives in the double-buffered load area
+    // split precision (ISG_MODE_BF16X3): every operand element is a bf16 pair hi + lo (hi = bf16(v), lo = bf16(v - hi)).
+    // passes: bit 0 = A_hi.W_hi, bit 1 = A_lo.W_hi, bit 2 = A_hi.W_lo accumulate into the same TMEM tile (0 = plain bf16)
+    int passes;
+    uint32_t a_lo[MAX_KS];         // K slice ks: distance from its hi planes to its lo planes, 16-byte units
+    uint32_t b_lo;                 // distance from the W_hi blocks to the W_lo blocks, 16-byte units
+    int res_lo;                    // bytes from a residual hi plane to its lo plane (0: residual is plain bf16)
+    int split_out;                 // 1: the output is written as hi + lo
+    int stage_lo;                  // bytes from a staging hi plane to its lo plane
+    int out_lo_chunks;             // 8-channel chunks from a channel's hi half to its lo half in the output tensor
+    int Ct_out;                    // storage channels of the output tensor (direct-store modes)
     int stage_in_load;             // staging planes alias a load region (follow the load buffer)
     int vec_off;                   // fp32 shift[N], slope[N]
     int pitch;                     // pitch of the M index space (TW + 2*halo of the tap planes)
@@ -77,6 +88,7 @@ struct Stencil {
     int vec_off;                   // fp32 shift[C], slope[C], then bw[5][C] when sep5
     int sep5;
     int out_off, out_plane_bytes;
+    int in_lo, out_lo;             // split precision: bytes from a hi plane to its lo plane (input / output planes)
 };
 
 struct Params {
@@ -90,6 +102,8 @@ struct Params {
     int pipe_slots;                // > 0: warp-specialised single-stage launch (fk_pipe_kernel) with this many load slots
     int acc_stride;                // ... and two TMEM accumulators this many columns apart
     int pipe_groups;               // ... and this many epilogue warp groups (of 4 warps); the rest issue MMAs
+    int split;                     // 1: split-precision launch (the *<true> kernel instantiations)
+    int tab_n;                     // split: (A, B) pairs per (stage, load buffer) table
     int nlbuf;                     // load buffers of the generic loop: 2 = double buffered; 1 = the co-resident
                                    // CTA hides the load latency instead (two 256-thread CTAs per SM)
     int early_load;                // nlbuf == 1: the load buffer is dead once the stage-0 MMAs completed
@@ -98,6 +112,8 @@ struct Params {
     // optional 2x2 max-pool of a folded space-to-depth load (BottleneckDown2's residual, segment.py:145):
     // max over the four sub-pixel plane groups -> pool planes -> TMA store through the second out map
     int pool_on, pool_in_off, pool_in_plane_bytes, pool_nchunks, pool_off, pool_plane_bytes, pool_planar;
+    int pool_grp_planes;           // planes between the sub-pixel groups of the folded load (pool_nchunks, or twice that when split)
+    int pool_lo_in, pool_lo_out, pool_lo_chunks;   // split precision: hi -> lo distances (bytes, bytes, output chunks)
     int nstages; Stage stage[2];
     int bar_off;                   // 3 mbarriers + tmem slot
     long long* prof;               // debug (ISG_FK_PROF=1): per-CTA phase time stamps, else null
@@ -156,6 +172,13 @@ __device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
     return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
 }
 
+// split precision: v = hi + lo with hi = bf16(v), lo = bf16(v - hi) (two channels per word)
+__device__ __forceinline__ void split_bf16(float a, float b, uint32_t& hi, uint32_t& lo) {
+    hi = pack_bf16(a, b);
+    const float2 h = bf2_to_f2(hi);
+    lo = pack_bf16(a - h.x, b - h.y);
+}
+
 // ---- depthwise stencil: haloed input planes -> A operand planes ----
 // SEP5 = false: 3x3 with dilation; SEP5 = true: the composed (5,1)x(1,5) pair (25 taps).
 // A thread owns one channel pair of one column and a strip of ST_ROWS output rows DIL apart, so every
@@ -164,7 +187,8 @@ __device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
 // neighbouring columns = 128 contiguous bytes, one shared-memory wavefront.  Each output accumulates its
 // taps in (ty, tx) order from zero, whatever the strip it falls in.
 // Output rows [rb, TH) of the tile; ST_ROWS = rows per strip.
-template <int KS, int DIL, int ST_ROWS, int NT>
+// SPLIT: input and output planes are hi + lo pairs (s.in_lo / s.out_lo bytes apart); the arithmetic is the same fp32.
+template <int KS, int DIL, int ST_ROWS, int NT, bool SPLIT = false>
 __device__ __forceinline__ void stencil_strips(uint8_t* smem, const Stencil& s, int rb, int TH, int TW, int Wimg, int x0, int boff) {
     constexpr int NW = NT / 32, R = KS / 2;
     const int C = s.nchunks * 8, pitch16 = s.in_pitch * 16;
@@ -199,7 +223,13 @@ __device__ __forceinline__ void stencil_strips(uint8_t* smem, const Stencil& s, 
             const uint8_t* row = in + (row0 + min(iy * DIL, rmax)) * pitch16;
             float2 v[KS];
 #pragma unroll
-            for (int tx = 0; tx < KS; ++tx) v[tx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(row + tx * DIL * 16));
+            for (int tx = 0; tx < KS; ++tx) {
+                v[tx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(row + tx * DIL * 16));
+                if (SPLIT) {
+                    const float2 l = bf2_to_f2(*reinterpret_cast<const uint32_t*>(row + s.in_lo + tx * DIL * 16));
+                    v[tx].x += l.x; v[tx].y += l.y;
+                }
+            }
 #pragma unroll
             for (int j = 0; j < ST_ROWS; ++j) {
                 const int ty = iy - j;
@@ -229,20 +259,29 @@ __device__ __forceinline__ void stencil_strips(uint8_t* smem, const Stencil& s, 
         for (int j = 0; j < ST_ROWS; ++j) {
             float a0 = acc[j].x + sh.x, a1 = acc[j].y + sh.y;
             a0 = a0 >= 0.f ? a0 : a0 * sl.x; a1 = a1 >= 0.f ? a1 : a1 * sl.y;
-            const uint32_t o = pack_bf16(a0, a1);
-            if (j * DIL < nrows) *reinterpret_cast<uint32_t*>(out + j * DIL * TW * 16) = o;
+            if (SPLIT) {
+                uint32_t oh, ol;
+                split_bf16(a0, a1, oh, ol);
+                if (j * DIL < nrows) {
+                    *reinterpret_cast<uint32_t*>(out + j * DIL * TW * 16) = oh;
+                    *reinterpret_cast<uint32_t*>(out + s.out_lo + j * DIL * TW * 16) = ol;
+                }
+            } else {
+                const uint32_t o = pack_bf16(a0, a1);
+                if (j * DIL < nrows) *reinterpret_cast<uint32_t*>(out + j * DIL * TW * 16) = o;
+            }
         }
         cg += NW;
     }
 }
 
 // SEP5 = false: 3x3 with dilation 1 / 2 / 4 (segment.py:399-418); SEP5 = true: the composed 5x5
-template <bool SEP5, int NT>
+template <bool SEP5, int NT, bool SPLIT = false>
 __device__ __forceinline__ void run_stencil(uint8_t* smem, const Stencil& s, int TH, int TW, int Wimg, int x0, int boff) {
-    if (SEP5) stencil_strips<5, 1, 4, NT>(smem, s, 0, TH, TW, Wimg, x0, boff);
-    else if (s.dil == 1) stencil_strips<3, 1, 4, NT>(smem, s, 0, TH, TW, Wimg, x0, boff);
-    else if (s.dil == 2) stencil_strips<3, 2, 4, NT>(smem, s, 0, TH, TW, Wimg, x0, boff);
-    else stencil_strips<3, 4, 4, NT>(smem, s, 0, TH, TW, Wimg, x0, boff);
+    if (SEP5) stencil_strips<5, 1, 4, NT, SPLIT>(smem, s, 0, TH, TW, Wimg, x0, boff);
+    else if (s.dil == 1) stencil_strips<3, 1, 4, NT, SPLIT>(smem, s, 0, TH, TW, Wimg, x0, boff);
+    else if (s.dil == 2) stencil_strips<3, 2, 4, NT, SPLIT>(smem, s, 0, TH, TW, Wimg, x0, boff);
+    else stencil_strips<3, 4, 4, NT, SPLIT>(smem, s, 0, TH, TW, Wimg, x0, boff);
 }
 
 __device__ __forceinline__ uint32_t bf2max(uint32_t a, uint32_t b) {
@@ -254,47 +293,97 @@ __device__ __forceinline__ uint4 bf8max(uint4 a, uint4 b) {
 }
 
 // 2x2 max-pool from the four sub-pixel plane groups of a folded space-to-depth load
-template <int NT>
+// value of 8 channels stored as a hi and a lo chunk (the sum is exact in fp32)
+__device__ __forceinline__ void load_split8(const uint8_t* hi, int lo_off, float* f) {
+    float l[8];
+    unpack8(*reinterpret_cast<const uint4*>(hi), f);
+    unpack8(*reinterpret_cast<const uint4*>(hi + lo_off), l);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] += l[i];
+}
+
+template <int NT, bool SPLIT = false>
 __device__ __forceinline__ void run_pool(uint8_t* smem, const Params& p, int boff) {
     const int npix = p.TH * p.TW;
-    const size_t grp = (size_t)p.pool_nchunks * p.pool_in_plane_bytes;
+    const size_t grp = (size_t)p.pool_grp_planes * p.pool_in_plane_bytes;
     for (int item = threadIdx.x; item < npix * p.pool_nchunks; item += NT) {
         const int k = fastdiv(item, p.npix_magic), pix = item - k * npix;
         const uint8_t* src = smem + p.pool_in_off + boff + (size_t)k * p.pool_in_plane_bytes + (size_t)pix * 16;
-        const uint4 a = *reinterpret_cast<const uint4*>(src), b = *reinterpret_cast<const uint4*>(src + grp);
-        const uint4 c = *reinterpret_cast<const uint4*>(src + 2 * grp), d = *reinterpret_cast<const uint4*>(src + 3 * grp);
-        *reinterpret_cast<uint4*>(smem + p.pool_off + (size_t)k * p.pool_plane_bytes + (size_t)pix * 16) =
-            bf8max(bf8max(a, b), bf8max(c, d));
+        uint8_t* dst = smem + p.pool_off + (size_t)k * p.pool_plane_bytes + (size_t)pix * 16;
+        if (SPLIT) {
+            float m[8], f[8];
+            load_split8(src, p.pool_lo_in, m);
+#pragma unroll
+            for (int g = 1; g < 4; ++g) {
+                load_split8(src + g * grp, p.pool_lo_in, f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], f[i]);
+            }
+            uint32_t h[4], l[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) split_bf16(m[2 * i], m[2 * i + 1], h[i], l[i]);
+            *reinterpret_cast<uint4*>(dst) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(dst + p.pool_lo_out) = make_uint4(l[0], l[1], l[2], l[3]);
+        } else {
+            const uint4 a = *reinterpret_cast<const uint4*>(src), b = *reinterpret_cast<const uint4*>(src + grp);
+            const uint4 c = *reinterpret_cast<const uint4*>(src + 2 * grp), d = *reinterpret_cast<const uint4*>(src + 3 * grp);
+            *reinterpret_cast<uint4*>(dst) = bf8max(bf8max(a, b), bf8max(c, d));
+        }
     }
 }
 
-// MMAs of the M tiles mt = first, first + step, ...; called by ONE thread per issuing warp
-constexpr int TAB_N = 40;   // A descriptors per (stage, load buffer): ntaps * nks <= 40
+constexpr int TAB_N = 40;          // A descriptors per (stage, load buffer): ntaps * nks <= 40
+constexpr int TAB_N_SPLIT = 128;   // split precision: (A, B) descriptor pairs per table, passes * ntaps * nks <= 128
 
 // A-descriptor table of one stage and one load buffer, built once per CTA in shared memory:
-// entry (t * nks + ks) = descriptor of K slice ks shifted by conv tap t, absolute shared address
-template <int NT>
+// entry (t * nks + ks) = descriptor of K slice ks shifted by conv tap t, absolute shared address.
+// SPLIT: the table holds (A, B) descriptor pairs, one run of entries per pass of Stage::passes:
+//   A_hi . W_hi, then A_lo . W_hi (the same weight blocks again), then A_hi . W_lo.
+template <int NT, bool SPLIT = false>
 __device__ __forceinline__ void build_desc_table(const Params& p, uint64_t* tabs, uint32_t smem_base) {
     const uint64_t base16 = smem_base >> 4;
+    const int stride = SPLIT ? p.tab_n * 2 : TAB_N;
     for (int i = threadIdx.x; i < p.nstages * 3; i += NT) {   // one thread per (stage, load buffer) table
         const int k = i / 3, buf = i - 3 * k;
         const Stage& s = p.stage[k];
-        uint64_t* tab = tabs + i * TAB_N;
+        uint64_t* tab = tabs + i * stride;
         int j = 0;
-        for (int t = 0; t < s.ntaps; ++t)
-            for (int ks = 0; ks < s.nks; ++ks) {
-                if (!((s.tap_mask[t] >> ks) & 1u)) continue;
-                uint64_t d = s.a_desc[ks] + base16 + (uint64_t)(int64_t)s.tap_off[t];
-                if ((s.a_buf_mask >> ks) & 1u) d += (uint64_t)((buf * p.lbuf_stride) >> 4);
-                tab[j++] = d;
-            }
+        for (int pass = 0; pass < (SPLIT ? 3 : 1); ++pass) {
+            if (SPLIT && !((s.passes >> pass) & 1)) continue;
+            uint64_t bd = s.b_desc + base16 + (pass == 2 ? s.b_lo : 0u);
+            for (int t = 0; t < s.ntaps; ++t)
+                for (int ks = 0; ks < s.nks; ++ks) {
+                    if (!((s.tap_mask[t] >> ks) & 1u)) continue;
+                    uint64_t d = s.a_desc[ks] + base16 + (uint64_t)(int64_t)s.tap_off[t];
+                    if ((s.a_buf_mask >> ks) & 1u) d += (uint64_t)((buf * p.lbuf_stride) >> 4);
+                    if (SPLIT) {
+                        if (pass == 1) d += s.a_lo[ks];
+                        tab[2 * j] = d; tab[2 * j + 1] = bd;
+                        bd += (uint32_t)s.N * 2;
+                        ++j;
+                    } else {
+                        tab[j++] = d;
+                    }
+                }
+        }
     }
 }
 
 // MMAs of the M tiles mt = first, first + step, ...; called by ONE thread per issuing warp
+template <bool SPLIT = false>
 __device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, const uint64_t* tab, uint32_t smem_base,
                                           uint32_t tmem_base, int first, int step) {
     const uint32_t idesc = tc::umma_idesc_bf16(128, s.N);
+    if (SPLIT) {
+        const int n = s.nent_tab;
+        for (int mt = first; mt < p.n_mt; mt += step) {
+            const uint64_t row = (uint64_t)(mt * 128);
+            tc::umma_bf16(tmem_base + mt * s.N, tab[0] + row, tab[1], idesc, 0u);
+#pragma unroll 4
+            for (int j = 1; j < n; ++j) tc::umma_bf16(tmem_base + mt * s.N, tab[2 * j] + row, tab[2 * j + 1], idesc, 1u);
+        }
+        return;
+    }
     const uint64_t bd0 = s.b_desc + (smem_base >> 4);
     const uint32_t b_step = (uint32_t)s.N * 2;  // 16-byte units per [2][N][8] block
     const int n = s.nent;
@@ -347,6 +436,7 @@ __device__ __forceinline__ EpiGeom epi_geom(const Params& p, const Stage& s, int
     return g;
 }
 
+template <bool SPLIT = false>
 __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, const Stage& s, uint32_t tmem_base,
                                              int b, int x0, int y0, int boff, int grp, int NGROUPS) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -359,8 +449,8 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
     const int out_mode = s.out_mode, N = s.N;
     // per-tile bases: one 64-bit product per call, 32-bit offsets inside the image afterwards
     uint8_t* gimg = static_cast<uint8_t*>(s.gptr);
-    if (out_mode == OUT_S2D) gimg += (size_t)b * (p.H >> 1) * (p.W >> 1) * (4 * N) * sizeof(bf16);
-    else if (out_mode == OUT_SHUF_BF16) gimg += (size_t)b * p.H * p.W * (s.shuf * s.shuf * s.Cs_out) * sizeof(bf16);
+    if (out_mode == OUT_S2D) gimg += (size_t)b * (p.H >> 1) * (p.W >> 1) * (SPLIT ? s.Ct_out : 4 * N) * sizeof(bf16);
+    else if (out_mode == OUT_SHUF_BF16) gimg += (size_t)b * p.H * p.W * (s.shuf * s.shuf * (SPLIT ? s.Ct_out : s.Cs_out)) * sizeof(bf16);
     else if (out_mode == OUT_SHUF4_F32) gimg += (size_t)b * p.H * p.W * 16 * sizeof(float);
     uint8_t* stage = smem + s.stage_off + (s.stage_in_load ? boff : 0);
     const uint8_t* res = smem + s.res_off + boff;
@@ -388,6 +478,13 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
             float f[16];
             unpack8(*reinterpret_cast<const uint4*>(rp), f);
             unpack8(*reinterpret_cast<const uint4*>(rp + s.res_plane_bytes), f + 8);
+            if (SPLIT && s.res_lo) {   // residual value = hi + lo (exact in fp32), then one add as in the reference
+                float l[16];
+                unpack8(*reinterpret_cast<const uint4*>(rp + s.res_lo), l);
+                unpack8(*reinterpret_cast<const uint4*>(rp + s.res_lo + s.res_plane_bytes), l + 8);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] += l[i];
+            }
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] += f[i];
         }
@@ -409,14 +506,27 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
                     *reinterpret_cast<float4*>(o + ry * 4 * p.W) = make_float4(v[4 * ry], v[4 * ry + 1], v[4 * ry + 2], v[4 * ry + 3]);
             }
         } else {
-            const uint4 q0 = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-            const uint4 q1 = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
-                                        pack_bf16(v[14], v[15]));
+            uint4 q0, q1, l0, l1;
+            if (SPLIT && s.split_out) {
+                uint32_t h[8], l[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) split_bf16(v[2 * i], v[2 * i + 1], h[i], l[i]);
+                q0 = make_uint4(h[0], h[1], h[2], h[3]); q1 = make_uint4(h[4], h[5], h[6], h[7]);
+                l0 = make_uint4(l[0], l[1], l[2], l[3]); l1 = make_uint4(l[4], l[5], l[6], l[7]);
+            } else {
+                q0 = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                q1 = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
+                l0 = l1 = make_uint4(0, 0, 0, 0);
+            }
             if (out_mode == OUT_STAGE) {
                 if (!s.stage_compact || g.geom) {
                     uint8_t* d = stage + (size_t)(col0 >> 3) * s.stage_plane_bytes + (size_t)(s.stage_compact ? g.pc : g.m) * 16;
                     *reinterpret_cast<uint4*>(d) = q0;
                     *reinterpret_cast<uint4*>(d + s.stage_plane_bytes) = q1;
+                    if (SPLIT && s.split_out) {
+                        *reinterpret_cast<uint4*>(d + s.stage_lo) = l0;
+                        *reinterpret_cast<uint4*>(d + s.stage_lo + s.stage_plane_bytes) = l1;
+                    }
                 }
             } else if (g.inimg) {
                 bf16* o;
@@ -424,16 +534,21 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
                 if (out_mode == OUT_S2D) {
                     const int sc = ((g.y & 1) * 2 + (g.x & 1)) * N + col0, pix = (g.y >> 1) * (p.W >> 1) + (g.x >> 1);
                     if (s.out_planar) { plane = (p.H >> 1) * (p.W >> 1) * 8; o = reinterpret_cast<bf16*>(gimg) + (sc >> 3) * plane + pix * 8; }
-                    else o = reinterpret_cast<bf16*>(gimg) + pix * (4 * N) + sc;
+                    else o = reinterpret_cast<bf16*>(gimg) + pix * (SPLIT ? s.Ct_out : 4 * N) + sc;
                 } else {  // OUT_SHUF_BF16: column = phase * Cp + channel, phase = (py, px) of the x`shuf` upsampling
                     const int phase = fastdiv(cc, s.cp_magic), ch = col0 - phase * s.Cp;
                     const int py = phase >> 1, px = phase & 1;   // shuf == 2 (ConvT k4 s2)
                     const int pix = (g.y * s.shuf + py) * (p.W * s.shuf) + g.x * s.shuf + px;
                     if (s.out_planar) { plane = p.H * p.W * s.shuf * s.shuf * 8; o = reinterpret_cast<bf16*>(gimg) + (ch >> 3) * plane + pix * 8; }
-                    else o = reinterpret_cast<bf16*>(gimg) + pix * s.Cs_out + ch;
+                    else o = reinterpret_cast<bf16*>(gimg) + pix * (SPLIT ? s.Ct_out : s.Cs_out) + ch;
                 }
                 st_global_16(o, q0);
                 st_global_16(o + plane, q1);
+                if (SPLIT && s.split_out) {   // the lo half sits out_lo_chunks chunks after the hi half (planes or 8-channel groups)
+                    o += (size_t)s.out_lo_chunks * plane;
+                    st_global_16(o, l0);
+                    st_global_16(o + plane, l1);
+                }
             }
         }
         if (nxt >= nitems) break;
@@ -443,7 +558,7 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
     }
 }
 
-template <int NT>
+template <int NT, bool SPLIT = false>
 __global__ void __launch_bounds__(NT, NT == 512 ? 1 : (NT == 256 ? 2 : 4))
 fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtensorMap m1,
           const __grid_constant__ CUtensorMap m2, const __grid_constant__ CUtensorMap m3,
@@ -473,7 +588,8 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, p.tmem_cols);
-    build_desc_table<NT>(p, tabs, tc::smem_u32(smem));
+    build_desc_table<NT, SPLIT>(p, tabs, tc::smem_u32(smem));
+    const int tab_stride = SPLIT ? p.tab_n * 2 : TAB_N;
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
@@ -526,8 +642,8 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
         if (it == 0) FK_STAMP(2);
 
         if (p.st.on) {
-            if (p.st.sep5) run_stencil<true, NT>(smem, p.st, p.TH, p.TW, p.W, x0, boff);
-            else run_stencil<false, NT>(smem, p.st, p.TH, p.TW, p.W, x0, boff);
+            if (p.st.sep5) run_stencil<true, NT, SPLIT>(smem, p.st, p.TH, p.TW, p.W, x0, boff);
+            else run_stencil<false, NT, SPLIT>(smem, p.st, p.TH, p.TW, p.W, x0, boff);
             tc::fence_proxy_async();
             __syncthreads();
         }
@@ -537,7 +653,7 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             const Stage& s = p.stage[k];
             if ((tid & 31) == 0 && warp < n_issuers) {
                 tc::tc_fence_after();
-                issue_mma(p, s, tabs + (3 * k + buf) * TAB_N, smem_base, tmem_base, warp, NWARPS);
+                issue_mma<SPLIT>(p, s, tabs + (3 * k + buf) * tab_stride, smem_base, tmem_base, warp, NWARPS);
                 tc::umma_commit(&bars[2 + k]);
             }
             __syncwarp();
@@ -545,21 +661,24 @@ fk_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtens
             if (it == 0) FK_STAMP(4 + 2 * k);
             FK_ACC(10 + 2 * k);
             tc::tc_fence_after();
-            if (k == 0 && p.pool_on) run_pool<NT>(smem, p, boff);   // before the load buffer may be refilled
+            if (k == 0 && p.pool_on) run_pool<NT, SPLIT>(smem, p, boff);   // before the load buffer may be refilled
             if (k == 0 && tid == 0 && !dbl && p.early_load && next < p.total_tiles) issue_loads(next, 0);
-            run_epilogue(smem, p, s, tmem_base, b, x0, y0, boff, warp >> 2, NT / 128);
+            run_epilogue<SPLIT>(smem, p, s, tmem_base, b, x0, y0, boff, warp >> 2, NT / 128);
             tc::fence_proxy_async();
             tc::tc_fence_before();
             __syncthreads();
             if (it == 0) FK_STAMP(5 + 2 * k);
             FK_ACC(11 + 2 * k);
             if (tid == 0 && s.out_mode == OUT_STAGE && s.store) {
-                tc::tma_store_act(k ? &mo1 : &mo0, smem + s.stage_off + (s.stage_in_load ? boff : 0), s.out_planar, x0, y0,
-                                  s.store_chunk0, b);
+                const uint8_t* src = smem + s.stage_off + (s.stage_in_load ? boff : 0);
+                tc::tma_store_act(k ? &mo1 : &mo0, src, s.out_planar, x0, y0, s.store_chunk0, b);
+                if (SPLIT && s.split_out)
+                    tc::tma_store_act(k ? &mo1 : &mo0, src + s.stage_lo, s.out_planar, x0, y0, s.store_chunk0 + s.out_lo_chunks, b);
                 tc::tma_store_commit();
             }
             if (k == 0 && tid == 0 && p.pool_on) {
                 tc::tma_store_act(&mo1, smem + p.pool_off, p.pool_planar, x0, y0, 0, b);
+                if (SPLIT) tc::tma_store_act(&mo1, smem + p.pool_off + p.pool_lo_out, p.pool_planar, x0, y0, p.pool_lo_chunks, b);
                 tc::tma_store_commit();
             }
         }
@@ -588,6 +707,7 @@ constexpr int PIPE_THREADS = 512;
 
 __device__ __forceinline__ void epi_bar_sync(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
 
+template <bool SPLIT = false>
 __global__ void __launch_bounds__(PIPE_THREADS, 1)
 fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ CUtensorMap m1,
                const __grid_constant__ CUtensorMap m2, const __grid_constant__ CUtensorMap m3,
@@ -614,7 +734,8 @@ fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ C
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, p.tmem_cols);
-    build_desc_table<PIPE_THREADS>(p, tabs, tc::smem_u32(smem));
+    build_desc_table<PIPE_THREADS, SPLIT>(p, tabs, tc::smem_u32(smem));
+    const int tab_stride = SPLIT ? p.tab_n * 2 : TAB_N;
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
@@ -658,7 +779,7 @@ fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ C
                 tc::mbar_wait_backoff(&bars[slot], use & 1);
                 if (it >= 2) tc::mbar_wait_backoff(&bars[8 + acc], ((it >> 1) - 1) & 1);   // the epilogue has drained this accumulator
                 tc::tc_fence_after();
-                issue_mma(p, s, tabs + slot * TAB_N, smem_base, tmem_base + acc * p.acc_stride, first, PIPE_ISSUERS);
+                issue_mma<SPLIT>(p, s, tabs + slot * tab_stride, smem_base, tmem_base + acc * p.acc_stride, first, PIPE_ISSUERS);
                 tc::umma_commit(&bars[3 + slot]);
                 tc::umma_commit(&bars[6 + acc]);
             }
@@ -679,7 +800,7 @@ fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ C
                 if (leader) tc::tma_store_wait_read();
                 epi_bar_sync(PIPE_EPI_WARPS * 32);
             }
-            run_epilogue(smem, p, s, tmem_base + acc * p.acc_stride, b, x0, y0, 0, (warp - PIPE_EPI_WARP0) >> 2, p.pipe_groups);
+            run_epilogue<SPLIT>(smem, p, s, tmem_base + acc * p.acc_stride, b, x0, y0, 0, (warp - PIPE_EPI_WARP0) >> 2, p.pipe_groups);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&bars[8 + acc]);
@@ -688,6 +809,8 @@ fk_pipe_kernel(const __grid_constant__ CUtensorMap m0, const __grid_constant__ C
                 epi_bar_sync(PIPE_EPI_WARPS * 32);
                 if (leader) {
                     tc::tma_store_act(&mo0, smem + s.stage_off, s.out_planar, x0, y0, s.store_chunk0, b);
+                    if (SPLIT && s.split_out)
+                        tc::tma_store_act(&mo0, smem + s.stage_off + s.stage_lo, s.out_planar, x0, y0, s.store_chunk0 + s.out_lo_chunks, b);
                     tc::tma_store_commit();
                 }
             }

@@ -60,7 +60,7 @@ int isg_plan_create(int device, int in_channel, int height, int width, int max_b
     if (height < 16 || width < 16 || height % 16 || width % 16)
         return fail(ISG_ERR_ARG, "H and W must be multiples of 16 (>=16), got %dx%d", height, width);
     if (max_batch < 1) return fail(ISG_ERR_ARG, "max_batch must be >= 1");
-    if (mode != ISG_MODE_FP32 && mode != ISG_MODE_BF16) return fail(ISG_ERR_ARG, "unknown mode %d", mode);
+    if (mode != ISG_MODE_FP32 && mode != ISG_MODE_BF16 && mode != ISG_MODE_BF16X3) return fail(ISG_ERR_ARG, "unknown mode %d", mode);
     ISG_CUDA(cudaSetDevice(device));
     cudaDeviceProp prop;
     ISG_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -97,6 +97,20 @@ int isg_plan_create(int device, int in_channel, int height, int width, int max_b
     ISG_CUDA(cudaDeviceSynchronize());
     *out = p.release();
     return ISG_OK;
+}
+
+int isg_plan_dry_run(int in_channel, int height, int width, int max_batch, int mode) {
+    if (in_channel < 1 || in_channel > 64 || height < 16 || width < 16 || height % 16 || width % 16 || max_batch < 1 ||
+        (mode != ISG_MODE_FP32 && mode != ISG_MODE_BF16 && mode != ISG_MODE_BF16X3))
+        return fail(ISG_ERR_ARG, "isg_plan_dry_run: bad argument");
+    isg_plan p;
+    p.device = 0; p.cin = in_channel; p.H = height; p.W = width; p.max_batch = max_batch; p.mode = mode;
+    p.spec = build_state_spec(in_channel);
+    build_plan(&p);            // aborts with a message when a fused launch has no feasible tile
+    cudaGetLastError();        // attribute calls fail without a device: irrelevant here
+    if (getenv("ISG_FK_VERBOSE"))
+        for (auto& op : p.ops) fprintf(stderr, "dry-run launch: %s\n", op.name.c_str());
+    return (int)p.ops.size();
 }
 
 int isg_plan_destroy(isg_plan* plan) {
@@ -259,8 +273,9 @@ int isg_plan_tap_read(isg_plan* plan, int index, int n, float* out_host) {
         return fail(ISG_ERR_ARG, "isg_plan_tap_read: bad argument");
     if (n < 1 || n > plan->max_batch) return fail(ISG_ERR_ARG, "tap read of %d images (max_batch %d)", n, plan->max_batch);
     const TensorD& t = plan->tensors[plan->taps[index]];
-    const bool is_bf16 = plan->mode == ISG_MODE_BF16;
-    const size_t per_img = (size_t)t.H * t.W * t.Cs, es = is_bf16 ? 2 : 4;
+    const bool is_bf16 = plan->mode != ISG_MODE_FP32;
+    const int Ct = t.Ct();   // storage channels (twice Cs when the tensor is stored as hi + lo)
+    const size_t per_img = (size_t)t.H * t.W * Ct, es = is_bf16 ? 2 : 4;
     std::vector<uint8_t> raw(per_img * n * es);
     ISG_CUDA(cudaSetDevice(plan->device));
     ISG_CUDA(cudaDeviceSynchronize());
@@ -271,11 +286,17 @@ int isg_plan_tap_read(isg_plan* plan, int index, int n, float* out_host) {
             for (int y = 0; y < t.H; ++y)
                 for (int x = 0; x < t.W; ++x) {
                     size_t i;   // element index in the workspace tensor (image b included)
-                    if (t.layout == 1)
-                        i = t.index(b, y >> 1, x >> 1, ((y & 1) * 2 + (x & 1)) * t.Cs + sc, t.H >> 1, t.W >> 1, 4 * t.Cs);
-                    else
-                        i = t.index(b, y, x, sc, t.H, t.W, t.Cs);
-                    out_host[(((size_t)b * t.C + c) * t.H + y) * t.W + x] = raw_to_float(raw.data(), i, is_bf16);
+                    float v = 0.f;
+                    for (int part = 0; part < (t.split ? 2 : 1); ++part) {   // hi (+ lo)
+                        if (t.layout == 1) {
+                            const int sub = ((y & 1) * 2 + (x & 1)) * t.Cs + sc + part * 4 * t.Cs;
+                            i = t.index(b, y >> 1, x >> 1, sub, t.H >> 1, t.W >> 1, 4 * Ct);
+                        } else {
+                            i = t.index(b, y, x, sc + part * t.Cs, t.H, t.W, Ct);
+                        }
+                        v += raw_to_float(raw.data(), i, is_bf16);
+                    }
+                    out_host[(((size_t)b * t.C + c) * t.H + y) * t.W + x] = v;
                 }
         }
     return ISG_OK;

@@ -103,5 +103,12 @@ inline uint16_t f2bf(float f) {  // round-to-nearest-even, like __float2bfloat16
     return (uint16_t)(u >> 16);
 }
 
+inline float bf2f(uint16_t h) {
+    uint32_t u = (uint32_t)h << 16;
+    float f;
+    std::memcpy(&f, &u, 4);
+    return f;
+}
+
 }  // namespace tc
 }  // namespace isg

@@ -6,7 +6,7 @@ import torch
 
 from . import _lib
 
-_MODES = {"fp32": _lib.MODE_FP32, "bf16": _lib.MODE_BF16}
+_MODES = {"fp32": _lib.MODE_FP32, "bf16": _lib.MODE_BF16, "bf16x3": _lib.MODE_BF16X3}
 
 
 def state_names(in_channel):
