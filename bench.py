@@ -19,7 +19,7 @@ sys.path.insert(0, ROOT)
 
 FLOP_PER_IMAGE_512 = 1.1876e9      # 2 x 593.8 M MACs of the reference graph
 DECODE_BYTES_PER_PIXEL = 5         # fp32 logit in + 1 mask byte out (identity size) + 20 B stats/instance
-HEADLINE_PRECISION = "bf16"        # the mode `value` is measured in (see run_ours)
+HEADLINE_PRECISION = "bf16x3"      # the tensor-core mode inside the north_star tolerance; plain bf16 is an extra key
 
 
 def parse():

@@ -1,7 +1,8 @@
 """GPU parity tests of the forward: CUDA engine (through the C ABI) vs the oracle restatement
 and the committed reference logits.  Tolerances: fp32 mode 1e-4 max-abs on logits
-(BASELINE.json north_star); bf16 mode is reported against torch's own bf16 error, see
-DESIGN.md section 5."""
+(BASELINE.json north_star); tensor-core mode "bf16x3" (split-precision operands) max-abs 2e-2 /
+mean-abs 2e-3 (north_star's bf16 tolerance); plain "bf16" is an extra mode OUTSIDE that tolerance
+(reported, sanity-bounded), see DESIGN.md section 5."""
 import json
 import os
 
@@ -146,9 +147,57 @@ def test_bf16_layerwise_against_oracle(golden_state, H, W):
     assert not bad, bad
 
 
-def test_bf16_mode_error_is_reported_and_bounded(golden_state):
-    """bf16 storage: error must stay below torch's own bf16 execution of the same network
-    (SURVEY 7.3-A measured 1.0 max / 0.08 mean for it)."""
+X3_MAX, X3_MEAN = 2e-2, 2e-3    # north_star: logits within max-abs 2e-2 / mean-abs 2e-3 on the tensor-core path
+
+
+@pytest.mark.parametrize("B,H,W", [(2, 512, 512), (1, 1024, 1024), (2, 96, 160), (3, 64, 64), (1, 16, 16)])
+def test_bf16x3_logits_within_north_star_tolerance(golden_state, B, H, W):
+    """The tensor-core mode the bench measures: split-precision bf16 operands (hi + lo, three MMA passes)."""
+    x = torch.from_numpy(synth.batch(B, H, W, seed=77 + H))
+    want = segment_forward(golden_state, x)
+    m = _model(golden_state, precision="bf16x3", max_batch=2)
+    with torch.no_grad():
+        got = m(x.cuda()).cpu()
+    d = (got - want).abs()
+    print(f"bf16x3 {B}x{H}x{W}: max {float(d.max()):.3e} mean {float(d.mean()):.3e}")
+    assert float(d.max()) <= X3_MAX and float(d.mean()) <= X3_MEAN
+
+
+def test_bf16x3_matches_committed_reference_logits(golden_state, golden_logits):
+    """the same bar against logits written by the unmodified reference module (tests/golden/make_golden.py)"""
+    meta = json.load(open(os.path.join(GOLDEN, "segment3_golden.json")))
+    m = _model(golden_state, precision="bf16x3")
+    for name, c in meta["cases"].items():
+        x = torch.from_numpy(synth.batch(c["B"], c["H"], c["W"], seed=c["seed"], kind=c["kind"])).cuda()
+        with torch.no_grad():
+            y = m(x)
+        d = np.abs(y.cpu().numpy() - golden_logits[name])
+        scale = max(1.0, c["logit_absmax"] / 3.0)   # the noise case has logits ~4x larger
+        print(f"{name}: max-abs {d.max():.3e} mean-abs {d.mean():.3e}")
+        assert d.max() <= X3_MAX * scale and d.mean() <= X3_MEAN * scale, name
+
+
+@pytest.mark.parametrize("H,W", [(96, 160), (512, 512), (208, 48), (16, 16), (1024, 1024), (64, 2048), (1536, 32)])
+def test_bf16x3_layerwise_against_oracle(golden_state, H, W):
+    """Every tapped activation within 2e-3 of the tensor's scale (measured <= 3.2e-4): a wrong descriptor, tap
+    offset, weight slot or hi/lo plane shows up orders of magnitude above that, also in a low-energy channel."""
+    m = _model(golden_state, precision="bf16x3", max_batch=2)
+    x = torch.from_numpy(synth.batch(2, H, W, seed=4321))
+    taps = {}
+    segment_forward(golden_state, x, taps)
+    with torch.no_grad():
+        m(x.cuda())
+    mine = _engine(m).taps(2)
+    report = {k: float((t - taps[k]).abs().max() / taps[k].abs().max().clamp_min(1e-6)) for k, t in mine.items()}
+    print({k: f"{v:.1e}" for k, v in report.items()})
+    bad = {k: v for k, v in report.items() if not v < 2e-3}
+    assert not bad, bad
+
+
+def test_plain_bf16_mode_is_labelled_out_of_tolerance(golden_state):
+    """Plain bf16 operands (ISG_MODE_BF16) do NOT meet the north_star tolerance on this network (rounding
+    only the input image to bf16 already moves the logits by 0.25); the mode is kept as a faster, labelled extra.
+    This test reports its error beside torch's own bf16 execution and only sanity-bounds it."""
     x = torch.from_numpy(synth.batch(2, 256, 256, seed=77))
     want = segment_forward(golden_state, x)
     m = _model(golden_state, precision="bf16")
@@ -158,14 +207,13 @@ def test_bf16_mode_error_is_reported_and_bounded(golden_state):
     ref = Segment(3)
     ref.load_state_dict(golden_state)
     ref = ref.cuda().train(False)
-    # torch's bf16 path of the same graph (autograd route of the drop-in, eval BN)
     with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
         tb = ref._forward_autograd(x.cuda()).float().cpu()
     theirs = (tb - want).abs()
-    print(f"bf16 ours max {ours.max():.3e} mean {ours.mean():.3e} | torch autocast max "
+    print(f"plain bf16 (out of tolerance) max {ours.max():.3e} mean {ours.mean():.3e} | torch autocast max "
           f"{theirs.max():.3e} mean {theirs.mean():.3e}")
-    assert float(ours.mean()) <= max(float(theirs.mean()), 0.1)
-    assert float(ours.max()) <= max(float(theirs.max()), 1.5)
+    assert float(ours.mean()) <= 0.1 and float(ours.max()) <= 1.5     # sanity only; the contract is bf16x3's
+    assert float(ours.max()) > X3_MAX                                   # if this ever fails, drop the label
 
 
 def _u8_batch(B, H, W, seed):
@@ -181,7 +229,7 @@ def _normalize_like_reference(u8, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5)):
     return x.sub(m).div(s).contiguous()
 
 
-@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16", "bf16x3"])
 def test_forward_u8_equals_forward_of_normalized_input(golden_state, precision):
     """isg_forward_u8 (uint8 NHWC in, Normalize on the device) must give exactly the logits of
     isg_forward on the host-normalised fp32 tensor: the normalisation is the same IEEE sequence."""
@@ -202,7 +250,7 @@ sys.path.insert(0, sys.argv[1])
 from instancesegmentation_b200 import Segment, synth
 z = np.load(sys.argv[2])
 B, H, W = (int(v) for v in sys.argv[4].split("x"))
-m = Segment(3); m.load_state_dict({k: torch.from_numpy(z[k]) for k in z.files}); m.precision, m.max_batch = "bf16", B
+m = Segment(3); m.load_state_dict({k: torch.from_numpy(z[k]) for k in z.files}); m.precision, m.max_batch = sys.argv[5], B
 m = m.cuda().eval()
 x = torch.from_numpy(synth.batch(B, H, W, seed=3)).cuda()
 with torch.no_grad():
@@ -222,6 +270,10 @@ np.save(sys.argv[3], y.cpu().numpy())
     ("3x512x512", [{"ISG_FK_NO_MEGA": "1", "ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_NO_MEGA8": "1"}, {"ISG_FK_NO_PLANAR": "1"}]),
     # 1024x1024 (cfg4): the untuned default mode has no feasible tile for one launch -> fallback search
     ("2x1024x1024", [{"ISG_FK_NO_TUNE": "1"}, {}]),
+    # split-precision instantiations of the same kernels
+    ("bf16x3:4x128x192", [{"ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "1"}, {"ISG_FK_CTAS": "1", "ISG_FK_LBUF": "1"},
+                          {"ISG_FK_FORCE_PIPE": "1"}, {"ISG_FK_CTAS": "4", "ISG_FK_LBUF": "2"}, {"ISG_FK_NO_PLANAR": "1"}]),
+    ("bf16x3:2x512x512", [{"ISG_FK_NO_TUNE": "1"}, {}]),
 ])
 def test_bf16_launch_variants_are_bitwise_identical(tmp_path, size, envs):
     """Every way a fused launch may run (tile, CTAs per SM, load buffering -- the autotuner's choices -- and
@@ -232,10 +284,11 @@ def test_bf16_launch_variants_are_bitwise_identical(tmp_path, size, envs):
     script = tmp_path / "run.py"
     script.write_text(_MODE_SCRIPT)
     outs = []
+    precision, size = size.split(":") if ":" in size else ("bf16", size)
     for i, env in enumerate(envs):
         out = tmp_path / f"y{i}.npy"
         e = dict(os.environ, **env)
-        subprocess.run([sys.executable, str(script), root, os.path.join(GOLDEN, "segment3_state.npz"), str(out), size],
+        subprocess.run([sys.executable, str(script), root, os.path.join(GOLDEN, "segment3_state.npz"), str(out), size, precision],
                        check=True, env=e, timeout=600)
         outs.append(np.load(out))
     for i in range(1, len(outs)):
