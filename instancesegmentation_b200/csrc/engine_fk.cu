@@ -1488,7 +1488,14 @@ struct FkBuilder {
             }
         };
         s.stages.push_back(st);
-        if (P->split && candidates(s).empty()) {
+        bool ksplit = false;
+        if (P->split) {   // no tile at all, or only tiles that fill less than 3/4 of a 128-pixel M tile
+            const std::vector<Lay> c = candidates(s);
+            int best_px = 0;
+            for (const Lay& l : c) best_px = std::max(best_px, l.TH * l.TW);
+            ksplit = c.empty() || best_px < 96;
+        }
+        if (ksplit) {
             // the whole K (mid + C0 + C1 channels, hi + lo) and its weights do not fit one tile (bottle3_1: 304 x 128):
             // resconv runs split along K over the two concatenated inputs, r = W[:, :C0] . x0 + shift, r += W[:, C0:] . x1,
             // and the block launch takes r as its residual
