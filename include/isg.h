@@ -140,10 +140,16 @@ ISG_API int isg_idmap(const void* logits_dev, int logits_bf16, int h, int w, con
               const int32_t* img_first_dev, int n_img, int canvas_h, int canvas_w,
               float threshold, int32_t* idmap_dev, void* stream);
 
-/* intersection/union counts of two 0/1 byte masks (train_instance.py:402-403 mask_iou):
- * inter_union_dev[0] += |a&b|, [1] += |a|b| (caller zeroes them). */
+/* intersection/union counts of two byte masks (train_instance.py:402-403 mask_iou, applied there to tensor2mask
+ * outputs, i.e. 0-255 SOFT bytes of prediction and label; ymlib's source is absent, parity unpinned): a byte counts
+ * as set when it is nonzero -- what np.logical_and / np.logical_or, the usual implementation, do with such bytes
+ * (soft byte >= 1  <=>  p >= 1/255).  inter_union_dev[0] += |a&b|, [1] += |a|b| (caller zeroes them).
+ * isg_mask_iou_counts_thr: a byte of a (b) is set when >= thr_a (thr_b), thresholds in [1,255]; 128 = p >= 0.5 on soft
+ * bytes, 1 = the rule above. */
 ISG_API int isg_mask_iou_counts(const uint8_t* a_dev, const uint8_t* b_dev, int64_t n,
                         unsigned long long* inter_union_dev, void* stream);
+ISG_API int isg_mask_iou_counts_thr(const uint8_t* a_dev, const uint8_t* b_dev, int64_t n, int thr_a, int thr_b,
+                            unsigned long long* inter_union_dev, void* stream);
 
 /* ---- input side ------------------------------------------------------------
  * Keypoint heat maps of the Segment(20) variant (train_instance.py:33-68 keypoint2heatmaps,

@@ -37,6 +37,7 @@ SIGNATURES = {
     "isg_decode_tiled": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "isg_idmap": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _f, _vp, _vp]),
     "isg_mask_iou_counts": (_i, [_vp, _vp, _i64, _vp, _vp]),
+    "isg_mask_iou_counts_thr": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp]),
     "isg_keypoint_heatmaps": (_i, [_vp, _i, _i, _i, _i, _f, _f, _vp, _i64, _vp]),
     "isg_crop_resize_u8": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "isg_adam_step": (_i, [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp]),

@@ -571,11 +571,13 @@ idmap_finalize_kernel(const TL* __restrict__ logits, int h, int w, const int32_t
     idmap[i] = best;
 }
 
+// a byte counts as set when it is >= its threshold (1: any nonzero byte, numpy's logical_and / logical_or view of the
+// reference's 0-255 soft masks, train_instance.py:398-403)
 __global__ void iou_counts_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, int64_t n,
-                                  unsigned long long* out) {
+                                  unsigned long long* out, int thr_a, int thr_b) {
     unsigned inter = 0, uni = 0;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        bool pa = a[i] != 0, pb = b[i] != 0;
+        bool pa = a[i] >= thr_a, pb = b[i] >= thr_b;
         inter += pa && pb; uni += pa || pb;
     }
     inter = __reduce_add_sync(0xffffffffu, inter);
@@ -738,7 +740,19 @@ int isg_mask_iou_counts(const uint8_t* a_dev, const uint8_t* b_dev, int64_t n, u
     if (n <= 0) return ISG_OK;
     if (!a_dev || !b_dev || !inter_union_dev) return fail(ISG_ERR_ARG, "isg_mask_iou_counts: null argument");
     int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
-    iou_counts_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(a_dev, b_dev, n, inter_union_dev);
+    iou_counts_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(a_dev, b_dev, n, inter_union_dev, 1, 1);
+    ISG_CUDA(cudaGetLastError());
+    return ISG_OK;
+}
+
+int isg_mask_iou_counts_thr(const uint8_t* a_dev, const uint8_t* b_dev, int64_t n, int thr_a, int thr_b,
+                            unsigned long long* inter_union_dev, void* stream) {
+    if (n <= 0) return ISG_OK;
+    if (!a_dev || !b_dev || !inter_union_dev) return fail(ISG_ERR_ARG, "isg_mask_iou_counts_thr: null argument");
+    if (thr_a < 1 || thr_a > 255 || thr_b < 1 || thr_b > 255)
+        return fail(ISG_ERR_ARG, "isg_mask_iou_counts_thr: thresholds must be in [1,255], got %d and %d", thr_a, thr_b);
+    int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+    iou_counts_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(a_dev, b_dev, n, inter_union_dev, thr_a, thr_b);
     ISG_CUDA(cudaGetLastError());
     return ISG_OK;
 }

@@ -163,14 +163,21 @@ def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=N
     return DecodeResult(masks, soft, off, boxes, area, bbox, idmap)
 
 
-def mask_iou(a, b):
-    """intersection / union of two 0/1 uint8 CUDA tensors (train_instance.py:402-403)."""
+def mask_iou(a, b, threshold=1):
+    """intersection / union of two uint8 CUDA masks (train_instance.py:402-403, where both are ``tensor2mask``
+    soft bytes 0-255): a byte is set when it is >= ``threshold`` (an int, or a pair for a and b).  The default 1 =
+    any nonzero byte, numpy's logical view of soft bytes; 128 = probability >= 0.5.  0 when both masks are empty."""
+    if a.dtype != torch.uint8 or b.dtype != torch.uint8:
+        raise TypeError(f"mask_iou needs uint8 masks, got {a.dtype} and {b.dtype}")
+    if not (a.is_cuda and b.is_cuda):
+        raise _lib.IsgError("mask_iou runs on CUDA only; there is no CPU path")
     a, b = a.contiguous().view(-1), b.contiguous().view(-1)
     if a.numel() != b.numel():
         raise ValueError("mask sizes differ")
+    ta, tb = (threshold, threshold) if isinstance(threshold, int) else threshold
     cnt = torch.zeros(2, dtype=torch.int64, device=a.device)
     with torch.cuda.device(a.device):
-        _lib.check(_lib.lib().isg_mask_iou_counts(a.data_ptr(), b.data_ptr(), a.numel(), cnt.data_ptr(),
-                                                  torch.cuda.current_stream().cuda_stream))
+        _lib.check(_lib.lib().isg_mask_iou_counts_thr(a.data_ptr(), b.data_ptr(), a.numel(), int(ta), int(tb),
+                                                      cnt.data_ptr(), torch.cuda.current_stream().cuda_stream))
     inter, union = cnt.tolist()
     return inter / union if union else 0.0

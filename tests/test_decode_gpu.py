@@ -5,6 +5,7 @@ import pytest
 import torch
 
 from instancesegmentation_b200 import synth
+from instancesegmentation_b200 import _lib as _lib_mod
 from instancesegmentation_b200.decode import decode_masks, mask_iou
 from oracle import decode_oracle as D
 
@@ -168,3 +169,26 @@ def test_full_size_properties():
     assert np.array_equal(sub.masks.cpu().numpy()[:128 * 128], o["masks"])
     assert abs(int(up.area[0]) - 4 * int(r.area[0])) <= 0.02 * 4 * int(r.area[0]) + 64
     assert mask_iou(r.masks, again.masks) == 1.0
+
+
+def test_mask_iou_counts_against_oracle_on_random_and_soft_masks():
+    """isg_mask_iou_counts(_thr) vs oracle_mask_iou (nonzero = set): 0/1 masks, the reference's 0-255 soft bytes
+    (train_instance.py:398-403 feeds tensor2mask outputs), thresholded soft bytes, odd sizes, empty masks."""
+    from oracle import decode_oracle as D
+    rng = np.random.default_rng(3)
+    for n in (1, 31, 4097, 480 * 480, 3 * 512 * 512 + 5):
+        a = (rng.random(n) < 0.4).astype(np.uint8)
+        b = (rng.random(n) < 0.55).astype(np.uint8)
+        assert mask_iou(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()) == D.mask_iou(a, b)
+        sa = rng.integers(0, 256, n, dtype=np.uint8) * (rng.random(n) < 0.7).astype(np.uint8)   # soft bytes with exact zeros
+        sb = rng.integers(0, 256, n, dtype=np.uint8) * (rng.random(n) < 0.6).astype(np.uint8)
+        ta, tb = torch.from_numpy(sa).cuda(), torch.from_numpy(sb).cuda()
+        assert mask_iou(ta, tb) == D.mask_iou(sa, sb)                                            # nonzero rule
+        assert mask_iou(ta, tb, 128) == D.mask_iou((sa >= 128).astype(np.uint8), (sb >= 128).astype(np.uint8))
+        assert mask_iou(ta, tb, (200, 3)) == D.mask_iou((sa >= 200).astype(np.uint8), (sb >= 3).astype(np.uint8))
+    z = torch.zeros(1000, dtype=torch.uint8, device="cuda")
+    assert mask_iou(z, z) == 0.0
+    with pytest.raises(TypeError):
+        mask_iou(z.float(), z)
+    with pytest.raises(_lib_mod.IsgError):
+        mask_iou(z, z, 0)
