@@ -87,13 +87,14 @@ __device__ __forceinline__ unsigned sat_u8(float v) { return __float_as_uint(__f
 
 __global__ void __launch_bounds__(CR_THREADS)
 crop_resize3_kernel(const uint8_t* __restrict__ src, int Hs, int Ws, const int32_t* __restrict__ win,
-                    const int32_t* __restrict__ inst_img, int S_h, int S_w, uint8_t* __restrict__ out) {
+                    const int32_t* __restrict__ inst_img, int S_h, int S_w, uint8_t* __restrict__ out, int n_img) {
     __shared__ __align__(16) uint8_t chunk[CR_WARPS][CR_ROWS][96];   // 32 pixels x 3 bytes of each of the warp's rows
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = blockIdx.y, oy0 = (blockIdx.x * CR_WARPS + warp) * CR_ROWS;
     if (oy0 >= S_h) return;
     const int4 wn = __ldg(reinterpret_cast<const int4*>(win) + n);
-    const uint8_t* img = src + (size_t)__ldg(inst_img + n) * Hs * Ws * 3;
+    // an image index outside [0, n_img) is clamped: never a read outside the source batch
+    const uint8_t* img = src + (size_t)min(max(__ldg(inst_img + n), 0), n_img - 1) * Hs * Ws * 3;
     const float sy = __fdiv_rn((float)wn.w, (float)S_h), sx = __fdiv_rn((float)wn.z, (float)S_w);
     const int nrows = min(CR_ROWS, S_h - oy0);
     Tap ty[CR_ROWS];
@@ -179,7 +180,7 @@ int isg_crop_resize_u8(const uint8_t* src_dev, int n_img, int src_h, int src_w, 
     if (reinterpret_cast<uintptr_t>(out_dev) & 15) return fail(ISG_ERR_ARG, "isg_crop_resize_u8: output must be 16-byte aligned");
     dim3 grid(cdiv(out_h, CR_WARPS * CR_ROWS), n_inst);
     crop_resize3_kernel<<<grid, CR_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(src_dev, src_h, src_w, win_dev,
-                                                                                      inst_img_dev, out_h, out_w, out_dev);
+                                                                                      inst_img_dev, out_h, out_w, out_dev, n_img);
     ISG_CUDA(cudaGetLastError());
     return ISG_OK;
 }

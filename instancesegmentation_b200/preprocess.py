@@ -32,6 +32,11 @@ def crop_resize(images, windows, inst_img, size, out=None):
         if len(host) and (host.min() < 0 or host.max() >= images.shape[0]):
             raise ValueError("inst_img out of range")
         inst_img = torch.from_numpy(host).to(dev)
+    for name, t, shape_ok in (("windows", windows, windows.dim() == 2 and windows.shape[1] == 4),
+                              ("inst_img", inst_img, inst_img.dim() == 1)):
+        if t.dtype != torch.int32 or t.device != dev or not t.is_contiguous() or not shape_ok:
+            raise TypeError(f"{name} must be a contiguous int32 tensor on {dev} ([N,4] / [N]), got {t.dtype} "
+                            f"{tuple(t.shape)} on {t.device}")
     N = windows.shape[0]
     if inst_img.numel() != N:
         raise ValueError("one image index per window")
