@@ -35,9 +35,15 @@ def split(x):
     return hi, bf(x.double() - hi)
 
 
+def f16(x):
+    return x.float().half().double()
+
+
 def qstore(x, mode):
     if mode == "bf16":
         return bf(x)
+    if mode == "fp16":
+        return f16(x)
     if mode == "fp32":
         return x.float().double()
     hi, lo = split(x)
@@ -64,6 +70,11 @@ class Emu:
             return fn(x, w)
         if mode == "bf16":
             return fn(bf(x), bf(w))
+        if mode == "fp16":        # one pass with fp16 operands (11 significand bits)
+            return fn(f16(x), f16(w))
+        if mode == "fp16x2":      # fp16 activation pair hi + lo, fp16 weight: A_hi.W + A_lo.W
+            xh = f16(x)
+            return fn(xh, f16(w)) + fn(f16(x.double() - xh), f16(w))
         xh, xl = split(x)
         wh, wl = split(w)
         y = fn(xh, wh)
@@ -189,6 +200,11 @@ def main():
     report("all x2a (activation split only), hi+lo storage", every("x2a"), every("x3"))
     report("all x2w (weight split only), hi+lo storage", every("x2w"), every("x3"))
     report("all x3 operands but bf16 storage", every("x3"), every("bf16"))
+    report("all fp16 operands, fp16 storage (one MMA pass)", every("fp16"), every("fp16"))
+    report("all fp16 operands, hi+lo (bf16 pair) storage", every("fp16"), every("x3"))
+    report("fp16x2 (activation fp16 pair, fp16 weights), pair storage", every("fp16x2"), every("x3"))
+    if len(sys.argv) > 2 and sys.argv[2] == "fp16only":
+        return
     groups = {"stem": "init_conv", "enc8 (bottle1)": "bottle1", "enc16 (bottle2)": "bottle2", "mid16 (bottle3)": "bottle3",
               "dec8 (bottle4)": "bottle4", "dec4 (bottle5)": "bottle5", "tail": "tail"}
     for alt in ("bf16", "x2a", "x2w"):
