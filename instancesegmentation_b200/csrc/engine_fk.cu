@@ -12,6 +12,7 @@
 #include "engine.h"
 #include "fk.cuh"
 #include "mega.cuh"
+#include "mega3.cuh"
 #include "kernels_misc.cuh"
 #include "pack_util.h"
 #include "tc_host.h"
@@ -1375,6 +1376,164 @@ struct FkBuilder {
     }
 
 
+    // ---- split-precision plans: a run of residual bottlenecks as ONE launch of 8-CTA clusters (csrc/mega3.cuh) ----
+    struct Mega3Lay { mega3::Params q; size_t smem = 0; bool ok = false; };
+    Mega3Lay mega3_layout(int H, int W, int C, int mid, int nblocks) const {
+        Mega3Lay L;
+        mega3::Params& q = L.q;
+        std::memset(&q, 0, sizeof q);
+        if (!P->split || getenv("ISG_FK_NO_MEGA") || nblocks > mega3::MAX_BLOCKS || H % mega3::CLUSTER) return L;
+        q.H = H; q.W = W; q.R = H / mega3::CLUSTER;
+        q.Cs = round_up(C, 16); q.Cm = round_up(mid, 16);
+        q.npx = q.R * W;
+        if (q.npx % 128 || q.R < mega3::HALO || W > 128 || q.R > 256) return L;
+        q.n_mt = q.npx / 128;
+        q.pitch = W + 2 * mega3::HALO; q.rows_p = q.R + 2 * mega3::HALO;
+        q.w_magic = W > 1 ? (uint32_t)(((1ull << 32) + W - 1) / W) : 0u;
+        q.nblocks = nblocks;
+        const int cols = q.n_mt * std::max(q.Cs, q.Cm);
+        if (cols > 512) return L;
+        q.tmem_cols = tc::tmem_cols_pow2(cols);
+        // global blob of one block
+        q.w0_bytes = q.Cs * q.Cm * 2 * 2; q.w2_bytes = q.Cm * q.Cs * 2 * 2;   // hi + lo
+        int rel = 0;
+        q.v0_off = rel; rel = r128(rel + 2 * q.Cm * 4);
+        q.dw_off = rel; rel = r128(rel + 25 * q.Cm * 4);
+        q.dv_off = rel; rel = r128(rel + 7 * q.Cm * 4);
+        q.v2_off = rel; rel = r128(rel + 2 * q.Cs * 4);
+        q.c_bytes = rel;
+        q.w0_goff = 0; q.w2_goff = r128(q.w0_bytes); q.c_goff = q.w2_goff + r128(q.w2_bytes);
+        q.blob_stride = (q.c_goff + q.c_bytes + 255) / 256 * 256;
+        // shared memory
+        int off = 0;
+        const int xh = (q.Cs / 8) * q.npx * 16, mh = (q.Cm / 8) * q.rows_p * q.pitch * 16, dh = (q.Cm / 8) * q.npx * 16;
+        q.x_off = off; q.x_lo = r128(xh); off = r128(off + q.x_lo + xh);
+        q.m1_off = off; q.m1_lo = r128(mh); off = r128(off + q.m1_lo + mh);
+        q.d_off = off; q.d_lo = r128(dh); off = r128(off + q.d_lo + dh);
+        q.wg_off = off; off = r128(off + std::max(q.w0_bytes, q.w2_bytes));
+        q.wc_off[0] = off; off = r128(off + q.c_bytes);
+        q.wc_off[1] = off; off = r128(off + q.c_bytes);
+        q.bar_off = off; off += 128;
+        L.smem = off;
+        L.ok = L.smem <= 227 * 1024;
+        return L;
+    }
+    int mega3_run(const std::string& name, int x, int mid, const std::vector<MegaBlock>& blocks, const std::string& outname) {
+        isg_plan* P = this->P;
+        const TensorD tx = td(x);
+        const int C = tx.C;
+        Mega3Lay L = mega3_layout(tx.H, tx.W, C, mid, (int)blocks.size());
+        mega3::Params q = L.q;
+        const int out = tensor(outname, C, tx.H, tx.W, true);
+        struct Fills { StageFill f0, f2; StencilFill fs; };
+        auto fills = std::make_shared<std::vector<Fills>>();
+        for (size_t i = 0; i < blocks.size(); ++i) {
+            const MegaBlock& b = blocks[i];
+            q.blk[i].dil = b.five ? 1 : b.dil; q.blk[i].sep5 = b.five ? 1 : 0;
+            const int d = q.blk[i].dil;
+            q.blk[i].sr = 4 * d <= q.R ? 4 : (2 * d <= q.R ? 2 : 1);   // stencil strip height (rows `dil` apart) within the CTA's rows
+            if (b.five && q.blk[i].sr == 1) q.blk[i].sr = 2;
+            Next n0; n0.on = true; n0.unit = b.p + ".convs.0"; n0.mid = mid; n0.act = ACT_PRELU;
+            Fills f;
+            f.f0 = chain_stage(n0, C, q.Cs).fill;
+            f.fs = b.five ? sep5_stencil(b.p, 0, mid).fill : dw3_stencil(b.p + ".convs.1", 0, mid, b.dil).fill;
+            f.f2 = res_out_fill(b.p, b.five ? b.p + ".convs.3" : b.p + ".convs.2", C, mid, q.Cs);
+            fills->push_back(f);
+            macs(mid, C, 1, 1, tx.H, tx.W);
+            if (b.five) { macs(mid, 1, 5, 1, tx.H, tx.W); macs(mid, 1, 1, 5, tx.H, tx.W); }
+            else macs(mid, 1, 3, 3, tx.H, tx.W);
+            macs(C, mid, 1, 1, tx.H, tx.W);
+        }
+        const size_t blob = arena((size_t)q.blob_stride * blocks.size() / 4);
+        Op op;
+        op.name = name + " (" + std::to_string(blocks.size()) + " residual bottlenecks, cluster-resident, split precision) [mega3]";
+        const int nb = (int)blocks.size();
+        op.pack = [=](const HostWeights& w, float* A) {
+            // B[K][N] -> blocked [k16][2][N][8] bf16: W_hi blocks, then W_lo = bf16(w - W_hi) blocks `half` bytes later
+            auto pack_b = [](uint8_t* dst, int half, const float* B, int K, int N) {
+                uint16_t* hi = reinterpret_cast<uint16_t*>(dst);
+                uint16_t* lo = reinterpret_cast<uint16_t*>(dst + half);
+                for (int kk = 0; kk < K; ++kk)
+                    for (int n = 0; n < N; ++n) {
+                        const size_t idx = (size_t)(kk / 16) * N * 16 + (size_t)((kk % 16) / 8) * N * 8 + (size_t)n * 8 + (kk % 8);
+                        const float v = B[(size_t)kk * N + n];
+                        hi[idx] = tc::f2bf(v);
+                        lo[idx] = tc::f2bf(v - tc::bf2f(hi[idx]));
+                    }
+            };
+            for (int i = 0; i < nb; ++i) {
+                uint8_t* base = reinterpret_cast<uint8_t*>(A + blob) + (size_t)i * q.blob_stride;
+                std::memset(base, 0, q.blob_stride);
+                const Fills& f = (*fills)[i];
+                float* c = reinterpret_cast<float*>(base + q.c_goff);
+                {
+                    std::vector<float> B((size_t)q.Cs * q.Cm, 0.f), sh(q.Cm, 0.f), sl(q.Cm, 1.f);
+                    f.f0(w, B.data(), sh.data(), sl.data());
+                    pack_b(base + q.w0_goff, q.w0_bytes / 2, B.data(), q.Cs, q.Cm);
+                    float* v = c + q.v0_off / 4;
+                    std::memcpy(v, sh.data(), 4 * q.Cm); std::memcpy(v + q.Cm, sl.data(), 4 * q.Cm);
+                }
+                {
+                    std::vector<float> wt((size_t)25 * q.Cm, 0.f), sh(q.Cm, 0.f), sl(q.Cm, 1.f), bw((size_t)5 * q.Cm, 0.f);
+                    f.fs(w, wt.data(), sh.data(), sl.data(), bw.data());
+                    std::memcpy(c + q.dw_off / 4, wt.data(), 4 * wt.size());
+                    float* v = c + q.dv_off / 4;
+                    std::memcpy(v, sh.data(), 4 * q.Cm); std::memcpy(v + q.Cm, sl.data(), 4 * q.Cm);
+                    std::memcpy(v + 2 * q.Cm, bw.data(), 4 * bw.size());
+                }
+                {
+                    std::vector<float> B((size_t)q.Cm * q.Cs, 0.f), sh(q.Cs, 0.f), sl(q.Cs, 1.f);
+                    f.f2(w, B.data(), sh.data(), sl.data());
+                    pack_b(base + q.w2_goff, q.w2_bytes / 2, B.data(), q.Cm, q.Cs);
+                    float* v = c + q.v2_off / 4;
+                    std::memcpy(v, sh.data(), 4 * q.Cs); std::memcpy(v + q.Cs, sl.data(), 4 * q.Cs);
+                }
+            }
+        };
+        auto maps = std::make_shared<FkMaps>();
+        const int maxB = P->max_batch;
+        const TensorD to = td(out);
+        P->finalizers.push_back([=]() -> int {
+            int rc = tc::make_act_map_chunks(&maps->in[0], P->ws + tx.off, maxB, tx.H, tx.W, tx.Ct(), tx.W, q.R, tx.Cs / 8, name.c_str(),
+                                             tx.planar);
+            if (rc) return rc;
+            return tc::make_act_map_chunks(&maps->out[0], P->ws + to.off, maxB, to.H, to.W, to.Ct(), to.W, q.R, to.Cs / 8, name.c_str(),
+                                           to.planar);
+        });
+        cudaFuncSetAttribute(mega3::mega3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaFuncSetAttribute(mega3::mega3_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        const size_t smem = L.smem;
+        auto nclusters = std::make_shared<int>(0);
+        op.launch = [=](int n, const float*, float*, cudaStream_t stream) -> cudaError_t {
+            mega3::Params p = q;
+            p.in_planar = tx.planar ? 1 : 0; p.out_planar = to.planar ? 1 : 0;
+            p.blob = reinterpret_cast<const uint8_t*>(P->arena + blob);
+            p.nimg = n;
+            cudaLaunchConfig_t cfg;
+            std::memset(&cfg, 0, sizeof cfg);
+            cfg.blockDim = dim3(mega3::THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+            cudaLaunchAttribute at[2];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = mega3::CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[1].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = 2;
+            if (*nclusters == 0) {   // co-resident clusters of this footprint: once
+                cfg.gridDim = dim3(mega3::CLUSTER * 32);
+                int nc = 0;
+                cudaError_t e = cudaOccupancyMaxActiveClusters(&nc, mega3::mega3_kernel, &cfg);
+                if (e != cudaSuccess) return e;
+                if (nc < 1) return cudaErrorLaunchOutOfResources;
+                *nclusters = nc;
+                if (getenv("ISG_FK_VERBOSE")) fprintf(stderr, "mega3 %s: %d co-resident clusters of %d, smem %zu\n", name.c_str(), nc, mega3::CLUSTER, smem);
+            }
+            cfg.gridDim = dim3(mega3::CLUSTER * std::min(*nclusters, std::max(n, 1)));
+            return cudaLaunchKernelEx(&cfg, mega3::mega3_kernel, maps->in[0], maps->out[0], p);
+        };
+        P->ops.push_back(op);
+        return out;
+    }
+
     // BottleneckDown2 (segment.py:114-150)
     int block_down(const std::string& p, int x, int mid, int cout, int* keep, const std::string& outname,
                    const std::string& keepname, const Next& nx) {
@@ -1834,14 +1993,15 @@ struct FkBuilder {
 
         const int h8 = H / 8, w8 = W / 8, h16 = H / 16, w16 = W / 16;
         int keep1, keep2;
-        const bool mega8 = mega_layout(h8, w8, 48, 16, 4).ok && !getenv("ISG_FK_NO_MEGA8");
+        const bool split = P->split;
+        const bool mega8 = (split ? mega3_layout(h8, w8, 48, 16, 4).ok : mega_layout(h8, w8, 48, 16, 4).ok) && !getenv("ISG_FK_NO_MEGA8");
         Next nx = mega8 ? Next() : next_of("bottle1_x.0.convs.0", 16, ACT_PRELU, h8, w8);
         const int d1 = block_down("bottle1_1", init, 16, 48, &keep1, "bottle1_down", "keep1", nx);
         int y = d1, m1 = nx.out;
         if (mega8) {
             std::vector<MegaBlock> blocks;
             for (int i = 0; i < 4; ++i) blocks.push_back(MegaBlock{"bottle1_x." + std::to_string(i), 1, false});
-            y = mega_run("bottle1_x", d1, 16, blocks, "bottle1_5");
+            y = split ? mega3_run("bottle1_x", d1, 16, blocks, "bottle1_5") : mega_run("bottle1_x", d1, 16, blocks, "bottle1_5");
         }
         for (int i = 0; i < 4 && !mega8; ++i) {
             const std::string p = "bottle1_x." + std::to_string(i);
@@ -1850,7 +2010,7 @@ struct FkBuilder {
             y = block_res(p, y, m1, 16, 1, false, n2, i == 3 ? "bottle1_5" : p, i == 3);
             m1 = n2.out;
         }
-        const bool mega16 = mega_layout(h16, w16, 128, 48, 5).ok;
+        const bool mega16 = split ? mega3_layout(h16, w16, 128, 48, 5).ok : mega_layout(h16, w16, 128, 48, 5).ok;
         nx = mega16 ? Next() : next_of("bottle2_x.0.convs.0", 48, ACT_PRELU, h16, w16);
         const int d2 = block_down("bottle2_1", y, 16, 128, &keep2, "bottle2_down", "keep2", nx);
         const int dils[4] = {1, 2, 1, 4};
@@ -1858,7 +2018,7 @@ struct FkBuilder {
             if (mega16) {
                 std::vector<MegaBlock> blocks;
                 for (int i = 0; i < 5; ++i) blocks.push_back(MegaBlock{pre + "." + std::to_string(i), i < 4 ? dils[i] : 1, i == 4});
-                return mega_run(pre, t, 48, blocks, outname);
+                return split ? mega3_run(pre, t, 48, blocks, outname) : mega_run(pre, t, 48, blocks, outname);
             }
             for (int i = 0; i < 5; ++i) {
                 const std::string p = pre + "." + std::to_string(i);

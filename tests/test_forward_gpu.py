@@ -273,7 +273,8 @@ np.save(sys.argv[3], y.cpu().numpy())
     # split-precision instantiations of the same kernels
     ("bf16x3:4x128x192", [{"ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_CTAS": "2", "ISG_FK_LBUF": "1"}, {"ISG_FK_CTAS": "1", "ISG_FK_LBUF": "1"},
                           {"ISG_FK_FORCE_PIPE": "1"}, {"ISG_FK_CTAS": "4", "ISG_FK_LBUF": "2"}, {"ISG_FK_NO_PLANAR": "1"}]),
-    ("bf16x3:2x512x512", [{"ISG_FK_NO_TUNE": "1"}, {}]),
+    # 512x512: the residual runs go through the 8-CTA-cluster launch (csrc/mega3.cuh) unless ISG_FK_NO_MEGA
+    ("bf16x3:3x512x512", [{"ISG_FK_NO_TUNE": "1"}, {}, {"ISG_FK_NO_MEGA": "1", "ISG_FK_NO_TUNE": "1"}, {"ISG_FK_NO_MEGA8": "1"}]),
 ])
 def test_bf16_launch_variants_are_bitwise_identical(tmp_path, size, envs):
     """Every way a fused launch may run (tile, CTAs per SM, load buffering -- the autotuner's choices -- and
