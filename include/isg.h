@@ -116,6 +116,16 @@ ISG_API int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int 
                float threshold, uint8_t* masks_dev, uint8_t* soft_dev, int32_t* area_dev,
                int32_t* bbox_dev, void* stream);
 
+/* Accumulator workspace of the decode kernels (per-instance area / bbox partials, arrival tickets, tile counters).
+ * By default they live in arrays of the library, which allows ONE decode in flight per device and <= 65535 instances
+ * per call.  A caller that decodes on several streams at once (pipeline slots), or more instances with
+ * isg_decode_tiled, binds its own: ws_dev = isg_decode_workspace_bytes(max_inst) bytes of device memory, 16-byte
+ * aligned, zeroed ONCE (every launch leaves it zeroed); isg_decode_bind_workspace(ws_dev, max_inst) makes the
+ * isg_decode / isg_decode_tiled calls of the calling host thread use it until rebound (NULL: back to the default).
+ * The binding is host-thread-local state; the memory stays caller-owned; one workspace per concurrent decode. */
+ISG_API int64_t isg_decode_workspace_bytes(int max_inst);
+ISG_API int isg_decode_bind_workspace(void* ws_dev, int max_inst);
+
 /* Tiled decode for ragged box sizes (0/1 masks only), optionally fused with the id map.
  * Same inputs/outputs as isg_decode; the work is cut into tiles of isg_decode_tile_rows()
  * consecutive mask rows of one instance, handed out dynamically so that boxes of very

@@ -34,6 +34,8 @@ SIGNATURES = {
     "isg_plan_tap_read": (_i, [_vp, _i, _i, _vp]),
     "isg_decode": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _f, _vp, _vp, _vp, _vp, _vp]),
     "isg_decode_tile_rows": (_i, []),
+    "isg_decode_workspace_bytes": (_i64, [_i]),
+    "isg_decode_bind_workspace": (_i, [_vp, _i]),
     "isg_decode_tiled": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "isg_idmap": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _f, _vp, _vp]),
     "isg_mask_iou_counts": (_i, [_vp, _vp, _i64, _vp, _vp]),

@@ -21,6 +21,19 @@ constexpr int DEC_MAX_INST = 65536;
 // init or finalize launch.  One decode per device may be in flight at a time (stream order).
 __device__ int g_dec_acc[DEC_MAX_INST][5];
 __device__ unsigned g_dec_ticket[DEC_MAX_INST];
+__device__ unsigned g_dt[4];   // tiled kernel: [0] next tile, [1] CTAs that ran dry
+
+// Accumulators of one decode in flight: per-instance {area, xmin, ymin, xmax, ymax} + arrival tickets + the tile counters
+// of the tiled kernel.  Default = the arrays above (one decode in flight per device, <= DEC_MAX_INST instances); a caller
+// workspace (isg_decode_bind_workspace: [4 x u32 counters][max_inst x u32 tickets][max_inst x 5 x i32], zeroed once, left
+// zeroed by every launch) gives every stream / pipeline slot its own.
+struct DecWs { unsigned* dt; unsigned* ticket; int (*acc)[5]; };
+__device__ __forceinline__ DecWs dec_ws(unsigned* ws, int ws_inst) {
+    DecWs r;
+    if (ws) { r.dt = ws; r.ticket = ws + 4; r.acc = reinterpret_cast<int(*)[5]>(ws + 4 + ws_inst); }
+    else { r.dt = g_dt; r.ticket = g_dec_ticket; r.acc = g_dec_acc; }
+    return r;
+}
 
 // rarely taken exact re-evaluations stay out of line: the hot loop must fit the instruction cache
 __device__ __noinline__ float exact_sigmoid_nl(float x) { return exact_sigmoid(x); }
@@ -211,10 +224,11 @@ __global__ void __launch_bounds__(DEC_THREADS, 4)
 decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restrict__ boxes,
               const int64_t* __restrict__ mask_off, float thr, float thr_logit, float margin, int use_logit_cmp,
               uint8_t* __restrict__ masks, uint8_t* __restrict__ soft, int32_t* __restrict__ area,
-              int32_t* __restrict__ bbox) {
+              int32_t* __restrict__ bbox, unsigned* ws, int ws_inst) {
     // launched with programmatic stream serialization: the grid is staged while the previous kernel of the
     // stream drains; nothing is read or written before that kernel has completed
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    const DecWs W = dec_ws(ws, ws_inst);
     const int n = blockIdx.y;
     const int4 bx = __ldg(reinterpret_cast<const int4*>(boxes) + n);
     const int wk = bx.z, hk = bx.w;
@@ -296,7 +310,7 @@ decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __rest
             xmin = min(xmin, red[i][1]); ymin = min(ymin, red[i][2]);
             xmax = max(xmax, red[i][3]); ymax = max(ymax, red[i][4]);
         }
-        int* acc = g_dec_acc[n];
+        int* acc = W.acc[n];
         if (cnt) {
             atomicAdd(acc, cnt);
             atomicMax(acc + 1, INT_MAX - xmin); atomicMax(acc + 2, INT_MAX - ymin);
@@ -304,12 +318,12 @@ decode_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __rest
         }
         __threadfence();
         const unsigned nblk = (unsigned)min((int)gridDim.x, ngroups);   // CTAs of this instance that take part
-        if (atomicAdd(&g_dec_ticket[n], 1u) == nblk - 1) {
+        if (atomicAdd(&W.ticket[n], 1u) == nblk - 1) {
             __threadfence();
             const int a = atomicExch(acc, 0);
             const int e1 = atomicExch(acc + 1, 0), e2 = atomicExch(acc + 2, 0);
             const int e3 = atomicExch(acc + 3, 0), e4 = atomicExch(acc + 4, 0);
-            g_dec_ticket[n] = 0;
+            W.ticket[n] = 0;
             area[n] = a;
             if (a == 0) { bbox[4 * n] = bbox[4 * n + 1] = bbox[4 * n + 2] = bbox[4 * n + 3] = 0; }
             else {
@@ -363,7 +377,7 @@ idmap_kernel(const TL* __restrict__ logits, int h, int w, const int32_t* __restr
 // (index within its image, < 32) into the canvas word; idmap_finalize_kernel turns the bit sets into
 // ids and compares probabilities only where two or more instances claim the same pixel.
 constexpr int DT_THREADS = 256, DT_WARPS = DT_THREADS / 32, DT_RPW = 2, DT_ROWS = DT_WARPS * DT_RPW;
-__device__ unsigned g_dt_next, g_dt_done;
+
 
 // source indices of the align_corners=False rule; returns the clamped source coordinate s, from which the
 // weights follow as make_tap derives them: l1 = s - i0, l0 = 1 - l1
@@ -382,12 +396,13 @@ decode_tiled_kernel(const TL* __restrict__ logits, int n_inst, int h, int w, con
                     float thr, float thr_logit, float margin, uint8_t* __restrict__ masks,
                     int32_t* __restrict__ area, int32_t* __restrict__ bbox,
                     const int32_t* __restrict__ inst_img, const int32_t* __restrict__ img_first,
-                    int Hs, int Ws, unsigned* __restrict__ claims) {
+                    int Hs, int Ws, unsigned* __restrict__ claims, unsigned* ws, int ws_inst) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const DecWs W = dec_ws(ws, ws_inst);
     __shared__ int s_tile[2][2];   // {tile, instance} of the current and the next tile
     asm volatile("griddepcontrol.wait;" ::: "memory");   // see decode_kernel
     auto fetch = [&](int slot) {   // thread 0: next tile index and the instance it belongs to
-        const int t = (int)atomicAdd(&g_dt_next, 1u);
+        const int t = (int)atomicAdd(&W.dt[0], 1u);
         int lo = 0;
         if (t < n_tiles) {
             int hi = n_inst - 1;
@@ -497,19 +512,19 @@ decode_tiled_kernel(const TL* __restrict__ logits, int n_inst, int h, int w, con
             if (rcnt) { cnt += rcnt; ymin = min(ymin, oy); ymax = max(ymax, oy); }
         }
         if (lane == 0 && rows) {
-            int* acc = g_dec_acc[n];
+            int* acc = W.acc[n];
             if (cnt) {
                 atomicAdd(acc, cnt);
                 atomicMax(acc + 1, INT_MAX - xmin); atomicMax(acc + 2, INT_MAX - ymin);
                 atomicMax(acc + 3, xmax + 1); atomicMax(acc + 4, ymax + 1);
             }
             __threadfence();
-            if (atomicAdd(&g_dec_ticket[n], (unsigned)rows) + (unsigned)rows == (unsigned)hk) {   // all rows are in
+            if (atomicAdd(&W.ticket[n], (unsigned)rows) + (unsigned)rows == (unsigned)hk) {   // all rows are in
                 __threadfence();
                 const int ar = atomicExch(acc, 0);
                 const int e1 = atomicExch(acc + 1, 0), e2 = atomicExch(acc + 2, 0);
                 const int e3 = atomicExch(acc + 3, 0), e4 = atomicExch(acc + 4, 0);
-                g_dec_ticket[n] = 0;
+                W.ticket[n] = 0;
                 area[n] = ar;
                 if (ar == 0) { bbox[4 * n] = bbox[4 * n + 1] = bbox[4 * n + 2] = bbox[4 * n + 3] = 0; }
                 else {
@@ -522,7 +537,7 @@ decode_tiled_kernel(const TL* __restrict__ logits, int n_inst, int h, int w, con
     }
     if (threadIdx.x == 0) {   // the last CTA to run dry re-arms the tile counter for the next launch
         __threadfence();
-        if (atomicAdd(&g_dt_done, 1u) == gridDim.x - 1) { g_dt_next = 0; g_dt_done = 0; __threadfence(); }
+        if (atomicAdd(&W.dt[1], 1u) == gridDim.x - 1) { W.dt[0] = 0; W.dt[1] = 0; __threadfence(); }
     }
 }
 
@@ -607,7 +622,25 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
 
 using namespace isg;
 
+namespace {
+// workspace bound by isg_decode_bind_workspace for the decode calls of THIS host thread (null: the default arrays)
+thread_local unsigned* t_ws = nullptr;
+thread_local int t_ws_inst = 0;
+}  // namespace
+
 extern "C" {
+
+int64_t isg_decode_workspace_bytes(int max_inst) {
+    return max_inst < 1 ? 0 : 16 + (int64_t)max_inst * 4 + (int64_t)max_inst * 20;
+}
+
+int isg_decode_bind_workspace(void* ws_dev, int max_inst) {
+    if (ws_dev && (max_inst < 1 || (reinterpret_cast<uintptr_t>(ws_dev) & 15)))
+        return fail(ISG_ERR_ARG, "isg_decode_bind_workspace: workspace must be 16-byte aligned with max_inst >= 1");
+    t_ws = static_cast<unsigned*>(ws_dev);
+    t_ws_inst = ws_dev ? max_inst : 0;
+    return ISG_OK;
+}
 
 int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int h, int w, const int32_t* boxes_dev,
                const int64_t* mask_off_dev, int max_wk, int max_hk, float threshold, uint8_t* masks_dev,
@@ -615,7 +648,7 @@ int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int h, int w
     if (n_inst == 0) return ISG_OK;
     if (!logits_dev || !boxes_dev || !mask_off_dev || !masks_dev || !area_dev || !bbox_dev)
         return fail(ISG_ERR_ARG, "isg_decode: null argument");
-    if (n_inst < 0 || n_inst > 65535 || h < 1 || w < 1 || max_wk < 1 || max_hk < 1)
+    if (n_inst < 0 || n_inst > 65535 || (t_ws && n_inst > t_ws_inst) || h < 1 || w < 1 || max_wk < 1 || max_hk < 1)
         return fail(ISG_ERR_ARG, "isg_decode: bad sizes (n_inst=%d h=%d w=%d max box %dx%d)", n_inst, h, w, max_wk, max_hk);
     if ((int64_t)max_wk * max_hk > INT_MAX) return fail(ISG_ERR_ARG, "isg_decode: box too large");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -651,7 +684,7 @@ int isg_decode(const void* logits_dev, int logits_bf16, int n_inst, int h, int w
 #define ISG_DEC(TL, SOFT)                                                                                        \
     ISG_CUDA(launch_pdl(decode_kernel<TL, SOFT>, grid, DEC_THREADS, st, static_cast<const TL*>(logits_dev), h, w, \
                         boxes_dev, mask_off_dev, threshold, thr_logit, margin, use_logit_cmp, masks_dev, soft_dev, \
-                        area_dev, bbox_dev))
+                        area_dev, bbox_dev, t_ws, t_ws_inst))
     if (logits_bf16) { if (soft_dev) ISG_DEC(bf16, true); else ISG_DEC(bf16, false); }
     else { if (soft_dev) ISG_DEC(float, true); else ISG_DEC(float, false); }
 #undef ISG_DEC
@@ -669,7 +702,7 @@ int isg_decode_tiled(const void* logits_dev, int logits_bf16, int n_inst, int h,
     if (n_inst == 0) return ISG_OK;
     if (!logits_dev || !boxes_dev || !mask_off_dev || !tile_first_dev || !masks_dev || !area_dev || !bbox_dev)
         return fail(ISG_ERR_ARG, "isg_decode_tiled: null argument");
-    if (n_inst < 0 || n_inst > 65535 || h < 1 || w < 1 || n_tiles < 0)
+    if (n_inst < 0 || n_inst > (t_ws ? t_ws_inst : 65535) || h < 1 || w < 1 || n_tiles < 0)
         return fail(ISG_ERR_ARG, "isg_decode_tiled: bad sizes (n_inst=%d h=%d w=%d n_tiles=%d)", n_inst, h, w, n_tiles);
     if (idmap_dev && (!inst_img_dev || !img_first_dev || n_img < 1 || canvas_h < 1 || canvas_w < 1))
         return fail(ISG_ERR_ARG, "isg_decode_tiled: id map requested without image table / canvas size");
@@ -697,11 +730,11 @@ int isg_decode_tiled(const void* logits_dev, int logits_bf16, int n_inst, int h,
     if (logits_bf16)
         ISG_CUDA(launch_pdl(decode_tiled_kernel<bf16>, dim3(grid), DT_THREADS, st, static_cast<const bf16*>(logits_dev), n_inst,
                             h, w, boxes_dev, mask_off_dev, tile_first_dev, n_tiles, threshold, thr_logit, margin, masks_dev,
-                            area_dev, bbox_dev, inst_img_dev, img_first_dev, canvas_h, canvas_w, claims));
+                            area_dev, bbox_dev, inst_img_dev, img_first_dev, canvas_h, canvas_w, claims, t_ws, t_ws_inst));
     else
         ISG_CUDA(launch_pdl(decode_tiled_kernel<float>, dim3(grid), DT_THREADS, st, static_cast<const float*>(logits_dev), n_inst,
                             h, w, boxes_dev, mask_off_dev, tile_first_dev, n_tiles, threshold, thr_logit, margin, masks_dev,
-                            area_dev, bbox_dev, inst_img_dev, img_first_dev, canvas_h, canvas_w, claims));
+                            area_dev, bbox_dev, inst_img_dev, img_first_dev, canvas_h, canvas_w, claims, t_ws, t_ws_inst));
     ISG_CUDA(cudaGetLastError());
     if (idmap_dev) {
         const unsigned blocks = (unsigned)((total + 255) / 256);

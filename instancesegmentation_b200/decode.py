@@ -72,6 +72,11 @@ class DecodePlan:
             raise ValueError("too many mask pixels for one decode call")
         self.n_tiles = int(tf[-1])
         self.tile_first_d = torch.from_numpy(tf.astype(np.int32)).to(self.device)
+        # this plan's own accumulator workspace (isg_decode_bind_workspace): decodes of different plans may overlap on
+        # the GPU (pipeline slots, several streams); zeroed once, every launch leaves it zeroed
+        self.ws_inst = max(n, 1)
+        self.ws = torch.zeros((_lib.lib().isg_decode_workspace_bytes(self.ws_inst) + 15) // 16 * 4, dtype=torch.int32,
+                              device=self.device)
         self._idmap_tables, self._identity = {}, {}
 
     def is_identity(self, h, w):
@@ -139,6 +144,7 @@ def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=N
             n_img = first_d.numel() - 1
             idmap = torch.empty((n_img, canvas[0], canvas[1]), dtype=torch.int32, device=dev)
         identity = plan.is_identity(h, w)
+        _lib.check(l.isg_decode_bind_workspace(plan.ws.data_ptr(), plan.ws_inst))
         fuse_ids = bool(idmap is not None and N and per_img <= 32 and not want_soft)
         if N and not want_soft and (fuse_ids or not identity):
             # ragged sizes: balanced tile list; the id map rides along as bit claims when it fits a word
@@ -160,6 +166,7 @@ def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=N
             _lib.check(l.isg_idmap(logits.data_ptr(), bf, h, w,
                                    boxes_d.data_ptr(), first_d.data_ptr(), n_img, canvas[0], canvas[1],
                                    float(threshold), idmap.data_ptr(), st))
+        l.isg_decode_bind_workspace(None, 0)
     return DecodeResult(masks, soft, off, boxes, area, bbox, idmap)
 
 

@@ -192,3 +192,51 @@ def test_mask_iou_counts_against_oracle_on_random_and_soft_masks():
         mask_iou(z.float(), z)
     with pytest.raises(_lib_mod.IsgError):
         mask_iou(z, z, 0)
+
+
+def test_decode_workspaces_allow_concurrent_streams_and_default_path_still_works():
+    """Every DecodePlan owns its accumulator workspace (isg_decode_bind_workspace): decodes on two streams may overlap.
+    The unbound default (the library's per-device arrays) is reached through the raw C ABI and gives the same result."""
+    import ctypes as C
+    from instancesegmentation_b200.decode import DecodePlan
+    N, h, w = 40, 96, 128
+    la = torch.from_numpy(synth.logits(N, h, w, seed=11)).cuda()
+    lb = torch.from_numpy(synth.logits(N, h, w, seed=12)).cuda()
+    boxes, _ = synth.boxes(2, 20, 300, 300, seed=3)
+    ref_a, ref_b = decode_masks(la, boxes), decode_masks(lb, boxes)
+    ident_a = decode_masks(la)
+    torch.cuda.synchronize()
+    pa, pb = DecodePlan(boxes, "cuda"), DecodePlan(boxes, "cuda")
+    pi = DecodePlan(np.tile(np.array([0, 0, w, h], np.int32), (N, 1)), "cuda")
+    assert pa.ws.data_ptr() != pb.ws.data_ptr()
+    sa, sb, sc = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+    for _ in range(20):
+        with torch.cuda.stream(sa):
+            ra = decode_masks(la, plan=pa)
+        with torch.cuda.stream(sb):
+            rb = decode_masks(lb, plan=pb)
+        with torch.cuda.stream(sc):
+            ri = decode_masks(la, plan=pi)
+    torch.cuda.synchronize()
+    def same(r, ref):   # per instance: the flat buffer has alignment padding between masks that nobody writes
+        return (all(torch.equal(r.mask(n), ref.mask(n)) for n in range(N)) and torch.equal(r.area, ref.area)
+                and torch.equal(r.bbox, ref.bbox))
+    assert same(ra, ref_a) and same(rb, ref_b) and same(ri, ident_a)
+    assert int(pa.ws.abs().sum()) == 0 and int(pi.ws.abs().sum()) == 0        # left zeroed for the next launch
+    # default path: no workspace bound
+    l = _lib_mod.lib()
+    masks = torch.zeros(pi.total, dtype=torch.uint8, device="cuda")
+    area = torch.zeros(N, dtype=torch.int32, device="cuda")
+    bbox = torch.zeros((N, 4), dtype=torch.int32, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib_mod.check(l.isg_decode_bind_workspace(None, 0))
+    _lib_mod.check(l.isg_decode(la.data_ptr(), 0, N, h, w, pi.boxes_d.data_ptr(), pi.off_d.data_ptr(), w, h, 0.5,
+                                masks.data_ptr(), None, area.data_ptr(), bbox.data_ptr(), st))
+    torch.cuda.synchronize()
+    assert all(torch.equal(masks[int(pi.offsets[n]):int(pi.offsets[n]) + h * w].view(h, w), ident_a.mask(n)) for n in range(N))
+    assert torch.equal(area, ident_a.area) and torch.equal(bbox, ident_a.bbox)
+    small = torch.zeros(16, dtype=torch.int32, device="cuda")
+    _lib_mod.check(l.isg_decode_bind_workspace(small.data_ptr(), 1))
+    assert l.isg_decode(la.data_ptr(), 0, N, h, w, pi.boxes_d.data_ptr(), pi.off_d.data_ptr(), w, h, 0.5,
+                        masks.data_ptr(), None, area.data_ptr(), bbox.data_ptr(), st) == -1     # 40 instances > workspace of 1
+    _lib_mod.check(l.isg_decode_bind_workspace(None, 0))
