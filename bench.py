@@ -540,6 +540,9 @@ def run_extras(args, model, make_model, measure, xs, dev, B, S):
                               ms_per_decode=j["roofline_decode"]["ms_per_decode"],
                               ms_decode_plus_idmap=j["roofline_decode"]["ms_decode_plus_idmap"],
                               crop_resize_ms=j["crop_resize"]["ms"])
+        j = sub_bench(["--workload", "cfg5", "--steps", "5"])
+        ex["cfg5"] = {k: j.get(k) for k in ("value", "ms_per_step", "eager_ms_per_step", "exchange", "loss", "error") if k in j}
+        ex["cfg5"]["what"] = "configs[4] on ONE GPU: train_instance.py step, 16 images at 512x512, bf16 autocast; graph replay"
     out["extra"] = ex
     return out
 

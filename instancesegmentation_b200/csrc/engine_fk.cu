@@ -2007,7 +2007,7 @@ struct FkBuilder {
             const std::string p = "bottle1_x." + std::to_string(i);
             Next n2;
             if (i < 3) n2 = next_of("bottle1_x." + std::to_string(i + 1) + ".convs.0", 16, ACT_PRELU, h8, w8);
-            y = block_res(p, y, m1, 16, 1, false, n2, i == 3 ? "bottle1_5" : p, i == 3);
+            y = block_res(p, y, m1, 16, 1, false, n2, i == 3 ? "bottle1_5" : p, true);   // every block output is a test tap
             m1 = n2.out;
         }
         const bool mega16 = split ? mega3_layout(h16, w16, 128, 48, 5).ok : mega_layout(h16, w16, 128, 48, 5).ok;
@@ -2024,7 +2024,7 @@ struct FkBuilder {
                 const std::string p = pre + "." + std::to_string(i);
                 Next n2 = after;
                 if (i < 4) n2 = next_of(pre + "." + std::to_string(i + 1) + ".convs.0", 48, ACT_PRELU, h16, w16);
-                t = block_res(p, t, m, 48, i < 4 ? dils[i] : 1, i == 4, n2, i == 4 ? outname : p, i == 4);
+                t = block_res(p, t, m, 48, i < 4 ? dils[i] : 1, i == 4, n2, i == 4 ? outname : p, true);
                 m = n2.out;
             }
             return t;

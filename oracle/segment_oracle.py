@@ -88,9 +88,11 @@ def _up(sd, p, x, skip):
 _DILS = (1, 2, 1, 4)
 
 
-def _wide(sd, p, x):
+def _wide(sd, p, x, taps=None):
     for i, d in enumerate(_DILS):
         x = _res3(sd, f"{p}.{i}", x, d)
+        if taps is not None:
+            taps[f"{p}.{i}"] = x
     return _res5(sd, f"{p}.4", x)
 
 
@@ -115,11 +117,12 @@ def segment_forward(sd, x, taps=None, dtype=torch.float32):
     y = d1
     for i in range(4):
         y = _res3(sd, f"bottle1_x.{i}", y, 1)                               # :479
+        t[f"bottle1_x.{i}"] = y
     t["bottle1_5"] = y
     t["bottle2_down"], t["keep2"] = d2, keep2 = _down(sd, "bottle2_1", y)  # :482
-    t["bottle2_8"] = y = _wide(sd, "bottle2_x", d2)                         # :483
+    t["bottle2_8"] = y = _wide(sd, "bottle2_x", d2, t)                      # :483 (per-block taps bottle2_x.0..3; .4 = bottle2_8)
     t["bottle3_1"] = y = _proj(sd, "bottle3_1", torch.cat((y, d2), 1), "prelu")  # :485-488
-    t["bottle3_8"] = y = _wide(sd, "bottle3_x", y)                          # :489
+    t["bottle3_8"] = y = _wide(sd, "bottle3_x", y, t)                       # :489
     t["bottle4_1"] = y = _up(sd, "bottle4_1up", y, keep2)                   # :492
     t["bottle4_2"] = y = _proj(sd, "bottle4_2", torch.cat((d1, y), 1), "relu")   # :494-496
     t["bottle4_3"] = y = _plain(sd, "bottle4_3", y)                         # :497

@@ -319,3 +319,48 @@ def test_pipeline_matches_direct_calls(golden_state):
         assert torch.equal(ah, r.area.cpu()) and torch.equal(bh, r.bbox.cpu())
     # uint8 and host-normalised fp32 batches of the same images agree
     assert torch.equal(outs[0][0], outs[3][0]) and torch.equal(outs[1][0], outs[4][0])
+
+
+_BLOCK_TAP_SCRIPT = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, sys.argv[1])
+from instancesegmentation_b200 import Segment, synth
+from oracle.segment_oracle import segment_forward
+z = np.load(sys.argv[2])
+sd = {k: torch.from_numpy(z[k]) for k in z.files}
+prec, H, W = sys.argv[3], int(sys.argv[4]), int(sys.argv[5])
+m = Segment(3); m.load_state_dict(sd); m.precision, m.max_batch = prec, 2
+m = m.cuda().eval()
+x = torch.from_numpy(synth.batch(2, H, W, seed=4321))
+taps = {}
+segment_forward(sd, x, taps)
+with torch.no_grad():
+    m(x.cuda())
+mine = next(iter(m._engines.values())).taps(2)
+blocks = [k for k in mine if ".x." in k.replace("_x.", ".x.")]
+assert len(blocks) >= 11, sorted(mine)
+for k, t in mine.items():
+    print(k, float((t - taps[k]).abs().max() / taps[k].abs().max().clamp_min(1e-6)))
+"""
+
+
+@pytest.mark.parametrize("precision,bound", [("bf16x3", 2e-3), ("bf16", 0.3)])
+def test_every_residual_block_is_tapped_with_per_block_launches(tmp_path, precision, bound):
+    """With ISG_FK_NO_MEGA=1 every Bottleneck3x3 / Bottleneck5x5 (segment.py:52-111) is its own launch and its output a
+    tap: each of the 14 blocks is compared with the oracle on its own (the Bottleneck5x5 blocks bottle2_x.4 = bottle2_8 and
+    bottle3_x.4 = bottle3_8 with their position-dependent bias included).  The cluster-resident launches are bitwise
+    identical to these (test_bf16_launch_variants_are_bitwise_identical)."""
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "taps.py"
+    script.write_text(_BLOCK_TAP_SCRIPT)
+    env = dict(os.environ, ISG_FK_NO_MEGA="1", ISG_FK_NO_TUNE="1")
+    out = subprocess.run([sys.executable, str(script), root, os.path.join(GOLDEN, "segment3_state.npz"), precision, "512", "512"],
+                         check=True, env=env, timeout=600, capture_output=True, text=True).stdout
+    report = {l.split()[0]: float(l.split()[1]) for l in out.splitlines() if len(l.split()) == 2}
+    print(report)
+    for k in ["bottle1_x.0", "bottle1_x.2", "bottle2_x.0", "bottle2_x.1", "bottle2_x.3", "bottle3_x.1", "bottle3_x.3",
+              "bottle2_8", "bottle3_8"]:
+        assert k in report, (k, sorted(report))
+    bad = {k: v for k, v in report.items() if not v < bound}
+    assert not bad, bad
