@@ -469,6 +469,11 @@ struct FkBuilder {
     // MMA passes of a stage: 0 = plain bf16 plan; split plans default to all three
     int passes_of(const StageSpec& st) const { return !P->split ? 0 : (st.passes < 0 ? 7 : st.passes); }
     static int npasses(int passes) { return passes ? (passes & 1) + ((passes >> 1) & 1) + ((passes >> 2) & 1) : 1; }
+    // narrow three-pass stages run pass A_hi as one MMA over [W_hi | W_lo] (fk::Stage::nmerge); ISG_X3_NO_NMERGE=1 disables
+    bool nmerge_of(const StageSpec& st) const {
+        static const bool off = getenv("ISG_X3_NO_NMERGE") != nullptr;
+        return !off && P->split && passes_of(st) == 7 && st.N <= 32;
+    }
 
     bool layout(const Spec& s, int TH, int TW, int ctas, int nlbuf, Lay& L, int pipe = 0) const {
         const int hx = s.stages[0].taps9 ? 1 : 0;
@@ -478,7 +483,7 @@ struct FkBuilder {
         const int mrows = TH * L.pitch;
         L.n_mt = cdiv(mrows, 128);
         int maxN = 0;
-        for (auto& st : s.stages) maxN = std::max(maxN, st.N);
+        for (auto& st : s.stages) maxN = std::max(maxN, nmerge_of(st) ? 2 * st.N : st.N);
         L.cols = L.n_mt * maxN;
         if (pipe && 2 * L.cols > 512) return false;   // two accumulators
         if (L.cols > 512 || (int)tc::tmem_cols_pow2(L.cols) > 512 / ctas) return false;
@@ -577,7 +582,7 @@ struct FkBuilder {
                 int n = 0;
                 for (int t = 0; t < (st.taps9 ? 9 : 1); ++t)
                     for (int ks = 0; ks < L.K[k] / 16; ++ks) n += (!st.used || st.used(t, ks)) ? 1 : 0;
-                L.tab_n = std::max(L.tab_n, n * npasses(passes_of(st)));
+                L.tab_n = std::max(L.tab_n, n * (nmerge_of(st) ? 2 : npasses(passes_of(st))));
             }
             if (L.tab_n > fk::TAB_N_SPLIT) return false;
             L.smem = (size_t)off + 128 + 2 * 3 * (size_t)L.tab_n * 16;
@@ -738,10 +743,12 @@ struct FkBuilder {
                     if (!st.used || st.used(t, ks)) { d.tap_mask[t] |= 1u << ks; ++d.nent; }
             }
             d.passes = passes_of(st);
-            d.nent_tab = d.nent * npasses(d.passes);
+            d.nmerge = nmerge_of(st) ? 1 : 0;
+            d.nent_tab = d.nent * (d.nmerge ? 2 : npasses(d.passes));
             d.b_lo = (uint32_t)d.nent * st.N * 2;
             if (P->split ? d.nent_tab > L.tab_n : d.nent > fk::TAB_N) { fprintf(stderr, "libisg: %s: %d MMAs per M tile exceed the descriptor table\n", s.name.c_str(), d.nent); abort(); }
-            d.b_desc = tc::umma_smem_desc(L.blob_off + L.b_off[k], st.N * 16, 128);
+            // merged blocks are [2][2N][8]: the K chunks of a block are 2N rows apart
+            d.b_desc = tc::umma_smem_desc(L.blob_off + L.b_off[k], (d.nmerge ? 2 : 1) * st.N * 16, 128);
             d.vec_off = L.blob_off + L.vec_off[k];
             if (st.res_load >= 0) {
                 d.res_on = 1; d.res_off = L.load_off[st.res_load]; d.res_plane_bytes = L.load_plane[st.res_load];
@@ -796,7 +803,8 @@ struct FkBuilder {
         const size_t blob = arena((size_t)L.blob_bytes / 4);
         const Spec sp = s;
         std::vector<int> pass_bits;
-        for (auto& st : s.stages) pass_bits.push_back(passes_of(st));
+        std::vector<int> merge_bits;
+        for (auto& st : s.stages) { pass_bits.push_back(passes_of(st)); merge_bits.push_back(nmerge_of(st) ? 1 : 0); }
         Op op;
         op.name = s.name + " [fk]";
         op.pack = [=](const HostWeights& w, float* A) {
@@ -824,8 +832,14 @@ struct FkBuilder {
                                 if (v != 0.f) { fprintf(stderr, "libisg: %s: weight in a K slice declared unused\n", sp.name.c_str()); abort(); }
                                 continue;
                             }
-                            const size_t idx = (size_t)blk * N * 16 + (size_t)((kk % 16) / 8) * N * 8 + (size_t)n * 8 + (kk % 8);
                             const uint16_t hi = tc::f2bf(v);
+                            if (merge_bits[k]) {   // [W_hi | W_lo] side by side: blocks of [2][2N][8]
+                                const size_t idx = (size_t)blk * N * 32 + (size_t)((kk % 16) / 8) * N * 16 + (size_t)n * 8 + (kk % 8);
+                                wb[idx] = hi;
+                                wb[idx + (size_t)N * 8] = tc::f2bf(v - tc::bf2f(hi));
+                                continue;
+                            }
+                            const size_t idx = (size_t)blk * N * 16 + (size_t)((kk % 16) / 8) * N * 8 + (size_t)n * 8 + (kk % 8);
                             wb[idx] = hi;
                             // split precision: W_lo = bf16(w - W_hi) in a second run of blocks (pass A_hi.W_lo)
                             if (lo_blocks) wb[(size_t)nslot * N * 16 + idx] = tc::f2bf(v - tc::bf2f(hi));
@@ -1528,6 +1542,25 @@ struct FkBuilder {
                 if (getenv("ISG_FK_VERBOSE")) fprintf(stderr, "mega3 %s: %d co-resident clusters of %d, smem %zu\n", name.c_str(), nc, mega3::CLUSTER, smem);
             }
             cfg.gridDim = dim3(mega3::CLUSTER * std::min(*nclusters, std::max(n, 1)));
+            static const bool prof_on = getenv("ISG_MEGA_PROF") != nullptr;
+            if (prof_on) {   // debug: per-phase cycle sums of every CTA
+                const int grid = cfg.gridDim.x;
+                cudaMalloc(&p.prof, (size_t)grid * 8 * sizeof(long long));
+                cudaMemset(p.prof, 0, (size_t)grid * 8 * sizeof(long long));
+                cudaError_t e = cudaLaunchKernelEx(&cfg, mega3::mega3_kernel, maps->in[0], maps->out[0], p);
+                cudaStreamSynchronize(stream);
+                std::vector<long long> h((size_t)grid * 8);
+                cudaMemcpy(h.data(), p.prof, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+                cudaFree(p.prof);
+                double ph[8] = {0};
+                for (int b = 0; b < grid; ++b) for (int k = 0; k < 8; ++k) ph[k] += (double)h[(size_t)b * 8 + k];
+                const double steps = (double)n * nb * mega3::CLUSTER;   // (image, block) steps summed over CTAs
+                fprintf(stderr, "mega3prof %-10s cycles per block and CTA: wgt+gemm0 %6.0f epi_m1+push %6.0f halo-barrier %6.0f stencil %6.0f "
+                        "w2+gemm2 %6.0f epi_x %6.0f | x load per image %6.0f | sum per block %6.0f\n", name.c_str(), ph[1] / steps,
+                        ph[2] / steps, ph[3] / steps, ph[4] / steps, ph[5] / steps, ph[6] / steps, ph[0] / ((double)n * mega3::CLUSTER),
+                        (ph[1] + ph[2] + ph[3] + ph[4] + ph[5] + ph[6]) / steps);
+                return e;
+            }
             return cudaLaunchKernelEx(&cfg, mega3::mega3_kernel, maps->in[0], maps->out[0], p);
         };
         P->ops.push_back(op);

@@ -58,6 +58,10 @@ struct Stage {
     // split precision (ISG_MODE_BF16X3): every operand element is a bf16 pair hi + lo (hi = bf16(v), lo = bf16(v - hi)).
     // passes: bit 0 = A_hi.W_hi, bit 1 = A_lo.W_hi, bit 2 = A_hi.W_lo accumulate into the same TMEM tile (0 = plain bf16)
     int passes;
+    // nmerge (narrow stages, N <= 32, whose MMAs are bound by reading the 4 KB A tile, not by math): the weight blocks are
+    // [W_hi | W_lo] side by side (2N columns), pass A_hi is ONE MMA of width 2N into TMEM columns [0,N) and [N,2N), pass
+    // A_lo uses the first N columns of the same blocks; the epilogue adds the two column halves.  2 MMAs per K slice, not 3.
+    int nmerge;
     uint32_t a_lo[MAX_KS];         // K slice ks: distance from its hi planes to its lo planes, 16-byte units
     uint32_t b_lo;                 // distance from the W_hi blocks to the W_lo blocks, 16-byte units
     int res_lo;                    // bytes from a residual hi plane to its lo plane (0: residual is plain bf16)
@@ -350,6 +354,7 @@ __device__ __forceinline__ void build_desc_table(const Params& p, uint64_t* tabs
         int j = 0;
         for (int pass = 0; pass < (SPLIT ? 3 : 1); ++pass) {
             if (SPLIT && !((s.passes >> pass) & 1)) continue;
+            if (SPLIT && s.nmerge && pass == 2) continue;      // W_lo rides in pass 0's wide blocks
             uint64_t bd = s.b_desc + base16 + (pass == 2 ? s.b_lo : 0u);
             for (int t = 0; t < s.ntaps; ++t)
                 for (int ks = 0; ks < s.nks; ++ks) {
@@ -359,7 +364,7 @@ __device__ __forceinline__ void build_desc_table(const Params& p, uint64_t* tabs
                     if (SPLIT) {
                         if (pass == 1) d += s.a_lo[ks];
                         tab[2 * j] = d; tab[2 * j + 1] = bd;
-                        bd += (uint32_t)s.N * 2;
+                        bd += (uint32_t)s.N * (s.nmerge ? 4 : 2);
                         ++j;
                     } else {
                         tab[j++] = d;
@@ -376,6 +381,20 @@ __device__ __forceinline__ void issue_mma(const Params& p, const Stage& s, const
     const uint32_t idesc = tc::umma_idesc_bf16(128, s.N);
     if (SPLIT) {
         const int n = s.nent_tab;
+        if (s.nmerge) {   // entries [0, nent): A_hi . [W_hi | W_lo] (width 2N); [nent, 2 nent): A_lo . W_hi (width N)
+            const uint32_t idesc2 = tc::umma_idesc_bf16(128, 2 * s.N);
+            const int nh = s.nent;
+            for (int mt = first; mt < p.n_mt; mt += step) {
+                const uint64_t row = (uint64_t)(mt * 128);
+                const uint32_t d = tmem_base + mt * 2 * s.N;
+                tc::umma_bf16(d, tab[0] + row, tab[1], idesc2, 0u);
+#pragma unroll 4
+                for (int j = 1; j < nh; ++j) tc::umma_bf16(d, tab[2 * j] + row, tab[2 * j + 1], idesc2, 1u);
+#pragma unroll 4
+                for (int j = nh; j < n; ++j) tc::umma_bf16(d, tab[2 * j] + row, tab[2 * j + 1], idesc, 1u);
+            }
+            return;
+        }
         for (int mt = first; mt < p.n_mt; mt += step) {
             const uint64_t row = (uint64_t)(mt * 128);
             tc::umma_bf16(tmem_base + mt * s.N, tab[0] + row, tab[1], idesc, 0u);
@@ -459,8 +478,10 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
     int mt_geom = -1;
     EpiGeom g = {};
     uint32_t ra[16];
+    const bool merged = SPLIT && s.nmerge;      // accumulator columns of M tile mt: [mt*2N, +N) and [mt*2N + N, +N)
+    auto tcol = [&](int it_) { return merged ? (it_ / ncc) * 2 * N + (it_ % ncc) * 16 : it_ * 16; };   // plain: mt*N + cc*16 = item*16
     __syncwarp();
-    tmem_ld16_nowait(lane_base + item * 16, ra);   // column of item = mt*N + cc*16 = item*16
+    tmem_ld16_nowait(lane_base + tcol(item), ra);
     while (true) {
         tmem_ld_wait_dep(ra);
         if (mt != mt_geom) { g = epi_geom(p, s, mt, quad, lane, x0, y0); mt_geom = mt; }
@@ -468,10 +489,17 @@ __device__ __forceinline__ void run_epilogue(uint8_t* smem, const Params& p, con
         float v[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(ra[i]);
+        if (merged) {   // + the A_hi . W_lo half
+            __syncwarp();
+            tmem_ld16_nowait(lane_base + tcol(item) + N, ra);
+            tmem_ld_wait_dep(ra);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += __uint_as_float(ra[i]);
+        }
         // the accumulators are in v: the next item's TMEM load overlaps the arithmetic below
         const int nxt = item + NGROUPS;
         __syncwarp();
-        if (nxt < nitems) tmem_ld16_nowait(lane_base + nxt * 16, ra);
+        if (nxt < nitems) tmem_ld16_nowait(lane_base + tcol(nxt), ra);
         if (s.res_on && g.geom) {
             const int ch0 = s.res_mod ? col0 - fastdiv(cc, s.res_magic) * s.res_mod : col0;
             const uint8_t* rp = res + (size_t)(ch0 >> 3) * s.res_plane_bytes + (size_t)g.pc * 16;

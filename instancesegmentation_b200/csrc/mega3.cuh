@@ -39,7 +39,10 @@ struct Params {
     int x_off, x_lo, m1_off, m1_lo, d_off, d_lo;      // shared memory: planes and hi -> lo distances (bytes)
     int wg_off, wc_off[2], bar_off;
     int tmem_cols;
+    long long* prof;              // debug (ISG_MEGA_PROF=1): per-CTA sums of phase cycles [8], else null
 };
+#define M3_ACC(i) do { if (p.prof && threadIdx.x == 0) { const long long t_ = clock64(); \
+    p.prof[(size_t)blockIdx.x * 8 + (i)] += t_ - tprev; tprev = t_; } } while (0)
 
 // three passes of one GEMM for the CTA's M tiles: A planes hi (+ a_lo for the lo planes), B blocks hi (+ b_lo)
 __device__ __forceinline__ void issue_gemm3(uint32_t a_addr, uint32_t a_lo, int a_plane_bytes, uint32_t b_addr, uint32_t b_lo,
@@ -230,6 +233,7 @@ mega3_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CU
 
     const int x_half_bytes = (p.Cs >> 3) * p.npx * 16;
     int seq = 0, mma_n = 0, it = 0, wg_n = 0;
+    long long tprev = p.prof ? clock64() : 0;
     bool pending2 = false;      // a cluster barrier arrival (m1 planes read) not yet waited for
     for (int img = cluster_id; img < p.nimg; img += nclusters, ++it) {
         if (tid == 0) {
@@ -239,6 +243,7 @@ mega3_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CU
             tc::tma_load_act(smem + p.x_off + p.x_lo, &min, &bars[0], p.in_planar, 0, (int)rank * p.R, p.Cs >> 3, img);
         }
         tc::mbar_wait(&bars[0], it & 1);
+        M3_ACC(0);   // x load (+ previous store drained)
         for (int k = 0; k < p.nblocks; ++k, ++seq) {
             const int wbi = seq & 1;
             const uint8_t* wc = smem + p.wc_off[wbi];
@@ -255,12 +260,15 @@ mega3_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CU
             __syncwarp();
             tc::mbar_wait(&bars[4], mma_n & 1); ++mma_n;
             tc::tc_fence_after();
+            M3_ACC(1);   // weights wait + GEMM0
             if (tid == 0) load_wg(2 * seq + 1);     // w0 has been consumed: w2 streams in under the epilogue + stencil
             if (pending2) { mega::cluster_wait(); pending2 = false; }   // neighbours have read their halo of the previous block
             epi_m1(smem, p, wc, tmem_base, blk.sep5 ? 2 : blk.dil, rank);
             tc::tc_fence_before();
+            M3_ACC(2);   // m1 epilogue + pushes (+ wait for the neighbours' previous reads)
             mega::cluster_arrive();       // release: my rows (local and pushed) are written ...
             mega::cluster_wait();         // ... acquire: so are the halo rows the neighbours pushed to me
+            M3_ACC(3);   // halo exchange barrier
             // ---- d = PReLU(dw(m1)) ----
             {
                 fk::Stencil st;
@@ -273,6 +281,7 @@ mega3_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CU
             }
             tc::fence_proxy_async();
             __syncthreads();
+            M3_ACC(4);   // stencil
             mega::cluster_arrive_relaxed();   // my reads of the m1 planes are done; waited for before the next block's pushes
             pending2 = true;
             // ---- x = PReLU(W2 . d + x) ----
@@ -286,11 +295,13 @@ mega3_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CU
             __syncwarp();
             tc::mbar_wait(&bars[4], mma_n & 1); ++mma_n;
             tc::tc_fence_after();
+            M3_ACC(5);   // w2 wait + GEMM2
             if (tid == 0 && seq + 1 < total_seq) load_wg(2 * (seq + 1));   // next block's w0 under the x epilogue
             epi_x(smem, p, wc, tmem_base);
             tc::fence_proxy_async();   // x planes: next read by tcgen05.mma / the TMA stores
             tc::tc_fence_before();
             __syncthreads();
+            M3_ACC(6);   // x epilogue
             if (tid == 0 && seq + 2 < total_seq) load_wc(seq + 2);   // this constants buffer is free
         }
         if (tid == 0) {
