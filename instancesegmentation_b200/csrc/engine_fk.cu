@@ -1422,7 +1422,7 @@ struct FkBuilder {
         int off = 0;
         const int xh = (q.Cs / 8) * q.npx * 16, mh = (q.Cm / 8) * q.rows_p * q.pitch * 16, dh = (q.Cm / 8) * q.npx * 16;
         q.x_off = off; q.x_lo = r128(xh); off = r128(off + q.x_lo + xh);
-        q.m1_off = off; q.m1_lo = r128(mh); off = r128(off + q.m1_lo + mh);
+        q.m1_off = off; q.m1_lo = 0; off = r128(off + 2 * mh);   // m1 as fp32 planes (32 bytes per pixel and chunk)
         q.d_off = off; q.d_lo = r128(dh); off = r128(off + q.d_lo + dh);
         q.wg_off = off; off = r128(off + std::max(q.w0_bytes, q.w2_bytes));
         q.wc_off[0] = off; off = r128(off + q.c_bytes);
@@ -1559,6 +1559,13 @@ struct FkBuilder {
                         "w2+gemm2 %6.0f epi_x %6.0f | x load per image %6.0f | sum per block %6.0f\n", name.c_str(), ph[1] / steps,
                         ph[2] / steps, ph[3] / steps, ph[4] / steps, ph[5] / steps, ph[6] / steps, ph[0] / ((double)n * mega3::CLUSTER),
                         (ph[1] + ph[2] + ph[3] + ph[4] + ph[5] + ph[6]) / steps);
+                {
+                    int n5 = 0, n4 = 0;
+                    for (int k = 0; k < nb; ++k) { n5 += p.blk[k].sep5; n4 += (!p.blk[k].sep5 && p.blk[k].dil == 4); }
+                    const double per = (double)n * mega3::CLUSTER;
+                    fprintf(stderr, "mega3prof %-10s stencil cycles per block by kind: dil 1/2 %6.0f | dil 4 (+ x load) %6.0f | 5x5 %6.0f\n", name.c_str(),
+                            nb - n5 - n4 > 0 ? ph[4] / (per * (nb - n5 - n4)) : 0.0, n4 ? ph[0] / (per * n4) : 0.0, n5 ? ph[7] / (per * n5) : 0.0);
+                }
                 return e;
             }
             return cudaLaunchKernelEx(&cfg, mega3::mega3_kernel, maps->in[0], maps->out[0], p);

@@ -192,7 +192,11 @@ __device__ __forceinline__ void split_bf16(float a, float b, uint32_t& hi, uint3
 // taps in (ty, tx) order from zero, whatever the strip it falls in.
 // Output rows [rb, TH) of the tile; ST_ROWS = rows per strip.
 // SPLIT: input and output planes are hi + lo pairs (s.in_lo / s.out_lo bytes apart); the arithmetic is the same fp32.
-template <int KS, int DIL, int ST_ROWS, int NT, bool SPLIT = false>
+// F32IN (with SPLIT): the input planes hold fp32 values as planes of FOUR channels, [4-channel group][row][col][4 x fp32]
+// (16 bytes per pixel, s.in_plane_bytes = one such plane) -- for an operand that only this stencil reads (mega3's m1)
+// that is the same bytes as a hi + lo pair and a quarter of the instructions per tap (one 8-byte load instead of two
+// loads, two unpacks and an add); 16-byte pixels keep the producer's 16-byte stores free of bank conflicts.
+template <int KS, int DIL, int ST_ROWS, int NT, bool SPLIT = false, bool F32IN = false>
 __device__ __forceinline__ void stencil_strips(uint8_t* smem, const Stencil& s, int rb, int TH, int TW, int Wimg, int x0, int boff) {
     constexpr int NW = NT / 32, R = KS / 2;
     const int C = s.nchunks * 8, pitch16 = s.in_pitch * 16;
@@ -217,7 +221,9 @@ __device__ __forceinline__ void stencil_strips(uint8_t* smem, const Stencil& s, 
 #pragma unroll
         for (int t = 0; t < KS * KS; ++t) w[t] = *reinterpret_cast<const float2*>(wt + t * C + ch);
         const int row0 = r0 + s.halo - R * DIL;            // plane row of the first input row
-        const uint8_t* in = smem + s.in_off + boff + (size_t)k * s.in_plane_bytes + sub * 4 + (cld + s.halo - R * DIL) * 16;
+        const uint8_t* in = F32IN
+            ? smem + s.in_off + boff + (size_t)(2 * k + (sub >> 1)) * s.in_plane_bytes + (sub & 1) * 8 + (cld + s.halo - R * DIL) * 16
+            : smem + s.in_off + boff + (size_t)k * s.in_plane_bytes + sub * 4 + (cld + s.halo - R * DIL) * 16;
         const int rmax = last_row - row0;                  // rows past the planes only feed outputs past the tile: clamp
         float2 acc[ST_ROWS];
 #pragma unroll
@@ -228,6 +234,7 @@ __device__ __forceinline__ void stencil_strips(uint8_t* smem, const Stencil& s, 
             float2 v[KS];
 #pragma unroll
             for (int tx = 0; tx < KS; ++tx) {
+                if (F32IN) { v[tx] = *reinterpret_cast<const float2*>(row + tx * DIL * 16); continue; }
                 v[tx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(row + tx * DIL * 16));
                 if (SPLIT) {
                     const float2 l = bf2_to_f2(*reinterpret_cast<const uint32_t*>(row + s.in_lo + tx * DIL * 16));

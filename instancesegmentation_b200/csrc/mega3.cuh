@@ -64,14 +64,15 @@ __device__ __forceinline__ void issue_gemm3(uint32_t a_addr, uint32_t a_lo, int 
     }
 }
 
-// m1 = PReLU(acc + shift) -> hi / lo into the zero-haloed m1 planes (+ the neighbours' halo rows)
+// m1 = PReLU(acc + shift) -> fp32 into the zero-haloed m1 planes [4-channel group][row][col][4 x fp32] (+ the neighbours' halo rows).
+// m1 is read by the depthwise stencil only, never by an MMA: fp32 costs the bytes of a hi + lo pair and no split.
 __device__ __forceinline__ void epi_m1(uint8_t* smem, const Params& p, const uint8_t* wc, uint32_t tmem_base, int reach,
                                        uint32_t rank) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, quad = warp & 3, grp = warp >> 2;
     const int ncc = p.Cm >> 4, nitems = p.n_mt * ncc;
     const float* vec = reinterpret_cast<const float*>(wc + p.v0_off);
     const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
-    const int plane_bytes = p.rows_p * p.pitch * 16;
+    const int plane_bytes = p.rows_p * p.pitch * 16;   // one plane = 4 channels, 16 bytes per pixel
     for (int item = grp; item < nitems; item += NGROUPS) {
         int mt = 0, cc = item;
         while (cc >= ncc) { cc -= ncc; ++mt; }
@@ -82,37 +83,32 @@ __device__ __forceinline__ void epi_m1(uint8_t* smem, const Params& p, const uin
         const int px = mt * 128 + quad * 32 + lane;
         const int r = fk::fastdiv(px, p.w_magic), c = px - r * p.W;
         const int col0 = cc * 16;
-        uint32_t h[8], l[8];
+        uint4 q[4];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float2 sh = *reinterpret_cast<const float2*>(vec + col0 + 2 * j);
-            const float2 sl = *reinterpret_cast<const float2*>(vec + p.Cm + col0 + 2 * j);
-            float a = __uint_as_float(ra[2 * j]) + sh.x, b = __uint_as_float(ra[2 * j + 1]) + sh.y;
-            a = a >= 0.f ? a : a * sl.x; b = b >= 0.f ? b : b * sl.y;
-            fk::split_bf16(a, b, h[j], l[j]);
+        for (int j = 0; j < 4; ++j) {
+            const float4 sh = *reinterpret_cast<const float4*>(vec + col0 + 4 * j);
+            const float4 sl = *reinterpret_cast<const float4*>(vec + p.Cm + col0 + 4 * j);
+            float a0 = __uint_as_float(ra[4 * j]) + sh.x, a1 = __uint_as_float(ra[4 * j + 1]) + sh.y;
+            float a2 = __uint_as_float(ra[4 * j + 2]) + sh.z, a3 = __uint_as_float(ra[4 * j + 3]) + sh.w;
+            a0 = a0 >= 0.f ? a0 : a0 * sl.x; a1 = a1 >= 0.f ? a1 : a1 * sl.y;
+            a2 = a2 >= 0.f ? a2 : a2 * sl.z; a3 = a3 >= 0.f ? a3 : a3 * sl.w;
+            q[j] = make_uint4(__float_as_uint(a0), __float_as_uint(a1), __float_as_uint(a2), __float_as_uint(a3));
         }
-        const uint4 q0 = make_uint4(h[0], h[1], h[2], h[3]), q1 = make_uint4(h[4], h[5], h[6], h[7]);
-        const uint4 l0 = make_uint4(l[0], l[1], l[2], l[3]), l1 = make_uint4(l[4], l[5], l[6], l[7]);
         if (px < p.npx) {
-            uint8_t* d = smem + p.m1_off + (size_t)(col0 >> 3) * plane_bytes + (size_t)((r + HALO) * p.pitch + c + HALO) * 16;
-            *reinterpret_cast<uint4*>(d) = q0;
-            *reinterpret_cast<uint4*>(d + plane_bytes) = q1;
-            *reinterpret_cast<uint4*>(d + p.m1_lo) = l0;
-            *reinterpret_cast<uint4*>(d + p.m1_lo + plane_bytes) = l1;
+            // channels col0 + 4j .. col0 + 4j + 3 -> plane col0/4 + j
+            uint8_t* d = smem + p.m1_off + (size_t)(col0 >> 2) * plane_bytes + (size_t)((r + HALO) * p.pitch + c + HALO) * 16;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(d + j * plane_bytes) = q[j];
             // edge rows are the neighbours' halo: the CTA above sees my row r as its row R + r, the one below as r - R
             if (r < reach && rank > 0) {
                 const uint32_t la = tc::smem_u32(d) + (uint32_t)(p.R * p.pitch * 16);
-                mega::st_remote_16(la, rank - 1, q0);
-                mega::st_remote_16(la + plane_bytes, rank - 1, q1);
-                mega::st_remote_16(la + p.m1_lo, rank - 1, l0);
-                mega::st_remote_16(la + p.m1_lo + plane_bytes, rank - 1, l1);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mega::st_remote_16(la + j * plane_bytes, rank - 1, q[j]);
             }
             if (r >= p.R - reach && rank < CLUSTER - 1) {
                 const uint32_t la = tc::smem_u32(d) - (uint32_t)(p.R * p.pitch * 16);
-                mega::st_remote_16(la, rank + 1, q0);
-                mega::st_remote_16(la + plane_bytes, rank + 1, q1);
-                mega::st_remote_16(la + p.m1_lo, rank + 1, l0);
-                mega::st_remote_16(la + p.m1_lo + plane_bytes, rank + 1, l1);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mega::st_remote_16(la + j * plane_bytes, rank + 1, q[j]);
             }
         }
     }
@@ -160,18 +156,18 @@ __device__ __forceinline__ void epi_x(uint8_t* smem, const Params& p, const uint
 // depthwise stencil of the CTA's rows with the strip height the host chose for this block (split planes)
 __device__ __forceinline__ void stencil(uint8_t* smem, const fk::Stencil& st, const Block& blk, int R, int W) {
     if (blk.sep5) {
-        if (blk.sr == 4) fk::stencil_strips<5, 1, 4, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
-        else fk::stencil_strips<5, 1, 2, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
+        if (blk.sr == 4) fk::stencil_strips<5, 1, 4, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
+        else fk::stencil_strips<5, 1, 2, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
     } else if (blk.dil == 1) {
-        if (blk.sr == 4) fk::stencil_strips<3, 1, 4, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
-        else fk::stencil_strips<3, 1, 2, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
+        if (blk.sr == 4) fk::stencil_strips<3, 1, 4, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
+        else fk::stencil_strips<3, 1, 2, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
     } else if (blk.dil == 2) {
-        if (blk.sr == 4) fk::stencil_strips<3, 2, 4, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
-        else fk::stencil_strips<3, 2, 2, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
+        if (blk.sr == 4) fk::stencil_strips<3, 2, 4, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
+        else fk::stencil_strips<3, 2, 2, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
     } else {
-        if (blk.sr == 4) fk::stencil_strips<3, 4, 4, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
-        else if (blk.sr == 2) fk::stencil_strips<3, 4, 2, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
-        else fk::stencil_strips<3, 4, 1, THREADS, true>(smem, st, 0, R, W, W, 0, 0);
+        if (blk.sr == 4) fk::stencil_strips<3, 4, 4, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
+        else if (blk.sr == 2) fk::stencil_strips<3, 4, 2, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
+        else fk::stencil_strips<3, 4, 1, THREADS, true, true>(smem, st, 0, R, W, W, 0, 0);
     }
 }
 
@@ -195,9 +191,9 @@ mega3_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CU
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, p.tmem_cols);
-    // m1 planes (hi and lo) start all zero: halo columns and the halo rows beyond the image stay zero for the launch
+    // m1 planes (fp32) start all zero: halo columns and the halo rows beyond the image stay zero for the launch
     {
-        const int n16 = (p.m1_lo + (p.Cm >> 3) * p.rows_p * p.pitch * 16) >> 4;
+        const int n16 = ((p.Cm >> 3) * p.rows_p * p.pitch * 32) >> 4;
         uint4* z = reinterpret_cast<uint4*>(smem + p.m1_off);
         for (int i = tid; i < n16; i += THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
@@ -272,16 +268,16 @@ mega3_kernel(const __grid_constant__ CUtensorMap min, const __grid_constant__ CU
             // ---- d = PReLU(dw(m1)) ----
             {
                 fk::Stencil st;
-                st.on = 1; st.in_off = p.m1_off; st.in_pitch = p.pitch; st.in_plane_bytes = p.rows_p * p.pitch * 16;
+                st.on = 1; st.in_off = p.m1_off; st.in_pitch = p.pitch; st.in_plane_bytes = p.rows_p * p.pitch * 16;   // 4-channel fp32 plane
                 st.halo = HALO; st.nchunks = p.Cm >> 3; st.dil = blk.dil;
                 st.w_off = p.wc_off[wbi] + p.dw_off; st.vec_off = p.wc_off[wbi] + p.dv_off; st.sep5 = blk.sep5;
                 st.out_off = p.d_off; st.out_plane_bytes = p.npx * 16;
-                st.in_lo = p.m1_lo; st.out_lo = p.d_lo;
+                st.in_lo = 0; st.out_lo = p.d_lo;
                 stencil(smem, st, blk, p.R, p.W);
             }
             tc::fence_proxy_async();
             __syncthreads();
-            M3_ACC(4);   // stencil
+            M3_ACC(blk.sep5 ? 7 : (blk.dil == 4 ? 0 : 4));   // stencil (debug slots: 7 = 5x5, 0 = dilation 4 [shared with x load], 4 = dilation 1/2)
             mega::cluster_arrive_relaxed();   // my reads of the m1 planes are done; waited for before the next block's pushes
             pending2 = true;
             // ---- x = PReLU(W2 . d + x) ----
