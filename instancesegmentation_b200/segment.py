@@ -292,11 +292,14 @@ class Segment(nn.Module):
 
     def _engine_for(self, device, B, H, W):
         from .engine import SegmentEngine
-        key = (device.index, H, W, self.precision, min(self.max_batch, max(B, 1)))
+        # one plan per (device, size, precision): a plan serves any batch up to its max_batch (isg_forward groups
+        # larger ones), so a new one -- autotune + its own workspace -- is only built when B exceeds the cached
+        # plan's capacity (and that one is then dropped), never per distinct batch size
+        key = (device.index, H, W, self.precision)
+        need = min(self.max_batch, max(B, 1))
         eng = self._engines.get(key)
-        if eng is None or eng.max_batch < min(B, self.max_batch):
-            eng = SegmentEngine(device, self.in_channel, H, W,
-                                min(self.max_batch, max(B, 1)), self.precision)
+        if eng is None or eng.max_batch < need:
+            eng = SegmentEngine(device, self.in_channel, H, W, need, self.precision)
             self._engines[key] = eng
         if eng.weights_epoch != self._weights_epoch:
             eng.load_state_dict(self.state_dict())

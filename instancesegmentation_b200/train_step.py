@@ -74,10 +74,53 @@ class FlatBucket:
             return 1.0 / dist.get_world_size()
         return 1.0
 
+    def check_aliasing(self):
+        """The parameters must still be views of ``flat`` (``model.to()`` / ``.float()`` after the bucket was built
+        re-allocates them: Adam would then update memory the model no longer reads)."""
+        o = 0
+        for p, n in zip(self.params, self.sizes):
+            if p.data_ptr() != self.flat.data_ptr() + 4 * o:
+                raise RuntimeError("FlatBucket: a parameter no longer aliases the flat buffer (the model was moved or "
+                                   "cast after the bucket was built); build a new FlatBucket")
+            o += n
+
+    def state_dict(self):
+        """Optimizer state in ``torch.optim.Adam.state_dict()`` format (per-parameter ``step`` / ``exp_avg`` /
+        ``exp_avg_sq``, one param group), as the reference saves it next to the model (train_instance.py:497-503)."""
+        state, o = {}, 0
+        for i, (p, n) in enumerate(zip(self.params, self.sizes)):
+            state[i] = {"step": torch.tensor(float(self.step_count)),
+                        "exp_avg": self.exp_avg[o:o + n].view_as(p).clone(),
+                        "exp_avg_sq": self.exp_avg_sq[o:o + n].view_as(p).clone()}
+            o += n
+        group = {"lr": 1e-3, "betas": (0.9, 0.999), "eps": 1e-8, "weight_decay": 0, "amsgrad": False,
+                 "params": list(range(len(self.params)))}
+        return {"state": state, "param_groups": [group]}
+
+    def load_state_dict(self, sd):
+        """Resume from a ``torch.optim.Adam`` (or ``FlatBucket``) state dict: moments and step count."""
+        state = sd["state"]
+        steps, o = set(), 0
+        for i, (p, n) in enumerate(zip(self.params, self.sizes)):
+            st = state.get(i, state.get(str(i)))
+            if st is None:                      # a parameter that never got a gradient has no entry in torch's dict
+                self.exp_avg[o:o + n].zero_(); self.exp_avg_sq[o:o + n].zero_()
+            else:
+                if st["exp_avg"].numel() != n:
+                    raise ValueError(f"optimizer state of parameter {i} has {st['exp_avg'].numel()} elements, expected {n}")
+                self.exp_avg[o:o + n].copy_(st["exp_avg"].reshape(-1))
+                self.exp_avg_sq[o:o + n].copy_(st["exp_avg_sq"].reshape(-1))
+                steps.add(int(float(st["step"])))
+            o += n
+        if len(steps) > 1:
+            raise ValueError(f"per-parameter step counts differ ({sorted(steps)}): the flat update keeps one")
+        self.step_count = steps.pop() if steps else 0
+
     def adam_step(self, grad_scale, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
         """torch.optim.Adam defaults of train_instance.py:297, in libisg (CUDA only)."""
         if not self.flat.is_cuda:
             raise _lib.IsgError("adam_step runs in libisg on CUDA only; there is no CPU path")
+        self.check_aliasing()
         self.step_count += 1
         with torch.cuda.device(self.flat.device):
             _lib.check(_lib.lib().isg_adam_step(

@@ -370,3 +370,20 @@ def test_every_residual_block_is_tapped_with_per_block_launches(tmp_path, precis
         assert k in report, (k, sorted(report))
     bad = {k: v for k, v in report.items() if not v < bound}
     assert not bad, bad
+
+
+def test_one_plan_per_size_serves_smaller_batches(golden_state):
+    """The engine cache is keyed by (device, size, precision): a smaller batch reuses the plan (no second autotune /
+    workspace), a larger one replaces it; results do not depend on which plan served them."""
+    m = _model(golden_state, precision="bf16x3", max_batch=8)
+    x = torch.from_numpy(synth.batch(6, 64, 64, seed=21)).cuda()
+    with torch.no_grad():
+        y3 = m(x[:3])
+        e3 = _engine(m)
+        y1 = m(x[:1])
+        assert _engine(m) is e3 and len(m._engines) == 1          # B = 1 rides on the plan built for 3
+        y6 = m(x)
+        e6 = _engine(m)
+        assert e6 is not e3 and e6.max_batch == 6 and len(m._engines) == 1
+        assert torch.equal(m(x[:3]), y3) and _engine(m) is e6
+    assert torch.equal(y1, y3[:1]) and torch.equal(y6[:3], y3)

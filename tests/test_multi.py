@@ -141,3 +141,39 @@ def test_adam_step_matches_torch_adam():
         if b.grad is None:
             continue
         assert torch.allclose(a, b, rtol=1e-4, atol=1e-6), n
+
+
+def test_flat_bucket_state_dict_round_trips_with_torch_adam_and_detects_broken_aliasing():
+    """FlatBucket.state_dict() has torch.optim.Adam's format (the reference checkpoints optimizer.state_dict() next to
+    the model, train_instance.py:497-503) and load_state_dict() accepts a real Adam state; moving / casting the model
+    after the bucket was built is detected instead of silently training stale tensors."""
+    import torch
+    from instancesegmentation_b200 import Segment
+    from instancesegmentation_b200.train_step import FlatBucket
+    torch.manual_seed(0)
+    m = Segment(3)
+    opt = torch.optim.Adam(m.parameters())
+    for p in m.parameters():
+        p.grad = torch.randn_like(p) * 1e-2
+    opt.step(); opt.step()
+    ref = opt.state_dict()
+    b = FlatBucket(m)
+    b.load_state_dict(ref)
+    assert b.step_count == 2
+    sd = b.state_dict()
+    assert set(sd) == {"state", "param_groups"} and sd["param_groups"][0]["params"] == list(range(len(b.params)))
+    for i, st in ref["state"].items():
+        assert torch.equal(sd["state"][i]["exp_avg"], st["exp_avg"]) and torch.equal(sd["state"][i]["exp_avg_sq"], st["exp_avg_sq"])
+        assert float(sd["state"][i]["step"]) == float(st["step"])
+    opt2 = torch.optim.Adam(m.parameters())
+    opt2.load_state_dict(sd)                       # torch accepts it back
+    b2 = FlatBucket(Segment(3))
+    b2.load_state_dict(sd)
+    assert torch.equal(b2.exp_avg, b.exp_avg) and torch.equal(b2.exp_avg_sq, b.exp_avg_sq) and b2.step_count == 2
+    b.check_aliasing()
+    m.double()                                     # re-allocates every parameter
+    try:
+        b.check_aliasing()
+        raise AssertionError("broken aliasing was not detected")
+    except RuntimeError as e:
+        assert "no longer aliases" in str(e)
