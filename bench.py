@@ -345,8 +345,8 @@ def run_ours(args, rank, world, local_rank):
     area_host = [torch.empty(B, dtype=torch.int32).pin_memory() for _ in range(2)]
     bbox_host = [torch.empty((B, 4), dtype=torch.int32).pin_memory() for _ in range(2)]
 
-    def e2e_run(batches, K2):
-        pipe = Pipeline(model, boxes, depth=2, graphs=True)
+    def e2e_run(batches, K2, packed=False):
+        pipe = Pipeline(model, boxes, depth=2, graphs=True, packed=packed)
         for i in range(4):
             pipe.submit(batches[i % NBUF], out_host[i % 2], (area_host[i % 2], bbox_host[i % 2]))
         pipe.finish()
@@ -359,6 +359,7 @@ def run_ours(args, rank, world, local_rank):
 
     e2e_u8_ms, _, e2e_ranks = gather_windows(e2e_run(host_u8, K), world, dev)
     e2e_ms, _, _ = gather_windows(e2e_run(host, K32), world, dev)
+    e2e_pk_ms, _, _ = gather_windows(e2e_run(host_u8, K, packed=True), world, dev)
 
     # what the host link gives this rank while every rank copies at once: pinned H2D of one uint8 batch and D2H of one
     # mask batch, concurrently on two streams
@@ -420,6 +421,10 @@ def run_ours(args, rank, world, local_rank):
                     "per_rank_ms": rank_stats(e2e_ranks),
                     "what": "Pipeline.submit per step (infer.py path): pinned uint8 NHWC images -> H2D -> ToTensor+Normalize "
                             "inside the first kernel -> forward + decode (graph replay) -> D2H masks+area+bbox; 3 streams"},
+            "e2e_packed_masks": {"value": imgs / (e2e_pk_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": B * 3 * S * S,
+                                 "d2h_bytes_per_step": (B * S * S + 7) // 8 + B * 20,
+                                 "what": "the e2e pipeline with the masks bit-packed on the device (isg_pack_mask_bits, 1 bit per "
+                                         "pixel): 8x fewer D2H bytes"},
             "e2e_fp32_nchw": {"value": world * B * K32 / (e2e_ms * 1e-3), "unit": "images/s",
                               "h2d_bytes_per_step": B * 3 * S * S * 4, "d2h_bytes_per_step": B * S * S + B * 20,
                               "what": "same pipeline fed the Segment.forward tensor itself (pinned fp32 NCHW, already "

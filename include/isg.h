@@ -150,6 +150,11 @@ ISG_API int isg_idmap(const void* logits_dev, int logits_bf16, int h, int w, con
               const int32_t* img_first_dev, int n_img, int canvas_h, int canvas_w,
               float threshold, int32_t* idmap_dev, void* stream);
 
+/* 0/1 mask bytes (the masks_dev layout of isg_decode / isg_decode_tiled, alignment padding included) -> 1 bit per pixel,
+ * little-endian within a byte: bit i of bits_dev[j] = masks_dev[8 j + i] (numpy.packbits(bitorder="little")).  bits_dev
+ * holds (n + 7) / 8 bytes.  For serving paths whose device -> host copy matters: 8x fewer bytes per mask. */
+ISG_API int isg_pack_mask_bits(const uint8_t* masks_dev, int64_t n, uint8_t* bits_dev, void* stream);
+
 /* intersection/union counts of two byte masks (train_instance.py:402-403 mask_iou, applied there to tensor2mask
  * outputs, i.e. 0-255 SOFT bytes of prediction and label; ymlib's source is absent, parity unpinned): a byte counts
  * as set when it is nonzero -- what np.logical_and / np.logical_or, the usual implementation, do with such bytes

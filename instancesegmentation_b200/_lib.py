@@ -38,6 +38,7 @@ SIGNATURES = {
     "isg_decode_bind_workspace": (_i, [_vp, _i]),
     "isg_decode_tiled": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "isg_idmap": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _f, _vp, _vp]),
+    "isg_pack_mask_bits": (_i, [_vp, _i64, _vp, _vp]),
     "isg_mask_iou_counts": (_i, [_vp, _vp, _i64, _vp, _vp]),
     "isg_mask_iou_counts_thr": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp]),
     "isg_keypoint_heatmaps": (_i, [_vp, _i, _i, _i, _i, _f, _f, _vp, _i64, _vp]),

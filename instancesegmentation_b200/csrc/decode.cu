@@ -603,6 +603,30 @@ __global__ void iou_counts_kernel(const uint8_t* __restrict__ a, const uint8_t* 
     }
 }
 
+// 0/1 mask bytes -> bits, little-endian within a byte (bit i of byte j = mask[8 j + i], numpy packbits(bitorder="little")):
+// one thread packs 16 mask bytes (one 16-byte load) into 2 output bytes; a warp reads 512 and writes 64 contiguous bytes
+__global__ void __launch_bounds__(256) pack_bits_kernel(const uint8_t* __restrict__ m, int64_t n, uint8_t* __restrict__ bits) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;   // group of 16 mask bytes
+    const int64_t base = i * 16;
+    if (base >= n) return;
+    unsigned out = 0;
+    if (base + 16 <= n) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(m) + i);
+        const unsigned w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            // bytes are 0/1: gather bit 0 of the four bytes of a word into a nibble
+            const unsigned v = w[k] & 0x01010101u;
+            out |= ((v | (v >> 7) | (v >> 14) | (v >> 21)) & 0xfu) << (4 * k);
+        }
+        *reinterpret_cast<uint16_t*>(bits + 2 * i) = (uint16_t)out;
+    } else {
+        for (int k = 0; base + k < n; ++k) out |= (unsigned)(m[base + k] & 1u) << k;
+        bits[2 * i] = (uint8_t)out;
+        if (base + 8 < n) bits[2 * i + 1] = (uint8_t)(out >> 8);
+    }
+}
+
 // train_instance.py:297,380 -- torch.optim.Adam defaults, applied to the flat bucket
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, int64_t n, float gs, float lr, float b1, float b2, float eps,
@@ -764,6 +788,17 @@ int isg_idmap(const void* logits_dev, int logits_bf16, int h, int w, const int32
     else
         idmap_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(logits_dev), h, w, boxes_dev,
                                                   img_first_dev, canvas_h, canvas_w, threshold, idmap_dev);
+    ISG_CUDA(cudaGetLastError());
+    return ISG_OK;
+}
+
+int isg_pack_mask_bits(const uint8_t* masks_dev, int64_t n, uint8_t* bits_dev, void* stream) {
+    if (n <= 0) return ISG_OK;
+    if (!masks_dev || !bits_dev) return fail(ISG_ERR_ARG, "isg_pack_mask_bits: null argument");
+    if ((reinterpret_cast<uintptr_t>(masks_dev) & 15) || (reinterpret_cast<uintptr_t>(bits_dev) & 1))
+        return fail(ISG_ERR_ARG, "isg_pack_mask_bits: masks must be 16-byte and bits 2-byte aligned");
+    const int64_t groups = (n + 15) / 16;
+    pack_bits_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(masks_dev, n, bits_dev);
     ISG_CUDA(cudaGetLastError());
     return ISG_OK;
 }

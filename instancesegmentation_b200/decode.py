@@ -170,6 +170,26 @@ def decode_masks(logits, boxes=None, threshold=0.5, want_soft=False, img_first=N
     return DecodeResult(masks, soft, off, boxes, area, bbox, idmap)
 
 
+def pack_mask_bits(masks, n=None, out=None):
+    """``masks``: flat uint8 0/1 CUDA tensor (``DecodeResult.masks``) -> uint8 tensor of ``(n + 7) // 8`` bytes with one
+    bit per pixel (bit i of byte j = masks[8 j + i], ``numpy.packbits(..., bitorder="little")``): 8x fewer bytes to copy
+    to the host.  ``numpy.unpackbits(bits, bitorder="little")[:n]`` restores the bytes."""
+    if masks.dtype != torch.uint8 or not masks.is_cuda:
+        raise TypeError("pack_mask_bits needs a uint8 CUDA tensor")
+    masks = masks.contiguous().view(-1)
+    n = masks.numel() if n is None else int(n)
+    if n > masks.numel():
+        raise ValueError("n exceeds the mask buffer")
+    nb = (n + 7) // 8
+    if out is None:
+        out = torch.empty(nb + (nb & 1), dtype=torch.uint8, device=masks.device)
+    if out.dtype != torch.uint8 or out.numel() < nb:
+        raise ValueError("out must be uint8 with at least (n + 7) // 8 bytes")
+    with torch.cuda.device(masks.device):
+        _lib.check(_lib.lib().isg_pack_mask_bits(masks.data_ptr(), n, out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    return out[:nb]
+
+
 def mask_iou(a, b, threshold=1):
     """intersection / union of two uint8 CUDA masks (train_instance.py:402-403, where both are ``tensor2mask``
     soft bytes 0-255): a byte is set when it is >= ``threshold`` (an int, or a pair for a and b).  The default 1 =

@@ -10,7 +10,7 @@ Everything on the device runs in libisg; this file only orders streams.
 import numpy as np
 import torch
 
-from .decode import DecodePlan, decode_masks
+from .decode import DecodePlan, decode_masks, pack_mask_bits
 
 
 class _Slot:
@@ -29,8 +29,12 @@ class _Slot:
 class Pipeline:
     """``submit(host_batch, masks_host, stats_host)`` enqueues one batch; ``finish()`` waits for all."""
 
-    def __init__(self, model, boxes, depth=2, threshold=0.5, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5), graphs=False):
-        """``graphs=True``: forward + decode of every slot is captured once (GraphedStep) and replayed."""
+    def __init__(self, model, boxes, depth=2, threshold=0.5, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5), graphs=False,
+                 packed=False):
+        """``graphs=True``: forward + decode of every slot is captured once (GraphedStep) and replayed.
+        ``packed=True``: the masks leave the device as 1 bit per pixel (``pack_mask_bits``; ``masks_host`` then receives
+        ``(plan.total + 7) // 8`` bytes, ``numpy.unpackbits(..., bitorder="little")`` restores them): 8x fewer D2H bytes."""
+        self.packed = packed
         p = next(model.parameters())
         self.graphs = graphs
         if not p.is_cuda:
@@ -78,10 +82,17 @@ class Pipeline:
                     logits = self.model(s.x)
                 s.consumed.record(compute)
                 s.res = decode_masks(logits, threshold=self.threshold, out=s.masks, plan=s.plan)
+        if self.packed:
+            if getattr(s, "bits", None) is None:
+                s.bits = torch.empty((self.plan.total + 7) // 8 + 1, dtype=torch.uint8, device=self.dev)
+            pack_mask_bits(s.masks, self.plan.total, out=s.bits)
         s.computed.record(compute)
         with torch.cuda.stream(self.d2h):
             self.d2h.wait_event(s.computed)
-            if masks_host is not None:
+            if masks_host is not None and self.packed:
+                nb = (self.plan.total + 7) // 8
+                masks_host[:nb].copy_(s.bits[:nb], non_blocking=True)
+            elif masks_host is not None:
                 masks_host[:self.plan.total].copy_(s.masks[:self.plan.total], non_blocking=True)
             if stats_host is not None:
                 stats_host[0].copy_(s.res.area, non_blocking=True)

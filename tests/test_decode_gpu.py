@@ -240,3 +240,24 @@ def test_decode_workspaces_allow_concurrent_streams_and_default_path_still_works
     assert l.isg_decode(la.data_ptr(), 0, N, h, w, pi.boxes_d.data_ptr(), pi.off_d.data_ptr(), w, h, 0.5,
                         masks.data_ptr(), None, area.data_ptr(), bbox.data_ptr(), st) == -1     # 40 instances > workspace of 1
     _lib_mod.check(l.isg_decode_bind_workspace(None, 0))
+
+
+def test_packed_mask_bits_equal_the_byte_masks():
+    """isg_pack_mask_bits: 1 bit per pixel, bit-exact against the byte masks for every length (tails of 1..15 bytes),
+    and through Pipeline(packed=True)."""
+    from instancesegmentation_b200.decode import pack_mask_bits
+    rng = np.random.default_rng(5)
+    for n in (1, 7, 8, 9, 15, 16, 17, 31, 4096, 4099, 3 * 512 * 512 + 13):
+        m = (rng.random(n) < 0.5).astype(np.uint8)
+        buf = torch.zeros((n + 15) // 16 * 16, dtype=torch.uint8, device="cuda")
+        buf[:n] = torch.from_numpy(m).cuda()
+        bits = pack_mask_bits(buf, n).cpu().numpy()
+        assert np.array_equal(bits, np.packbits(m, bitorder="little")), n
+        assert np.array_equal(np.unpackbits(bits, bitorder="little")[:n], m)
+    logits = torch.from_numpy(synth.logits(5, 96, 128, seed=9)).cuda()
+    r = decode_masks(logits)
+    bits = pack_mask_bits(r.masks, r.offsets[-1]).cpu().numpy()
+    back = np.unpackbits(bits, bitorder="little")
+    for k in range(5):
+        o = int(r.offsets[k])
+        assert np.array_equal(back[o:o + 96 * 128].reshape(96, 128), r.mask(k).cpu().numpy())
