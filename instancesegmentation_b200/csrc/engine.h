@@ -57,6 +57,8 @@ struct Op {
     std::function<void(const HostWeights&, float* arena_host)> pack;
     // enqueues the kernel for `n` images
     std::function<cudaError_t(int n, const float* x, float* logits, cudaStream_t)> launch;
+    // 0: always runs; 1: only on the exact-uint8 first-layer path (isg_plan::exact_u8); 2: only on the generic path
+    int when = 0;
 };
 
 }  // namespace isg
@@ -81,6 +83,14 @@ struct isg_plan {
     float* u8_scratch = nullptr;
     bool use_tc = false;       // bf16 modes: GEMM-shaped convs on tcgen05 (ISG_NO_TC=1 disables)
     bool split = false;        // ISG_MODE_BF16X3: split-precision operands (hi + lo bf16 pairs, 3 MMA passes)
+    // Exact first layer (split plans, 3 input channels, isg_forward_u8): when v - 255*mean[c] is exactly representable
+    // in bf16 for every byte v (the reference's Normalize(0.5, 0.5): v - 127.5), the stem reads those centred pixels as
+    // single bf16 values (no lo plane, no A_lo pass) and 1 / (255*std[c]) is folded into layer1's packed weights.
+    bool exact_u8 = false;             // the running forward takes that path
+    bool exact_packed = false;         // the exact variant's weights are packed for exact_mean / exact_std
+    float exact_mean[3] = {0, 0, 0}, exact_std[3] = {0, 0, 0};
+    std::vector<std::vector<float>> state_copy;   // the state_dict tensors of the last load (re-packing needs them)
+    std::vector<const void*> state_ptrs;
     std::vector<std::function<int()>> finalizers;  // run once after the workspace is allocated (tensor maps)
     // run once after the finalizers: each fused launch times its candidate tilings on the device
     // (scratch logits buffer of max_batch images, stream) and keeps the fastest

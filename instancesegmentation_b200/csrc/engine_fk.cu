@@ -124,7 +124,7 @@ prep_kernel(const float* __restrict__ x, int H, int W, bf16* __restrict__ x2, in
 // the same from uint8 NHWC [B,H,W,3] (isg_forward_u8): ToTensor + Normalize of the reference's data
 // path (train_instance.py:80-85) in fp32 with IEEE division, then exactly prep_kernel<3>.
 // One thread = one 4x4 patch = four 12-byte rows.
-struct NormU8 { float mean[3], std[3]; };
+struct NormU8 { float mean[3], std[3]; int exact; };   // exact: the space-to-depth planes get v - 255*mean[c] as single bf16 values
 __global__ void __launch_bounds__(128)
 prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x2, int Cs2, int planar2,
                bf16* __restrict__ init, int Cs_init, int total, NormU8 nm, int split, int init_lo) {
@@ -134,6 +134,7 @@ prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x
         const int c = e >> 8;
         lut[c][e & 255] = __fdiv_rn(__fdiv_rn((float)(e & 255), 255.f) - nm.mean[c], nm.std[c]);
     }
+    const float ctr[3] = {255.f * nm.mean[0], 255.f * nm.mean[1], 255.f * nm.mean[2]};
     __syncthreads();
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -141,10 +142,12 @@ prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x
     const int W4 = W >> 2, H4 = H >> 2;
     const int x4 = i % W4, y4 = (i / W4) % H4, b = i / (W4 * H4);
     float v[3][4][4];
+    uint32_t wsrc[4][3];   // the 4 x 12 source bytes (exact path: the planes get v - 255*mean[c])
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
         const uint32_t* src = reinterpret_cast<const uint32_t*>(x + (((size_t)b * H + 4 * y4 + r) * W + 4 * x4) * 3);
         const uint32_t w[3] = {__ldg(src), __ldg(src + 1), __ldg(src + 2)};
+        wsrc[r][0] = w[0]; wsrc[r][1] = w[1]; wsrc[r][2] = w[2];
 #pragma unroll
         for (int k = 0; k < 12; ++k) v[k % 3][r][k / 3] = lut[k % 3][(w[k >> 2] >> (8 * (k & 3))) & 0xffu];
     }
@@ -160,10 +163,14 @@ prep_u8_kernel(const uint8_t* __restrict__ x, int H, int W, bf16* __restrict__ x
 #pragma unroll
                 for (int rx = 0; rx < 2; ++rx)
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) f[(ry * 2 + rx) * 3 + c] = v[c][2 * a + ry][2 * bb + rx];
+                    for (int c = 0; c < 3; ++c) {
+                        const int row = 2 * a + ry, k = (2 * bb + rx) * 3 + c;
+                        f[(ry * 2 + rx) * 3 + c] = nm.exact ? (float)((wsrc[row][k >> 2] >> (8 * (k & 3))) & 0xffu) - ctr[c]
+                                                            : v[c][row][2 * bb + rx];
+                    }
             int half;
             bf16* d = x2_pixel(x2, b, 2 * y4 + a, 2 * x4 + bb, H >> 1, W >> 1, Cs2, planar2, half);
-            store16(d, half, f, split);
+            store16(d, half, f, nm.exact ? 0 : split);   // exact: bf16-exact values, hi planes only
         }
     float m[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -283,7 +290,8 @@ __global__ void __launch_bounds__(128) tail_fix_kernel(TailFixParams p) {
 // ---------------------------------------------------------------------------------
 // specification of one fused launch
 // ---------------------------------------------------------------------------------
-struct LoadSpec { int tensor; int chunk0 = 0; int nchunks = -1; int halo = 0; bool s2d = false; };
+struct LoadSpec { int tensor; int chunk0 = 0; int nchunks = -1; int halo = 0; bool s2d = false;
+                  bool hi_only = false; };   // split plans: only the hi planes are loaded (the operand has no lo part)
 enum PartKind { PART_LOAD = 0, PART_STENCIL = 1, PART_PREV = 2 };
 struct Part { int kind; int load; };
 typedef std::function<void(const HostWeights&, float* B, float* shift, float* slope)> StageFill;
@@ -472,7 +480,7 @@ struct FkBuilder {
     // narrow three-pass stages run pass A_hi as one MMA over [W_hi | W_lo] (fk::Stage::nmerge); ISG_X3_NO_NMERGE=1 disables
     bool nmerge_of(const StageSpec& st) const {
         static const bool off = getenv("ISG_X3_NO_NMERGE") != nullptr;
-        return !off && P->split && passes_of(st) == 7 && st.N <= 32;
+        return !off && P->split && (passes_of(st) == 7 || passes_of(st) == 5) && st.N <= 32;
     }
 
     bool layout(const Spec& s, int TH, int TW, int ctas, int nlbuf, Lay& L, int pipe = 0) const {
@@ -511,7 +519,7 @@ struct FkBuilder {
             int slack = 0;
             if (is_a0) slack = std::max(0, a_rows * 16 - L.load_plane[i]);
             if ((int)i == s.stages[0].res_load && chained) slack = std::max(slack, L.n_mt * 128 * 16 - L.load_plane[i]);
-            L.tx += (uint32_t)(planes * mult) * L.load_plane[i];
+            L.tx += (uint32_t)(planes * (l.hi_only ? 1 : mult)) * L.load_plane[i];
             off = r128(off + load_bytes + slack);
         }
         // persistent CTAs double-buffer the whole load area: tile i+1 streams in while tile i computes
@@ -582,7 +590,7 @@ struct FkBuilder {
                 int n = 0;
                 for (int t = 0; t < (st.taps9 ? 9 : 1); ++t)
                     for (int ks = 0; ks < L.K[k] / 16; ++ks) n += (!st.used || st.used(t, ks)) ? 1 : 0;
-                L.tab_n = std::max(L.tab_n, n * (nmerge_of(st) ? 2 : npasses(passes_of(st))));
+                L.tab_n = std::max(L.tab_n, n * (nmerge_of(st) ? ((passes_of(st) & 2) ? 2 : 1) : npasses(passes_of(st))));
             }
             if (L.tab_n > fk::TAB_N_SPLIT) return false;
             L.smem = (size_t)off + 128 + 2 * 3 * (size_t)L.tab_n * 16;
@@ -684,7 +692,7 @@ struct FkBuilder {
             const LoadSpec& l = s.loads[i];
             // split tensors arrive as two boxes through the same map: hi chunks, then the lo chunks Cs/8 later
             // (a folded 2x2 load takes every chunk of its pixel pairs in one box)
-            for (int part = 0; part < (P->split && !l.s2d ? 2 : 1); ++part) {
+            for (int part = 0; part < (P->split && !l.s2d && !l.hi_only ? 2 : 1); ++part) {
                 if (q.nloads >= fk::MAX_LOADS) { fprintf(stderr, "libisg: %s: too many TMA loads\n", s.name.c_str()); abort(); }
                 fk::Load& d = q.loads[q.nloads++];
                 d.map = i; d.smem_off = L.load_off[i] + part * L.load_lo[i]; d.dx = -l.halo; d.dy = -l.halo;
@@ -744,7 +752,7 @@ struct FkBuilder {
             }
             d.passes = passes_of(st);
             d.nmerge = nmerge_of(st) ? 1 : 0;
-            d.nent_tab = d.nent * (d.nmerge ? 2 : npasses(d.passes));
+            d.nent_tab = d.nent * (d.nmerge ? ((d.passes & 2) ? 2 : 1) : npasses(d.passes));
             d.b_lo = (uint32_t)d.nent * st.N * 2;
             if (P->split ? d.nent_tab > L.tab_n : d.nent > fk::TAB_N) { fprintf(stderr, "libisg: %s: %d MMAs per M tile exceed the descriptor table\n", s.name.c_str(), d.nent); abort(); }
             // merged blocks are [2][2N][8]: the K chunks of a block are 2N rows apart
@@ -986,6 +994,7 @@ struct FkBuilder {
             if (cin == 3 && P->u8_src) {
                 NormU8 nm;
                 for (int c = 0; c < 3; ++c) { nm.mean[c] = P->u8_mean[c]; nm.std[c] = P->u8_std[c]; }
+                nm.exact = P->exact_u8 ? 1 : 0;
                 const int total = n * (H / 4) * (W / 4);
                 return launch_pdl(prep_u8_kernel, cdiv(total, 128), 128, st, P->u8_src, H, W, px2, x2.Ct(), (int)x2.planar, pin, init.Ct(), total, nm,
                                   (int)x2.split, init.Cs);
@@ -1891,18 +1900,23 @@ struct FkBuilder {
     }
 
     // 5x5 stride-2 pad-2 Conv wrapper as a 9-tap GEMM over a space-to-depth input (segment.py:23-26)
-    void stem_conv(const std::string& unit, int src, int cin, int out_tensor, int out_mode, int qH, int qW) {
+    // exact (split plans, isg_forward_u8 with bf16-exact centred pixels): the input planes hold v - 255*mean[c] as single
+    // bf16 values (no lo planes, no A_lo pass) and the weights carry 1 / (255*std[c]); runs instead of the generic launch
+    void stem_conv(const std::string& unit, int src, int cin, int out_tensor, int out_mode, int qH, int qW, bool exact = false) {
+        isg_plan* P = this->P;
         Spec s;
-        s.name = unit + " (5x5 s2 via space-to-depth)";
+        s.name = unit + (exact ? " (5x5 s2 via space-to-depth, exact uint8 input)" : " (5x5 s2 via space-to-depth)");
         s.qH = qH; s.qW = qW;
         s.loads.push_back(LoadSpec{src, 0, -1, 1});
+        s.loads[0].hi_only = exact;
         StageSpec st;
         st.parts = {Part{PART_LOAD, 0}};
         st.taps9 = true;
         st.N = 16;
+        if (exact) st.passes = 5;   // A_hi.W_hi + A_hi.W_lo
         st.out_mode = out_mode;
         st.out_tensor = out_tensor;
-        macs(16, cin, 5, 5, qH, qW);
+        if (!exact) macs(16, cin, 5, 5, qH, qW);
         const int K = td(src).Cs;
         // a K slice of 16 rows is one sub-pixel (ry, rx) of the space-to-depth input when cin == 16: the taps
         // that would need kernel row / column 5 do not exist (25 of the 36 slices carry weights)
@@ -1916,14 +1930,19 @@ struct FkBuilder {
                 for (int ph = 0; ph < 4; ++ph) {
                     const int ky = 2 * (t / 3) + (ph >> 1), kx = 2 * (t % 3) + (ph & 1);
                     if (ky > 4 || kx > 4) continue;
-                    for (int c = 0; c < cin; ++c)
+                    for (int c = 0; c < cin; ++c) {
+                        // exact: normalised = (v - 255 mean) / (255 std); the input planes hold v - 255 mean
+                        const double in_scale = !exact ? 1.0 : (P->exact_std[c] != 0.f ? 1.0 / (255.0 * (double)P->exact_std[c]) : 0.0);
                         for (int o = 0; o < 16; ++o)
-                            B[((size_t)t * K + ph * cin + c) * 16 + o] = Wt[(((size_t)o * cin + c) * 5 + ky) * 5 + kx] * sc[o];
+                            B[((size_t)t * K + ph * cin + c) * 16 + o] =
+                                (float)((double)Wt[(((size_t)o * cin + c) * 5 + ky) * 5 + kx] * (double)sc[o] * in_scale);
+                    }
                 }
             for (int o = 0; o < 16; ++o) { shift[o] = sh[o]; slope[o] = w.get(unit + ".act.weight")[o]; }
         };
         s.stages.push_back(st);
         emit(s);
+        if (exact) P->ops.back().when = 1;
     }
 
     // bottle6_1 (ConvTranspose2d k8 s4 p2, 16->4) composed with bottle6_2 (Conv2d 3x3 p1, 4->1):
@@ -2029,6 +2048,10 @@ struct FkBuilder {
         }
         emit_prep(x2, init);
         stem_conv("init_conv.layer1", x2, cin, s1, fk::OUT_S2D, H / 2, W / 2);
+        if (P->split && cin == 3) {   // the two first-layer variants: exactly one of them runs (Op::when)
+            P->ops.back().when = 2;
+            stem_conv("init_conv.layer1", x2, cin, s1, fk::OUT_S2D, H / 2, W / 2, true);
+        }
         stem_conv("init_conv.layer2", s1, 16, init, fk::OUT_STAGE, H / 4, W / 4);
 
         const int h8 = H / 8, w8 = W / 8, h16 = H / 16, w16 = W / 16;

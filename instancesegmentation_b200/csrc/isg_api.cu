@@ -124,7 +124,12 @@ int isg_plan_destroy(isg_plan* plan) {
 }
 
 size_t isg_plan_workspace_bytes(const isg_plan* plan) { return plan ? plan->ws_bytes : 0; }
-int isg_plan_launches_per_forward(const isg_plan* plan) { return plan ? (int)plan->ops.size() : 0; }
+int isg_plan_launches_per_forward(const isg_plan* plan) {
+    if (!plan) return 0;
+    int n = 0;
+    for (auto& op : plan->ops) n += op.when != 1;   // of the two first-layer variants exactly one runs
+    return n;
+}
 int64_t isg_plan_macs_per_image(const isg_plan* plan) { return plan ? plan->macs_per_image : 0; }
 
 int isg_plan_load_weights(isg_plan* plan, const void* const* tensors_host, const int64_t* numels, int count) {
@@ -138,6 +143,17 @@ int isg_plan_load_weights(isg_plan* plan, const void* const* tensors_host, const
                         e[i].name.c_str(), (long long)e[i].numel, (long long)numels[i]);
         if (!tensors_host[i]) return fail(ISG_ERR_ARG, "state tensor %d (%s) is null", i, e[i].name.c_str());
     }
+    // keep a copy of the float tensors: the exact-uint8 stem variant is packed later, when mean / std are known
+    plan->state_copy.assign(count, std::vector<float>());
+    plan->state_ptrs.assign(count, nullptr);
+    for (int i = 0; i < count; ++i) {
+        if (!e[i].is_i64) {
+            const float* src = static_cast<const float*>(tensors_host[i]);
+            plan->state_copy[i].assign(src, src + e[i].numel);
+        }
+        plan->state_ptrs[i] = e[i].is_i64 ? nullptr : static_cast<const void*>(plan->state_copy[i].data());
+    }
+    plan->exact_packed = false;
     HostWeights hw{&plan->spec, tensors_host};
     for (auto& op : plan->ops) op.pack(hw, plan->arena_host.data());
     ISG_CUDA(cudaSetDevice(plan->device));
@@ -174,6 +190,10 @@ int run_group(isg_plan* plan, const float* x, const uint8_t* u8, int n, float* l
     plan->u8_src = u8;
     size_t oi = 0;
     for (auto& op : plan->ops) {
+        if (op.when && (op.when == 1) != plan->exact_u8) {   // variant of the other first-layer path
+            if (op_timing) cudaEventRecord(evs[++oi], st);
+            continue;
+        }
         cudaError_t e = op.launch(n, x, logits, st);
         if (e != cudaSuccess) {
             plan->u8_src = nullptr;
@@ -229,6 +249,32 @@ int isg_forward_u8(isg_plan* plan, const uint8_t* x_u8_dev, int batch, const flo
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const size_t in_img = (size_t)plan->cin * plan->H * plan->W, out_img = (size_t)plan->H * plan->W;
     const bool direct = plan->use_tc && plan->cin == 3;   // the bf16 plan's first kernel reads uint8 itself
+    // exact first layer: every centred pixel v - 255*mean[c] must be a bf16 value (see isg_plan::exact_u8)
+    bool exact = direct && plan->split && !getenv("ISG_X3_NO_EXACT_U8");
+    for (int c = 0; c < 3 && exact; ++c) {
+        const float center = 255.f * mean_host[c];
+        if ((double)center != 255.0 * (double)mean_host[c]) exact = false;
+        for (int v = 0; v < 256 && exact; ++v) {
+            const float u = (float)v - center;
+            uint32_t bits;
+            memcpy(&bits, &u, 4);
+            if (bits & 0xffffu) exact = false;
+        }
+    }
+    if (exact) {
+        bool same = plan->exact_packed;
+        for (int c = 0; c < 3; ++c) same = same && plan->exact_mean[c] == mean_host[c] && plan->exact_std[c] == std_host[c];
+        if (!same) {   // (re)pack the variant's weights for this mean / std: rare, synchronous
+            for (int c = 0; c < 3; ++c) { plan->exact_mean[c] = mean_host[c]; plan->exact_std[c] = std_host[c]; }
+            HostWeights hw{&plan->spec, plan->state_ptrs.data()};
+            for (auto& op : plan->ops) if (op.when == 1) op.pack(hw, plan->arena_host.data());
+            ISG_CUDA(cudaDeviceSynchronize());
+            ISG_CUDA(cudaMemcpy(plan->arena, plan->arena_host.data(), plan->arena_floats * sizeof(float), cudaMemcpyHostToDevice));
+            plan->exact_packed = true;
+        }
+    }
+    struct Flag { isg_plan* p; ~Flag() { p->exact_u8 = false; } } flag{plan};
+    plan->exact_u8 = exact;
     if (!direct && !plan->u8_scratch) {
         ISG_CUDA(cudaMalloc(&plan->u8_scratch, ((size_t)plan->max_batch * in_img + 16) * sizeof(float)));
     }

@@ -397,3 +397,33 @@ def test_one_plan_per_size_serves_smaller_batches(golden_state):
         assert e6 is not e3 and e6.max_batch == 6 and len(m._engines) == 1
         assert torch.equal(m(x[:3]), y3) and _engine(m) is e6
     assert torch.equal(y1, y3[:1]) and torch.equal(y6[:3], y3)
+
+
+def test_bf16x3_exact_uint8_first_layer(golden_state):
+    """isg_forward_u8 with the reference's Normalize(0.5, 0.5) (train_instance.py:80-85) on a split-precision plan takes
+    the exact first layer: centred pixels v - 127.5 as single bf16 values, 1 / (255 std) folded into layer1's weights.
+    Same bar against the oracle on the host-normalised tensor; agrees with the generic path (other mean / std fall back
+    to it, and forward() of the normalised fp32 tensor always uses it) to rounding; re-packs when mean / std change."""
+    u8 = _u8_batch(2, 96, 160, seed=8)
+    x = _normalize_like_reference(u8)
+    want = segment_forward(golden_state, x)
+    m = _model(golden_state, precision="bf16x3")
+    with torch.no_grad():
+        exact = m.forward_u8(u8.cuda()).cpu()                       # 0.5 / 0.5 -> exact path
+        generic = m(x.cuda()).cpu()
+        d = (exact - want).abs()
+        print(f"exact-u8 path: max {float(d.max()):.3e} mean {float(d.mean()):.3e}; vs generic {float((exact - generic).abs().max()):.3e}")
+        assert float(d.max()) <= X3_MAX and float(d.mean()) <= X3_MEAN
+        assert float((exact - generic).abs().max()) <= 2e-3
+        # integer centre (mean = 128/255) is exact too, with another std: the variant is re-packed
+        mean2, std2 = (128.0 / 255.0,) * 3, (0.25, 0.5, 0.2)
+        x2 = _normalize_like_reference(u8, mean2, std2)
+        got2 = m.forward_u8(u8.cuda(), mean2, std2).cpu()
+        d2 = (got2 - segment_forward(golden_state, x2)).abs()
+        assert float(d2.max()) <= X3_MAX * 2 and float(d2.mean()) <= X3_MEAN * 2     # inputs up to 4x larger
+        again = m.forward_u8(u8.cuda()).cpu()                       # back to 0.5 / 0.5: packed again, same result
+        assert torch.equal(again, exact)
+        # a mean whose centred pixels are not bf16 values falls back to the generic path: bitwise equal to forward(x)
+        mean3 = (0.4, 0.5, 0.6)
+        x3 = _normalize_like_reference(u8, mean3, (0.5, 0.25, 0.2))
+        assert torch.equal(m.forward_u8(u8.cuda(), mean3, (0.5, 0.25, 0.2)).cpu(), m(x3.cuda()).cpu())
