@@ -404,12 +404,15 @@ def run_ours(args, rank, world, local_rank):
                        "input": "uint8 NHWC resident in HBM (Normalize inside the first kernel)",
                        "images_per_s_fp32_nchw_input": world * B * K32 / (step32_ms * 1e-3)},
             "roofline": {"bound": "tensor", "achieved": conv_tf, "peak": pk["tf_sust"] / 1e0, "unit": "TFLOP/s",
-                         "frac": conv_tf / pk["tf_sust"], "traffic": 1373.8e6 if cfg2 else None,
+                         "frac": conv_tf / pk["tf_sust"],
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one forward of 64 images summed over its launches:
+                         # bf16x3 profiles/r2c_forward_bf16x3_per_launch.txt (generic first layer), bf16 profiles/r1i_forward_inst_per_launch.txt
+                         "traffic": (2829.0e6 if args.precision == "bf16x3" else 1373.8e6 if cfg2 else None) if (B == 64 and S == 512) else None,
                          "what": f"conv stack ({eng.launches_per_forward} launches/forward, mode {args.precision}), algorithmic "
                                  f"{flop_img / 1e9:.4f} GFLOP/image, peak = sustained bf16 of {pk['src']}",
                          "ms_per_forward": fwd_ms / K},
             "roofline_decode": {"bound": "hbm", "achieved": dec_gbs, "peak": pk["hbm"], "unit": "GB/s",
-                                "frac": dec_gbs / pk["hbm"], "traffic": 69.74e6 if cfg2 else None, "bytes_per_launch": dec_bytes,
+                                "frac": dec_gbs / pk["hbm"], "traffic": 69.74e6 if (B == 64 and S == 512) else None, "bytes_per_launch": dec_bytes,
                                 "ms_per_decode": dk_ms / K, "ms_per_decode_in_step": dec_in_step_ms,
                                 "frac_in_step": (dec_bytes / (dec_in_step_ms * 1e-3) / 1e9 / pk["hbm"]) if dec_in_step_ms > 0 else None,
                                 "what": "decode_kernel, average over K launches issued back to back on rotating logit "
