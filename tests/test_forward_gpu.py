@@ -427,3 +427,19 @@ def test_bf16x3_exact_uint8_first_layer(golden_state):
         mean3 = (0.4, 0.5, 0.6)
         x3 = _normalize_like_reference(u8, mean3, (0.5, 0.25, 0.2))
         assert torch.equal(m.forward_u8(u8.cuda(), mean3, (0.5, 0.25, 0.2)).cpu(), m(x3.cuda()).cpu())
+
+
+def test_bf16x3_in_channel_20():
+    """Segment(20) (17 keypoint heat maps + image, segment.py:531-533) in the split-precision mode: the generic-cin input
+    kernel writes hi + lo planes, layer1 has K = 80 per tap."""
+    ref = randomized_state(20, seed=5)
+    sd = ref.state_dict()
+    m = _model(sd, cin=20, precision="bf16x3")
+    x = torch.from_numpy(synth.batch(2, 64, 96, seed=1, channels=20))
+    want = segment_forward(sd, x)
+    with torch.no_grad():
+        got = m(x.cuda()).cpu()
+    d = (got - want).abs()
+    scale = max(1.0, float(want.abs().max()) / 3.0)
+    print(f"Segment(20) bf16x3: max {float(d.max()):.3e} mean {float(d.mean()):.3e} (logit absmax {float(want.abs().max()):.2f})")
+    assert float(d.max()) <= X3_MAX * scale and float(d.mean()) <= X3_MEAN * scale
