@@ -163,14 +163,17 @@ class _BceSigmoid(torch.autograd.Function):
                 logits.data_ptr(), int(logits.dtype == torch.bfloat16), target.data_ptr(), logits.numel(),
                 dlogits.data_ptr() if need_grad else None, _bce_workspace(logits.device).data_ptr(),
                 loss.data_ptr(), torch.cuda.current_stream().cuda_stream))
-        ctx.dlogits = dlogits
+        if need_grad:
+            ctx.save_for_backward(dlogits)     # survives retain_graph / a second backward, freed with the graph
+        ctx.has_grad = need_grad
         return loss
 
     @staticmethod
     def backward(ctx, g):
-        d = ctx.dlogits
-        ctx.dlogits = None
-        return (d * g.to(d.dtype) if d is not None else None), None
+        if not ctx.has_grad:
+            return None, None
+        (d,) = ctx.saved_tensors
+        return d * g.to(d.dtype), None
 
 
 def bce_sigmoid_loss(logits, target):

@@ -443,3 +443,28 @@ def test_bf16x3_in_channel_20():
     scale = max(1.0, float(want.abs().max()) / 3.0)
     print(f"Segment(20) bf16x3: max {float(d.max()):.3e} mean {float(d.mean()):.3e} (logit absmax {float(want.abs().max()):.2f})")
     assert float(d.max()) <= X3_MAX * scale and float(d.mean()) <= X3_MEAN * scale
+
+
+def test_bf16x3_masks_agree_with_fp32_mode_masks(golden_state, golden_logits):
+    """Mask-level view of the logits tolerance: thresholded masks from the tensor-core mode against masks from the fp32
+    mode on the golden inputs (which the unmodified reference wrote logits for): IoU and pixel-flip rate, plus the share
+    of flips that sit within the tolerance of the decision boundary (all of them must)."""
+    from instancesegmentation_b200.decode import decode_masks, mask_iou
+    meta = json.load(open(os.path.join(GOLDEN, "segment3_golden.json")))
+    m32, m3 = _model(golden_state, precision="fp32"), _model(golden_state, precision="bf16x3")
+    for name, c in meta["cases"].items():
+        x = torch.from_numpy(synth.batch(c["B"], c["H"], c["W"], seed=c["seed"], kind=c["kind"])).cuda()
+        with torch.no_grad():
+            l32, l3 = m32(x), m3(x)
+            r32, r3 = decode_masks(l32), decode_masks(l3)
+        n = c["B"] * c["H"] * c["W"]
+        a = torch.cat([r32.mask(k).reshape(-1) for k in range(c["B"])])
+        b = torch.cat([r3.mask(k).reshape(-1) for k in range(c["B"])])
+        flips = a != b
+        rate = float(flips.float().mean())
+        iou = mask_iou(a, b)
+        scale = max(1.0, c["logit_absmax"] / 3.0)
+        near = l32.reshape(-1)[flips].abs().max().item() if bool(flips.any()) else 0.0
+        print(f"{name}: IoU {iou:.6f} flip rate {rate:.2e} ({int(flips.sum())} of {n}), largest |fp32 logit| at a flip {near:.2e}")
+        assert iou >= 0.998 and rate <= 2e-3, (name, iou, rate)
+        assert near <= X3_MAX * scale, (name, near)      # a pixel only flips when its logit is within the tolerance of 0

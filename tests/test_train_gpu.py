@@ -331,3 +331,13 @@ def test_conv_transpose_k2s_matches_torch_float64(geom, dtype):
     close(m.bias.grad, br.grad, lib_tol)
     m.eval()
     assert not m.native(xg)
+
+
+def test_bce_sigmoid_backward_twice_with_retain_graph():
+    """the gradient is a saved tensor: a second backward (retain_graph) returns it again instead of None"""
+    x = torch.randn(4, 1, 32, 32, device="cuda", requires_grad=True)
+    y = (torch.rand(4, 1, 32, 32, device="cuda") < 0.4).float()
+    loss = bce_sigmoid_loss(x, y)
+    (g1,) = torch.autograd.grad(loss, x, retain_graph=True)
+    (g2,) = torch.autograd.grad(loss, x)
+    assert torch.equal(g1, g2) and float(g1.abs().sum()) > 0
