@@ -171,6 +171,30 @@ def cpu_reference_arm(B, size, steps, warmup, threads=None):
     return B / t, t, torch.get_num_threads(), kind
 
 
+def decode_oracle_vs_torch():
+    """Part of the cpu_baseline leg: the decode has no reference code to pin against (parity unpinned), so the line reports
+    how often the C restatement's mask differs from torch's own sigmoid -> F.interpolate(bilinear, align_corners=False) ->
+    > 0.5 on seeded logits (identity size, a x2 upsample and two non-integer ratios), per 1e7 pixels."""
+    import numpy as np
+    import torch
+    import torch.nn.functional as F
+
+    from instancesegmentation_b200 import synth
+    from oracle import decode_oracle
+    decode_oracle.build()
+    L = synth.logits(4, 256, 256, seed=5)
+    boxes = np.array([[0, 0, 256, 256], [0, 0, 512, 512], [3, 5, 367, 201], [1, 1, 97, 143]], np.int32)
+    r = decode_oracle.decode(L, boxes)
+    mism = total = 0
+    for n, (_, _, wk, hk) in enumerate(boxes):
+        p = F.interpolate(torch.sigmoid(torch.from_numpy(L[n:n + 1, None])), size=(int(hk), int(wk)), mode="bilinear",
+                          align_corners=False)[0, 0].numpy()
+        mine = r["masks"][r["off"][n]:r["off"][n + 1]].reshape(hk, wk)
+        mism += int((mine != (p > 0.5)).sum())
+        total += int(hk) * int(wk)
+    return {"torch_mismatch_per_1e7": mism * 1e7 / total, "pixels": total, "mismatches": mism}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's own CPU path, all host threads, bounded sample."""
     if rank != 0:
@@ -445,6 +469,7 @@ def run_ours(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": threads, "kind": kind,
                                     "sample": f"16 of {B} images per step x 10 steps (median), fp32 torch-CPU forward "
                                               f"+ scalar C decode"}
+            line["cpu_baseline"]["decode_oracle_vs_torch"] = decode_oracle_vs_torch()
         emit(line)
     if world > 1:
         dist.destroy_process_group()
