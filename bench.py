@@ -381,9 +381,9 @@ def run_ours(args, rank, world, local_rank):
                 pipe.finish()
         return windows(one, 3, K2)
 
-    e2e_u8_ms, _, e2e_ranks = gather_windows(e2e_run(host_u8, K), world, dev)
+    e2e_u8_ms, _, _ = gather_windows(e2e_run(host_u8, K), world, dev)
     e2e_ms, _, _ = gather_windows(e2e_run(host, K32), world, dev)
-    e2e_pk_ms, _, _ = gather_windows(e2e_run(host_u8, K, packed=True), world, dev)
+    e2e_pk_ms, _, e2e_ranks = gather_windows(e2e_run(host_u8, K, packed=True), world, dev)
 
     # what the host link gives this rank while every rank copies at once: pinned H2D of one uint8 batch and D2H of one
     # mask batch, concurrently on two streams
@@ -443,15 +443,15 @@ def run_ours(args, rank, world, local_rank):
                                         "batches; in_step = graph-replayed step minus graph-replayed forward"},
             # headline end-to-end = the infer.py call surface: host uint8 NHWC images (what cv2.imread gives,
             # infer.py:run) -> H2D -> Normalize + forward + decode -> D2H masks + area + bbox, every step
-            "e2e": {"value": imgs / (e2e_u8_ms * 1e-3), "unit": "images/s",
-                    "h2d_bytes_per_step": B * 3 * S * S, "d2h_bytes_per_step": B * S * S + B * 20,
+            "e2e": {"value": imgs / (e2e_pk_ms * 1e-3), "unit": "images/s",
+                    "h2d_bytes_per_step": B * 3 * S * S, "d2h_bytes_per_step": (B * S * S + 7) // 8 + B * 20,
                     "per_rank_ms": rank_stats(e2e_ranks),
-                    "what": "Pipeline.submit per step (infer.py path): pinned uint8 NHWC images -> H2D -> ToTensor+Normalize "
-                            "inside the first kernel -> forward + decode (graph replay) -> D2H masks+area+bbox; 3 streams"},
-            "e2e_packed_masks": {"value": imgs / (e2e_pk_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": B * 3 * S * S,
-                                 "d2h_bytes_per_step": (B * S * S + 7) // 8 + B * 20,
-                                 "what": "the e2e pipeline with the masks bit-packed on the device (isg_pack_mask_bits, 1 bit per "
-                                         "pixel): 8x fewer D2H bytes"},
+                    "what": "Pipeline(graphs=True, packed=True).submit per step (infer.py path): pinned uint8 NHWC images -> H2D -> "
+                            "ToTensor+Normalize inside the first kernel -> forward + decode (graph replay) -> masks bit-packed on the "
+                            "device (isg_pack_mask_bits, 1 bit per pixel, bit-exact) -> D2H masks+area+bbox; 3 streams"},
+            "e2e_byte_masks": {"value": imgs / (e2e_u8_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": B * 3 * S * S,
+                               "d2h_bytes_per_step": B * S * S + B * 20,
+                               "what": "the same pipeline returning one byte per mask pixel (8x the D2H bytes)"},
             "e2e_fp32_nchw": {"value": world * B * K32 / (e2e_ms * 1e-3), "unit": "images/s",
                               "h2d_bytes_per_step": B * 3 * S * S * 4, "d2h_bytes_per_step": B * S * S + B * 20,
                               "what": "same pipeline fed the Segment.forward tensor itself (pinned fp32 NCHW, already "
