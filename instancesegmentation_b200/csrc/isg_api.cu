@@ -153,8 +153,9 @@ int isg_plan_load_weights(isg_plan* plan, const void* const* tensors_host, const
         }
         plan->state_ptrs[i] = e[i].is_i64 ? nullptr : static_cast<const void*>(plan->state_copy[i].data());
     }
-    plan->exact_packed = false;
     HostWeights hw{&plan->spec, tensors_host};
+    // (the exact-uint8 stem variant, Op::when == 1, is packed for the mean / std of the last isg_forward_u8: when those are
+    // known it is re-packed here with the new weights, so that a captured CUDA graph replays with current weights too)
     for (auto& op : plan->ops) op.pack(hw, plan->arena_host.data());
     ISG_CUDA(cudaSetDevice(plan->device));
     ISG_CUDA(cudaDeviceSynchronize());  // no forward may still be reading the old weights

@@ -468,3 +468,28 @@ def test_bf16x3_masks_agree_with_fp32_mode_masks(golden_state, golden_logits):
         print(f"{name}: IoU {iou:.6f} flip rate {rate:.2e} ({int(flips.sum())} of {n}), largest |fp32 logit| at a flip {near:.2e}")
         assert iou >= 0.998 and rate <= 2e-3, (name, iou, rate)
         assert near <= X3_MAX * scale, (name, near)      # a pixel only flips when its logit is within the tolerance of 0
+
+
+def test_graph_replay_sees_reloaded_weights(golden_state):
+    """GraphedStep replays baked kernel arguments: a weight reload updates the packed weights in place (including the
+    exact-uint8 stem variant, which is otherwise packed lazily inside isg_forward_u8), so the replay equals a fresh call."""
+    from instancesegmentation_b200.pipeline import GraphedStep
+    m = _model(golden_state, precision="bf16x3", max_batch=2)
+    u8 = _u8_batch(2, 64, 96, seed=3).cuda()
+    g = GraphedStep(m, u8, decode=False)
+    g.replay()
+    torch.cuda.synchronize()
+    before = g.logits.clone()
+    with torch.no_grad():
+        assert torch.equal(before, m.forward_u8(u8))
+    sd2 = {k: (v * 1.05 if v.dtype.is_floating_point and k.endswith("conv.weight") else v) for k, v in golden_state.items()}
+    m.load_state_dict(sd2)
+    eng = _engine(m)
+    eng.load_state_dict(m.state_dict()); eng.weights_epoch = m._weights_epoch     # what the next eager call would do
+    g.replay()
+    torch.cuda.synchronize()
+    after = g.logits.clone()
+    with torch.no_grad():
+        fresh = m.forward_u8(u8)
+    assert float((after - before).abs().max()) > 1e-3
+    assert torch.equal(after, fresh)
