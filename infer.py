@@ -19,7 +19,9 @@ def parse_args(argv=None):
     # additions (the reference never loads a model, so it has no such flags)
     ap.add_argument("--checkpoint", default=None, help="*.pth written by train_instance.py:497-507")
     ap.add_argument("--size", type=int, default=480, help="network input size (multiple of 16)")
-    ap.add_argument("--precision", choices=("fp32", "bf16"), default="fp32")
+    ap.add_argument("--precision", choices=("fp32", "bf16x3", "bf16"), default="fp32",
+                    help="fp32: CUDA cores, <= 1e-4 of the reference; bf16x3: tensor cores, logits within 2e-2 / 2e-3; "
+                         "bf16: tensor cores, fastest, outside that tolerance")
     ap.add_argument("--batch", type=int, default=16)
     ap.add_argument("--soft", action="store_true", help="also write the 0-255 soft mask")
     return ap.parse_args(argv)
